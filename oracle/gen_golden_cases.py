@@ -1,0 +1,20 @@
+"""Case tables shared by oracle/gen_golden.py (generator) and tests/test_oracle_golden.py."""
+# (name, dim, heads, ffn_factor, bias, ln_type, B, H, W, seed)
+BLOCK_CASES = [
+    ("blk_c48_h1", 48, 1, 2.66, False, "WithBias", 2, 16, 24, 11),
+    ("blk_c96_h2_bias", 96, 2, 2.66, True, "WithBias", 1, 16, 16, 12),
+    ("blk_c96_h1_biasfree", 96, 1, 2.66, False, "BiasFree", 1, 8, 16, 13),
+    ("blk_c64_h2_f2_bias", 64, 2, 2.0, True, "BiasFree", 1, 8, 8, 14),
+    ("blk_c192_h4", 192, 4, 2.66, False, "WithBias", 1, 8, 8, 15),
+]
+
+# (name, cfg-overrides, B, H, W, weight seed, image seed)
+NET_CASES = [
+    ("net_default_64", {}, 1, 64, 64, 0, 1234),
+    ("net_dim16_bias_biasfree_32", dict(dim=16, num_blocks=[1, 2, 2, 1], num_refinement_blocks=1, bias=True,
+                                        LayerNorm_type="BiasFree"), 2, 32, 48, 3, 77),
+    ("net_dim32_dualpixel_32", dict(dim=32, inp_channels=6, num_blocks=[1, 1, 1, 2], num_refinement_blocks=2,
+                                    ffn_expansion_factor=2.0, dual_pixel_task=True), 1, 32, 32, 5, 78),
+]
+
+
