@@ -1,0 +1,7 @@
+"""b200ir — B200-native (sm_100a) Restormer-family transformer block behind the reference's nn.Module API."""
+from . import _lib, ops  # noqa: F401  (fails loudly if libb200ir.so is missing)
+from .modules import (Attention, BiasFree_LayerNorm, Downsample, FeedForward, LayerNorm, OverlapPatchEmbed,  # noqa: F401
+                      Restormer, TransformerBlock, Upsample, WithBias_LayerNorm)
+
+__all__ = ["Attention", "BiasFree_LayerNorm", "Downsample", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+           "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -1,0 +1,54 @@
+"""ctypes binding of libb200ir.so (the C ABI declared in include/b200ir.h).
+
+There is NO fallback: if the shared library is missing or a symbol is absent the import
+fails loudly, and every op raises if it is handed a non-CUDA tensor.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200ir.so")
+
+F32, BF16 = 0, 1
+LN_NONE, LN_WITHBIAS, LN_BIASFREE = 0, 1, 2
+SHUFFLE_NONE, UNSHUFFLE2, SHUFFLE2 = 0, 1, 2
+IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+
+_vp, _i64, _i, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_size_t
+
+# name -> argtypes; every symbol of include/b200ir.h must be listed here (tests/test_abi.py checks)
+SIGNATURES = {
+    "b200ir_version": [],
+    "b200ir_last_error_string": [],
+    "b200ir_ln_conv1x1_fwd": [_vp, _i64, _i, _vp, _i64, _vp, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i,
+                              _i, _i, _i, _i64, _vp],
+    "b200ir_dwconv3x3_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_gelu_gate_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
+    "b200ir_mdta_gram_nslab": [_i, _i, _i, _i64],
+    "b200ir_mdta_gram_fwd": [_vp, _i64, _i, _i, _i, _i, _i64, _vp, _i, _i, _vp],
+    "b200ir_mdta_softmax_fold_fwd": [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "b200ir_conv3x3_fwd": [_vp, _i64, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_copy_cast": [_vp, _i64, _i, _vp, _i64, _i, _i, _i64, _vp],
+}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python __graft_entry__.py` or "
+            f"`image-restoration_b200/csrc/build.sh` (there is no CPU/PyTorch fallback)")
+    lib = C.CDLL(LIB_PATH)
+    for name, argtypes in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing: loud by design
+        fn.argtypes = argtypes
+        fn.restype = C.c_char_p if name == "b200ir_last_error_string" else C.c_int
+    return lib
+
+
+lib = _load()
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = lib.b200ir_last_error_string()
+        raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")

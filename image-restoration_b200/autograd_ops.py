@@ -1,0 +1,69 @@
+"""Differentiable wrappers around ``ops`` (one ``torch.autograd.Function`` per fused kernel).
+
+With autograd off (inference, the headline path) these call the forward kernels directly and may
+write into caller-provided ``out`` views.  With autograd on, each op records what its hand-written
+backward needs (see ``backward.py`` as it lands); until an op's backward exists it raises instead of
+silently falling back to PyTorch.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib as L
+from . import ops
+
+
+def _needs_grad(*ts):
+    return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts)
+
+
+def _no_backward(name):
+    raise NotImplementedError(
+        f"b200ir: backward of {name} is not implemented yet; run under torch.no_grad() "
+        f"(no PyTorch fallback is provided by design)")
+
+
+def _p(t):
+    """fp32 contiguous view of a parameter for the kernels (conv weights keep their memory layout)."""
+    if t is None:
+        return None
+    t = t.detach()
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+def ln_conv1x1(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None):
+    if _needs_grad(x, w, bias, ln_w, ln_b, res):
+        _no_backward("ln_conv1x1")
+    return ops.ln_conv1x1(x, _p(w), _p(bias), ln_type, _p(ln_w), _p(ln_b), res, out=out, out_dtype=out_dtype)
+
+
+def dwconv3x3(x, w, bias):
+    if _needs_grad(x, w, bias):
+        _no_backward("dwconv3x3")
+    return ops.dwconv3x3(x, _p(w), _p(bias))
+
+
+def dwconv3x3_gelu_gate(x, w, bias):
+    if _needs_grad(x, w, bias):
+        _no_backward("dwconv3x3_gelu_gate")
+    return ops.dwconv3x3_gelu_gate(x, _p(w), _p(bias))
+
+
+def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
+    """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147)."""
+    if _needs_grad(qkv, temperature, w_out, b_out, res):
+        _no_backward("mdta_core")
+    B, C3, H, W = qkv.shape
+    C = C3 // 3
+    partials = ops.mdta_gram(qkv, heads)
+    m = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C))
+    v = qkv[:, 2 * C:]
+    return ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
+
+
+def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None):
+    if _needs_grad(x, w, bias, res):
+        _no_backward("conv3x3")
+    return ops.conv3x3(x, _p(w), _p(bias), res, shuffle, out=out, out_dtype=out_dtype)

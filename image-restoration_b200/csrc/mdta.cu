@@ -1,0 +1,215 @@
+// mdta.cu — MDTA transposed attention, stages 1 (Gram + norms, fp32 CUDA-core path) and 2
+// (slab reduce + normalise + temperature softmax + project_out fold).
+// Reference: Attention.forward Restormer.py:111-132.
+//   :117-119  q,k,v = heads of contiguous channel groups of the q|k|v chunks (index math only here)
+//   :121-122  F.normalize(dim=-1): x / max(||x||_2, 1e-12)  -> applied to the d x d Gram, never to q/k
+//   :124      (q @ k^T) * temperature[h]
+//   :125      softmax over the last dim (rows of length d = C/heads)
+//   :127-131  attn @ v, then project_out  -> folded into m[b] = W_out . blockdiag(attn[b,h])
+#include "common.cuh"
+
+namespace b200ir {
+
+constexpr int GPC = 32;  // pixels per smem chunk in the SIMT Gram
+
+// grid (nslab, heads, B), 256 threads as 16x16, thread (ty,tx) owns G[ty+16*ii][tx+16*jj]
+template <int TI>
+__global__ void __launch_bounds__(256)
+gram_simt_kernel(const void* __restrict__ qkv, int64_t bs, int dt, int C, int d, int64_t HW, int64_t slab_len,
+                 float* __restrict__ partials, int nslab) {
+  extern __shared__ float sm[];
+  float* qs = sm;                       // [d][GPC+1]
+  float* ks = sm + (size_t)d * (GPC + 1);
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int slab = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int64_t pbeg = (int64_t)slab * slab_len;
+  const int64_t pend = min(HW, pbeg + slab_len);
+  const int64_t qoff = (int64_t)b * bs + (int64_t)(h * d) * HW;
+  const int64_t koff = qoff + (int64_t)C * HW;
+
+  float acc[TI][TI];
+#pragma unroll
+  for (int i = 0; i < TI; ++i)
+#pragma unroll
+    for (int j = 0; j < TI; ++j) acc[i][j] = 0.f;
+  float nrm = 0.f;  // thread t<d: sum q[t]^2 ; d<=t<2d: sum k[t-d]^2
+
+  for (int64_t p0 = pbeg; p0 < pend; p0 += GPC) {
+    for (int e = tid; e < d * GPC; e += 256) {
+      const int r = e / GPC, cpx = e % GPC;
+      const int64_t p = p0 + cpx;
+      float qv = 0.f, kv = 0.f;
+      if (p < pend) {
+        qv = ld_any(qkv, dt, qoff + (int64_t)r * HW + p);
+        kv = ld_any(qkv, dt, koff + (int64_t)r * HW + p);
+      }
+      qs[r * (GPC + 1) + cpx] = qv;
+      ks[r * (GPC + 1) + cpx] = kv;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int k = 0; k < GPC; ++k) {
+      float a[TI], bb[TI];
+#pragma unroll
+      for (int i = 0; i < TI; ++i) {
+        const int r = ty + 16 * i;
+        a[i] = r < d ? qs[r * (GPC + 1) + k] : 0.f;
+        const int c2 = tx + 16 * i;
+        bb[i] = c2 < d ? ks[c2 * (GPC + 1) + k] : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < TI; ++i)
+#pragma unroll
+        for (int j = 0; j < TI; ++j) acc[i][j] = fmaf(a[i], bb[j], acc[i][j]);
+    }
+    if (tid < 2 * d) {
+      const float* src = tid < d ? qs + tid * (GPC + 1) : ks + (tid - d) * (GPC + 1);
+#pragma unroll 8
+      for (int k = 0; k < GPC; ++k) nrm = fmaf(src[k], src[k], nrm);
+    }
+    __syncthreads();
+  }
+  float* out = partials + (((size_t)b * gridDim.y + h) * nslab + slab) * ((size_t)d * d + 2 * d);
+#pragma unroll
+  for (int i = 0; i < TI; ++i)
+#pragma unroll
+    for (int j = 0; j < TI; ++j) {
+      const int r = ty + 16 * i, c2 = tx + 16 * j;
+      if (r < d && c2 < d) out[r * d + c2] = acc[i][j];
+    }
+  if (tid < 2 * d) out[d * d + tid] = nrm;
+}
+
+// grid (heads, B), 256 threads.  smem: attn[d][d+1] + nq[d] + nk[d]
+__global__ void __launch_bounds__(256)
+softmax_fold_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ temperature,
+                    const float* __restrict__ w_out, float* __restrict__ m, float* __restrict__ attn_out, int C,
+                    int d) {
+  extern __shared__ float sm[];
+  float* attn = sm;                      // [d][d+1]
+  float* nq = sm + (size_t)d * (d + 1);  // [d]
+  float* nk = nq + d;                    // [d]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int h = blockIdx.x, b = blockIdx.y, heads = gridDim.x;
+  const size_t per = (size_t)d * d + 2 * d;
+  const float* base = partials + ((size_t)b * heads + h) * nslab * per;
+
+  for (int e = tid; e < (int)per; e += 256) {
+    float s = 0.f;
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];  // fixed order: deterministic
+    if (e < d * d) attn[(e / d) * (d + 1) + (e % d)] = s;
+    else if (e < d * d + d) nq[e - d * d] = fmaxf(sqrtf(s), 1e-12f);      // max(||q||,eps) (:121)
+    else nk[e - d * d - d] = fmaxf(sqrtf(s), 1e-12f);
+  }
+  __syncthreads();
+  const float temp = temperature[h];
+  for (int i = warp; i < d; i += 8) {
+    float* row = attn + i * (d + 1);
+    float mx = -INFINITY;
+    for (int j = lane; j < d; j += 32) {
+      const float v = row[j] / (nq[i] * nk[j]) * temp;
+      row[j] = v;
+      mx = fmaxf(mx, v);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int j = lane; j < d; j += 32) {
+      const float e = expf(row[j] - mx);
+      row[j] = e;
+      sum += e;
+    }
+    sum = warp_sum(sum);
+    const float inv = 1.0f / sum;
+    for (int j = lane; j < d; j += 32) {
+      const float v = row[j] * inv;
+      row[j] = v;
+      if (attn_out) attn_out[(((size_t)b * heads + h) * d + i) * d + j] = v;
+    }
+  }
+  __syncthreads();
+  // fold: m[b][o][h*d+j] = sum_i w_out[o][h*d+i] * attn[i][j]
+  for (int e = tid; e < C * d; e += 256) {
+    const int o = e / d, j = e % d;
+    const float* wr = w_out + (size_t)o * C + h * d;
+    float s = 0.f;
+    for (int i = 0; i < d; ++i) s = fmaf(wr[i], attn[i * (d + 1) + j], s);
+    m[((size_t)b * C + o) * C + h * d + j] = s;
+  }
+}
+
+int gram_slab_len(int B, int heads, int64_t HW, int* nslab_out) {
+  // enough (b, head, slab) work items for ~2 waves of 148 SMs; slabs are multiples of 256 pixels
+  int64_t want = (2 * 148 + (int64_t)B * heads - 1) / ((int64_t)B * heads);
+  int64_t maxslab = (HW + 255) / 256;
+  if (want > maxslab) want = maxslab;
+  if (want < 1) want = 1;
+  int64_t len = (HW + want - 1) / want;
+  len = (len + 255) / 256 * 256;
+  int nslab = (int)((HW + len - 1) / len);
+  if (nslab_out) *nslab_out = nslab;
+  return (int)len;
+}
+
+}  // namespace b200ir
+
+using namespace b200ir;
+
+extern "C" int b200ir_mdta_gram_nslab(int B, int C, int heads, int64_t HW) {
+  if (B <= 0 || C <= 0 || heads <= 0 || HW <= 0) return B200IR_E_BADARG;
+  int n = 0;
+  gram_slab_len(B, heads, HW, &n);
+  return n;
+}
+
+namespace b200ir {
+int gram_tc_launch(const void* qkv, int64_t bstride, int B, int C, int heads, int64_t HW, float* partials, int nslab,
+                   int64_t slab_len, cudaStream_t st);  // gram_tc.cu
+bool gram_tc_supported(int dtype, int C, int heads, int64_t HW, int64_t bstride, const void* qkv);
+}
+
+extern "C" int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype, int B, int C, int heads,
+                                    int64_t HW, float* partials, int nslab, int impl, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(qkv && partials && B > 0 && C > 0 && heads > 0 && HW > 0, "mdta_gram: bad args");
+  B200IR_CHECK_ARG(C % heads == 0, "mdta_gram: C=%d not divisible by heads=%d", C, heads);
+  B200IR_CHECK_ARG(dtype_ok(dtype), "mdta_gram: bad dtype");
+  const int d = C / heads;
+  B200IR_UNSUPPORTED(d <= 128, "mdta_gram: head dim %d > 128 unsupported", d);
+  int want = 0;
+  const int64_t slab_len = gram_slab_len(B, heads, HW, &want);
+  B200IR_CHECK_ARG(nslab == want, "mdta_gram: nslab=%d, expected %d (b200ir_mdta_gram_nslab)", nslab, want);
+  B200IR_CHECK_ARG(B <= 65535 && heads <= 65535, "mdta_gram: grid too large");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (impl != B200IR_IMPL_SIMT && gram_tc_supported(dtype, C, heads, HW, bstride, qkv))
+    return gram_tc_launch(qkv, bstride, B, C, heads, HW, partials, nslab, slab_len, st);
+  B200IR_UNSUPPORTED(impl != B200IR_IMPL_TC, "mdta_gram: tcgen05 path unsupported for this shape/dtype");
+  dim3 grid((unsigned)nslab, (unsigned)heads, (unsigned)B);
+  const size_t smem = 2 * (size_t)d * (GPC + 1) * sizeof(float);
+  const int ti = (d + 15) / 16;
+#define LAUNCH(TI) gram_simt_kernel<TI><<<grid, 256, smem, st>>>(qkv, bstride, dtype, C, d, HW, slab_len, partials, nslab)
+  if (ti <= 2) LAUNCH(2);
+  else if (ti <= 3) LAUNCH(3);
+  else if (ti <= 4) LAUNCH(4);
+  else if (ti <= 6) LAUNCH(6);
+  else LAUNCH(8);
+#undef LAUNCH
+  return check_launch("mdta_gram_simt");
+}
+
+extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
+                                            const float* w_out, float* m, float* attn_out, int B, int C, int heads,
+                                            b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(partials && temperature && w_out && m && nslab > 0 && B > 0 && C > 0 && heads > 0,
+                   "mdta_softmax_fold: bad args");
+  B200IR_CHECK_ARG(C % heads == 0 && B <= 65535, "mdta_softmax_fold: bad C/heads/B");
+  const int d = C / heads;
+  B200IR_UNSUPPORTED(d <= 128, "mdta_softmax_fold: head dim %d > 128 unsupported", d);
+  const size_t smem = ((size_t)d * (d + 1) + 2 * d) * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(softmax_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
+    attr_set = true;
+  }
+  softmax_fold_kernel<<<dim3((unsigned)heads, (unsigned)B), 256, smem, (cudaStream_t)stream>>>(
+      partials, nslab, temperature, w_out, m, attn_out, C, d);
+  return check_launch("mdta_softmax_fold");
+}

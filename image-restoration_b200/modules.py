@@ -1,0 +1,307 @@
+"""Drop-in mirror of the reference's nn.Module surface for the Restormer block path.
+
+Same class names, constructor signatures, attribute / parameter names and shapes as
+``/root/reference/Restormer.py`` (LayerNorm :60-70, FeedForward :76-93, Attention :99-132,
+TransformerBlock :137-150, OverlapPatchEmbed :156-165, Downsample :171-179, Upsample :181-189,
+Restormer :193-284), so ``load_state_dict(reference.state_dict(), strict=True)`` is exact and the
+reference's train.py / test.py run unchanged on top.  ``forward`` launches hand-written sm_100a
+kernels through the C ABI (``ops``); there is no PyTorch/CPU fallback.
+
+Compute dtype = dtype of the activation tensor handed in (float32: exact CUDA-core path;
+bfloat16: bf16 storage, fp32 accumulation/statistics, tcgen05 GEMMs).  ``Restormer`` takes the
+image in float32 like the reference and runs its trunk in ``self.compute_dtype``.
+"""
+from __future__ import annotations
+
+import os
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from . import ops
+from . import autograd_ops as A
+
+
+def _w2d(conv: nn.Conv2d) -> torch.Tensor:
+    return conv.weight
+
+
+def _ln_args(norm: "LayerNorm"):
+    body = norm.body
+    if isinstance(body, WithBias_LayerNorm):
+        return L.LN_WITHBIAS, body.weight, body.bias
+    return L.LN_BIASFREE, body.weight, None
+
+
+##########################################################################
+## Layer Norm  (Restormer.py:25-70)
+class BiasFree_LayerNorm(nn.Module):
+    def __init__(self, normalized_shape):
+        super().__init__()
+        if isinstance(normalized_shape, int):
+            normalized_shape = (normalized_shape,)
+        normalized_shape = torch.Size(normalized_shape)
+        assert len(normalized_shape) == 1
+        self.weight = nn.Parameter(torch.ones(normalized_shape))
+        self.normalized_shape = normalized_shape
+
+
+class WithBias_LayerNorm(nn.Module):
+    def __init__(self, normalized_shape):
+        super().__init__()
+        if isinstance(normalized_shape, int):
+            normalized_shape = (normalized_shape,)
+        normalized_shape = torch.Size(normalized_shape)
+        assert len(normalized_shape) == 1
+        self.weight = nn.Parameter(torch.ones(normalized_shape))
+        self.bias = nn.Parameter(torch.zeros(normalized_shape))
+        self.normalized_shape = normalized_shape
+
+
+class LayerNorm(nn.Module):
+    """Channel LayerNorm over an NCHW tensor (Restormer.py:60-70).  Inside TransformerBlock it is
+    fused into the following 1x1 conv; called on its own it runs the same kernel with W = I."""
+
+    def __init__(self, dim, LayerNorm_type):
+        super().__init__()
+        if LayerNorm_type == 'BiasFree':
+            self.body = BiasFree_LayerNorm(dim)
+        else:
+            self.body = WithBias_LayerNorm(dim)
+        self._eye = None
+
+    def forward(self, x):
+        ln_type, w, b = _ln_args(self)
+        c = x.shape[1]
+        if self._eye is None or self._eye.device != x.device:
+            self._eye = torch.eye(c, device=x.device, dtype=torch.float32)
+        return A.ln_conv1x1(x, self._eye, None, ln_type, w, b, None)
+
+
+##########################################################################
+## Gated-Dconv Feed-Forward Network (GDFN)  (Restormer.py:76-93)
+class FeedForward(nn.Module):
+    def __init__(self, dim, ffn_expansion_factor, bias):
+        super().__init__()
+        hidden_features = int(dim * ffn_expansion_factor)
+        self.project_in = nn.Conv2d(dim, hidden_features * 2, kernel_size=1, bias=bias)
+        self.dwconv = nn.Conv2d(hidden_features * 2, hidden_features * 2, kernel_size=3, stride=1, padding=1,
+                                groups=hidden_features * 2, bias=bias)
+        self.project_out = nn.Conv2d(hidden_features, dim, kernel_size=1, bias=bias)
+
+    def _run(self, x, norm=None, res=None, out=None):
+        ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
+        t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None)
+        g = A.dwconv3x3_gelu_gate(t, self.dwconv.weight, self.dwconv.bias)
+        del t
+        return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out)
+
+    def forward(self, x):
+        return self._run(x)
+
+
+##########################################################################
+## Multi-DConv Head Transposed Self-Attention (MDTA)  (Restormer.py:99-132)
+class Attention(nn.Module):
+    def __init__(self, dim, num_heads, bias):
+        super().__init__()
+        self.num_heads = num_heads
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.qkv = nn.Conv2d(dim, dim * 3, kernel_size=1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(dim * 3, dim * 3, kernel_size=3, stride=1, padding=1, groups=dim * 3, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
+
+    def _run(self, x, norm=None, res=None, out=None):
+        ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
+        t = A.ln_conv1x1(x, self.qkv.weight, self.qkv.bias, ln_type, lw, lb, None)
+        qkv = A.dwconv3x3(t, self.qkv_dwconv.weight, self.qkv_dwconv.bias)
+        del t
+        return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
+                           res, out=out)
+
+    def forward(self, x):
+        return self._run(x)
+
+
+##########################################################################
+class TransformerBlock(nn.Module):
+    """x = x + attn(norm1(x)); x = x + ffn(norm2(x))   (Restormer.py:137-150), as 8 kernel launches:
+    LN+qkv | dw3x3 | Gram+norms | softmax+fold | attn.v+proj+res | LN+project_in | dw3x3+GELU gate |
+    project_out+res."""
+
+    def __init__(self, dim, num_heads, ffn_expansion_factor, bias, LayerNorm_type):
+        super().__init__()
+        self.norm1 = LayerNorm(dim, LayerNorm_type)
+        self.attn = Attention(dim, num_heads, bias)
+        self.norm2 = LayerNorm(dim, LayerNorm_type)
+        self.ffn = FeedForward(dim, ffn_expansion_factor, bias)
+
+    def forward(self, x, out=None):
+        x = self.attn._run(x, norm=self.norm1, res=x)
+        x = self.ffn._run(x, norm=self.norm2, res=x, out=out)
+        return x
+
+
+##########################################################################
+## Overlapped image patch embedding with 3x3 Conv  (Restormer.py:156-165)
+class OverlapPatchEmbed(nn.Module):
+    def __init__(self, in_c=3, embed_dim=48, bias=False):
+        super().__init__()
+        self.proj = nn.Conv2d(in_c, embed_dim, kernel_size=3, stride=1, padding=1, bias=bias)
+
+    def forward(self, x, out_dtype=None):
+        return A.conv3x3(x, self.proj.weight, self.proj.bias, None, L.SHUFFLE_NONE, out_dtype=out_dtype)
+
+
+##########################################################################
+## Resizing modules  (Restormer.py:171-189)
+class Downsample(nn.Module):
+    def __init__(self, n_feat):
+        super().__init__()
+        self.body = nn.Sequential(nn.Conv2d(n_feat, n_feat // 2, kernel_size=3, stride=1, padding=1, bias=False),
+                                  nn.PixelUnshuffle(2))
+
+    def forward(self, x, out=None):
+        return A.conv3x3(x, self.body[0].weight, None, None, L.UNSHUFFLE2, out=out)
+
+
+class Upsample(nn.Module):
+    def __init__(self, n_feat):
+        super().__init__()
+        self.body = nn.Sequential(nn.Conv2d(n_feat, n_feat * 2, kernel_size=3, stride=1, padding=1, bias=False),
+                                  nn.PixelShuffle(2))
+
+    def forward(self, x, out=None):
+        return A.conv3x3(x, self.body[0].weight, None, None, L.SHUFFLE2, out=out)
+
+
+##########################################################################
+##---------- Restormer -----------------------  (Restormer.py:193-284)
+def _default_compute_dtype():
+    v = os.environ.get("B200IR_COMPUTE_DTYPE", "fp32").lower()
+    return torch.bfloat16 if v in ("bf16", "bfloat16") else torch.float32
+
+
+class Restormer(nn.Module):
+    def __init__(self,
+                 inp_channels=3,
+                 out_channels=3,
+                 dim=48,
+                 num_blocks=[4, 6, 6, 8],
+                 num_refinement_blocks=4,
+                 heads=[1, 2, 4, 8],
+                 ffn_expansion_factor=2.66,
+                 bias=False,
+                 LayerNorm_type='WithBias',  ## Other option 'BiasFree'
+                 dual_pixel_task=False  ## True for dual-pixel defocus deblurring only. Also set inp_channels=6
+                 ):
+        super().__init__()
+
+        def stack(d, h, n):
+            return nn.Sequential(*[TransformerBlock(dim=d, num_heads=h, ffn_expansion_factor=ffn_expansion_factor,
+                                                    bias=bias, LayerNorm_type=LayerNorm_type) for _ in range(n)])
+
+        self.patch_embed = OverlapPatchEmbed(inp_channels, dim)
+        self.encoder_level1 = stack(dim, heads[0], num_blocks[0])
+        self.down1_2 = Downsample(dim)
+        self.encoder_level2 = stack(int(dim * 2 ** 1), heads[1], num_blocks[1])
+        self.down2_3 = Downsample(int(dim * 2 ** 1))
+        self.encoder_level3 = stack(int(dim * 2 ** 2), heads[2], num_blocks[2])
+        self.down3_4 = Downsample(int(dim * 2 ** 2))
+        self.latent = stack(int(dim * 2 ** 3), heads[3], num_blocks[3])
+        self.up4_3 = Upsample(int(dim * 2 ** 3))
+        self.reduce_chan_level3 = nn.Conv2d(int(dim * 2 ** 3), int(dim * 2 ** 2), kernel_size=1, bias=bias)
+        self.decoder_level3 = stack(int(dim * 2 ** 2), heads[2], num_blocks[2])
+        self.up3_2 = Upsample(int(dim * 2 ** 2))
+        self.reduce_chan_level2 = nn.Conv2d(int(dim * 2 ** 2), int(dim * 2 ** 1), kernel_size=1, bias=bias)
+        self.decoder_level2 = stack(int(dim * 2 ** 1), heads[1], num_blocks[1])
+        self.up2_1 = Upsample(int(dim * 2 ** 1))
+        self.decoder_level1 = stack(int(dim * 2 ** 1), heads[0], num_blocks[0])
+        self.refinement = stack(int(dim * 2 ** 1), heads[0], num_refinement_blocks)
+        self.dual_pixel_task = dual_pixel_task
+        if self.dual_pixel_task:
+            self.skip_conv = nn.Conv2d(dim, int(dim * 2 ** 1), kernel_size=1, bias=bias)
+        self.output = nn.Conv2d(int(dim * 2 ** 1), out_channels, kernel_size=3, stride=1, padding=1, bias=bias)
+
+        self.compute_dtype = _default_compute_dtype()  # not a parameter/buffer: state_dict stays the reference's
+
+    def set_compute_dtype(self, dtype):
+        if dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("compute dtype must be torch.float32 or torch.bfloat16")
+        self.compute_dtype = dtype
+        return self
+
+    @staticmethod
+    def _run_stack(seq, x, out_last=None):
+        n = len(seq)
+        for i, blk in enumerate(seq):
+            x = blk(x, out=out_last if i == n - 1 else None)
+        return x
+
+    def forward(self, inp_img):
+        if inp_img.dim() != 4:
+            raise ValueError("expected NCHW input")
+        if not inp_img.is_cuda:
+            raise ValueError("b200ir.Restormer runs on CUDA only (no CPU fallback)")
+        B, _, H, W = inp_img.shape
+        if H % 8 or W % 8:
+            raise ValueError(f"H and W must be multiples of 8 (three PixelUnshuffle(2) levels), got {H}x{W}")
+        inp_img = inp_img.contiguous()
+        cd = self.compute_dtype
+        grad = torch.is_grad_enabled() and (inp_img.requires_grad or any(p.requires_grad for p in self.parameters()))
+        dev = inp_img.device
+        dim = self.patch_embed.proj.out_channels
+
+        # skip tensors are produced directly inside their concat buffers (no torch.cat copy) when no
+        # autograd graph is needed; with autograd the plain cat is used.
+        def cat_buf(c_up, c_skip, h, w):
+            return None if grad else torch.empty((B, c_up + c_skip, h, w), device=dev, dtype=cd)
+
+        cat1 = cat_buf(dim, dim, H, W)
+        cat2 = cat_buf(dim * 2, dim * 2, H // 2, W // 2)
+        cat3 = cat_buf(dim * 4, dim * 4, H // 4, W // 4)
+
+        inp_enc_level1 = self.patch_embed(inp_img, out_dtype=cd)
+        out_enc_level1 = self._run_stack(self.encoder_level1, inp_enc_level1,
+                                         None if grad or len(self.encoder_level1) == 0 else cat1[:, dim:])
+        inp_enc_level2 = self.down1_2(out_enc_level1)
+        out_enc_level2 = self._run_stack(self.encoder_level2, inp_enc_level2,
+                                         None if grad or len(self.encoder_level2) == 0 else cat2[:, dim * 2:])
+        inp_enc_level3 = self.down2_3(out_enc_level2)
+        out_enc_level3 = self._run_stack(self.encoder_level3, inp_enc_level3,
+                                         None if grad or len(self.encoder_level3) == 0 else cat3[:, dim * 4:])
+        inp_enc_level4 = self.down3_4(out_enc_level3)
+        latent = self._run_stack(self.latent, inp_enc_level4)
+
+        inp_dec_level3 = self._cat(self.up4_3, latent, out_enc_level3, cat3, dim * 4)
+        inp_dec_level3 = A.ln_conv1x1(inp_dec_level3, self.reduce_chan_level3.weight, self.reduce_chan_level3.bias,
+                                      L.LN_NONE, None, None, None)
+        out_dec_level3 = self._run_stack(self.decoder_level3, inp_dec_level3)
+
+        inp_dec_level2 = self._cat(self.up3_2, out_dec_level3, out_enc_level2, cat2, dim * 2)
+        inp_dec_level2 = A.ln_conv1x1(inp_dec_level2, self.reduce_chan_level2.weight, self.reduce_chan_level2.bias,
+                                      L.LN_NONE, None, None, None)
+        out_dec_level2 = self._run_stack(self.decoder_level2, inp_dec_level2)
+
+        inp_dec_level1 = self._cat(self.up2_1, out_dec_level2, out_enc_level1, cat1, dim)
+        out_dec_level1 = self._run_stack(self.decoder_level1, inp_dec_level1)
+        out_dec_level1 = self._run_stack(self.refinement, out_dec_level1)
+
+        if self.dual_pixel_task:
+            out_dec_level1 = A.ln_conv1x1(inp_enc_level1, self.skip_conv.weight, self.skip_conv.bias, L.LN_NONE, None,
+                                          None, out_dec_level1)
+            return A.conv3x3(out_dec_level1, self.output.weight, self.output.bias, None, L.SHUFFLE_NONE,
+                             out_dtype=inp_img.dtype)
+        return A.conv3x3(out_dec_level1, self.output.weight, self.output.bias, inp_img, L.SHUFFLE_NONE,
+                         out_dtype=inp_img.dtype)
+
+    @staticmethod
+    def _cat(up, x, skip, buf, c_up):
+        """torch.cat([up(x), skip], 1) (Restormer.py:259-260,264-265,269-270) without the copy when possible."""
+        if buf is None:
+            return torch.cat([up(x), skip], 1)
+        up(x, out=buf[:, :c_up])
+        if skip.data_ptr() != buf[:, c_up:].data_ptr():  # skip was not produced in place (empty stack)
+            ops.copy_cast(skip, buf[:, c_up:])
+        return buf

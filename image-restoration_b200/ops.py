@@ -1,0 +1,215 @@
+"""Tensor-level wrappers of the C ABI: torch only provides device memory and the stream.
+
+Every function enqueues hand-written CUDA kernels from libb200ir.so on torch's current stream.
+Activations are NCHW (possibly channel-slices of a wider buffer: only the batch stride is free).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import _lib as L
+
+lib = L.lib
+_DT = {torch.float32: L.F32, torch.bfloat16: L.BF16}
+
+# ---- instrumentation (bench.py): launch counter and optional per-kernel CUDA-event timing ----
+LAUNCHES = 0            # kernels of libb200ir.so enqueued since import (each wrapper adds its launch count)
+_TIMING = None          # None, or dict: key -> list of (start_event, end_event)
+_TIMING_FILTER = None   # None = time every op; else a set of op names
+
+
+def timing_start(only=None):
+    global _TIMING, _TIMING_FILTER
+    _TIMING, _TIMING_FILTER = {}, (set(only) if only else None)
+
+
+def timing_stop():
+    """-> {key: (n_launches, mean_ms)}; caller must have synchronised the stream."""
+    global _TIMING
+    t, _TIMING = _TIMING, None
+    return {k: (len(v), sum(a.elapsed_time(b) for a, b in v) / len(v)) for k, v in (t or {}).items()}
+
+
+class _timed:
+    __slots__ = ("key", "ev")
+
+    def __init__(self, name, *shape):
+        global LAUNCHES
+        LAUNCHES += 1
+        self.key = None
+        if _TIMING is not None and (_TIMING_FILTER is None or name in _TIMING_FILTER):
+            self.key = (name,) + tuple(shape)
+
+    def __enter__(self):
+        if self.key is not None:
+            self.ev = torch.cuda.Event(enable_timing=True)
+            self.ev.record()
+        return self
+
+    def __exit__(self, *a):
+        if self.key is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            _TIMING.setdefault(self.key, []).append((self.ev, e))
+        return False
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _act(t: torch.Tensor, name: str):
+    """(ptr, batch_stride, dtype_code) of an NCHW activation view."""
+    if not t.is_cuda:
+        raise ValueError(f"{name}: expected a CUDA tensor (this package has no CPU fallback)")
+    if t.dtype not in _DT:
+        raise ValueError(f"{name}: dtype {t.dtype} unsupported (float32 / bfloat16)")
+    if t.dim() != 4:
+        raise ValueError(f"{name}: expected NCHW, got shape {tuple(t.shape)}")
+    b, c, h, w = t.shape
+    s = t.stride()
+    ok = (s[3] == 1 or w == 1) and (s[2] == w or h == 1) and (s[1] == h * w or c == 1)
+    if not ok:
+        raise ValueError(f"{name}: not NCHW-contiguous within a sample (shape {tuple(t.shape)}, strides {s})")
+    bs = s[0] if b > 1 else c * h * w
+    return t.data_ptr(), bs, _DT[t.dtype]
+
+
+def _par(t: Optional[torch.Tensor], name: str, numel: Optional[int] = None) -> Optional[int]:
+    """Device pointer of an fp32 contiguous parameter (None -> NULL)."""
+    if t is None:
+        return None
+    if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous():
+        raise ValueError(f"{name}: parameters must be contiguous float32 CUDA tensors")
+    if numel is not None and t.numel() != numel:
+        raise ValueError(f"{name}: expected {numel} elements, got {t.numel()}")
+    return t.data_ptr()
+
+
+def ln_conv1x1(x, w, bias=None, ln_type=L.LN_NONE, ln_w=None, ln_b=None, res=None, out=None,
+               out_dtype=None, per_sample_w=False):
+    """y = res + bias + W . LN(x)   (LayerNorm + 1x1 conv + residual), fp32 CUDA-core path."""
+    B, Cin, H, W_ = x.shape
+    Cout = w.shape[-2] if per_sample_w else w.shape[0]
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        out = torch.empty((B, Cout, H, W_), device=x.device, dtype=out_dtype or x.dtype)
+    yp, ybs, ydt = _act(out, "out")
+    rp, rbs, rdt = (None, 0, 0)
+    if res is not None:
+        if tuple(res.shape) != (B, Cout, H, W_):
+            raise ValueError("res shape mismatch")
+        rp, rbs, rdt = _act(res, "res")
+    wp = _par(w, "w", (B if per_sample_w else 1) * Cout * Cin)
+    with _timed("ln_conv1x1", B, Cin, Cout, H * W_, ln_type, int(res is not None), int(per_sample_w), xdt, ydt):
+      rc = lib.b200ir_ln_conv1x1_fwd(xp, xbs, xdt, wp, Cout * Cin if per_sample_w else 0, _par(bias, "bias", Cout),
+                                   ln_type, _par(ln_w, "ln_w", Cin if ln_type else None),
+                                   _par(ln_b, "ln_b", Cin if ln_type == L.LN_WITHBIAS else None),
+                                     rp, rbs, rdt, yp, ybs, ydt, B, Cin, Cout, H * W_, _stream())
+    L.check(rc, "b200ir_ln_conv1x1_fwd")
+    return out
+
+
+def dwconv3x3(x, w, bias=None, out=None):
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        out = torch.empty_like(x, memory_format=torch.contiguous_format)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != xdt:
+        raise ValueError("dwconv3x3: in/out dtype mismatch")
+    with _timed("dwconv3x3", B, C, H, W_, xdt):
+        rc = lib.b200ir_dwconv3x3_fwd(xp, xbs, _par(w, "w", C * 9), _par(bias, "bias", C), yp, ybs, xdt, B, C, H, W_,
+                                      _stream())
+    L.check(rc, "b200ir_dwconv3x3_fwd")
+    return out
+
+
+def dwconv3x3_gelu_gate(x, w, bias=None, out=None):
+    B, C2, H, W_ = x.shape
+    if C2 % 2:
+        raise ValueError("dwconv3x3_gelu_gate: channel count must be even")
+    Hd = C2 // 2
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        out = torch.empty((B, Hd, H, W_), device=x.device, dtype=x.dtype)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != xdt:
+        raise ValueError("dwconv3x3_gelu_gate: in/out dtype mismatch")
+    with _timed("dwconv3x3_gelu_gate", B, Hd, H, W_, xdt):
+        rc = lib.b200ir_dwconv3x3_gelu_gate_fwd(xp, xbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), yp, ybs, xdt,
+                                                B, Hd, H, W_, _stream())
+    L.check(rc, "b200ir_dwconv3x3_gelu_gate_fwd")
+    return out
+
+
+def mdta_gram(qkv, heads, impl=L.IMPL_AUTO):
+    """Partial Grams / norms per (b, head, HW-slab): fp32 [B, heads, nslab, d*d+2d]."""
+    B, C3, H, W_ = qkv.shape
+    C = C3 // 3
+    d = C // heads
+    qp, qbs, qdt = _act(qkv, "qkv")
+    nslab = lib.b200ir_mdta_gram_nslab(B, C, heads, H * W_)
+    if nslab <= 0:
+        raise RuntimeError("b200ir_mdta_gram_nslab failed")
+    partials = torch.empty((B, heads, nslab, d * d + 2 * d), device=qkv.device, dtype=torch.float32)
+    with _timed("mdta_gram", B, C, heads, H * W_, qdt):
+        rc = lib.b200ir_mdta_gram_fwd(qp, qbs, qdt, B, C, heads, H * W_, partials.data_ptr(), nslab, impl, _stream())
+    L.check(rc, "b200ir_mdta_gram_fwd")
+    return partials
+
+
+def mdta_softmax_fold(partials, temperature, w_out, want_attn=False):
+    """attn = softmax(normalised Gram * temperature); returns m = W_out . blockdiag(attn) [B,C,C] (and attn)."""
+    B, heads, nslab, per = partials.shape
+    C = w_out.shape[0]
+    d = C // heads
+    m = torch.empty((B, C, C), device=partials.device, dtype=torch.float32)
+    attn = torch.empty((B, heads, d, d), device=partials.device, dtype=torch.float32) if want_attn else None
+    with _timed("mdta_softmax_fold", B, C, heads, nslab):
+        rc = lib.b200ir_mdta_softmax_fold_fwd(partials.data_ptr(), nslab, _par(temperature, "temperature", heads),
+                                              _par(w_out, "w_out", C * C), m.data_ptr(),
+                                              attn.data_ptr() if want_attn else None, B, C, heads, _stream())
+    L.check(rc, "b200ir_mdta_softmax_fold_fwd")
+    return (m, attn) if want_attn else m
+
+
+def conv3x3(x, w, bias=None, res=None, shuffle=L.SHUFFLE_NONE, out=None, out_dtype=None):
+    B, Cin, H, W_ = x.shape
+    Cout = w.shape[0]
+    xp, xbs, xdt = _act(x, "x")
+    if shuffle == L.UNSHUFFLE2:
+        oshape = (B, Cout * 4, H // 2, W_ // 2)
+    elif shuffle == L.SHUFFLE2:
+        oshape = (B, Cout // 4, H * 2, W_ * 2)
+    else:
+        oshape = (B, Cout, H, W_)
+    if out is None:
+        out = torch.empty(oshape, device=x.device, dtype=out_dtype or x.dtype)
+    elif tuple(out.shape) != oshape:
+        raise ValueError(f"conv3x3: out shape {tuple(out.shape)} != {oshape}")
+    yp, ybs, ydt = _act(out, "out")
+    rp, rbs, rdt = (None, 0, 0)
+    if res is not None:
+        if tuple(res.shape) != oshape:
+            raise ValueError("conv3x3: res shape mismatch")
+        rp, rbs, rdt = _act(res, "res")
+    with _timed("conv3x3", B, Cin, Cout, H, W_, shuffle, xdt, ydt):
+        rc = lib.b200ir_conv3x3_fwd(xp, xbs, xdt, _par(w, "w", Cout * Cin * 9), _par(bias, "bias", Cout), rp, rbs, rdt,
+                                    yp, ybs, ydt, B, Cin, Cout, H, W_, shuffle, _stream())
+    L.check(rc, "b200ir_conv3x3_fwd")
+    return out
+
+
+def copy_cast(x, out):
+    """out[...] = x (dtype cast allowed); both NCHW views of identical shape."""
+    if tuple(x.shape) != tuple(out.shape):
+        raise ValueError("copy_cast: shape mismatch")
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    yp, ybs, ydt = _act(out, "out")
+    with _timed("copy_cast", B, C * H * W_, xdt, ydt):
+        L.check(lib.b200ir_copy_cast(xp, xbs, xdt, yp, ybs, ydt, B, C * H * W_, _stream()), "b200ir_copy_cast")
+    return out

@@ -1,0 +1,100 @@
+/* b200ir.h — C ABI of libb200ir.so: hand-written sm_100a kernels for the Restormer-family
+ * transformer block (LayerNorm -> MDTA -> LayerNorm -> GDFN) and its U-Net glue.
+ *
+ * The reference (1601339895/Image-Restoration) has no FFI layer: its boundary for this path is
+ * the nn.Module surface of Restormer.py.  Each entry point below replaces the chain of stock
+ * ATen calls of one reference forward() and cites it (file:line in /root/reference).  The
+ * Python mirror of the reference modules (image-restoration_b200/modules.py) binds these with
+ * ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *  - All activations are NCHW, channel stride = H*W elements, explicit batch stride (elements),
+ *    so channel slices of a wider buffer (q|k|v chunks, concat halves) are passed without copies.
+ *  - dtype: B200IR_F32 or B200IR_BF16 for activations; parameters are always fp32 device arrays
+ *    in the reference's own state_dict layout (packed/bf16 copies are made by b200ir_pack_*).
+ *  - The library never allocates, frees or synchronises: caller owns every buffer (including
+ *    workspaces) and the stream; every call only enqueues work on `stream`.
+ *  - Return 0 on success; >0 = cudaError_t; <0 = B200IR_E_* (bad argument / unsupported shape).
+ *    b200ir_last_error_string() gives the thread-local message.  No C++ exception crosses.
+ */
+#ifndef B200IR_H
+#define B200IR_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* b200ir_stream_t; /* cudaStream_t */
+
+enum { B200IR_F32 = 0, B200IR_BF16 = 1 };
+enum { B200IR_LN_NONE = 0, B200IR_LN_WITHBIAS = 1, B200IR_LN_BIASFREE = 2 };
+enum { B200IR_SHUFFLE_NONE = 0, B200IR_UNSHUFFLE2 = 1, B200IR_SHUFFLE2 = 2 };
+enum { B200IR_IMPL_AUTO = 0, B200IR_IMPL_SIMT = 1, B200IR_IMPL_TC = 2 };
+enum { B200IR_E_BADARG = -1, B200IR_E_UNSUPPORTED = -2, B200IR_E_WORKSPACE = -3, B200IR_E_DRIVER = -4 };
+
+int b200ir_version(void);
+const char* b200ir_last_error_string(void);
+
+/* y[b,o,p] = (res[b,o,p]) + bias[o] + sum_c w[b][o,c] * LN(x)[b,c,p]
+ * Replaces LayerNorm.forward + the following 1x1 nn.Conv2d (+ the residual add of
+ * TransformerBlock.forward): Restormer.py:37-39,54-57,68-70 + :114 (qkv), :89 (project_in),
+ * :92 (project_out), :131 (project_out of attention, with the per-sample folded weight),
+ * :147-148 (x = x + ...), :261,:266 (reduce_chan_level{3,2}).
+ * w: fp32 [Cout,Cin] (w_bstride = 0) or per-sample [B,Cout,Cin] (w_bstride = Cout*Cin).
+ * ln_type NONE: ln_w/ln_b ignored.  res may be NULL.  SIMT fp32-FMA implementation. */
+int b200ir_ln_conv1x1_fwd(const void* x, int64_t x_bstride, int x_dtype,
+                          const float* w, int64_t w_bstride, const float* bias,
+                          int ln_type, const float* ln_w, const float* ln_b,
+                          const void* res, int64_t res_bstride, int res_dtype,
+                          void* y, int64_t y_bstride, int y_dtype,
+                          int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);
+
+/* Depthwise 3x3, stride 1, zero pad 1 (+bias): Attention.qkv_dwconv, Restormer.py:106,114.
+ * w fp32 [C,3,3]. */
+int b200ir_dwconv3x3_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias,
+                         void* y, int64_t y_bstride, int dtype,
+                         int B, int C, int H, int W, b200ir_stream_t stream);
+
+/* FeedForward.dwconv + chunk(2) + gelu(x1)*x2: Restormer.py:84,90-91.
+ * x has 2*Hd channels, y has Hd: y[c] = gelu_erf(dw(x)[c]) * dw(x)[c+Hd].  w fp32 [2Hd,3,3]. */
+int b200ir_dwconv3x3_gelu_gate_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias,
+                                   void* y, int64_t y_bstride, int dtype,
+                                   int B, int Hd, int H, int W, b200ir_stream_t stream);
+
+/* MDTA stage 1 — split-K Gram over HW slabs: for every (b, head, slab) the partial
+ * q.k^T [d,d] and partial sum q^2 [d], sum k^2 [d] (d = C/heads), fp32, fixed order
+ * (deterministic).  Replaces F.normalize + q@k^T, Restormer.py:117-124.
+ * qkv: [B,3C,HW] (q|k|v chunks, Restormer.py:115).  partials: [B,heads,nslab,d*d+2d] fp32.
+ * b200ir_mdta_gram_nslab gives nslab for a shape (so the caller can size `partials`). */
+int b200ir_mdta_gram_nslab(int B, int C, int heads, int64_t HW);
+int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype, int B, int C, int heads, int64_t HW,
+                         float* partials, int nslab, int impl, b200ir_stream_t stream);
+
+/* MDTA stage 2 — reduce slabs, attn = softmax(q^.k^^T * temperature) (Restormer.py:121-125) and
+ * fold the output projection: m[b][o, h*d+j] = sum_i w_out[o, h*d+i] * attn[b,h][i,j], so that
+ * project_out(attn @ v) (Restormer.py:127-131) becomes ONE 1x1 GEMM with per-sample weight m
+ * (b200ir_ln_conv1x1_fwd / b200ir_gemm_tc_fwd with w_bstride = C*C).
+ * m: fp32 [B,C,C]; attn_out (optional, may be NULL): fp32 [B,heads,d,d] (kept for backward). */
+int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
+                                 const float* w_out, float* m, float* attn_out,
+                                 int B, int C, int heads, b200ir_stream_t stream);
+
+/* Dense 3x3 conv, pad 1 (+bias) (+res) with PixelUnshuffle(2)/PixelShuffle(2) folded into the
+ * store: OverlapPatchEmbed (Restormer.py:162-165), Downsample (:171-179), Upsample (:181-189),
+ * output conv + inp_img (:281).  w fp32 [Cout,Cin,3,3].  res (optional) has the OUTPUT shape.
+ * y shape: NONE [B,Cout,H,W]; UNSHUFFLE2 [B,4Cout,H/2,W/2]; SHUFFLE2 [B,Cout/4,2H,2W]. */
+int b200ir_conv3x3_fwd(const void* x, int64_t x_bstride, int x_dtype, const float* w, const float* bias,
+                       const void* res, int64_t res_bstride, int res_dtype,
+                       void* y, int64_t y_bstride, int y_dtype,
+                       int B, int Cin, int Cout, int H, int W, int shuffle_mode, b200ir_stream_t stream);
+
+/* Strided NCHW channel-slice copy / dtype cast (used to place a skip tensor into a concat
+ * buffer, Restormer.py:260,265,270, and for fp32<->bf16 I/O casts at the module boundary). */
+int b200ir_copy_cast(const void* x, int64_t x_bstride, int x_dtype, void* y, int64_t y_bstride, int y_dtype,
+                     int B, int64_t CHW, b200ir_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,67 @@
+"""GPU parity of the whole Restormer forward: fp32 max-abs <= 1e-4, bf16 PSNR >= 50 dB (BASELINE.json)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import restormer_oracle as O
+from oracle.gen_golden_cases import NET_CASES
+
+pytestmark = pytest.mark.gpu
+
+
+def _net(cfg, wseed):
+    import b200ir
+    full = dict(O.DEFAULT_CFG)
+    full.update(cfg)
+    net = b200ir.Restormer(**full).cuda().eval()
+    net.load_state_dict(O.synth_state_dict(cfg, seed=wseed), strict=True)
+    return net, full
+
+
+@pytest.mark.parametrize("case", NET_CASES, ids=[c[0] for c in NET_CASES])
+def test_net_fp32_vs_reference_golden(case):
+    name, cfg, b, h, w, wseed, iseed = case
+    net, full = _net(cfg, wseed)
+    x = O.synth_image(b, h, w, seed=iseed, c=full["inp_channels"])
+    with torch.no_grad():
+        y = net.set_compute_dtype(torch.float32)(x.cuda()).cpu()
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))["y"]
+    assert np.abs(y.numpy() - gold).max() <= 1e-4
+
+
+@pytest.mark.parametrize("case", NET_CASES, ids=[c[0] for c in NET_CASES])
+def test_net_bf16_psnr(case):
+    name, cfg, b, h, w, wseed, iseed = case
+    net, full = _net(cfg, wseed)
+    x = O.synth_image(b, h, w, seed=iseed, c=full["inp_channels"])
+    with torch.no_grad():
+        y = net.set_compute_dtype(torch.bfloat16)(x.cuda()).cpu()
+    gold = torch.from_numpy(np.load(os.path.join(GOLDEN, name + ".npz"))["y"])
+    assert y.dtype == torch.float32
+    assert O.psnr(y, gold) >= 50.0, O.psnr(y, gold)
+
+
+def test_cfg1_fp32_128_vs_oracle():
+    """BASELINE configs[0]: default Restormer, 1x3x128x128 fp32, against the CPU oracle run here."""
+    net, full = _net({}, 0)
+    x = O.synth_image(1, 128, 128, seed=1234)
+    with torch.no_grad():
+        y = net(x.cuda()).cpu()
+        ref = O.restormer_forward(O.synth_state_dict({}, seed=0), x)
+    assert (y - ref).abs().max() <= 1e-4
+
+
+def test_fp32_linearity_of_skip_and_determinism():
+    """Size-independent properties at a larger size: bitwise run-to-run determinism (fixed-order split-K)
+    and batch independence (each sample's output does not depend on its batch-mates)."""
+    net, full = _net({}, 0)
+    x = O.synth_image(3, 64, 96, seed=9).cuda()
+    with torch.no_grad():
+        y1 = net(x)
+        y2 = net(x)
+        y_single = net(x[1:2].contiguous())
+    assert torch.equal(y1, y2)
+    assert (y1[1:2] - y_single).abs().max() <= 1e-5
