@@ -1,0 +1,241 @@
+#!/usr/bin/env python
+"""bench.py — megapixels/s of the Restormer forward (BASELINE.json configs[1]: bf16, 256x256, batch 16/GPU).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+
+One "step" = one forward of the default Restormer over one batch of 16 synthetic 256x256 RGB images per GPU
+(batch-sharded, no data-path collective => weak scaling).  Prints ONE JSON line (rank 0).
+  value     : whole-job MP/s, inputs already resident in HBM, CUDA-event timed, max over ranks.
+  e2e       : same metric through the public nn.Module call with pinned-HOST input and output inside the
+              timed region (H2D of the fp32 batch, forward, D2H of the restored fp32 batch).
+  roofline  : dominant kernel (the GDFN depthwise-3x3 + GELU gate at the full-resolution C=96 levels),
+              algorithmic bytes / live CUDA-event duration vs MEASURED_PEAKS.json hbm_gbs.
+  cpu_baseline / --impl reference: the oracle port (same ATen CPU ops as the reference's Restormer.py) on the
+              host cores, bounded sample (B=1).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = "megapixels/sec (Restormer 256x256 fwd, bf16, batch 16 per GPU)"
+H = W = 256
+BATCH = 16
+N_INPUT_SETS = 12  # 12 x 12.6 MB fp32 inputs (151 MB) > 126 MB L2; every level-1 activation is 100-268 MB anyway
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm = sorted(int(r[1]) for r in self.rows if len(r) > 2 and r[1].isdigit())
+        mx = [int(r[2]) for r in self.rows if len(r) > 2 and r[2].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = set()
+        for r in self.rows:
+            for i, n in enumerate(names):
+                if len(r) > 5 + i and r[5 + i].lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(self.rows)}
+
+
+def cpu_reference_run(steps, warmup, sample_hw=256):
+    """The reference's CPU path (oracle port: identical ATen CPU ops) on all host cores; B=1 sample per step."""
+    from oracle import restormer_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    sd = O.synth_state_dict({}, seed=0)
+    x = O.synth_image(1, sample_hw, sample_hw, seed=1234)
+    with torch.no_grad():
+        for _ in range(warmup):
+            O.restormer_forward(sd, x)
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            O.restormer_forward(sd, x)
+        dt = (time.perf_counter() - t0) / max(steps, 1)
+    return (sample_hw * sample_hw / 1e6) / dt, dt, cores, f"1 of the 16 images ({sample_hw}x{sample_hw}, fp32) per step"
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    steps, warmup = max(1, min(args.steps, 3)), max(1, min(args.warmup, 1))
+    v, dt, cores, sample = cpu_reference_run(steps, warmup)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "MP/s", "n_gpus": args.gpus, "steps": steps,
+        "warmup": warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "Restormer(dim=48,[4,6,6,8]) forward 256x256, CPU fp32 eager (oracle port of Restormer.py)"},
+        "cpu_baseline": {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "MP/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=BATCH)
+    ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    args.warmup = max(args.warmup, 3)
+
+    import torch.distributed as dist
+    import b200ir
+    from b200ir import ops
+    from oracle import restormer_oracle as O  # weights/inputs generator + cpu_baseline leg only
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    cd = torch.bfloat16 if args.dtype == "bf16" else torch.float32
+    B = args.batch
+
+    net = b200ir.Restormer().to(dev).eval().set_compute_dtype(cd)
+    net.load_state_dict(O.synth_state_dict({}, seed=0), strict=True)
+    host = [O.synth_image(B, H, W, seed=1234 + 100 * rank + i).pin_memory() for i in range(N_INPUT_SETS)]
+    dev_in = [h.to(dev) for h in host]
+    host_out = torch.empty((B, 3, H, W), dtype=torch.float32).pin_memory()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    mp_per_step_total = world * B * H * W / 1e6
+    GATE_KEY = "dwconv3x3_gelu_gate"
+    with torch.no_grad():
+        for i in range(args.warmup):
+            net(dev_in[i % N_INPUT_SETS])
+        # ---- device-resident timing -------------------------------------------------------
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        barrier()
+        l0 = ops.LAUNCHES
+        ops.timing_start(only=[GATE_KEY])
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(args.steps):
+            net(dev_in[i % N_INPUT_SETS])
+        e1.record()
+        barrier()
+        ms = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        gate_t = ops.timing_stop()
+        launches = (ops.LAUNCHES - l0)
+        clocks = sampler.stop() if rank == 0 else None
+        # ---- end-to-end: pinned host in -> forward -> pinned host out ---------------------
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            x = host[i % N_INPUT_SETS].to(dev, non_blocking=True)
+            y = net(x)
+            host_out.copy_(y, non_blocking=True)
+        e1.record()
+        barrier()
+        ms_e2e = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        # ---- optional per-kernel table (separate pass, not part of any reported number) ----
+        table = None
+        if args.kernel_table and rank == 0:
+            ops.timing_start()
+            net(dev_in[0])
+            torch.cuda.synchronize()
+            table = ops.timing_stop()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    pk, pk_src = peaks()
+    # dominant kernel: GDFN dw3x3 + GELU gate at full-resolution C=96 (Hd=255): 8 of 44 blocks, the largest tensor
+    key = max((k for k in gate_t), key=lambda k: gate_t[k][0] * gate_t[k][1])
+    _, kb, khd, kh, kw, kdt = key
+    esz = 2 if kdt == 1 else 4
+    alg_bytes = kb * kh * kw * (2 * khd + khd) * esz  # read 2*Hd planes, write Hd planes (K5 = 2Hd+Hd)
+    kms = gate_t[key][1]
+    achieved = alg_bytes / (kms * 1e-3) / 1e9
+    roofline = {"kernel": f"dwconv3x3_gelu_gate B{kb} Hd{khd} {kh}x{kw}", "bound": "hbm", "achieved": achieved,
+                "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                "traffic": None, "launch_ms": kms, "launches_timed": gate_t[key][0], "alg_bytes_per_launch": alg_bytes}
+    out = {
+        "metric": METRIC, "value": mp_per_step_total / (ms * 1e-3), "unit": "MP/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": {"workload": f"Restormer(dim=48,[4,6,6,8],heads[1,2,4,8]) forward, {H}x{W} RGB, batch {B}/GPU, "
+                               f"batch-sharded; BASELINE configs[1]",
+                   "l2": f"{N_INPUT_SETS} rotating input batches (151 MB) > 126 MB L2; activations 100-268 MB each",
+                   "parallelism": f"dp{world} (no data-path collective)"},
+        "e2e": {"value": mp_per_step_total / (ms_e2e * 1e-3), "unit": "MP/s", "ms_per_step": ms_e2e,
+                "h2d_bytes_per_step": B * 3 * H * W * 4, "d2h_bytes_per_step": B * 3 * H * W * 4},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
+    }
+    if not args.no_cpu_baseline:
+        v, dt, cores, sample = cpu_reference_run(2, 1)
+        out["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample,
+                               "s_per_step": dt}
+    if table is not None:
+        rows = sorted(([list(k), n, m, n * m] for k, (n, m) in table.items()), key=lambda r: -r[3])
+        json.dump({"total_ms": sum(r[3] for r in rows), "rows": rows}, open(args.kernel_table, "w"), indent=0)
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
