@@ -33,9 +33,33 @@ def _p(t):
     return t.contiguous()
 
 
-def ln_conv1x1(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None):
+def _sig(*ts):
+    return tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
+
+
+def packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b):
+    """bf16-packed (LayerNorm-folded) copy of a 1x1 conv weight for the tcgen05 GEMM, rebuilt only when a
+    parameter changed (optimizer step / load_state_dict bump ``_version``; .to()/.cuda() change the pointer)."""
+    sig = _sig(w, bias, ln_w, ln_b) + (ln_type,)
+    ent = cache.get(key) if cache is not None else None
+    if ent is None or ent[0] != sig:
+        cout, cin = w.shape[0], w.shape[1]
+        ent = (sig, ops.pack_conv1x1(_p(w).reshape(cout, cin), _p(bias), ln_type, _p(ln_w), _p(ln_b)))
+        if cache is not None:
+            cache[key] = ent
+    return ent[1]
+
+
+USE_TC = True  # bf16 activations -> tcgen05 GEMMs (set False to force the CUDA-core kernels, e.g. for A/B tests)
+
+
+def ln_conv1x1(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None, cache=None, key=None):
     if _needs_grad(x, w, bias, ln_w, ln_b, res):
         _no_backward("ln_conv1x1")
+    cout = w.shape[0]
+    if USE_TC and ops.gemm_tc_usable(x, cout):
+        packed = packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b)
+        return ops.gemm_tc(x, packed, cout, ln_type, res, out=out, out_dtype=out_dtype)
     return ops.ln_conv1x1(x, _p(w), _p(bias), ln_type, _p(ln_w), _p(ln_b), res, out=out, out_dtype=out_dtype)
 
 
@@ -60,6 +84,9 @@ def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
     partials = ops.mdta_gram(qkv, heads)
     m = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C))
     v = qkv[:, 2 * C:]
+    if USE_TC and ops.gemm_tc_usable(v, C):
+        packed = ops.pack_conv1x1(m, _p(b_out), per_sample=True)
+        return ops.gemm_tc(v, packed, C, L.LN_NONE, res, out=out)
     return ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
 
 

@@ -1,0 +1,535 @@
+// gemm_tc.cu — LayerNorm + 1x1 conv (+bias, +residual) as a persistent tcgen05 GEMM, bf16 in HBM.
+//
+//   D[pixel, out_ch] = X^T[pixel, in_ch] . W^T[in_ch, out_ch]        (fp32 accumulators in TMEM)
+//
+// Reference ops replaced: LayerNorm.forward (Restormer.py:37-39,54-57,68-70) + the 1x1 nn.Conv2d that
+// follows it (:114 qkv, :89 project_in), plain 1x1 convs (:92 project_out, :261/:266 reduce_chan), the
+// folded attn.v+project_out (:127-131) with a per-sample weight, and the residual adds (:147-148).
+//
+// Layout / roles (320 threads, 1 CTA per SM, grid = (persistent CTAs, out-channel slices)):
+//   A operand = activation tile, 128 pixels x BK channels, straight from NCHW by TMA: box {64 px, BK ch}
+//               twice -> two MN-major SWIZZLE_128B blocks (pixels contiguous), ring of S stages.
+//   B operand = the CTA's weight slice [Nslice x Kpad] bf16 (LayerNorm gamma pre-multiplied), K-major
+//               SWIZZLE_128B, loaded ONCE by TMA and kept resident in shared memory (re-loaded only when
+//               the sample changes for per-sample weights).
+//   warp 4    = TMA producer; warp 5 = MMA issuer (one thread, tcgen05.mma M=128, N<=256, K=16);
+//   warps 6-9 = LayerNorm statistics: read the activation tile from the swizzled smem stage while the MMA
+//               consumes it (shifted single pass, fp32) -> (mu, rstd) per pixel;
+//   warps 0-3 = epilogue: tcgen05.ld 32 lanes x 32 columns, y = rstd*(acc - mu*s[o]) + t[o] (+res), coalesced
+//               NCHW stores (a warp writes 32 consecutive pixels of one channel).
+//   LayerNorm is folded algebraically: W.LN(x) = rstd*(W.diag(g).x - mu*s) + t with s[o]=sum_c bf16(W g)[o,c],
+//   t[o] = bias[o] + sum_c W[o,c] b[c], so the tensor core consumes the raw bf16 activations.
+//   TMEM: 2 accumulator stages x 256 columns; the epilogue of chunk i overlaps the MMAs of chunk i+1.
+#include <mutex>
+#include <type_traits>
+
+#include "tc_common.cuh"
+
+namespace b200ir {
+
+// ---------------------------------------------------------------------------------------------
+// host: driver entry point + tensor maps
+// ---------------------------------------------------------------------------------------------
+PFN_encodeTiled get_encode_tiled() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (PFN_encodeTiled)p;
+  });
+  return fn;
+}
+
+int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box) {
+  PFN_encodeTiled enc = get_encode_tiled();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return B200IR_E_DRIVER;
+  }
+  cuuint64_t gd[5], gs[5];
+  cuuint32_t bx[5], es[5];
+  for (int i = 0; i < rank; ++i) {
+    gd[i] = dims[i];
+    bx[i] = box[i];
+    es[i] = 1;
+    if (i > 0) gs[i - 1] = strides_bytes[i];
+  }
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu] box [%u,%u,%u]", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)dims[1], (unsigned long long)(rank > 2 ? dims[2] : 0),
+              box[0], box[1], rank > 2 ? box[2] : 0);
+    return B200IR_E_DRIVER;
+  }
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// geometry shared by the packer and the launcher
+// ---------------------------------------------------------------------------------------------
+struct GemmGeom {
+  int Kpad, BK, kchunks, Nslice, nslices, Nrows, NC, nchunks, nbox, S;
+  size_t smem;
+};
+
+static inline int ceil_to(int v, int m) { return (v + m - 1) / m * m; }
+
+bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g) {
+  if (Cin < 16 || Cout < 1) return false;
+  g->Kpad = ceil_to(Cin, 64);
+  // BK: channels per pipeline stage (multiple of 16, <= 64), least zero-padding first, then larger
+  int best = 64;
+  double beste = -1;
+  for (int bk = 64; bk >= 16; bk -= 16) {
+    if (bk > ceil_to(Cin, 16)) continue;
+    double e = (double)Cin / (double)(ceil_to(Cin, bk));
+    if (e > beste + 1e-9) beste = e, best = bk;
+  }
+  g->BK = best;
+  g->kchunks = (Cin + g->BK - 1) / g->BK;
+  const int Npad = ceil_to(Cout, 16);
+  int nmax = (112 * 1024) / (g->Kpad * 2) / 16 * 16;
+  if (nmax > 512) nmax = 512;
+  if (nmax < 16) return false;
+  g->nslices = (Npad + nmax - 1) / nmax;
+  g->Nslice = ceil_to((Npad + g->nslices - 1) / g->nslices, 16);
+  g->Nrows = g->Nslice * g->nslices;
+  g->nchunks = (g->Nslice + 255) / 256;
+  g->NC = ceil_to((g->Nslice + g->nchunks - 1) / g->nchunks, 16);
+  g->nbox = 16;
+  for (int nb = 256; nb >= 16; nb -= 16)
+    if (g->Nslice % nb == 0) {
+      g->nbox = nb;
+      break;
+    }
+  const size_t wbytes = (size_t)(g->Kpad / 64) * g->Nslice * 128;
+  const size_t fixed = 8192 + 1024;  // barriers + stats + s/t vectors + alignment slack
+  int S = (int)((227 * 1024 - wbytes - fixed) / 16384);
+  if (S > 8) S = 8;
+  g->S = S;
+  g->smem = wbytes + (size_t)S * 16384 + fixed;
+  const int need = g->nchunks > 1 ? g->kchunks + 1 : 2;
+  return S >= need && S >= 2;
+}
+
+// ---------------------------------------------------------------------------------------------
+// weight packer: wp[b][Nrows][Kpad] bf16 = w[b][o][c] * ln_w[c];  st[0][o] = sum_c bf16(.) ; st[1][o] = bias + W.ln_b
+// one warp per output row
+// ---------------------------------------------------------------------------------------------
+__global__ void pack_conv1x1_kernel(const float* __restrict__ w, int64_t w_bs, const float* __restrict__ bias,
+                                    int ln_type, const float* __restrict__ ln_w, const float* __restrict__ ln_b,
+                                    int Cin, int Cout, int Kpad, int Nrows, bf16* __restrict__ wp,
+                                    float* __restrict__ st) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int b = blockIdx.y;
+  if (row >= Nrows) return;
+  bf16* dst = wp + ((size_t)b * Nrows + row) * Kpad;
+  float s = 0.f, t = 0.f;
+  if (row < Cout) {
+    const float* src = w + (size_t)b * w_bs + (size_t)row * Cin;
+    for (int c = lane; c < Kpad; c += 32) {
+      float v = 0.f;
+      if (c < Cin) {
+        const float wv = src[c];
+        v = ln_type != B200IR_LN_NONE ? wv * ln_w[c] : wv;
+        if (ln_type == B200IR_LN_WITHBIAS) t = fmaf(wv, ln_b[c], t);
+      }
+      const bf16 q = __float2bfloat16_rn(v);
+      s += __bfloat162float(q);
+      dst[c] = q;
+    }
+  } else {
+    for (int c = lane; c < Kpad; c += 32) dst[c] = __float2bfloat16_rn(0.f);
+  }
+  s = warp_sum(s);
+  t = warp_sum(t);
+  if (lane == 0 && b == 0) {
+    st[row] = s;
+    st[Nrows + row] = (row < Cout) ? t + (bias ? bias[row] : 0.f) : 0.f;
+  }
+}
+
+}  // namespace b200ir
+
+namespace b200ir {
+
+struct GemmTcParams {
+  void* y; int64_t y_bs; int y_dt;
+  const void* res; int64_t res_bs; int res_dt;
+  const float* s; const float* t;
+  int ln_type, Cin, Cout;
+  int64_t HW;
+  int tiles_per_sample, total_tiles;
+  int BK, kchunks, Nslice, NC, nchunks, nbox, kc64, S;
+  int per_sample_w;
+  float inv_cin;
+};
+
+constexpr int kStageBytes = 16384;  // 128 px x 64 ch x 2 B
+constexpr int kEpiWarps = 16;       // 4 per TMEM lane quadrant
+constexpr int kWarpProducer = 16, kWarpMma = 17, kWarpStats0 = 18;
+constexpr int kThreads = (kWarpStats0 + 4) * 32;  // 704
+constexpr int kFixedSmem = 8192;    // barriers, stats, s/t vectors
+
+template <typename T> __device__ __forceinline__ float ldf(const T* p);
+template <> __device__ __forceinline__ float ldf<bf16>(const bf16* p) { return __bfloat162float(*p); }
+template <> __device__ __forceinline__ float ldf<float>(const float* p) { return *p; }
+template <typename T> __device__ __forceinline__ void stf(T* p, float v);
+template <> __device__ __forceinline__ void stf<bf16>(bf16* p, float v) { *p = __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
+
+// TRES: void (no residual) | bf16 | float ; TOUT: bf16 | float
+template <typename TRES, typename TOUT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+               const GemmTcParams P) {
+  using namespace tc;
+  constexpr bool HAS_RES = !std::is_same<TRES, void>::value;
+  typedef typename std::conditional<HAS_RES, TRES, float>::type TR;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const uint32_t wbytes = (uint32_t)P.kc64 * P.Nslice * 128;
+  uint8_t* Wsm = smem;
+  uint8_t* ring = smem + wbytes;
+  uint8_t* tail = ring + (size_t)P.S * kStageBytes;
+  uint64_t* bar_full = (uint64_t*)tail;            // [8]
+  uint64_t* bar_empty = bar_full + 8;              // [8]
+  uint64_t* bar_wfull = bar_empty + 8;             // [1]
+  uint64_t* bar_wempty = bar_wfull + 1;            // [1]
+  uint64_t* bar_accfull = bar_wempty + 1;          // [2]
+  uint64_t* bar_accempty = bar_accfull + 2;        // [2]
+  uint64_t* bar_stfull = bar_accempty + 2;         // [2]
+  uint64_t* bar_stempty = bar_stfull + 2;          // [2]
+  uint32_t* tmem_slot = (uint32_t*)(bar_stempty + 2);
+  float* s_mu = (float*)(tail + 256);              // [2][128]
+  float* s_rstd = s_mu + 256;                      // [2][128]
+  float2* s_st = (float2*)(tail + 256 + 2048);     // [Nslice] (s, t) of this CTA's out-channel slice
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool has_ln = P.ln_type != B200IR_LN_NONE;
+  const int n_lo = blockIdx.y * P.Nslice;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < P.S; ++i) {
+      mbar_init(&bar_full[i], 1);
+      mbar_init(&bar_empty[i], has_ln ? 5 : 1);
+    }
+    mbar_init(bar_wfull, 1);
+    mbar_init(bar_wempty, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar_accfull[i], 1);
+      mbar_init(&bar_accempty[i], kEpiWarps);
+      mbar_init(&bar_stfull[i], 128);
+      mbar_init(&bar_stempty[i], kEpiWarps);
+    }
+    fence_barrier_init();
+  }
+  for (int i = threadIdx.x; i < P.Nslice; i += kThreads) s_st[i] = make_float2(P.s[n_lo + i], P.t[n_lo + i]);
+  if (warp == kWarpProducer) {
+    if (lane == 0) {
+      tma_prefetch_desc(&tmX);
+      tma_prefetch_desc(&tmW);
+    }
+    tmem_alloc(tmem_slot, 512);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  // contiguous tile range of this CTA
+  const int gx = gridDim.x;
+  const int t_begin = (int)(((int64_t)P.total_tiles * blockIdx.x) / gx);
+  const int t_end = (int)(((int64_t)P.total_tiles * (blockIdx.x + 1)) / gx);
+
+  if (warp == kWarpProducer) {
+    // ================= TMA producer =================
+    if (lane == 0) {
+      uint32_t it = 0, wload = 0;
+      int cur = -1;
+      for (int tile = t_begin; tile < t_end; ++tile) {
+        const int b = tile / P.tiles_per_sample;
+        const int p0 = (tile - b * P.tiles_per_sample) * 128;
+        if (cur < 0 || (P.per_sample_w && b != cur)) {
+          if (wload > 0) mbar_wait(bar_wempty, (wload - 1) & 1);
+          mbar_arrive_expect_tx(bar_wfull, wbytes);
+          for (int k64 = 0; k64 < P.kc64; ++k64)
+            for (int r0 = 0; r0 < P.Nslice; r0 += P.nbox)
+              tma_load_3d(Wsm + ((size_t)k64 * P.Nslice + r0) * 128, &tmW, bar_wfull, k64 * 64, n_lo + r0,
+                          P.per_sample_w ? b : 0);
+          ++wload;
+          cur = b;
+        }
+        for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
+          const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
+          mbar_wait(&bar_empty[stage], ph ^ 1);
+          mbar_arrive_expect_tx(&bar_full[stage], 2u * P.BK * 128u);
+          uint8_t* dst = ring + (size_t)stage * kStageBytes;
+          tma_load_3d(dst, &tmX, &bar_full[stage], p0, kc * P.BK, b);
+          tma_load_3d(dst + P.BK * 128, &tmX, &bar_full[stage], p0 + 64, kc * P.BK, b);
+        }
+      }
+    }
+  } else if (warp == kWarpMma) {
+    // ================= MMA issuer =================
+    if (lane == 0) {
+      uint32_t it = 0, acc_it = 0, wload = 0;
+      int cur = -1;
+      const uint32_t ring_addr = smem_u32(ring), w_addr = smem_u32(Wsm);
+      for (int tile = t_begin; tile < t_end; ++tile) {
+        const int b = tile / P.tiles_per_sample;
+        if (cur < 0 || (P.per_sample_w && b != cur)) {
+          mbar_wait(bar_wfull, wload & 1);
+          ++wload;
+          cur = b;
+        }
+        for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
+          const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
+          mbar_wait(&bar_accempty[as], aph ^ 1);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + as * 256;
+          const int ncols = min(P.NC, P.Nslice - ch * P.NC);
+          const uint32_t idesc = make_idesc_bf16(128, ncols, 1, 0);
+          for (int kc = 0; kc < P.kchunks; ++kc) {
+            const uint32_t cit = it + kc, stage = cit % P.S, ph = (cit / P.S) & 1;
+            if (ch == 0) {
+              mbar_wait(&bar_full[stage], ph);
+              tc_fence_after();
+            }
+            const int rows = min(P.BK, P.Cin - kc * P.BK);
+            const int ksteps = (rows + 15) >> 4;
+            for (int ks = 0; ks < ksteps; ++ks) {
+              const int kglob = kc * P.BK + ks * 16;
+              const uint64_t adesc =
+                  make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048, (uint32_t)P.BK * 128u, 1024u);
+              const uint32_t baddr =
+                  w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)(ch * P.NC) * 128u + (kglob & 63) * 2u;
+              const uint64_t bdesc = make_smem_desc_sw128(baddr, 16u, 1024u);
+              umma_bf16(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
+            }
+            if (ch == P.nchunks - 1) umma_commit(&bar_empty[stage]);
+          }
+          umma_commit(&bar_accfull[as]);
+        }
+        it += P.kchunks;
+        if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit(bar_wempty);
+      }
+    }
+  } else if (warp >= kWarpStats0) {
+    // ================= LayerNorm statistics =================
+    if (has_ln) {
+      const int m = (warp - kWarpStats0) * 32 + lane;
+      const uint32_t mblk = m >> 6, pi = m & 63;
+      uint32_t it = 0, tcount = 0;
+      for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
+        float x0 = 0.f, sum = 0.f, sq = 0.f;
+        for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
+          const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
+          mbar_wait(&bar_full[stage], ph);
+          const int rows = min(P.BK, P.Cin - kc * P.BK);
+          const uint8_t* base = ring + (size_t)stage * kStageBytes + mblk * P.BK * 128 + (pi & 7) * 2;
+          if (kc == 0) x0 = __bfloat162float(*(const bf16*)(base + ((pi >> 3) << 4)));
+#pragma unroll 8
+          for (int r = 0; r < rows; ++r) {
+            const float v = __bfloat162float(*(const bf16*)(base + r * 128 + (((pi >> 3) ^ (r & 7)) << 4)));
+            const float d = v - x0;
+            sum += d;
+            sq = fmaf(d, d, sq);
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_empty[stage]);
+        }
+        const float md = sum * P.inv_cin;
+        const float var = fmaxf(sq * P.inv_cin - md * md, 0.f);
+        const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+        mbar_wait(&bar_stempty[sp], sph ^ 1);
+        const float rstd = 1.0f / sqrtf(var + 1e-5f);
+        // epilogue form: y = acc*rstd + (-rstd*mu)*s[o] + t[o]
+        s_mu[sp * 128 + m] = (P.ln_type == B200IR_LN_WITHBIAS) ? -rstd * (x0 + md) : 0.f;
+        s_rstd[sp * 128 + m] = rstd;
+        mbar_arrive(&bar_stfull[sp]);
+      }
+    }
+  } else {
+    // ===== epilogue: warp w <-> TMEM lane quadrant w%4, 16-column groups g = w/4, w/4+4, ... =====
+    const int quad = warp & 3, wq = warp >> 2;
+    const int m = quad * 32 + lane;
+    uint32_t acc_it = 0, tcount = 0;
+    for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
+      const int b = tile / P.tiles_per_sample;
+      const int64_t p = (int64_t)(tile - b * P.tiles_per_sample) * 128 + m;
+      const bool valid = p < P.HW;
+      TOUT* yb = (TOUT*)P.y + (int64_t)b * P.y_bs + p;
+      const TR* rb = HAS_RES ? (const TR*)P.res + (int64_t)b * P.res_bs + p : nullptr;
+      float nmr = 0.f, rstd = 1.f;  // (-rstd*mu, rstd)
+      for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
+        const int ncols = min(P.NC, P.Nslice - ch * P.NC);
+        const int nbase = ch * P.NC;  // within the slice
+        const int ngroups = ncols >> 4;
+        // residual prefetch for this warp's first group (independent of the MMA)
+        float rv[16];
+        if (HAS_RES) {
+          const int c0 = wq * 16;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int n = n_lo + nbase + c0 + j;
+            rv[j] = (valid && wq < ngroups && n < P.Cout) ? ldf<TR>(rb + (int64_t)n * P.HW) : 0.f;
+          }
+        }
+        if (ch == 0 && has_ln) {
+          const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+          mbar_wait(&bar_stfull[sp], sph);
+          nmr = s_mu[sp * 128 + m];
+          rstd = s_rstd[sp * 128 + m];
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_stempty[sp]);
+        }
+        const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
+        mbar_wait(&bar_accfull[as], aph);
+        tc_fence_after();
+        const uint32_t tbase = tmem_base + as * 256 + ((uint32_t)(quad * 32) << 16);
+        for (int g = wq; g < ngroups; g += 4) {
+          const int c0 = g * 16;
+          uint32_t r[16];
+          tmem_ld_32x16(tbase + c0, r);
+          float rn[16];
+          if (HAS_RES) {  // prefetch the next group's residuals while this one is processed
+            const int c1 = c0 + 64;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int n = n_lo + nbase + c1 + j;
+              rn[j] = (valid && g + 4 < ngroups && n < P.Cout) ? ldf<TR>(rb + (int64_t)n * P.HW) : 0.f;
+            }
+          }
+          tmem_ld_wait();
+          if (valid) {
+            TOUT* yp = yb + (int64_t)(n_lo + nbase + c0) * P.HW;
+            const int nlim = P.Cout - (n_lo + nbase + c0);
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              if (j < nlim) {
+                const float2 st = s_st[nbase + c0 + j];
+                float v = fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, st.x, st.y));
+                if (HAS_RES) v += rv[j];
+                stf<TOUT>(yp + (int64_t)j * P.HW, v);
+              }
+            }
+          }
+          if (HAS_RES) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) rv[j] = rn[j];
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_accempty[as]);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpProducer) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace b200ir
+
+using namespace b200ir;
+
+extern "C" int b200ir_gemm_tc_geometry(int Cin, int Cout, int* kpad, int* nrows) {
+  GemmGeom g;
+  if (!gemm_tc_geometry(Cin, Cout, &g)) {
+    set_error("gemm_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
+    return B200IR_E_UNSUPPORTED;
+  }
+  if (kpad) *kpad = g.Kpad;
+  if (nrows) *nrows = g.Nrows;
+  return 0;
+}
+
+extern "C" int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, const float* bias, int ln_type,
+                                   const float* ln_w, const float* ln_b, int Cin, int Cout, void* wp, float* st,
+                                   b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(w && wp && st && Bw > 0 && Bw <= 65535, "pack_conv1x1: bad args");
+  B200IR_CHECK_ARG(ln_type == B200IR_LN_NONE || ln_w, "pack_conv1x1: ln_w missing");
+  B200IR_CHECK_ARG(ln_type != B200IR_LN_WITHBIAS || ln_b, "pack_conv1x1: ln_b missing");
+  GemmGeom g;
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g), "pack_conv1x1: unsupported Cin=%d Cout=%d", Cin, Cout);
+  dim3 grid((unsigned)((g.Nrows + 7) / 8), (unsigned)Bw);
+  pack_conv1x1_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, w_bstride, bias, ln_type, ln_w, ln_b, Cin, Cout,
+                                                              g.Kpad, g.Nrows, (bf16*)wp, st);
+  return check_launch("pack_conv1x1");
+}
+
+extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st,
+                                  int ln_type, const void* res, int64_t res_bstride, int res_dtype, void* y,
+                                  int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int64_t HW,
+                                  b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && wp && st && y && B > 0 && HW > 0, "gemm_tc: bad args");
+  B200IR_CHECK_ARG(Bw == 1 || Bw == B, "gemm_tc: Bw must be 1 or B");
+  B200IR_CHECK_ARG(dtype_ok(y_dtype) && (!res || dtype_ok(res_dtype)), "gemm_tc: bad dtype");
+  GemmGeom g;
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g), "gemm_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
+  B200IR_UNSUPPORTED(HW % 8 == 0 && HW >= 64 && x_bstride % 8 == 0 && ((uintptr_t)x % 16) == 0,
+                     "gemm_tc: needs HW%%8==0, HW>=64 and 16B-aligned activations (HW=%lld)", (long long)HW);
+  B200IR_UNSUPPORTED(HW < (1ll << 31) && (int64_t)B * ((HW + 127) / 128) < (1ll << 31), "gemm_tc: too many tiles");
+
+  CUtensorMap tmX, tmW;
+  {
+    const uint64_t dims[3] = {(uint64_t)HW, (uint64_t)Cin, (uint64_t)B};
+    const uint64_t str[3] = {2, (uint64_t)HW * 2, (uint64_t)x_bstride * 2};
+    const uint32_t box[3] = {64, (uint32_t)g.BK, 1};
+    int rc = make_tmap_bf16(&tmX, x, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)g.Kpad, (uint64_t)g.Nrows, (uint64_t)Bw};
+    const uint64_t str[3] = {2, (uint64_t)g.Kpad * 2, (uint64_t)g.Nrows * g.Kpad * 2};
+    const uint32_t box[3] = {64, (uint32_t)g.nbox, 1};
+    int rc = make_tmap_bf16(&tmW, wp, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  GemmTcParams P;
+  P.y = y; P.y_bs = y_bstride; P.y_dt = y_dtype;
+  P.res = res; P.res_bs = res_bstride; P.res_dt = res_dtype;
+  P.s = st; P.t = st + g.Nrows;
+  P.ln_type = ln_type; P.Cin = Cin; P.Cout = Cout; P.HW = HW;
+  P.tiles_per_sample = (int)((HW + 127) / 128);
+  P.total_tiles = P.tiles_per_sample * B;
+  P.BK = g.BK; P.kchunks = g.kchunks; P.Nslice = g.Nslice; P.NC = g.NC; P.nchunks = g.nchunks; P.nbox = g.nbox;
+  P.kc64 = g.Kpad / 64; P.S = g.S;
+  P.per_sample_w = (Bw > 1) ? 1 : 0;
+  P.inv_cin = 1.0f / (float)Cin;
+
+  int sms = 148;
+  int gx = sms / g.nslices;
+  if (gx < 1) gx = 1;
+  if (gx > P.total_tiles) gx = P.total_tiles;
+  const dim3 grid((unsigned)gx, (unsigned)g.nslices);
+  cudaStream_t st_ = (cudaStream_t)stream;
+#define B200IR_LAUNCH_GEMM(TRES, TOUT)                                                                          \
+  do {                                                                                                          \
+    static std::once_flag once;                                                                                 \
+    std::call_once(once, [] {                                                                                   \
+      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+    });                                                                                                         \
+    gemm_tc_kernel<TRES, TOUT><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                                   \
+  } while (0)
+  const bool ob = y_dtype == B200IR_BF16;
+  if (!res) {
+    if (ob) B200IR_LAUNCH_GEMM(void, bf16); else B200IR_LAUNCH_GEMM(void, float);
+  } else if (res_dtype == B200IR_BF16) {
+    if (ob) B200IR_LAUNCH_GEMM(bf16, bf16); else B200IR_LAUNCH_GEMM(bf16, float);
+  } else {
+    if (ob) B200IR_LAUNCH_GEMM(float, bf16); else B200IR_LAUNCH_GEMM(float, float);
+  }
+#undef B200IR_LAUNCH_GEMM
+  return check_launch("gemm_tc");
+}

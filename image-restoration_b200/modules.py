@@ -92,10 +92,13 @@ class FeedForward(nn.Module):
 
     def _run(self, x, norm=None, res=None, out=None):
         ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
-        t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None)
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None,
+                         cache=cache, key=("in", id(norm)))
         g = A.dwconv3x3_gelu_gate(t, self.dwconv.weight, self.dwconv.bias)
         del t
-        return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out)
+        return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
+                            cache=cache, key="out")
 
     def forward(self, x):
         return self._run(x)
@@ -114,7 +117,8 @@ class Attention(nn.Module):
 
     def _run(self, x, norm=None, res=None, out=None):
         ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
-        t = A.ln_conv1x1(x, self.qkv.weight, self.qkv.bias, ln_type, lw, lb, None)
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        t = A.ln_conv1x1(x, self.qkv.weight, self.qkv.bias, ln_type, lw, lb, None, cache=cache, key=("qkv", id(norm)))
         qkv = A.dwconv3x3(t, self.qkv_dwconv.weight, self.qkv_dwconv.bias)
         del t
         return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
@@ -275,13 +279,14 @@ class Restormer(nn.Module):
         latent = self._run_stack(self.latent, inp_enc_level4)
 
         inp_dec_level3 = self._cat(self.up4_3, latent, out_enc_level3, cat3, dim * 4)
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
         inp_dec_level3 = A.ln_conv1x1(inp_dec_level3, self.reduce_chan_level3.weight, self.reduce_chan_level3.bias,
-                                      L.LN_NONE, None, None, None)
+                                      L.LN_NONE, None, None, None, cache=cache, key="rc3")
         out_dec_level3 = self._run_stack(self.decoder_level3, inp_dec_level3)
 
         inp_dec_level2 = self._cat(self.up3_2, out_dec_level3, out_enc_level2, cat2, dim * 2)
         inp_dec_level2 = A.ln_conv1x1(inp_dec_level2, self.reduce_chan_level2.weight, self.reduce_chan_level2.bias,
-                                      L.LN_NONE, None, None, None)
+                                      L.LN_NONE, None, None, None, cache=cache, key="rc2")
         out_dec_level2 = self._run_stack(self.decoder_level2, inp_dec_level2)
 
         inp_dec_level1 = self._cat(self.up2_1, out_dec_level2, out_enc_level1, cat1, dim)
@@ -290,7 +295,7 @@ class Restormer(nn.Module):
 
         if self.dual_pixel_task:
             out_dec_level1 = A.ln_conv1x1(inp_enc_level1, self.skip_conv.weight, self.skip_conv.bias, L.LN_NONE, None,
-                                          None, out_dec_level1)
+                                          None, out_dec_level1, cache=cache, key="skip")
             return A.conv3x3(out_dec_level1, self.output.weight, self.output.bias, None, L.SHUFFLE_NONE,
                              out_dtype=inp_img.dtype)
         return A.conv3x3(out_dec_level1, self.output.weight, self.output.bias, inp_img, L.SHUFFLE_NONE,

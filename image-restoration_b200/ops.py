@@ -213,3 +213,72 @@ def copy_cast(x, out):
     with _timed("copy_cast", B, C * H * W_, xdt, ydt):
         L.check(lib.b200ir_copy_cast(xp, xbs, xdt, yp, ybs, ydt, B, C * H * W_, _stream()), "b200ir_copy_cast")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# tcgen05 path
+# ---------------------------------------------------------------------------------------------------
+import ctypes as _C
+
+_GEOM = {}
+
+
+def gemm_tc_geometry(Cin, Cout):
+    """(kpad, nrows) of the packed weight, or None if the tcgen05 GEMM does not support (Cin, Cout)."""
+    key = (Cin, Cout)
+    if key not in _GEOM:
+        kp, nr = _C.c_int(0), _C.c_int(0)
+        rc = lib.b200ir_gemm_tc_geometry(Cin, Cout, _C.byref(kp), _C.byref(nr))
+        _GEOM[key] = (kp.value, nr.value) if rc == 0 else None
+    return _GEOM[key]
+
+
+def gemm_tc_usable(x, Cout):
+    B, Cin, H, W_ = x.shape
+    hw = H * W_
+    return (x.dtype == torch.bfloat16 and hw % 8 == 0 and hw >= 64 and x.data_ptr() % 16 == 0
+            and (B == 1 or x.stride(0) % 8 == 0) and gemm_tc_geometry(Cin, Cout) is not None)
+
+
+def pack_conv1x1(w, bias=None, ln_type=L.LN_NONE, ln_w=None, ln_b=None, per_sample=False):
+    """Pack fp32 1x1-conv weights ([Cout,Cin] or [B,Cout,Cin]) for gemm_tc: (wp bf16 [Bw,nrows,kpad], st fp32 [2,nrows])."""
+    if per_sample:
+        Bw, Cout, Cin = w.shape
+    else:
+        Bw, Cout, Cin = 1, w.shape[0], w.shape[1]
+    geo = gemm_tc_geometry(Cin, Cout)
+    if geo is None:
+        raise ValueError(f"pack_conv1x1: ({Cin},{Cout}) unsupported by the tcgen05 GEMM")
+    kpad, nrows = geo
+    wp = torch.empty((Bw, nrows, kpad), device=w.device, dtype=torch.bfloat16)
+    st = torch.empty((2, nrows), device=w.device, dtype=torch.float32)
+    with _timed("pack_conv1x1", Bw, Cin, Cout):
+        rc = lib.b200ir_pack_conv1x1(_par(w, "w", Bw * Cout * Cin), Cout * Cin if per_sample else 0, Bw,
+                                     _par(bias, "bias", Cout), ln_type, _par(ln_w, "ln_w", Cin if ln_type else None),
+                                     _par(ln_b, "ln_b", Cin if ln_type == L.LN_WITHBIAS else None), Cin, Cout,
+                                     wp.data_ptr(), st.data_ptr(), _stream())
+    L.check(rc, "b200ir_pack_conv1x1")
+    return wp, st
+
+
+def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=None):
+    """y = res + W.LN(x) + bias on tcgen05 tensor cores; `packed` = pack_conv1x1(...)."""
+    wp, st = packed
+    B, Cin, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if xdt != L.BF16:
+        raise ValueError("gemm_tc: activations must be bfloat16")
+    if out is None:
+        out = torch.empty((B, Cout, H, W_), device=x.device, dtype=out_dtype or x.dtype)
+    yp, ybs, ydt = _act(out, "out")
+    rp, rbs, rdt = (None, 0, 0)
+    if res is not None:
+        if tuple(res.shape) != (B, Cout, H, W_):
+            raise ValueError("res shape mismatch")
+        rp, rbs, rdt = _act(res, "res")
+    Bw = wp.shape[0]
+    with _timed("gemm_tc", B, Cin, Cout, H * W_, ln_type, int(res is not None), int(Bw > 1), xdt, ydt):
+        rc = lib.b200ir_gemm_tc_fwd(xp, xbs, wp.data_ptr(), Bw, st.data_ptr(), ln_type, rp, rbs, rdt, yp, ybs, ydt,
+                                    B, Cin, Cout, H * W_, _stream())
+    L.check(rc, "b200ir_gemm_tc_fwd")
+    return out

@@ -94,6 +94,23 @@ int b200ir_conv3x3_fwd(const void* x, int64_t x_bstride, int x_dtype, const floa
 int b200ir_copy_cast(const void* x, int64_t x_bstride, int x_dtype, void* y, int64_t y_bstride, int y_dtype,
                      int B, int64_t CHW, b200ir_stream_t stream);
 
+/* ---- tcgen05 / TMEM / TMA path (bf16 activations) -------------------------------------------------
+ * Same math as b200ir_ln_conv1x1_fwd, as a persistent tensor-core GEMM (csrc/gemm_tc.cu).  Weights are
+ * first packed once per parameter update:
+ *   wp[b][nrows][kpad] bf16 = w[b][o][c] * ln_w[c] (zero padded),
+ *   st[0][o] = sum_c bf16(w*ln_w)[o,c],  st[1][o] = bias[o] + sum_c w[o,c]*ln_b[c]     (fp32 [2,nrows])
+ * so that W.LN(x) = rstd*(wp.x - mu*st0) + st1 is applied in the GEMM epilogue.
+ * b200ir_gemm_tc_geometry returns 0 and the padded sizes if (Cin,Cout) is supported.
+ * x must be bf16 with HW%8==0, HW>=64; Bw = 1 (shared weight) or B (per-sample weight, e.g. the folded
+ * MDTA matrix of b200ir_mdta_softmax_fold_fwd). */
+int b200ir_gemm_tc_geometry(int Cin, int Cout, int* kpad, int* nrows);
+int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, const float* bias, int ln_type,
+                        const float* ln_w, const float* ln_b, int Cin, int Cout, void* wp, float* st,
+                        b200ir_stream_t stream);
+int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st, int ln_type,
+                       const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
+                       int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
