@@ -90,7 +90,16 @@ def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
     return ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
 
 
-def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None):
+def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=None):
     if _needs_grad(x, w, bias, res):
         _no_backward("conv3x3")
+    cout = w.shape[0]
+    if USE_TC and res is None and ops.conv3x3_tc_usable(x, cout):
+        sig = _sig(w, bias)
+        ent = cache.get(key) if cache is not None else None
+        if ent is None or ent[0] != sig:
+            ent = (sig, ops.pack_conv3x3(_p(w), _p(bias)))
+            if cache is not None:
+                cache[key] = ent
+        return ops.conv3x3_tc(x, ent[1], cout, shuffle, out=out, out_dtype=out_dtype)
     return ops.conv3x3(x, _p(w), _p(bias), res, shuffle, out=out, out_dtype=out_dtype)

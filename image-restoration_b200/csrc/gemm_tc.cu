@@ -74,15 +74,14 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
 // geometry shared by the packer and the launcher
 // ---------------------------------------------------------------------------------------------
 struct GemmGeom {
-  int Kpad, BK, kchunks, Nslice, nslices, Nrows, NC, nchunks, nbox, S;
+  int Kpad, BK, kchunks, kpt, Nslice, nslices, Nrows, NC, nchunks, nbox, S;
   size_t smem;
 };
 
 static inline int ceil_to(int v, int m) { return (v + m - 1) / m * m; }
 
-bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g) {
+bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1) {
   if (Cin < 16 || Cout < 1) return false;
-  g->Kpad = ceil_to(Cin, 64);
   // BK: channels per pipeline stage (multiple of 16, <= 64), least zero-padding first, then larger
   int best = 64;
   double beste = -1;
@@ -91,11 +90,14 @@ bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g) {
     double e = (double)Cin / (double)(ceil_to(Cin, bk));
     if (e > beste + 1e-9) beste = e, best = bk;
   }
+  if (taps != 1) best = 64;  // conv: K-major activation rows are 64 channels (128 B) wide
   g->BK = best;
-  g->kchunks = (Cin + g->BK - 1) / g->BK;
+  g->kpt = (Cin + g->BK - 1) / g->BK;
+  g->kchunks = taps * g->kpt;
+  g->Kpad = taps == 1 ? ceil_to(Cin, 64) : ceil_to(taps * g->kpt * g->BK, 64);
   const int Npad = ceil_to(Cout, 16);
   int nmax = (112 * 1024) / (g->Kpad * 2) / 16 * 16;
-  if (nmax > 512) nmax = 512;
+  if (nmax > (taps == 1 ? 512 : 256)) nmax = (taps == 1 ? 512 : 256);
   if (nmax < 16) return false;
   g->nslices = (Npad + nmax - 1) / nmax;
   g->Nslice = ceil_to((Npad + g->nslices - 1) / g->nslices, 16);
@@ -170,6 +172,9 @@ struct GemmTcParams {
   int BK, kchunks, Nslice, NC, nchunks, nbox, kc64, S;
   int per_sample_w;
   float inv_cin;
+  // 3x3 conv mode (MODE > 0): K loop = 9 taps x kpt channel chunks, A tiles come from tap-shifted 4D TMA boxes
+  int kpt;                 // channel chunks per tap (== kchunks for 1x1)
+  int H, W, TW, TWs, TH, tiles_x, tiles_y;   // conv tile = TW x TH pixels (TW*TH = 128, TW = 1<<TWs)
 };
 
 constexpr int kStageBytes = 16384;  // 128 px x 64 ch x 2 B
@@ -186,7 +191,13 @@ template <> __device__ __forceinline__ void stf<bf16>(bf16* p, float v) { *p = _
 template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p = v; }
 
 // TRES: void (no residual) | bf16 | float ; TOUT: bf16 | float
-template <typename TRES, typename TOUT>
+// MODE 0: 1x1 conv over flattened HW (A = NCHW activations, MN-major).
+// MODE 1/2/3: 3x3 conv (pad 1) as 9 tap-shifted GEMMs accumulated in TMEM, store = plain / PixelUnshuffle(2) /
+// PixelShuffle(2) (Restormer.py:171-189).  The activation operand is the NHWC copy of the input (channels
+// contiguous = K-major): an M tile is a TW x TH pixel patch fetched by ONE 4D TMA box {64 ch, TW, TH, 1} at
+// (x0+dx, y0+dy) -- only non-innermost coordinates are shifted (the innermost TMA coordinate must stay 16-byte
+// aligned, measured with tools/tma4d_probe.cu) and the zero padding comes from TMA out-of-bounds fill.
+template <typename TRES, typename TOUT, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
                const GemmTcParams P) {
@@ -255,7 +266,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       uint32_t it = 0, wload = 0;
       int cur = -1;
       for (int tile = t_begin; tile < t_end; ++tile) {
-        const int b = tile / P.tiles_per_sample;
+        const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
         const int p0 = (tile - b * P.tiles_per_sample) * 128;
         if (cur < 0 || (P.per_sample_w && b != cur)) {
           if (wload > 0) mbar_wait(bar_wempty, (wload - 1) & 1);
@@ -267,13 +278,27 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           ++wload;
           cur = b;
         }
+        int cx0 = 0, cy0 = 0, cb = 0;
+        if (MODE != 0) {
+          const int tpi = P.tiles_x * P.tiles_y;
+          cb = tile / tpi;
+          const int r = tile - cb * tpi;
+          cy0 = (r / P.tiles_x) * P.TH;
+          cx0 = (r % P.tiles_x) * P.TW;
+        }
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_empty[stage], ph ^ 1);
-          mbar_arrive_expect_tx(&bar_full[stage], 2u * P.BK * 128u);
+          mbar_arrive_expect_tx(&bar_full[stage], MODE == 0 ? 2u * P.BK * 128u : (uint32_t)kStageBytes);
           uint8_t* dst = ring + (size_t)stage * kStageBytes;
-          tma_load_3d(dst, &tmX, &bar_full[stage], p0, kc * P.BK, b);
-          tma_load_3d(dst + P.BK * 128, &tmX, &bar_full[stage], p0 + 64, kc * P.BK, b);
+          if (MODE == 0) {
+            tma_load_3d(dst, &tmX, &bar_full[stage], p0, kc * P.BK, b);
+            tma_load_3d(dst + P.BK * 128, &tmX, &bar_full[stage], p0 + 64, kc * P.BK, b);
+          } else {
+            const int tap = kc / P.kpt, cc = kc - tap * P.kpt;
+            const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
+            tma_load_4d(dst, &tmX, &bar_full[stage], cc * 64, cx0 + dx, cy0 + dy, cb);
+          }
         }
       }
     }
@@ -284,7 +309,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       int cur = -1;
       const uint32_t ring_addr = smem_u32(ring), w_addr = smem_u32(Wsm);
       for (int tile = t_begin; tile < t_end; ++tile) {
-        const int b = tile / P.tiles_per_sample;
+        const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
         if (cur < 0 || (P.per_sample_w && b != cur)) {
           mbar_wait(bar_wfull, wload & 1);
           ++wload;
@@ -296,19 +321,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + as * 256;
           const int ncols = min(P.NC, P.Nslice - ch * P.NC);
-          const uint32_t idesc = make_idesc_bf16(128, ncols, 1, 0);
+          const uint32_t idesc = make_idesc_bf16(128, ncols, MODE == 0 ? 1 : 0, 0);
           for (int kc = 0; kc < P.kchunks; ++kc) {
             const uint32_t cit = it + kc, stage = cit % P.S, ph = (cit / P.S) & 1;
             if (ch == 0) {
               mbar_wait(&bar_full[stage], ph);
               tc_fence_after();
             }
-            const int rows = min(P.BK, P.Cin - kc * P.BK);
+            const int rows = min(P.BK, P.Cin - (MODE == 0 ? kc : kc % P.kpt) * P.BK);
             const int ksteps = (rows + 15) >> 4;
             for (int ks = 0; ks < ksteps; ++ks) {
               const int kglob = kc * P.BK + ks * 16;
               const uint64_t adesc =
-                  make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048, (uint32_t)P.BK * 128u, 1024u);
+                  MODE == 0 ? make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048, (uint32_t)P.BK * 128u, 1024u)
+                            : make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 32, 16u, 1024u);
               const uint32_t baddr =
                   w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)(ch * P.NC) * 128u + (kglob & 63) * 2u;
               const uint64_t bdesc = make_smem_desc_sw128(baddr, 16u, 1024u);
@@ -319,7 +345,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           umma_commit(&bar_accfull[as]);
         }
         it += P.kchunks;
-        if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit(bar_wempty);
+        if (MODE == 0 && P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b)
+          umma_commit(bar_wempty);
       }
     }
   } else if (warp >= kWarpStats0) {
@@ -363,10 +390,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     const int m = quad * 32 + lane;
     uint32_t acc_it = 0, tcount = 0;
     for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
-      const int b = tile / P.tiles_per_sample;
-      const int64_t p = (int64_t)(tile - b * P.tiles_per_sample) * 128 + m;
-      const bool valid = p < P.HW;
-      TOUT* yb = (TOUT*)P.y + (int64_t)b * P.y_bs + p;
+      int b;
+      int64_t p;
+      bool valid;
+      int py = 0, px = 0;
+      if (MODE == 0) {
+        b = tile / P.tiles_per_sample;
+        p = (int64_t)(tile - b * P.tiles_per_sample) * 128 + m;
+        valid = p < P.HW;
+      } else {
+        const int tpi = P.tiles_x * P.tiles_y;
+        b = tile / tpi;
+        const int r = tile - b * tpi;
+        py = (r / P.tiles_x) * P.TH + (m >> P.TWs);
+        px = (r % P.tiles_x) * P.TW + (m & (P.TW - 1));
+        valid = py < P.H && px < P.W;
+        p = (int64_t)py * P.W + px;
+      }
+      TOUT* yb = (TOUT*)P.y + (int64_t)b * P.y_bs + (MODE <= 1 ? p : 0);
       const TR* rb = HAS_RES ? (const TR*)P.res + (int64_t)b * P.res_bs + p : nullptr;
       float nmr = 0.f, rstd = 1.f;  // (-rstd*mu, rstd)
       for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
@@ -410,15 +451,43 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           }
           tmem_ld_wait();
           if (valid) {
-            TOUT* yp = yb + (int64_t)(n_lo + nbase + c0) * P.HW;
-            const int nlim = P.Cout - (n_lo + nbase + c0);
+            const int n0 = n_lo + nbase + c0;
+            const int nlim = P.Cout - n0;
+            if (MODE <= 1) {
+              TOUT* yp = yb + (int64_t)n0 * P.HW;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (j < nlim) {
-                const float2 st = s_st[nbase + c0 + j];
-                float v = fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, st.x, st.y));
-                if (HAS_RES) v += rv[j];
-                stf<TOUT>(yp + (int64_t)j * P.HW, v);
+              for (int j = 0; j < 16; ++j) {
+                if (j < nlim) {
+                  const float2 st = s_st[nbase + c0 + j];
+                  float v = fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, st.x, st.y));
+                  if (HAS_RES) v += rv[j];
+                  stf<TOUT>(yp + (int64_t)j * P.HW, v);
+                }
+              }
+            } else if (MODE == 2) {
+              // PixelUnshuffle(2): out[n*4 + (y&1)*2 + (x&1), y/2, x/2]
+              const int64_t hwq = P.HW >> 2;
+              TOUT* yp = yb + (int64_t)(n0 * 4 + (py & 1) * 2 + (px & 1)) * hwq + (int64_t)(py >> 1) * (P.W >> 1) + (px >> 1);
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (j < nlim) stf<TOUT>(yp + (int64_t)j * 4 * hwq, __uint_as_float(r[j]) + s_st[nbase + c0 + j].y);
+            } else {
+              // PixelShuffle(2): out[n/4, 2y + (n/2)%2, 2x + n%2]; channels (n, n+1) are horizontal neighbours
+              const int64_t hw4 = P.HW << 2;
+              const int W2 = P.W * 2;
+#pragma unroll
+              for (int j = 0; j < 16; j += 2) {
+                if (j < nlim) {
+                  const int n = n0 + j;
+                  TOUT* yp = yb + (int64_t)(n >> 2) * hw4 + (int64_t)(2 * py + ((n >> 1) & 1)) * W2 + 2 * px;
+                  const float v0 = __uint_as_float(r[j]) + s_st[nbase + c0 + j].y;
+                  const float v1 = __uint_as_float(r[j + 1]) + s_st[nbase + c0 + j + 1].y;
+                  if (std::is_same<TOUT, bf16>::value) {
+                    *reinterpret_cast<__nv_bfloat162*>(yp) = __floats2bfloat162_rn(v0, v1);
+                  } else {
+                    *reinterpret_cast<float2*>(yp) = make_float2(v0, v1);
+                  }
+                }
               }
             }
           }
@@ -507,6 +576,7 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   P.kc64 = g.Kpad / 64; P.S = g.S;
   P.per_sample_w = (Bw > 1) ? 1 : 0;
   P.inv_cin = 1.0f / (float)Cin;
+  P.kpt = g.kchunks; P.H = P.W = P.TW = P.TWs = P.TH = P.tiles_x = P.tiles_y = 0;
 
   int sms = 148;
   int gx = sms / g.nslices;
@@ -518,9 +588,9 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   do {                                                                                                          \
     static std::once_flag once;                                                                                 \
     std::call_once(once, [] {                                                                                   \
-      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
     });                                                                                                         \
-    gemm_tc_kernel<TRES, TOUT><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                                   \
+    gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                                \
   } while (0)
   const bool ob = y_dtype == B200IR_BF16;
   if (!res) {
@@ -532,4 +602,151 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   }
 #undef B200IR_LAUNCH_GEMM
   return check_launch("gemm_tc");
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// 3x3 dense conv on the same kernel (MODE 1..3)
+// ---------------------------------------------------------------------------------------------
+namespace b200ir {
+// wp[n][tap*Kt + c] = w[n][c][tap] (Kt = kpt*BK), zero padded; st[1][n] = bias
+__global__ void pack_conv3x3_kernel(const float* __restrict__ w, const float* __restrict__ bias, int Cin, int Cout,
+                                    int Kt, int Kpad, int Nrows, bf16* __restrict__ wp, float* __restrict__ st) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= Nrows) return;
+  bf16* dst = wp + (size_t)row * Kpad;
+  for (int k = lane; k < Kpad; k += 32) {
+    const int tap = k / Kt, c = k - tap * Kt;
+    float v = 0.f;
+    if (row < Cout && tap < 9 && c < Cin) v = w[((size_t)row * Cin + c) * 9 + tap];
+    dst[k] = __float2bfloat16_rn(v);
+  }
+  if (lane == 0) {
+    st[row] = 0.f;
+    st[Nrows + row] = (row < Cout && bias) ? bias[row] : 0.f;
+  }
+}
+}  // namespace b200ir
+
+extern "C" int b200ir_conv3x3_tc_geometry(int Cin, int Cout, int* kpad, int* nrows) {
+  GemmGeom g;
+  if (!gemm_tc_geometry(Cin, Cout, &g, 9)) {
+    set_error("conv3x3_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
+    return B200IR_E_UNSUPPORTED;
+  }
+  if (kpad) *kpad = g.Kpad;
+  if (nrows) *nrows = g.Nrows;
+  return 0;
+}
+
+extern "C" int b200ir_pack_conv3x3(const float* w, const float* bias, int Cin, int Cout, void* wp, float* st,
+                                   b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(w && wp && st, "pack_conv3x3: bad args");
+  GemmGeom g;
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g, 9), "pack_conv3x3: unsupported Cin=%d Cout=%d", Cin, Cout);
+  pack_conv3x3_kernel<<<(g.Nrows + 7) / 8, 256, 0, (cudaStream_t)stream>>>(w, bias, Cin, Cout, g.kpt * g.BK, g.Kpad,
+                                                                            g.Nrows, (bf16*)wp, st);
+  return check_launch("pack_conv3x3");
+}
+
+extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, const float* st, void* y,
+                                     int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int H, int W,
+                                     int shuffle_mode, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && wp && st && y && B > 0 && H > 0 && W > 0, "conv3x3_tc: bad args");
+  B200IR_CHECK_ARG(shuffle_mode >= 0 && shuffle_mode <= 2, "conv3x3_tc: bad shuffle mode");
+  B200IR_CHECK_ARG(dtype_ok(y_dtype), "conv3x3_tc: bad dtype");
+  GemmGeom g;
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g, 9), "conv3x3_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
+  B200IR_UNSUPPORTED(Cin % 8 == 0 && x_bstride % 8 == 0 && ((uintptr_t)x % 16) == 0,
+                     "conv3x3_tc: needs Cin%%8==0 and 16B-aligned NHWC activations");
+  B200IR_CHECK_ARG(shuffle_mode != B200IR_UNSHUFFLE2 || (H % 2 == 0 && W % 2 == 0), "conv3x3_tc: odd H/W");
+  B200IR_CHECK_ARG(shuffle_mode != B200IR_SHUFFLE2 || Cout % 4 == 0, "conv3x3_tc: Cout%%4 != 0");
+  int TWs = 0;
+  while ((1 << TWs) < W && TWs < 7) ++TWs;
+  const int TW = 1 << TWs, TH = 128 / TW;
+  CUtensorMap tmX, tmW;
+  {
+    // x is the NHWC copy: [B][H][W][Cin], Cin contiguous
+    const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+    const uint64_t str[4] = {2, (uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)x_bstride * 2};
+    const uint32_t box[4] = {64, (uint32_t)TW, (uint32_t)TH, 1};
+    int rc = make_tmap_bf16(&tmX, x, 4, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    const uint64_t dims[3] = {(uint64_t)g.Kpad, (uint64_t)g.Nrows, 1};
+    const uint64_t str[3] = {2, (uint64_t)g.Kpad * 2, (uint64_t)g.Nrows * g.Kpad * 2};
+    const uint32_t box[3] = {64, (uint32_t)g.nbox, 1};
+    int rc = make_tmap_bf16(&tmW, wp, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  GemmTcParams P;
+  P.y = y; P.y_bs = y_bstride; P.y_dt = y_dtype;
+  P.res = nullptr; P.res_bs = 0; P.res_dt = 0;
+  P.s = st; P.t = st + g.Nrows;
+  P.ln_type = B200IR_LN_NONE; P.Cin = Cin; P.Cout = Cout; P.HW = (int64_t)H * W;
+  P.H = H; P.W = W; P.TW = TW; P.TWs = TWs; P.TH = TH;
+  P.tiles_x = (W + TW - 1) / TW; P.tiles_y = (H + TH - 1) / TH;
+  P.tiles_per_sample = 1 << 30;
+  P.total_tiles = B * P.tiles_x * P.tiles_y;
+  P.BK = g.BK; P.kchunks = g.kchunks; P.kpt = g.kpt; P.Nslice = g.Nslice; P.NC = g.NC; P.nchunks = g.nchunks;
+  P.nbox = g.nbox; P.kc64 = g.Kpad / 64; P.S = g.S;
+  P.per_sample_w = 0;
+  P.inv_cin = 0.f;
+  int gx = 148 / g.nslices;
+  if (gx < 1) gx = 1;
+  if (gx > P.total_tiles) gx = P.total_tiles;
+  const dim3 grid((unsigned)gx, (unsigned)g.nslices);
+  cudaStream_t st_ = (cudaStream_t)stream;
+#define B200IR_LAUNCH_CONV(TOUT, MODE)                                                                           \
+  do {                                                                                                           \
+    static std::once_flag once;                                                                                  \
+    std::call_once(once, [] {                                                                                    \
+      cudaFuncSetAttribute(gemm_tc_kernel<void, TOUT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+    });                                                                                                          \
+    gemm_tc_kernel<void, TOUT, MODE><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                              \
+  } while (0)
+  const int mode = shuffle_mode + 1;
+  if (y_dtype == B200IR_BF16) {
+    if (mode == 1) B200IR_LAUNCH_CONV(bf16, 1); else if (mode == 2) B200IR_LAUNCH_CONV(bf16, 2); else B200IR_LAUNCH_CONV(bf16, 3);
+  } else {
+    if (mode == 1) B200IR_LAUNCH_CONV(float, 1); else if (mode == 2) B200IR_LAUNCH_CONV(float, 2); else B200IR_LAUNCH_CONV(float, 3);
+  }
+#undef B200IR_LAUNCH_CONV
+  return check_launch("conv3x3_tc");
+}
+
+
+// ---------------------------------------------------------------------------------------------
+// NCHW -> NHWC (bf16) staging copy for the conv activation operand
+// ---------------------------------------------------------------------------------------------
+namespace b200ir {
+__global__ void __launch_bounds__(256)
+nchw_to_nhwc_kernel(const bf16* __restrict__ x, int64_t x_bs, bf16* __restrict__ y, int C, int64_t HW) {
+  __shared__ bf16 t[64][66];
+  const int b = blockIdx.z;
+  const int64_t p0 = (int64_t)blockIdx.x * 64;
+  const int c0 = blockIdx.y * 64;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;  // 64 x 4
+  for (int i = ty; i < 64; i += 4) {
+    const int c = c0 + i;
+    const int64_t p = p0 + tx;
+    t[i][tx] = (c < C && p < HW) ? x[(int64_t)b * x_bs + (int64_t)c * HW + p] : __float2bfloat16_rn(0.f);
+  }
+  __syncthreads();
+  for (int i = ty; i < 64; i += 4) {
+    const int64_t p = p0 + i;
+    const int c = c0 + tx;
+    if (c < C && p < HW) y[((int64_t)b * HW + p) * C + c] = t[tx][i];
+  }
+}
+}  // namespace b200ir
+
+extern "C" int b200ir_nchw_to_nhwc(const void* x, int64_t x_bstride, void* y, int B, int C, int64_t HW,
+                                   b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && y && B > 0 && C > 0 && HW > 0 && B <= 65535, "nchw_to_nhwc: bad args");
+  dim3 grid((unsigned)((HW + 63) / 64), (unsigned)((C + 63) / 64), (unsigned)B);
+  nchw_to_nhwc_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_bstride, (bf16*)y, C, HW);
+  return check_launch("nchw_to_nhwc");
 }

@@ -167,7 +167,8 @@ class Downsample(nn.Module):
                                   nn.PixelUnshuffle(2))
 
     def forward(self, x, out=None):
-        return A.conv3x3(x, self.body[0].weight, None, None, L.UNSHUFFLE2, out=out)
+        return A.conv3x3(x, self.body[0].weight, None, None, L.UNSHUFFLE2, out=out,
+                         cache=self.__dict__.setdefault("_b200ir_cache", {}), key="w")
 
 
 class Upsample(nn.Module):
@@ -177,7 +178,8 @@ class Upsample(nn.Module):
                                   nn.PixelShuffle(2))
 
     def forward(self, x, out=None):
-        return A.conv3x3(x, self.body[0].weight, None, None, L.SHUFFLE2, out=out)
+        return A.conv3x3(x, self.body[0].weight, None, None, L.SHUFFLE2, out=out,
+                         cache=self.__dict__.setdefault("_b200ir_cache", {}), key="w")
 
 
 ##########################################################################

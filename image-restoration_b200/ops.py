@@ -282,3 +282,74 @@ def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=No
                                     B, Cin, Cout, H * W_, _stream())
     L.check(rc, "b200ir_gemm_tc_fwd")
     return out
+
+
+_GEOM3 = {}
+
+
+def conv3x3_tc_geometry(Cin, Cout):
+    key = (Cin, Cout)
+    if key not in _GEOM3:
+        kp, nr = _C.c_int(0), _C.c_int(0)
+        rc = lib.b200ir_conv3x3_tc_geometry(Cin, Cout, _C.byref(kp), _C.byref(nr))
+        _GEOM3[key] = (kp.value, nr.value) if rc == 0 else None
+    return _GEOM3[key]
+
+
+def conv3x3_tc_usable(x, Cout):
+    B, Cin, H, W_ = x.shape
+    return (x.dtype == torch.bfloat16 and Cin % 8 == 0 and Cout >= 16
+            and conv3x3_tc_geometry(Cin, Cout) is not None)
+
+
+def nchw_to_nhwc(x):
+    """bf16 [B,C,H,W] -> [B,H,W,C] staging copy (activation operand of the tcgen05 3x3 conv)."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if xdt != L.BF16:
+        raise ValueError("nchw_to_nhwc: bfloat16 only")
+    y = torch.empty((B, H, W_, C), device=x.device, dtype=torch.bfloat16)
+    with _timed("nchw_to_nhwc", B, C, H * W_):
+        rc = lib.b200ir_nchw_to_nhwc(xp, xbs, y.data_ptr(), B, C, H * W_, _stream())
+    L.check(rc, "b200ir_nchw_to_nhwc")
+    return y
+
+
+def pack_conv3x3(w, bias=None):
+    Cout, Cin = w.shape[0], w.shape[1]
+    geo = conv3x3_tc_geometry(Cin, Cout)
+    if geo is None:
+        raise ValueError(f"pack_conv3x3: ({Cin},{Cout}) unsupported by the tcgen05 conv")
+    kpad, nrows = geo
+    wp = torch.empty((nrows, kpad), device=w.device, dtype=torch.bfloat16)
+    st = torch.empty((2, nrows), device=w.device, dtype=torch.float32)
+    with _timed("pack_conv3x3", Cin, Cout):
+        rc = lib.b200ir_pack_conv3x3(_par(w, "w", Cout * Cin * 9), _par(bias, "bias", Cout), Cin, Cout, wp.data_ptr(),
+                                     st.data_ptr(), _stream())
+    L.check(rc, "b200ir_pack_conv3x3")
+    return wp, st
+
+
+def conv3x3_tc(x, packed, Cout, shuffle=L.SHUFFLE_NONE, out=None, out_dtype=None):
+    wp, st = packed
+    B, Cin, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if xdt != L.BF16:
+        raise ValueError("conv3x3_tc: activations must be bfloat16")
+    if shuffle == L.UNSHUFFLE2:
+        oshape = (B, Cout * 4, H // 2, W_ // 2)
+    elif shuffle == L.SHUFFLE2:
+        oshape = (B, Cout // 4, H * 2, W_ * 2)
+    else:
+        oshape = (B, Cout, H, W_)
+    if out is None:
+        out = torch.empty(oshape, device=x.device, dtype=out_dtype or x.dtype)
+    elif tuple(out.shape) != oshape:
+        raise ValueError(f"conv3x3_tc: out shape {tuple(out.shape)} != {oshape}")
+    yp, ybs, ydt = _act(out, "out")
+    xt = nchw_to_nhwc(x)
+    with _timed("conv3x3_tc", B, Cin, Cout, H, W_, shuffle, xdt, ydt):
+        rc = lib.b200ir_conv3x3_tc_fwd(xt.data_ptr(), H * W_ * Cin, wp.data_ptr(), st.data_ptr(), yp, ybs, ydt, B, Cin,
+                                       Cout, H, W_, shuffle, _stream())
+    L.check(rc, "b200ir_conv3x3_tc_fwd")
+    return out

@@ -111,6 +111,19 @@ int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw,
                        const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
                        int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);
 
+/* Dense 3x3 conv (pad 1, +bias) on the same tcgen05 kernel: 9 tap-shifted GEMMs accumulated in TMEM, zero padding
+ * from TMA out-of-bounds fill, PixelUnshuffle(2)/PixelShuffle(2) folded into the store (Downsample / Upsample,
+ * Restormer.py:171-189).  x bf16 NHWC with Cin%8==0; wp/st from b200ir_pack_conv3x3 (w fp32 [Cout,Cin,3,3]). */
+int b200ir_conv3x3_tc_geometry(int Cin, int Cout, int* kpad, int* nrows);
+/* bf16 NCHW -> NHWC staging copy: b200ir_conv3x3_tc_fwd takes its activations as [B][H][W][Cin] (channels
+ * contiguous, x_bstride = H*W*Cin) so that tap shifts only touch non-innermost TMA coordinates. */
+int b200ir_nchw_to_nhwc(const void* x, int64_t x_bstride, void* y, int B, int C, int64_t HW, b200ir_stream_t stream);
+int b200ir_pack_conv3x3(const float* w, const float* bias, int Cin, int Cout, void* wp, float* st,
+                        b200ir_stream_t stream);
+int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, const float* st, void* y,
+                          int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int H, int W, int shuffle_mode,
+                          b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
