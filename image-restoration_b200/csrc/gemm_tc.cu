@@ -44,7 +44,7 @@ PFN_encodeTiled get_encode_tiled() {
 }
 
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
-                   const uint32_t* box) {
+                   const uint32_t* box, bool swizzle128) {
   PFN_encodeTiled enc = get_encode_tiled();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point unavailable");
@@ -59,7 +59,8 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
     if (i > 0) gs[i - 1] = strides_bytes[i];
   }
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeTiled failed (%d): rank %d dims [%llu,%llu,%llu] box [%u,%u,%u]", (int)r, rank,
@@ -75,12 +76,16 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
 // ---------------------------------------------------------------------------------------------
 struct GemmGeom {
   int Kpad, BK, kchunks, kpt, Nslice, nslices, Nrows, NC, nchunks, nbox, S;
+  int gpw;              // 16-column groups per epilogue warp (TMA epilogue staging)
+  size_t epi_warp_bytes;
   size_t smem;
 };
 
 static inline int ceil_to(int v, int m) { return (v + m - 1) / m * m; }
 
-bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1) {
+// Packing (Kpad, Nrows) depends only on (Cin, Cout, taps); the out-channel slicing may additionally depend on
+// whether a residual tile is staged in shared memory (has_res) and whether the TMA-store epilogue is used.
+bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1, bool has_res = false, bool tma_epi = false) {
   if (Cin < 16 || Cout < 1) return false;
   // BK: channels per pipeline stage (multiple of 16, <= 64), least zero-padding first, then larger
   int best = 64;
@@ -96,28 +101,37 @@ bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1) {
   g->kchunks = taps * g->kpt;
   g->Kpad = taps == 1 ? ceil_to(Cin, 64) : ceil_to(taps * g->kpt * g->BK, 64);
   const int Npad = ceil_to(Cout, 16);
-  int nmax = (112 * 1024) / (g->Kpad * 2) / 16 * 16;
-  if (nmax > (taps == 1 ? 512 : 256)) nmax = (taps == 1 ? 512 : 256);
-  if (nmax < 16) return false;
-  g->nslices = (Npad + nmax - 1) / nmax;
-  g->Nslice = ceil_to((Npad + g->nslices - 1) / g->nslices, 16);
-  g->Nrows = g->Nslice * g->nslices;
-  g->nchunks = (g->Nslice + 255) / 256;
-  g->NC = ceil_to((g->Nslice + g->nchunks - 1) / g->nchunks, 16);
-  g->nbox = 16;
-  for (int nb = 256; nb >= 16; nb -= 16)
-    if (g->Nslice % nb == 0) {
-      g->nbox = nb;
-      break;
-    }
-  const size_t wbytes = (size_t)(g->Kpad / 64) * g->Nslice * 128;
-  const size_t fixed = 8192 + 1024;  // barriers + stats + s/t vectors + alignment slack
-  int S = (int)((227 * 1024 - wbytes - fixed) / 16384);
-  if (S > 8) S = 8;
-  g->S = S;
-  g->smem = wbytes + (size_t)S * 16384 + fixed;
-  const int need = g->nchunks > 1 ? g->kchunks + 1 : 2;
-  return S >= need && S >= 2;
+  g->Nrows = Npad;
+  // shrink the resident weight slice until the activation ring has enough stages next to the epilogue staging
+  for (int wkb = 112; wkb >= 16; wkb -= 16) {
+    int nmax = (wkb * 1024) / (g->Kpad * 2) / 16 * 16;
+    if (nmax > (taps == 1 ? 512 : 256)) nmax = (taps == 1 ? 512 : 256);
+    if (tma_epi && has_res && nmax > 128) nmax = 128;
+    if (nmax < 16) continue;
+    g->nslices = (Npad + nmax - 1) / nmax;
+    g->Nslice = ceil_to((Npad + g->nslices - 1) / g->nslices, 16);
+    g->nchunks = (g->Nslice + 255) / 256;
+    g->NC = ceil_to((g->Nslice + g->nchunks - 1) / g->nchunks, 16);
+    g->nbox = 16;
+    for (int nb = 256; nb >= 16; nb -= 16)
+      if (g->Nslice % nb == 0) {
+        g->nbox = nb;
+        break;
+      }
+    const size_t wbytes = (size_t)(g->Kpad / 64) * g->Nslice * 128;
+    g->gpw = ((g->NC >> 4) + 3) / 4;
+    g->epi_warp_bytes = tma_epi ? (size_t)g->gpw * 1024 * (has_res ? 3 : 1) : 0;
+    const size_t fixed = 1024 + 16 * g->epi_warp_bytes;  // alignment slack + per-warp epilogue staging
+    // static shared (barriers, LayerNorm stats, s/t vectors) is ~7 KB and counts against the 227 KB too
+    const long avail = 227 * 1024 - 8 * 1024 - (long)wbytes - (long)fixed;
+    int S = avail > 0 ? (int)(avail / 16384) : 0;
+    if (S > 8) S = 8;
+    g->S = S;
+    g->smem = wbytes + (size_t)S * 16384 + fixed;
+    const int need = g->nchunks > 1 ? g->kchunks + 1 : 3;
+    if (S >= need) return true;
+  }
+  return false;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -173,6 +187,8 @@ struct GemmTcParams {
   int per_sample_w;
   float inv_cin;
   // 3x3 conv mode (MODE > 0): K loop = 9 taps x kpt channel chunks, A tiles come from tap-shifted 4D TMA boxes
+  int Nrows;               // rows of the packed weight / length of s,t
+  int gpw, epi_warp_bytes; // TMA epilogue: 16-col groups per warp, bytes of staging per warp
   int kpt;                 // channel chunks per tap (== kchunks for 1x1)
   int H, W, TW, TWs, TH, tiles_x, tiles_y;   // conv tile = TW x TH pixels (TW*TH = 128, TW = 1<<TWs)
 };
@@ -200,28 +216,25 @@ template <> __device__ __forceinline__ void stf<float>(float* p, float v) { *p =
 template <typename TRES, typename TOUT, int MODE>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ CUtensorMap tmW,
+               const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmR,
                const GemmTcParams P) {
   using namespace tc;
   constexpr bool HAS_RES = !std::is_same<TRES, void>::value;
   typedef typename std::conditional<HAS_RES, TRES, float>::type TR;
+  // bf16 NCHW output (and bf16 residual) of the 1x1 path goes through shared memory + TMA (see epilogue)
+  constexpr bool TMA_EPI = MODE == 0 && std::is_same<TOUT, bf16>::value &&
+                           (!HAS_RES || std::is_same<TRES, bf16>::value);
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   const uint32_t wbytes = (uint32_t)P.kc64 * P.Nslice * 128;
   uint8_t* Wsm = smem;
   uint8_t* ring = smem + wbytes;
-  uint8_t* tail = ring + (size_t)P.S * kStageBytes;
-  uint64_t* bar_full = (uint64_t*)tail;            // [8]
-  uint64_t* bar_empty = bar_full + 8;              // [8]
-  uint64_t* bar_wfull = bar_empty + 8;             // [1]
-  uint64_t* bar_wempty = bar_wfull + 1;            // [1]
-  uint64_t* bar_accfull = bar_wempty + 1;          // [2]
-  uint64_t* bar_accempty = bar_accfull + 2;        // [2]
-  uint64_t* bar_stfull = bar_accempty + 2;         // [2]
-  uint64_t* bar_stempty = bar_stfull + 2;          // [2]
-  uint32_t* tmem_slot = (uint32_t*)(bar_stempty + 2);
-  float* s_mu = (float*)(tail + 256);              // [2][128]
-  float* s_rstd = s_mu + 256;                      // [2][128]
-  float2* s_st = (float2*)(tail + 256 + 2048);     // [Nslice] (s, t) of this CTA's out-channel slice
+  uint8_t* epi_smem = ring + (size_t)P.S * kStageBytes;   // [16 warps][epi_warp_bytes]
+  __shared__ uint64_t bar_full[8], bar_empty[8], bar_wfull[1], bar_wempty[1], bar_accfull[2], bar_accempty[2],
+      bar_stfull[2], bar_stempty[2], bar_res[2 * kEpiWarps];
+  __shared__ uint32_t tmem_slot[1];
+  __shared__ float s_mu[256], s_rstd[256];   // [2][128]: (-rstd*mu, rstd) per pixel, double buffered
+  __shared__ __align__(16) float2 s_st[512];               // (s, t) of this CTA's out-channel slice
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const bool has_ln = P.ln_type != B200IR_LN_NONE;
@@ -234,6 +247,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     }
     mbar_init(bar_wfull, 1);
     mbar_init(bar_wempty, 1);
+    for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&bar_res[i], 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar_accfull[i], 1);
       mbar_init(&bar_accempty[i], kEpiWarps);
@@ -242,11 +256,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     }
     fence_barrier_init();
   }
-  for (int i = threadIdx.x; i < P.Nslice; i += kThreads) s_st[i] = make_float2(P.s[n_lo + i], P.t[n_lo + i]);
+  for (int i = threadIdx.x; i < P.Nslice; i += kThreads)
+    s_st[i] = (n_lo + i < P.Nrows) ? make_float2(P.s[n_lo + i], P.t[n_lo + i]) : make_float2(0.f, 0.f);
   if (warp == kWarpProducer) {
     if (lane == 0) {
       tma_prefetch_desc(&tmX);
       tma_prefetch_desc(&tmW);
+      if (TMA_EPI) tma_prefetch_desc(&tmY);
+      if (TMA_EPI && HAS_RES) tma_prefetch_desc(&tmR);
     }
     tmem_alloc(tmem_slot, 512);
   }
@@ -384,6 +401,102 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         mbar_arrive(&bar_stfull[sp]);
       }
     }
+  } else if (TMA_EPI) {
+    // ===== epilogue (bf16 NCHW via TMA): warp w <-> TMEM lane quadrant w%4 and a contiguous quarter of the chunk's
+    // 16-column groups.  Each warp is self-contained: tcgen05.ld -> fp32 math -> bf16 into its private staging
+    // [group][16 ch][32 px] -> one TMA store box {32 px, 16 ch} per group.  The residual tile of the NEXT
+    // (tile, chunk) is TMA-loaded into the warp's private double buffer while the current one is processed.
+    const int quad = warp & 3, wq = warp >> 2;
+    const int m = quad * 32 + lane;
+    uint8_t* stg = epi_smem + (size_t)warp * P.epi_warp_bytes;          // [gpw][16][64 B]
+    uint8_t* resb = stg + (size_t)P.gpw * 1024;                          // [2][gpw][16][64 B]
+    uint64_t* rbar = &bar_res[warp * 2];
+    auto groups_of = [&](int ch, int& g_lo, int& g_hi) {
+      const int G = min(P.NC, P.Nslice - ch * P.NC) >> 4;
+      g_lo = (wq * G) >> 2;
+      g_hi = ((wq + 1) * G) >> 2;
+    };
+    auto issue_res = [&](int tile, int ch, uint32_t buf) {   // lane 0 only
+      int g_lo, g_hi;
+      groups_of(ch, g_lo, g_hi);
+      if (g_hi <= g_lo) return;
+      const int b = tile / P.tiles_per_sample;
+      const int p0 = (tile - b * P.tiles_per_sample) * 128 + quad * 32;
+      mbar_arrive_expect_tx(&rbar[buf], (uint32_t)(g_hi - g_lo) * 1024u);
+      for (int g = g_lo; g < g_hi; ++g)
+        tma_load_3d(resb + ((size_t)buf * P.gpw + (g - g_lo)) * 1024, &tmR, &rbar[buf], p0,
+                    n_lo + ch * P.NC + g * 16, b);
+    };
+    uint32_t acc_it = 0, tcount = 0;
+    if (HAS_RES && lane == 0 && t_begin < t_end) issue_res(t_begin, 0, 0);
+    for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
+      const int b = tile / P.tiles_per_sample;
+      const int p0 = (tile - b * P.tiles_per_sample) * 128 + quad * 32;
+      float nmr = 0.f, rstd = 1.f;  // (-rstd*mu, rstd)
+      for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
+        int g_lo, g_hi;
+        groups_of(ch, g_lo, g_hi);
+        const int nbase = ch * P.NC;
+        if (HAS_RES && lane == 0) {  // prefetch the next item's residual
+          int ntile = tile, nch = ch + 1;
+          if (nch == P.nchunks) nch = 0, ++ntile;
+          if (ntile < t_end) {
+            fence_proxy_async();
+            issue_res(ntile, nch, (acc_it + 1) & 1);
+          }
+        }
+        if (ch == 0 && has_ln) {
+          const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+          mbar_wait(&bar_stfull[sp], sph);
+          nmr = s_mu[sp * 128 + m];
+          rstd = s_rstd[sp * 128 + m];
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_stempty[sp]);
+        }
+        const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
+        mbar_wait(&bar_accfull[as], aph);
+        tc_fence_after();
+        if (lane == 0) bulk_wait_read<0>();   // the stores of the previous item have drained the staging buffer
+        __syncwarp();
+        if (HAS_RES && g_hi > g_lo) mbar_wait(&rbar[acc_it & 1], (acc_it >> 1) & 1);
+        const uint32_t tbase = tmem_base + as * 256 + ((uint32_t)(quad * 32) << 16);
+        const uint32_t rsrc = smem_u32(resb) + (uint32_t)(acc_it & 1) * P.gpw * 1024u + lane * 2u;
+        const uint32_t sdst = smem_u32(stg) + lane * 2u;
+        for (int g = g_lo; g < g_hi; ++g) {
+          uint32_t r[16];
+          tmem_ld_32x16(tbase + g * 16, r);
+          const float4* stp = reinterpret_cast<const float4*>(&s_st[nbase + g * 16]);  // (s,t) pairs of 2 columns
+          float4 st4[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) st4[j] = stp[j];
+          float rr[16];
+          if (HAS_RES) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) rr[j] = ld_shared_bf16(rsrc + (uint32_t)(g - g_lo) * 1024u + j * 64u);
+          }
+          tmem_ld_wait();
+          const uint32_t d0 = sdst + (uint32_t)(g - g_lo) * 1024u;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float sx = (j & 1) ? st4[j >> 1].z : st4[j >> 1].x;
+            const float ty = (j & 1) ? st4[j >> 1].w : st4[j >> 1].y;
+            float v = has_ln ? fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, sx, ty)) : __uint_as_float(r[j]) + ty;
+            if (HAS_RES) v += rr[j];
+            st_shared_bf16(d0 + j * 64u, v);
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&bar_accempty[as]);
+          for (int g = g_lo; g < g_hi; ++g)
+            tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
+          bulk_commit();
+        }
+      }
+    }
+    if (lane == 0) bulk_wait<0>();
   } else {
     // ===== epilogue: warp w <-> TMEM lane quadrant w%4, 16-column groups g = w/4, w/4+4, ... =====
     const int quad = warp & 3, wq = warp >> 2;
@@ -545,7 +658,12 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   B200IR_CHECK_ARG(Bw == 1 || Bw == B, "gemm_tc: Bw must be 1 or B");
   B200IR_CHECK_ARG(dtype_ok(y_dtype) && (!res || dtype_ok(res_dtype)), "gemm_tc: bad dtype");
   GemmGeom g;
-  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g), "gemm_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
+  const bool tma_epi = y_dtype == B200IR_BF16 && (!res || res_dtype == B200IR_BF16) && y_bstride % 8 == 0 &&
+                       ((uintptr_t)y % 16) == 0 && (!res || (res_bstride % 8 == 0 && ((uintptr_t)res % 16) == 0));
+  B200IR_UNSUPPORTED(tma_epi || y_dtype == B200IR_F32,
+                     "gemm_tc: bf16 output / residual must be 16B-aligned with batch strides %% 8 == 0");
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g, 1, res != nullptr, tma_epi),
+                     "gemm_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
   B200IR_UNSUPPORTED(HW % 8 == 0 && HW >= 64 && x_bstride % 8 == 0 && ((uintptr_t)x % 16) == 0,
                      "gemm_tc: needs HW%%8==0, HW>=64 and 16B-aligned activations (HW=%lld)", (long long)HW);
   B200IR_UNSUPPORTED(HW < (1ll << 31) && (int64_t)B * ((HW + 127) / 128) < (1ll << 31), "gemm_tc: too many tiles");
@@ -565,10 +683,24 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
     int rc = make_tmap_bf16(&tmW, wp, 3, dims, str, box);
     if (rc) return rc;
   }
+  CUtensorMap tmY = tmX, tmR = tmX;
+  if (tma_epi) {
+    const uint64_t dims[3] = {(uint64_t)HW, (uint64_t)Cout, (uint64_t)B};
+    const uint32_t box[3] = {32, 16, 1};
+    const uint64_t stry[3] = {2, (uint64_t)HW * 2, (uint64_t)y_bstride * 2};
+    int rc = make_tmap_bf16(&tmY, y, 3, dims, stry, box, false);
+    if (rc) return rc;
+    if (res) {
+      const uint64_t strr[3] = {2, (uint64_t)HW * 2, (uint64_t)res_bstride * 2};
+      rc = make_tmap_bf16(&tmR, res, 3, dims, strr, box, false);
+      if (rc) return rc;
+    }
+  }
   GemmTcParams P;
   P.y = y; P.y_bs = y_bstride; P.y_dt = y_dtype;
   P.res = res; P.res_bs = res_bstride; P.res_dt = res_dtype;
   P.s = st; P.t = st + g.Nrows;
+  P.Nrows = g.Nrows; P.gpw = g.gpw; P.epi_warp_bytes = (int)g.epi_warp_bytes;
   P.ln_type = ln_type; P.Cin = Cin; P.Cout = Cout; P.HW = HW;
   P.tiles_per_sample = (int)((HW + 127) / 128);
   P.total_tiles = P.tiles_per_sample * B;
@@ -588,9 +720,9 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   do {                                                                                                          \
     static std::once_flag once;                                                                                 \
     std::call_once(once, [] {                                                                                   \
-      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
     });                                                                                                         \
-    gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                                \
+    gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);                      \
   } while (0)
   const bool ob = y_dtype == B200IR_BF16;
   if (!res) {
@@ -685,6 +817,7 @@ extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const voi
   P.y = y; P.y_bs = y_bstride; P.y_dt = y_dtype;
   P.res = nullptr; P.res_bs = 0; P.res_dt = 0;
   P.s = st; P.t = st + g.Nrows;
+  P.Nrows = g.Nrows; P.gpw = 0; P.epi_warp_bytes = 0;
   P.ln_type = B200IR_LN_NONE; P.Cin = Cin; P.Cout = Cout; P.HW = (int64_t)H * W;
   P.H = H; P.W = W; P.TW = TW; P.TWs = TWs; P.TH = TH;
   P.tiles_x = (W + TW - 1) / TW; P.tiles_y = (H + TH - 1) / TH;
@@ -703,9 +836,9 @@ extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const voi
   do {                                                                                                           \
     static std::once_flag once;                                                                                  \
     std::call_once(once, [] {                                                                                    \
-      cudaFuncSetAttribute(gemm_tc_kernel<void, TOUT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024); \
+      cudaFuncSetAttribute(gemm_tc_kernel<void, TOUT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
     });                                                                                                          \
-    gemm_tc_kernel<void, TOUT, MODE><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, P);                              \
+    gemm_tc_kernel<void, TOUT, MODE><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmX, tmX, P);                    \
   } while (0)
   const int mode = shuffle_mode + 1;
   if (y_dtype == B200IR_BF16) {
