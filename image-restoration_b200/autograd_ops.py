@@ -82,12 +82,29 @@ def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
     B, C3, H, W = qkv.shape
     C = C3 // 3
     partials = ops.mdta_gram(qkv, heads)
-    m = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C))
     v = qkv[:, 2 * C:]
     if USE_TC and ops.gemm_tc_usable(v, C):
-        packed = ops.pack_conv1x1(m, _p(b_out), per_sample=True)
-        return ops.gemm_tc(v, packed, C, L.LN_NONE, res, out=out)
+        mp = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), packed=True)
+        return ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device)), C, L.LN_NONE, res, out=out)
+    m = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C))
     return ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
+
+
+_ST_CACHE = {}
+
+
+def _bias_st(bias, C, nrows, device):
+    """(s, t) epilogue vectors of the per-sample GEMM: s unused (no LayerNorm), t = project_out bias."""
+    key = (None if bias is None else (bias.data_ptr(), bias._version), C, nrows, str(device))
+    st = _ST_CACHE.get(key)
+    if st is None:
+        if len(_ST_CACHE) > 4096:
+            _ST_CACHE.clear()
+        st = torch.zeros((2, nrows), device=device, dtype=torch.float32)
+        if bias is not None:
+            st[1, :C] = bias.detach().float()
+        _ST_CACHE[key] = st
+    return st
 
 
 def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=None):

@@ -80,60 +80,92 @@ gram_simt_kernel(const void* __restrict__ qkv, int64_t bs, int dt, int C, int d,
   if (tid < 2 * d) out[d * d + tid] = nrm;
 }
 
-// grid (heads, B), 256 threads.  smem: attn[d][d+1] + nq[d] + nk[d]
+// ---- stage 2a: slab reduce + normalise + temperature + row softmax.  grid (ceil(d/8), heads, B), 256 threads:
+// one warp per attention row (8 rows per block), so B*heads*d/8 blocks share the slab reduction.
 __global__ void __launch_bounds__(256)
-softmax_fold_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ temperature,
-                    const float* __restrict__ w_out, float* __restrict__ m, float* __restrict__ attn_out, int C,
-                    int d) {
+mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ temperature,
+                    float* __restrict__ attn, int d) {
   extern __shared__ float sm[];
-  float* attn = sm;                      // [d][d+1]
-  float* nq = sm + (size_t)d * (d + 1);  // [d]
-  float* nk = nq + d;                    // [d]
+  float* nk = sm;             // [d]  max(||k_j||, eps)
+  float* rowbuf = sm + d;     // [8][d]
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int h = blockIdx.x, b = blockIdx.y, heads = gridDim.x;
+  const int h = blockIdx.y, b = blockIdx.z, heads = gridDim.y;
   const size_t per = (size_t)d * d + 2 * d;
   const float* base = partials + ((size_t)b * heads + h) * nslab * per;
-
-  for (int e = tid; e < (int)per; e += 256) {
+  for (int j = tid; j < d; j += 256) {
     float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];  // fixed order: deterministic
-    if (e < d * d) attn[(e / d) * (d + 1) + (e % d)] = s;
-    else if (e < d * d + d) nq[e - d * d] = fmaxf(sqrtf(s), 1e-12f);      // max(||q||,eps) (:121)
-    else nk[e - d * d - d] = fmaxf(sqrtf(s), 1e-12f);
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + d + j];  // fixed order
+    nk[j] = fmaxf(sqrtf(s), 1e-12f);                                                          // (:122)
   }
   __syncthreads();
+  const int i = blockIdx.x * 8 + warp;
+  if (i >= d) return;
+  float nq = 0.f;
+  if (lane == 0) {
+    float s = 0.f;
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + i];
+    nq = fmaxf(sqrtf(s), 1e-12f);                                                             // (:121)
+  }
+  nq = __shfl_sync(0xffffffffu, nq, 0);
   const float temp = temperature[h];
-  for (int i = warp; i < d; i += 8) {
-    float* row = attn + i * (d + 1);
-    float mx = -INFINITY;
-    for (int j = lane; j < d; j += 32) {
-      const float v = row[j] / (nq[i] * nk[j]) * temp;
-      row[j] = v;
-      mx = fmaxf(mx, v);
-    }
-    mx = warp_max(mx);
-    float sum = 0.f;
-    for (int j = lane; j < d; j += 32) {
-      const float e = expf(row[j] - mx);
-      row[j] = e;
-      sum += e;
-    }
-    sum = warp_sum(sum);
-    const float inv = 1.0f / sum;
-    for (int j = lane; j < d; j += 32) {
-      const float v = row[j] * inv;
-      row[j] = v;
-      if (attn_out) attn_out[(((size_t)b * heads + h) * d + i) * d + j] = v;
-    }
+  float* row = rowbuf + warp * d;
+  float mx = -INFINITY;
+  for (int j = lane; j < d; j += 32) {
+    float s = 0.f;
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)i * d + j];       // fixed order
+    const float v = s / (nq * nk[j]) * temp;                                                  // (:124)
+    row[j] = v;
+    mx = fmaxf(mx, v);
+  }
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int j = lane; j < d; j += 32) {
+    const float e = expf(row[j] - mx);
+    row[j] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  const float inv = 1.0f / sum;
+  float* out = attn + (((size_t)b * heads + h) * d + i) * d;
+  for (int j = lane; j < d; j += 32) out[j] = row[j] * inv;                                   // (:125)
+}
+
+// ---- stage 2b: fold project_out into the attention matrix: m[b][o][h*d+j] = sum_i w_out[o][h*d+i] attn[b,h][i][j]
+// grid (ceil(C/32), heads, B), 256 threads.  Writes fp32 m [B,C,C] and/or the bf16 operand of the tcgen05 GEMM
+// mp [B][nrows][kpad] (zero padded) so that no separate packing launch is needed.
+__global__ void __launch_bounds__(256)
+mdta_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out, float* __restrict__ m,
+                 bf16* __restrict__ mp, int kpad, int nrows, int C, int d) {
+  extern __shared__ float sm[];
+  float* at = sm;                    // [d][d+1]
+  float* ws = sm + (size_t)d * (d + 1);  // [32][d+1]
+  const int tid = threadIdx.x;
+  const int h = blockIdx.y, b = blockIdx.z, heads = gridDim.y;
+  const int o0 = blockIdx.x * 32;
+  const float* a = attn + ((size_t)b * heads + h) * d * d;
+  for (int e = tid; e < d * d; e += 256) at[(e / d) * (d + 1) + (e % d)] = a[e];
+  for (int e = tid; e < 32 * d; e += 256) {
+    const int o = o0 + e / d, i = e % d;
+    ws[(e / d) * (d + 1) + i] = o < C ? w_out[(size_t)o * C + h * d + i] : 0.f;
   }
   __syncthreads();
-  // fold: m[b][o][h*d+j] = sum_i w_out[o][h*d+i] * attn[i][j]
-  for (int e = tid; e < C * d; e += 256) {
-    const int o = e / d, j = e % d;
-    const float* wr = w_out + (size_t)o * C + h * d;
+  for (int e = tid; e < 32 * d; e += 256) {
+    const int ol = e / d, j = e % d, o = o0 + ol;
+    if (o >= C) continue;
     float s = 0.f;
-    for (int i = 0; i < d; ++i) s = fmaf(wr[i], attn[i * (d + 1) + j], s);
-    m[((size_t)b * C + o) * C + h * d + j] = s;
+    for (int i = 0; i < d; ++i) s = fmaf(ws[ol * (d + 1) + i], at[i * (d + 1) + j], s);
+    if (m) m[((size_t)b * C + o) * C + h * d + j] = s;
+    if (mp) mp[((size_t)b * nrows + o) * kpad + h * d + j] = __float2bfloat16_rn(s);
+  }
+  if (mp) {  // zero padding: columns [C,kpad) of valid rows (head 0 blocks) and whole rows [C,nrows) (last row block)
+    if (h == 0)
+      for (int e = tid; e < 32 * (kpad - C); e += 256) {
+        const int o = o0 + e / (kpad - C), c = C + e % (kpad - C);
+        if (o < C) mp[((size_t)b * nrows + o) * kpad + c] = __float2bfloat16_rn(0.f);
+      }
+    if (h == 0 && blockIdx.x == gridDim.x - 1)
+      for (int e = tid; e < (nrows - C) * kpad; e += 256)
+        mp[((size_t)b * nrows + C + e / kpad) * kpad + e % kpad] = __float2bfloat16_rn(0.f);
   }
 }
 
@@ -196,20 +228,26 @@ extern "C" int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype,
 }
 
 extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
-                                            const float* w_out, float* m, float* attn_out, int B, int C, int heads,
-                                            b200ir_stream_t stream) {
-  B200IR_CHECK_ARG(partials && temperature && w_out && m && nslab > 0 && B > 0 && C > 0 && heads > 0,
+                                            const float* w_out, float* m, float* attn, void* mp, int kpad, int nrows,
+                                            int B, int C, int heads, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(partials && temperature && w_out && attn && (m || mp) && nslab > 0 && B > 0 && C > 0 && heads > 0,
                    "mdta_softmax_fold: bad args");
-  B200IR_CHECK_ARG(C % heads == 0 && B <= 65535, "mdta_softmax_fold: bad C/heads/B");
+  B200IR_CHECK_ARG(C % heads == 0 && B <= 65535 && heads <= 65535, "mdta_softmax_fold: bad C/heads/B");
+  B200IR_CHECK_ARG(!mp || (kpad >= C && nrows >= C), "mdta_softmax_fold: bad packed geometry");
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_softmax_fold: head dim %d > 128 unsupported", d);
-  const size_t smem = ((size_t)d * (d + 1) + 2 * d) * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  mdta_softmax_kernel<<<dim3((unsigned)((d + 7) / 8), (unsigned)heads, (unsigned)B), 256, (size_t)9 * d * sizeof(float),
+                        st>>>(partials, nslab, temperature, attn, d);
+  int rc = check_launch("mdta_softmax");
+  if (rc) return rc;
+  const size_t smem = ((size_t)d * (d + 1) + 32 * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(softmax_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 72 * 1024);
+    cudaFuncSetAttribute(mdta_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     attr_set = true;
   }
-  softmax_fold_kernel<<<dim3((unsigned)heads, (unsigned)B), 256, smem, (cudaStream_t)stream>>>(
-      partials, nslab, temperature, w_out, m, attn_out, C, d);
-  return check_launch("mdta_softmax_fold");
+  mdta_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem, st>>>(
+      attn, w_out, m, (bf16*)mp, kpad, nrows, C, d);
+  return check_launch("mdta_fold");
 }

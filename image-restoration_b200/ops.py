@@ -161,19 +161,29 @@ def mdta_gram(qkv, heads, impl=L.IMPL_AUTO):
     return partials
 
 
-def mdta_softmax_fold(partials, temperature, w_out, want_attn=False):
-    """attn = softmax(normalised Gram * temperature); returns m = W_out . blockdiag(attn) [B,C,C] (and attn)."""
+def mdta_softmax_fold(partials, temperature, w_out, want_attn=False, packed=False):
+    """attn = softmax(normalised Gram * temperature); m = W_out . blockdiag(attn).
+    packed=False -> fp32 m [B,C,C]; packed=True -> bf16 [B,nrows,kpad] operand of gemm_tc.  (+attn if asked)"""
     B, heads, nslab, per = partials.shape
     C = w_out.shape[0]
     d = C // heads
-    m = torch.empty((B, C, C), device=partials.device, dtype=torch.float32)
-    attn = torch.empty((B, heads, d, d), device=partials.device, dtype=torch.float32) if want_attn else None
+    attn = torch.empty((B, heads, d, d), device=partials.device, dtype=torch.float32)
+    m, mp, kpad, nrows = None, None, 0, 0
+    if packed:
+        kpad, nrows = gemm_tc_geometry(C, C)
+        mp = torch.empty((B, nrows, kpad), device=partials.device, dtype=torch.bfloat16)
+    else:
+        m = torch.empty((B, C, C), device=partials.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1  # two kernels (softmax, fold)
     with _timed("mdta_softmax_fold", B, C, heads, nslab):
         rc = lib.b200ir_mdta_softmax_fold_fwd(partials.data_ptr(), nslab, _par(temperature, "temperature", heads),
-                                              _par(w_out, "w_out", C * C), m.data_ptr(),
-                                              attn.data_ptr() if want_attn else None, B, C, heads, _stream())
+                                              _par(w_out, "w_out", C * C), m.data_ptr() if m is not None else None,
+                                              attn.data_ptr(), mp.data_ptr() if mp is not None else None, kpad, nrows,
+                                              B, C, heads, _stream())
     L.check(rc, "b200ir_mdta_softmax_fold_fwd")
-    return (m, attn) if want_attn else m
+    out = mp if packed else m
+    return (out, attn) if want_attn else out
 
 
 def conv3x3(x, w, bias=None, res=None, shuffle=L.SHUFFLE_NONE, out=None, out_dtype=None):

@@ -71,13 +71,13 @@ int b200ir_mdta_gram_nslab(int B, int C, int heads, int64_t HW);
 int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype, int B, int C, int heads, int64_t HW,
                          float* partials, int nslab, int impl, b200ir_stream_t stream);
 
-/* MDTA stage 2 — reduce slabs, attn = softmax(q^.k^^T * temperature) (Restormer.py:121-125) and
- * fold the output projection: m[b][o, h*d+j] = sum_i w_out[o, h*d+i] * attn[b,h][i,j], so that
- * project_out(attn @ v) (Restormer.py:127-131) becomes ONE 1x1 GEMM with per-sample weight m
- * (b200ir_ln_conv1x1_fwd / b200ir_gemm_tc_fwd with w_bstride = C*C).
- * m: fp32 [B,C,C]; attn_out (optional, may be NULL): fp32 [B,heads,d,d] (kept for backward). */
+/* MDTA stage 2 — (a) reduce slabs, attn = softmax(q^.k^^T * temperature) (Restormer.py:121-125), then (b) fold the
+ * output projection: m[b][o, h*d+j] = sum_i w_out[o, h*d+i] * attn[b,h][i,j], so that project_out(attn @ v)
+ * (Restormer.py:127-131) becomes ONE 1x1 GEMM with a per-sample weight.
+ * attn: fp32 [B,heads,d,d] (always written; kept for backward).  m: fp32 [B,C,C] or NULL.
+ * mp: bf16 [B,nrows,kpad] operand of b200ir_gemm_tc_fwd (geometry from b200ir_gemm_tc_geometry(C,C)) or NULL. */
 int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
-                                 const float* w_out, float* m, float* attn_out,
+                                 const float* w_out, float* m, float* attn, void* mp, int kpad, int nrows,
                                  int B, int C, int heads, b200ir_stream_t stream);
 
 /* Dense 3x3 conv, pad 1 (+bias) (+res) with PixelUnshuffle(2)/PixelShuffle(2) folded into the
