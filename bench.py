@@ -39,6 +39,23 @@ def peaks():
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
 
 
+def ncu_traffic(kernel_tag="gate"):
+    """dram read+write bytes per launch of the dominant kernel from the committed `ncu --set full` summary."""
+    import glob
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", f"*_{kernel_tag}_ncu_full_summary.json")), reverse=True):
+        try:
+            d = json.load(open(f))
+            tot = 0.0
+            for k in ("dram__bytes_read.sum", "dram__bytes_write.sum"):
+                v, u = d[k]
+                tot += float(v) * unit[u]
+            return tot, os.path.basename(f)
+        except Exception:
+            continue
+    return None, None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -212,7 +229,7 @@ def main():
     achieved = alg_bytes / (kms * 1e-3) / 1e9
     roofline = {"kernel": f"dwconv3x3_gelu_gate B{kb} Hd{khd} {kh}x{kw}", "bound": "hbm", "achieved": achieved,
                 "peak": pk["hbm_gbs"], "peak_source": pk_src, "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
-                "traffic": None, "launch_ms": kms, "launches_timed": gate_t[key][0], "alg_bytes_per_launch": alg_bytes}
+                "traffic": ncu_traffic()[0], "traffic_source": ncu_traffic()[1], "launch_ms": kms, "launches_timed": gate_t[key][0], "alg_bytes_per_launch": alg_bytes}
     out = {
         "metric": METRIC, "value": mp_per_step_total / (ms * 1e-3), "unit": "MP/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
