@@ -175,6 +175,12 @@ static int launch_dwconv(const void* x, int64_t x_bs, const float* w, const floa
   return check_launch(GATE ? "dwconv3x3_gelu_gate" : "dwconv3x3");
 }
 
+// dwconv_tma.cu: TMA-staged bf16 path
+bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, const void* x, const void* y);
+template <bool GATE>
+int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs, int B,
+                      int Cout, int H, int W, cudaStream_t st);
+
 }  // namespace b200ir
 
 using namespace b200ir;
@@ -184,6 +190,8 @@ extern "C" int b200ir_dwconv3x3_fwd(const void* x, int64_t x_bstride, const floa
                                     b200ir_stream_t stream) {
   B200IR_CHECK_ARG(x && w && y && B > 0 && C > 0 && H > 0 && W > 0, "dwconv3x3: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3: bad dtype %d", dtype);
+  if (dwconv_tma_supported(dtype, H, W, x_bstride, y_bstride, x, y))
+    return dwconv_tma_launch<false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
   if (dtype == B200IR_BF16)
     return launch_dwconv<bf16, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
   return launch_dwconv<float, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
@@ -194,6 +202,8 @@ extern "C" int b200ir_dwconv3x3_gelu_gate_fwd(const void* x, int64_t x_bstride, 
                                               b200ir_stream_t stream) {
   B200IR_CHECK_ARG(x && w && y && B > 0 && Hd > 0 && H > 0 && W > 0, "dwconv3x3_gelu_gate: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_gelu_gate: bad dtype %d", dtype);
+  if (dwconv_tma_supported(dtype, H, W, x_bstride, y_bstride, x, y))
+    return dwconv_tma_launch<true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
   if (dtype == B200IR_BF16)
     return launch_dwconv<bf16, true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
   return launch_dwconv<float, true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);

@@ -1,0 +1,267 @@
+// dwconv_tma.cu — depthwise 3x3 (stride 1, zero pad 1) for bf16 NCHW planes as a shared-memory-staged, halo-tiled,
+// vectorised bandwidth kernel, optionally with the GDFN gate gelu(x1)*x2 fused.
+// Reference: Attention.qkv_dwconv Restormer.py:106,114; FeedForward.dwconv + chunk(2) + F.gelu(x1)*x2 :84,90-91.
+//
+// One work item = (sample, channel [and channel+Hd], TH x TW output tile).  A persistent CTA streams items through a
+// ring of shared-memory stages: ONE 4D TMA box per plane brings the (TH+2) x (TW+16) halo tile (the x origin is moved
+// 8 pixels left so that the innermost TMA coordinate stays 16-byte aligned; zero padding = TMA out-of-bounds fill, so
+// the inner loops carry no boundary predicates).  A thread owns an 8-pixel-wide column strip and slides a 3-row fp32
+// register window down 8 output rows: per row one LDS.128 + two LDS.32 (left/right neighbour), 72 FFMA per plane,
+// one 128-bit coalesced global store.  fp32 accumulation, bf16 storage.
+// The gate uses x*sigmoid(p(x)), p an odd degree-5 polynomial fitted to the exact erf GELU (max abs error 2.5e-5,
+// i.e. below bf16 resolution); the fp32 path (dwconv.cu) keeps erff.
+#include <mutex>
+
+#include "tc_common.cuh"
+
+namespace b200ir {
+
+struct DwTmaParams {
+  bf16* y;
+  int64_t y_bs;
+  const float* w;
+  const float* bias;
+  int Cout, H, W, TW, TH, nxg, nstrips, tiles_x, tiles_y, S;
+  int nitems;
+};
+
+constexpr int DW_RS = 8;   // output rows per thread
+constexpr int DW_XP = 8;   // left/right padding of the staged tile in pixels (keeps TMA coordinates 16B aligned)
+
+__device__ __forceinline__ float gelu_fast(float x) {
+  // x * sigmoid(x * q(min(x^2, 64))): clamping x^2 keeps the odd polynomial monotone outside the fitted range
+  // (|x| > 8 -> exact 0 / x in fp32 anyway); coefficients pre-multiplied by -log2(e) for ex2
+  const float x2 = fminf(x * x, 64.f);
+  float t = fmaf(1.0142652e-3f, x2, -1.0677574e-1f);   // -log2e * (-7.030350675e-4, 7.401130191e-2)
+  t = fmaf(t, x2, -2.3011213f);                        // -log2e * 1.5950157569
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return x * r;
+}
+
+// packed fp32x2 FMA (sm_100): d = a * b + c on both halves, one issue slot
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;"
+      : "=l"(d)
+      : "l"(*reinterpret_cast<uint64_t*>(&a)), "l"(*reinterpret_cast<uint64_t*>(&b)),
+        "l"(*reinterpret_cast<uint64_t*>(&c)));
+  return *reinterpret_cast<float2*>(&d);
+}
+
+
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+// gated variant: both planes at once, window element = (plane A value, plane B value) for packed FMA
+__device__ __forceinline__ void dw_load_row2(uint32_t sa, uint32_t sb, float2* o) {
+  uint32_t l0, r0, a0, b0, c0, d0, l1, r1, a1, b1, c1, d1;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(l0) : "r"(sa - 4));
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a0), "=r"(b0), "=r"(c0), "=r"(d0) : "r"(sa));
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r0) : "r"(sa + 16));
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(l1) : "r"(sb - 4));
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a1), "=r"(b1), "=r"(c1), "=r"(d1) : "r"(sb));
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r1) : "r"(sb + 16));
+  o[0] = make_float2(bf_hi(l0), bf_hi(l1));
+  o[1] = make_float2(bf_lo(a0), bf_lo(a1)); o[2] = make_float2(bf_hi(a0), bf_hi(a1));
+  o[3] = make_float2(bf_lo(b0), bf_lo(b1)); o[4] = make_float2(bf_hi(b0), bf_hi(b1));
+  o[5] = make_float2(bf_lo(c0), bf_lo(c1)); o[6] = make_float2(bf_hi(c0), bf_hi(c1));
+  o[7] = make_float2(bf_lo(d0), bf_lo(d1)); o[8] = make_float2(bf_hi(d0), bf_hi(d1));
+  o[9] = make_float2(bf_lo(r0), bf_lo(r1));
+}
+
+// load the 10-pixel window row (x-1 .. x+8) of one staged plane
+__device__ __forceinline__ void dw_load_row(uint32_t saddr, float* o) {
+  uint32_t l, r, a, b, c, d;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(l) : "r"(saddr - 4));
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(saddr));
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(r) : "r"(saddr + 16));
+  o[0] = bf_hi(l);
+  o[1] = bf_lo(a); o[2] = bf_hi(a); o[3] = bf_lo(b); o[4] = bf_hi(b);
+  o[5] = bf_lo(c); o[6] = bf_hi(c); o[7] = bf_lo(d); o[8] = bf_hi(d);
+  o[9] = bf_lo(r);
+}
+
+template <bool GATE>
+__global__ void __launch_bounds__(128)
+dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) {
+  using namespace tc;
+  constexpr int NIN = GATE ? 2 : 1;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
+  __shared__ uint64_t bar_full[4];
+  const int tid = threadIdx.x;
+  const int nthreads = P.nxg * P.nstrips;
+  const uint32_t pitch = (uint32_t)(P.TW + 2 * DW_XP) * 2u;            // bytes per staged row
+  const uint32_t plane_bytes = ((uint32_t)(P.TH + 2) * pitch + 127u) & ~127u;
+  const uint32_t stage_bytes = plane_bytes * NIN;
+
+  if (tid == 0) {
+    for (int i = 0; i < P.S; ++i) mbar_init(&bar_full[i], 1);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmX);
+  }
+  __syncthreads();
+
+  const int tiles = P.tiles_x * P.tiles_y;
+  auto issue = [&](uint32_t item, int stage) {   // thread 0
+    const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
+    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
+    mbar_arrive_expect_tx(&bar_full[stage], (uint32_t)(P.TH + 2) * pitch * NIN);
+#pragma unroll
+    for (int k = 0; k < NIN; ++k)
+      tma_load_4d(smem + (size_t)stage * stage_bytes + (size_t)k * plane_bytes, &tmX, &bar_full[stage], x0 - DW_XP,
+                  y0 - 1, c + k * P.Cout, b);
+  };
+
+  const uint32_t first = blockIdx.x, step = gridDim.x;
+  if (tid == 0)
+    for (int s = 0; s < P.S; ++s)
+      if (first + s * step < (uint32_t)P.nitems) issue(first + s * step, s);
+
+  const int xg = tid % P.nxg, strip = tid / P.nxg;
+  const int64_t HWp = (int64_t)P.H * P.W;
+  uint32_t it = 0;
+  for (uint32_t item = first; item < (uint32_t)P.nitems; item += step, ++it) {
+    const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
+    const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
+    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
+
+    if (tid < nthreads) {
+      const int gx = x0 + xg * 8;
+      bf16* orow = P.y + (int64_t)b * P.y_bs + (int64_t)c * HWp + (int64_t)(y0 + strip * DW_RS) * P.W + gx;
+      const bool xok = gx < P.W;
+      const int yrem = P.H - (y0 + strip * DW_RS);
+      // staged row r <-> image row y0-1+r ; staged col 8+i <-> image col x0+i
+      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * DW_RS) * pitch +
+                            (uint32_t)(DW_XP + xg * 8) * 2u;
+      if (GATE) {
+        float2 wk[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) wk[i] = make_float2(__ldg(P.w + c * 9 + i), __ldg(P.w + (c + P.Cout) * 9 + i));
+        const float2 bs = P.bias ? make_float2(__ldg(P.bias + c), __ldg(P.bias + c + P.Cout)) : make_float2(0.f, 0.f);
+        mbar_wait(&bar_full[stage], ph);
+        float2 win[3][10];
+        dw_load_row2(base, base + plane_bytes, win[0]);
+        dw_load_row2(base + pitch, base + plane_bytes + pitch, win[1]);
+#pragma unroll
+        for (int j = 0; j < DW_RS; ++j) {
+          const uint32_t ra = base + (uint32_t)(j + 2) * pitch;
+          dw_load_row2(ra, ra + plane_bytes, win[(j + 2) % 3]);
+          uint32_t pk[4];
+#pragma unroll
+          for (int i = 0; i < 8; i += 2) {
+            float2 a0 = bs, a1 = bs;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int s2 = 0; s2 < 3; ++s2) {
+                a0 = ffma2(wk[r * 3 + s2], win[(j + r) % 3][i + s2], a0);
+                a1 = ffma2(wk[r * 3 + s2], win[(j + r) % 3][i + 1 + s2], a1);
+              }
+            __nv_bfloat162 h = __floats2bfloat162_rn(gelu_fast(a0.x) * a0.y, gelu_fast(a1.x) * a1.y);
+            pk[i >> 1] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          if (xok && j < yrem) *reinterpret_cast<uint4*>(orow + (int64_t)j * P.W) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+      } else {
+        float wk[9];
+#pragma unroll
+        for (int i = 0; i < 9; ++i) wk[i] = __ldg(P.w + c * 9 + i);
+        const float bs = P.bias ? __ldg(P.bias + c) : 0.f;
+        mbar_wait(&bar_full[stage], ph);
+        float win[3][10];
+        dw_load_row(base, win[0]);
+        dw_load_row(base + pitch, win[1]);
+#pragma unroll
+        for (int j = 0; j < DW_RS; ++j) {
+          dw_load_row(base + (uint32_t)(j + 2) * pitch, win[(j + 2) % 3]);
+          float o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            float a = bs;
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int s2 = 0; s2 < 3; ++s2) a = fmaf(wk[r * 3 + s2], win[(j + r) % 3][i + s2], a);
+            o[i] = a;
+          }
+          uint32_t pk[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(o[2 * i], o[2 * i + 1]);
+            pk[i] = *reinterpret_cast<uint32_t*>(&h);
+          }
+          if (xok && j < yrem) *reinterpret_cast<uint4*>(orow + (int64_t)j * P.W) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+      }
+    }
+    __syncthreads();   // every thread is done reading this stage
+    if (tid == 0) {
+      const uint32_t nxt = item + (uint32_t)P.S * step;
+      if (nxt < (uint32_t)P.nitems) {
+        fence_proxy_async();
+        issue(nxt, stage);
+      }
+    }
+  }
+}
+
+bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, const void* x, const void* y) {
+  return dtype == B200IR_BF16 && W % 8 == 0 && W >= 64 && H >= 8 && x_bs % 8 == 0 && y_bs % 8 == 0 &&
+         ((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0;
+}
+
+template <bool GATE>
+int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs, int B,
+                      int Cout, int H, int W, cudaStream_t st) {
+  DwTmaParams P;
+  P.y = (bf16*)y; P.y_bs = y_bs; P.w = w; P.bias = bias; P.Cout = Cout; P.H = H; P.W = W;
+  P.TW = W >= 128 ? 128 : 64;
+  P.nxg = P.TW / 8;
+  P.nstrips = 128 / P.nxg;                       // 8 (TW=128) or 16 (TW=64)
+  const int maxstrips = (H + DW_RS - 1) / DW_RS;
+  if (P.nstrips > maxstrips) P.nstrips = maxstrips;
+  P.TH = P.nstrips * DW_RS;
+  P.tiles_x = (W + P.TW - 1) / P.TW;
+  P.tiles_y = (H + P.TH - 1) / P.TH;
+  const int64_t nitems64 = (int64_t)B * Cout * P.tiles_x * P.tiles_y;
+  if (nitems64 >= (1ll << 30)) {
+    set_error("dwconv_tma: too many work items");
+    return B200IR_E_UNSUPPORTED;
+  }
+  P.nitems = (int)nitems64;
+  const int Ctot = GATE ? 2 * Cout : Cout;
+  CUtensorMap tm;
+  const uint64_t dims[4] = {(uint64_t)W, (uint64_t)H, (uint64_t)Ctot, (uint64_t)B};
+  const uint64_t str[4] = {2, (uint64_t)W * 2, (uint64_t)H * W * 2, (uint64_t)x_bs * 2};
+  const uint32_t box[4] = {(uint32_t)(P.TW + 2 * DW_XP), (uint32_t)(P.TH + 2), 1, 1};
+  int rc = make_tmap_bf16(&tm, x, 4, dims, str, box, false);
+  if (rc) return rc;
+  const size_t pitch = (size_t)(P.TW + 2 * DW_XP) * 2;
+  const size_t plane = ((size_t)(P.TH + 2) * pitch + 127) & ~(size_t)127;
+  const size_t stage = plane * (GATE ? 2 : 1);
+  P.S = GATE ? 2 : 3;
+  const size_t smem = stage * P.S + 256;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(dwconv_tma_kernel<GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  });
+  int ctas_per_sm = (int)((220 * 1024) / (smem + 1024));
+  if (ctas_per_sm > 8) ctas_per_sm = 8;
+  if (ctas_per_sm < 1) ctas_per_sm = 1;
+  int64_t grid = 148ll * ctas_per_sm;
+  if (grid > P.nitems) grid = P.nitems;
+  dwconv_tma_kernel<GATE><<<(unsigned)grid, 128, smem, st>>>(tm, P);
+  return check_launch(GATE ? "dwconv3x3_gelu_gate_tma" : "dwconv3x3_tma");
+}
+
+template int dwconv_tma_launch<false>(const void*, int64_t, const float*, const float*, void*, int64_t, int, int, int,
+                                      int, cudaStream_t);
+template int dwconv_tma_launch<true>(const void*, int64_t, const float*, const float*, void*, int64_t, int, int, int,
+                                     int, cudaStream_t);
+
+}  // namespace b200ir
