@@ -14,7 +14,7 @@ LN_NONE, LN_WITHBIAS, LN_BIASFREE = 0, 1, 2
 SHUFFLE_NONE, UNSHUFFLE2, SHUFFLE2 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
 
-_vp, _i64, _i, _sz = C.c_void_p, C.c_int64, C.c_int, C.c_size_t
+_vp, _i64, _i, _sz, _f = C.c_void_p, C.c_int64, C.c_int, C.c_size_t, C.c_float
 
 # name -> argtypes; every symbol of include/b200ir.h must be listed here (tests/test_abi.py checks)
 SIGNATURES = {
@@ -36,6 +36,19 @@ SIGNATURES = {
     "b200ir_pack_conv3x3": [_vp, _vp, _i, _i, _vp, _vp, _vp],
     "b200ir_conv3x3_tc_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_gemm_tc_fwd": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _vp],
+    "b200ir_ln_fwd": [_vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_ln_bwd_nparts": [_i, _i64],
+    "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i, _i, _i, _i64, _vp],
+    "b200ir_reduce_partials": [_vp, _vp, _i, _i64, _i64, _vp],
+    "b200ir_conv_wgrad_nsplit": [_i, _i, _i, _i, _i64, _i],
+    "b200ir_conv_wgrad": [_vp, _i64, _i, _vp, _i64, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_wgrad": [_vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_gelu_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _vp],
+    "b200ir_mdta_bwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
+    "b200ir_l1_loss_bwd": [_vp, _i, _vp, _i, _i64, _vp, _vp, _i, _vp],
+    "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _f, _vp],
 }
 
 

@@ -1,9 +1,11 @@
 """Differentiable wrappers around ``ops`` (one ``torch.autograd.Function`` per fused kernel).
 
 With autograd off (inference, the headline path) these call the forward kernels directly and may
-write into caller-provided ``out`` views.  With autograd on, each op records what its hand-written
-backward needs (see ``backward.py`` as it lands); until an op's backward exists it raises instead of
-silently falling back to PyTorch.
+write into caller-provided ``out`` views.  With autograd on, each op goes through a
+``torch.autograd.Function`` whose backward launches the hand-written kernels of ``csrc/backward.cu``
+(reductions, LayerNorm / gate / softmax backward) and re-uses the forward GEMM / conv kernels with
+transposed or flipped weights for the input gradients.  torch's autograd engine only sequences the
+calls and sums gradients where a tensor fans out; there is no PyTorch fallback for any op.
 """
 from __future__ import annotations
 
@@ -15,12 +17,6 @@ from . import ops
 
 def _needs_grad(*ts):
     return torch.is_grad_enabled() and any(t is not None and t.requires_grad for t in ts)
-
-
-def _no_backward(name):
-    raise NotImplementedError(
-        f"b200ir: backward of {name} is not implemented yet; run under torch.no_grad() "
-        f"(no PyTorch fallback is provided by design)")
 
 
 def _p(t):
@@ -55,7 +51,11 @@ USE_TC = True  # bf16 activations -> tcgen05 GEMMs (set False to force the CUDA-
 
 def ln_conv1x1(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None, cache=None, key=None):
     if _needs_grad(x, w, bias, ln_w, ln_b, res):
-        _no_backward("ln_conv1x1")
+        return _LnConv1x1.apply(x, w, bias, ln_w, ln_b, res, ln_type, out_dtype, cache, key)
+    return _ln_conv1x1_fwd(x, w, bias, ln_type, ln_w, ln_b, res, out, out_dtype, cache, key)
+
+
+def _ln_conv1x1_fwd(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None, cache=None, key=None):
     cout = w.shape[0]
     if USE_TC and ops.gemm_tc_usable(x, cout):
         packed = packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b)
@@ -65,29 +65,45 @@ def ln_conv1x1(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=None, c
 
 def dwconv3x3(x, w, bias):
     if _needs_grad(x, w, bias):
-        _no_backward("dwconv3x3")
+        return _DwConv.apply(x, w, bias)
     return ops.dwconv3x3(x, _p(w), _p(bias))
 
 
 def dwconv3x3_gelu_gate(x, w, bias):
     if _needs_grad(x, w, bias):
-        _no_backward("dwconv3x3_gelu_gate")
+        return _DwGate.apply(x, w, bias)
     return ops.dwconv3x3_gelu_gate(x, _p(w), _p(bias))
 
 
 def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
     """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147)."""
     if _needs_grad(qkv, temperature, w_out, b_out, res):
-        _no_backward("mdta_core")
+        return _MdtaCore.apply(qkv, temperature, w_out, b_out, res, heads)
+    return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out)[0]
+
+
+def _per_sample_gemm(x, m, bias, res, out=None):
+    """y = res + bias + m[b] . x[b] with a per-sample fp32 weight m [B,Cout,Cin] (tcgen05 when bf16)."""
+    cout = m.shape[1]
+    if USE_TC and ops.gemm_tc_usable(x, cout):
+        wp, st = ops.pack_conv1x1(m, bias, per_sample=True)
+        return ops.gemm_tc(x, (wp, st), cout, L.LN_NONE, res, out=out)
+    return ops.ln_conv1x1(x, m, bias, L.LN_NONE, None, None, res, out=out, per_sample_w=True)
+
+
+def _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out=None, want_saved=False):
     B, C3, H, W = qkv.shape
     C = C3 // 3
     partials = ops.mdta_gram(qkv, heads)
     v = qkv[:, 2 * C:]
     if USE_TC and ops.gemm_tc_usable(v, C):
-        mp = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), packed=True)
-        return ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device)), C, L.LN_NONE, res, out=out)
-    m = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C))
-    return ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
+        mp, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), packed=True,
+                                         want_attn=True)
+        y = ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device)), C, L.LN_NONE, res, out=out)
+    else:
+        m, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), want_attn=True)
+        y = ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
+    return y, partials, attn
 
 
 _ST_CACHE = {}
@@ -109,7 +125,11 @@ def _bias_st(bias, C, nrows, device):
 
 def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=None):
     if _needs_grad(x, w, bias, res):
-        _no_backward("conv3x3")
+        return _Conv3x3.apply(x, w, bias, res, shuffle, out_dtype, cache, key)
+    return _conv3x3_fwd(x, w, bias, res, shuffle, out, out_dtype, cache, key)
+
+
+def _conv3x3_fwd(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=None):
     cout = w.shape[0]
     if USE_TC and res is None and ops.conv3x3_tc_usable(x, cout):
         sig = _sig(w, bias)
@@ -120,3 +140,173 @@ def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=
                 cache[key] = ent
         return ops.conv3x3_tc(x, ent[1], cout, shuffle, out=out, out_dtype=out_dtype)
     return ops.conv3x3(x, _p(w), _p(bias), res, shuffle, out=out, out_dtype=out_dtype)
+
+
+# ---------------------------------------------------------------------------------------------------
+# autograd.Functions: forward = the kernels above, backward = csrc/backward.cu + forward kernels re-used
+# ---------------------------------------------------------------------------------------------------
+def _cg(g):
+    """Incoming gradient as an NCHW view our kernels accept (autograd may hand over expanded / permuted views)."""
+    s = g.stride()
+    b, c, h, w = g.shape
+    ok = (s[3] == 1 or w == 1) and (s[2] == w or h == 1) and (s[1] == h * w or c == 1)
+    return g if ok else g.contiguous()
+
+
+class _LnConv1x1(torch.autograd.Function):
+    """y = res + bias + W.LN(x)  (Restormer.py:37-39,54-57 + the 1x1 nn.Conv2d + :147-148)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, ln_w, ln_b, res, ln_type, out_dtype, cache, key):
+        y = _ln_conv1x1_fwd(x, w, bias, ln_type, ln_w, ln_b, res, None, out_dtype, cache, key)
+        ctx.save_for_backward(x, w, ln_w, ln_b)
+        ctx.ln_type, ctx.has_bias, ctx.has_res = ln_type, bias is not None, res is not None
+        ctx.cache, ctx.key = cache, key
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, ln_w, ln_b = ctx.saved_tensors
+        dy = _cg(dy)
+        cout, cin = w.shape[0], w.shape[1]
+        need = ctx.needs_input_grad
+        xn = ops.ln_fwd(x, ctx.ln_type, _p(ln_w), _p(ln_b)) if ctx.ln_type != L.LN_NONE else x
+        dw, db = ops.conv_wgrad(dy, xn, 1, want_bias=ctx.has_bias)
+        del xn
+        dx = dlw = dlb = None
+        if need[0] or ctx.ln_type != L.LN_NONE:
+            wt = _p(w).reshape(cout, cin).t().contiguous()
+            if USE_TC and ops.gemm_tc_usable(dy, cin) and x.dtype == torch.bfloat16:
+                dn = ops.gemm_tc(dy, ops.pack_conv1x1(wt), cin, L.LN_NONE, None, out_dtype=x.dtype)
+            else:
+                dn = ops.ln_conv1x1(dy, wt, None, L.LN_NONE, None, None, None, out_dtype=x.dtype)
+            if ctx.ln_type != L.LN_NONE:
+                dx, dlw, dlb = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w))
+                if ctx.ln_type != L.LN_WITHBIAS:
+                    dlb = None
+            else:
+                dx = dn
+        dres = dy if ctx.has_res else None
+        return (dx, dw.view(w.shape).to(w.dtype), db, dlw, dlb, dres, None, None, None, None)
+
+
+def _flip_dw(w):
+    return _p(w).flip(2, 3).contiguous()
+
+
+class _DwConv(torch.autograd.Function):
+    """Depthwise 3x3 (Restormer.py:106,114)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        return ops.dwconv3x3(x, _p(w), _p(bias))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = _cg(dy)
+        dx = ops.dwconv3x3(dy, _flip_dw(w), None) if ctx.needs_input_grad[0] else None
+        dw, db = ops.dwconv3x3_wgrad(dy, x, want_bias=ctx.has_bias)
+        return dx, dw.to(w.dtype), db
+
+
+class _DwGate(torch.autograd.Function):
+    """dwconv + chunk + gelu(x1)*x2 (Restormer.py:84,90-91); the conv output is recomputed in backward."""
+
+    @staticmethod
+    def forward(ctx, t, w, bias):
+        ctx.save_for_backward(t, w, bias)
+        return ops.dwconv3x3_gelu_gate(t, _p(w), _p(bias))
+
+    @staticmethod
+    def backward(ctx, dg):
+        t, w, bias = ctx.saved_tensors
+        dg = _cg(dg)
+        da = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg)
+        dt = ops.dwconv3x3(da, _flip_dw(w), None) if ctx.needs_input_grad[0] else None
+        dw, db = ops.dwconv3x3_wgrad(da, t, want_bias=bias is not None)
+        return dt, dw.to(w.dtype), db
+
+
+class _MdtaCore(torch.autograd.Function):
+    """F.normalize + q.k^T*temperature + softmax + attn.v + project_out + residual (Restormer.py:117-131,147)."""
+
+    @staticmethod
+    def forward(ctx, qkv, temperature, w_out, b_out, res, heads):
+        y, partials, attn = _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res)
+        ctx.save_for_backward(qkv, temperature, w_out, partials, attn)
+        ctx.has_bias, ctx.has_res, ctx.heads = b_out is not None, res is not None, heads
+        return y
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, temperature, w_out, partials, attn = ctx.saved_tensors
+        dout = _cg(dout)
+        B, C3, H, W = qkv.shape
+        C = C3 // 3
+        v = qkv[:, 2 * C:]
+        dM, db = ops.conv_wgrad(dout, v, 1, per_sample=True, want_bias=ctx.has_bias)
+        mt, mqk, dw, dtemp = ops.mdta_bwd(partials, attn, _p(temperature).reshape(-1), _p(w_out).reshape(C, C),
+                                          dM.contiguous())
+        dqkv = torch.empty_like(qkv)
+        _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
+        _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])
+        return (dqkv, dtemp.view(temperature.shape).to(temperature.dtype), dw.view(w_out.shape).to(w_out.dtype), db,
+                dout if ctx.has_res else None, None)
+
+
+class _Conv3x3(torch.autograd.Function):
+    """Dense 3x3 conv (+bias, +res) with PixelUnshuffle/PixelShuffle folded (Restormer.py:162-189,281)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, res, shuffle, out_dtype, cache, key):
+        y = _conv3x3_fwd(x, w, bias, res, shuffle, None, out_dtype, cache, key)
+        ctx.save_for_backward(x, w)
+        ctx.has_bias, ctx.has_res, ctx.shuffle = bias is not None, res is not None, shuffle
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = _cg(dy)
+        need = ctx.needs_input_grad
+        if ctx.shuffle == L.UNSHUFFLE2:      # y = unshuffle(conv(x)) -> dconv = shuffle(dy)
+            dc = ops.pixel_shuffle(dy, L.SHUFFLE2)
+        elif ctx.shuffle == L.SHUFFLE2:
+            dc = ops.pixel_shuffle(dy, L.UNSHUFFLE2)
+        else:
+            dc = dy
+        dw, db = ops.conv_wgrad(dc, x, 9, want_bias=ctx.has_bias)
+        dx = None
+        if need[0]:
+            cin = w.shape[1]
+            wt = _p(w).transpose(0, 1).flip(2, 3).contiguous()
+            if USE_TC and ops.conv3x3_tc_usable(dc, cin) and x.dtype == torch.bfloat16:
+                dx = ops.conv3x3_tc(dc, ops.pack_conv3x3(wt, None), cin, L.SHUFFLE_NONE, out_dtype=x.dtype)
+            else:
+                dx = ops.conv3x3(dc, wt, None, None, L.SHUFFLE_NONE, out_dtype=x.dtype)
+        dres = dy if (ctx.has_res and need[3]) else None
+        return dx, dw.view(w.shape).to(w.dtype), db, dres, None, None, None, None
+
+
+class _L1Loss(torch.autograd.Function):
+    """nn.L1Loss() (mean reduction), MoCE-IR-main/src/train.py:51,65."""
+
+    @staticmethod
+    def forward(ctx, pred, target):
+        pred, target = pred.contiguous(), target.contiguous()
+        ctx.save_for_backward(pred, target)
+        return ops.l1_loss_fwd(pred, target)
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, target = ctx.saved_tensors
+        return ops.l1_loss_bwd(pred, target, g.contiguous().float()), None
+
+
+def l1_loss(pred, target):
+    if _needs_grad(pred):
+        return _L1Loss.apply(pred, target)
+    return ops.l1_loss_fwd(pred.contiguous(), target.contiguous())

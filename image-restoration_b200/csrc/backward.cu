@@ -1,0 +1,689 @@
+// backward.cu — backward (training) kernels of the Restormer block path, dtype-generic CUDA-core versions.
+// These are the gradients of the forward kernels in gemm_simt.cu / dwconv.cu / mdta.cu / conv3x3.cu, i.e. of
+// Restormer.py:37-39,54-57 (LayerNorm), :89-92 (GDFN), :114-131 (MDTA), :162-189 (3x3 convs + pixel shuffles), as the
+// reference gets them from torch autograd (MoCE-IR-main/src/train.py:59-72: loss.backward inside Lightning).
+// Input-gradient GEMMs / depthwise convs reuse the forward kernels with transposed / flipped weights (host side);
+// what lives here are the reductions over pixels (weight / bias / LayerNorm-parameter gradients), the LayerNorm and
+// GELU-gate input gradients, and the small per-(sample, head) softmax / normalisation backward of MDTA.
+// Every reduction is split into fixed-order partials + b200ir_reduce_partials: bitwise deterministic.
+#include <math.h>
+
+#include "common.cuh"
+
+namespace b200ir {
+
+// =====================================================================================================
+// LayerNorm materialised: y = LN(x)   (operand of the weight-gradient GEMM of the fused LN+1x1 conv)
+// =====================================================================================================
+__global__ void __launch_bounds__(128)
+ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, const float* __restrict__ lw,
+              const float* __restrict__ lb, void* __restrict__ y, int64_t y_bs, int y_dt, int C, int64_t HW, int tps,
+              int64_t ntiles) {
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int b = (int)(t / tps);
+    const int64_t p = (t % tps) * 128 + threadIdx.x;
+    if (p >= HW) continue;
+    const int64_t xo = (int64_t)b * x_bs + p, yo = (int64_t)b * y_bs + p;
+    float s = 0.f;
+    for (int c = 0; c < C; ++c) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
+    const float mu = s / (float)C;
+    float v = 0.f;
+    for (int c = 0; c < C; ++c) {
+      const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
+      v += d * d;
+    }
+    const float rstd = 1.0f / sqrtf(v / (float)C + 1e-5f);
+    for (int c = 0; c < C; ++c) {
+      const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
+      float n;
+      if (ln_type == B200IR_LN_WITHBIAS) n = (xv - mu) * rstd * lw[c] + lb[c];   // Restormer.py:57
+      else n = xv * rstd * lw[c];                                                // Restormer.py:39
+      st_any(y, y_dt, yo + (int64_t)c * HW, n);
+    }
+  }
+}
+
+// =====================================================================================================
+// LayerNorm backward.  g = dL/dLN(x), h = g*gamma, xh = (x-mu)*rstd:
+//   WithBias: dx = rstd*(h - mean(h) - xh*mean(h*xh)),  dgamma = sum_p g*xh,  dbeta = sum_p g
+//   BiasFree: dx = rstd*h - rstd^3*(x-mu)*sum_c(h*x)/C,  dgamma = sum_p g*x*rstd
+// dx (+)= res (gradient arriving through the residual path of TransformerBlock, Restormer.py:147-148).
+// parts: fp32 [gridDim.x][2][C] partial dgamma / dbeta (fixed order inside a CTA: per-warp accumulators).
+// =====================================================================================================
+__global__ void __launch_bounds__(128)
+ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __restrict__ g, int64_t g_bs, int g_dt,
+              int ln_type, const float* __restrict__ lw, const void* __restrict__ res, int64_t res_bs, int res_dt,
+              void* __restrict__ dx, int64_t dx_bs, int dx_dt, float* __restrict__ parts, int C, int64_t HW, int tps,
+              int64_t ntiles) {
+  extern __shared__ float acc[];  // [4 warps][2][C]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 8 * C; i += 128) acc[i] = 0.f;
+  __syncthreads();
+  float* wacc = acc + (size_t)warp * 2 * C;
+  const float invC = 1.0f / (float)C;
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int b = (int)(t / tps);
+    const int64_t p = (t % tps) * 128 + threadIdx.x;
+    const bool valid = p < HW;
+    const int64_t xo = (int64_t)b * x_bs + p, go = (int64_t)b * g_bs + p;
+    float mu = 0.f, rstd = 0.f;
+    if (valid) {
+      float s = 0.f;
+      for (int c = 0; c < C; ++c) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
+      mu = s * invC;
+      float v = 0.f;
+      for (int c = 0; c < C; ++c) {
+        const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
+        v += d * d;
+      }
+      rstd = 1.0f / sqrtf(v * invC + 1e-5f);
+    }
+    float s1 = 0.f, s2 = 0.f;
+    for (int c = 0; c < C; ++c) {
+      float xv = 0.f, gv = 0.f;
+      if (valid) {
+        xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
+        gv = ld_any(g, g_dt, go + (int64_t)c * HW);
+      }
+      const float h = gv * lw[c];
+      float dgam, dbet = gv;
+      if (ln_type == B200IR_LN_WITHBIAS) {
+        const float xh = (xv - mu) * rstd;
+        s1 += h;
+        s2 += h * xh;
+        dgam = gv * xh;
+      } else {
+        s2 += h * xv;
+        dgam = gv * xv * rstd;
+      }
+      dgam = warp_sum(dgam);
+      dbet = warp_sum(dbet);
+      if (lane == 0) {
+        wacc[c] += dgam;
+        wacc[C + c] += dbet;
+      }
+    }
+    if (valid) {
+      const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p;
+      for (int c = 0; c < C; ++c) {
+        const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
+        const float h = ld_any(g, g_dt, go + (int64_t)c * HW) * lw[c];
+        float d;
+        if (ln_type == B200IR_LN_WITHBIAS) {
+          const float xh = (xv - mu) * rstd;
+          d = rstd * (h - s1 * invC - xh * s2 * invC);
+        } else {
+          d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2 * invC;
+        }
+        if (res) d += ld_any(res, res_dt, ro + (int64_t)c * HW);
+        st_any(dx, dx_dt, dxo + (int64_t)c * HW, d);
+      }
+    }
+  }
+  __syncthreads();
+  float* out = parts + (size_t)blockIdx.x * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += 128) out[i] = acc[i] + acc[2 * C + i] + acc[4 * C + i] + acc[6 * C + i];
+}
+
+// out[k] = sum_{i<n} in[i*stride + k]   (fixed order)
+__global__ void reduce_partials_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int64_t K,
+                                       int64_t stride) {
+  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < K; k += (int64_t)gridDim.x * blockDim.x) {
+    float s = 0.f;
+    for (int i = 0; i < n; ++i) s += in[(size_t)i * stride + k];
+    out[k] = s;
+  }
+}
+
+// =====================================================================================================
+// Weight gradient of a 1x1 conv (taps=1) or a dense 3x3 conv (taps=9): reduction over pixels
+//   dW[g][o][c*taps+t] = sum_{b in g} sum_p dy[b,o,p] * x[b,c,p+shift(t)],   db[g][o] = sum dy[b,o,p]
+// g = sample (per_sample, MDTA dM_b = dout_b . v_b^T) or the whole batch.  Split-K over 32-pixel chunks.
+// CUDA-core fp32 FMA version (exact path); grid (n-tiles, m-tiles, G*nsplit).
+// =====================================================================================================
+constexpr int WM = 64, WN = 64, WK = 32;
+
+__global__ void __launch_bounds__(256)
+wgrad_simt_kernel(const void* __restrict__ A, int64_t a_bs, int a_dt, const void* __restrict__ X, int64_t x_bs, int x_dt,
+                  float* __restrict__ pw, float* __restrict__ pb, int M, int Cin, int taps, int H, int W,
+                  int nsplit, int chunks_per_sample, int chunks_per_split, int chunks_total, int per_sample) {
+  __shared__ __align__(16) float As[WK][WM + 4];
+  __shared__ __align__(16) float Bs[WK][WN + 4];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int n0 = blockIdx.x * WN, o0 = blockIdx.y * WM;
+  const int g = blockIdx.z / nsplit, split = blockIdx.z % nsplit;
+  const int N = Cin * taps;
+  const int64_t HW = (int64_t)H * W;
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  float bsum = 0.f;
+
+  const int cbeg = split * chunks_per_split;
+  const int cend = min(chunks_total, cbeg + chunks_per_split);
+  for (int ch = cbeg; ch < cend; ++ch) {
+    const int b = per_sample ? g : ch / chunks_per_sample;
+    const int64_t p0 = (int64_t)(ch % chunks_per_sample) * WK;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int e = tid + i * 256;
+      const int r = e >> 5, cpx = e & 31;
+      const int64_t p = p0 + cpx;
+      float av = 0.f, xv = 0.f;
+      if (p < HW) {
+        if (o0 + r < M) av = ld_any(A, a_dt, (int64_t)b * a_bs + (int64_t)(o0 + r) * HW + p);
+        const int n = n0 + r;
+        if (n < N) {
+          if (taps == 1) {
+            xv = ld_any(X, x_dt, (int64_t)b * x_bs + (int64_t)n * HW + p);
+          } else {
+            const int c = n / 9, t = n - c * 9;
+            const int yy = (int)(p / W) + t / 3 - 1, xx = (int)(p % W) + t % 3 - 1;
+            if (yy >= 0 && yy < H && xx >= 0 && xx < W)
+              xv = ld_any(X, x_dt, (int64_t)b * x_bs + (int64_t)c * HW + (int64_t)yy * W + xx);
+          }
+        }
+      }
+      As[cpx][r] = av;
+      Bs[cpx][r] = xv;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int k = 0; k < WK; ++k) {
+      const float4 a = *reinterpret_cast<const float4*>(&As[k][ty * 4]);
+      const float4 bb = *reinterpret_cast<const float4*>(&Bs[k][tx * 4]);
+      const float av[4] = {a.x, a.y, a.z, a.w};
+      const float bv[4] = {bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+    }
+    if (pb && blockIdx.x == 0 && tid < WM) {
+#pragma unroll 8
+      for (int k = 0; k < WK; ++k) bsum += As[k][tid];
+    }
+    __syncthreads();
+  }
+  const size_t slot = (size_t)split * (gridDim.z / nsplit) + g;  // partials laid out [split][g][M][N]
+  float* out = pw + slot * M * N;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int o = o0 + ty * 4 + i;
+    if (o >= M) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n < N) out[(size_t)o * N + n] = acc[i][j];
+    }
+  }
+  if (pb && blockIdx.x == 0 && tid < WM && o0 + tid < M) pb[slot * M + o0 + tid] = bsum;
+}
+
+// =====================================================================================================
+// Depthwise 3x3 weight / bias gradient: parts[b][c][t] = sum_p dy[b,c,p]*x[b,c,p+shift(t)] (t<9), [9] = sum dy.
+// grid (C, B); one CTA per plane.
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+dwconv_wgrad_kernel(const void* __restrict__ dy, int64_t dy_bs, const void* __restrict__ x, int64_t x_bs, int dt,
+                    float* __restrict__ parts, int C, int H, int W) {
+  const int c = blockIdx.x, b = blockIdx.y;
+  const int64_t HW = (int64_t)H * W;
+  const int64_t dyo = (int64_t)b * dy_bs + (int64_t)c * HW, xo = (int64_t)b * x_bs + (int64_t)c * HW;
+  float acc[10];
+#pragma unroll
+  for (int i = 0; i < 10; ++i) acc[i] = 0.f;
+  for (int64_t p = threadIdx.x; p < HW; p += 256) {
+    const float g = ld_any(dy, dt, dyo + p);
+    const int yy = (int)(p / W), xx = (int)(p % W);
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+      const int y2 = yy + t / 3 - 1, x2 = xx + t % 3 - 1;
+      if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) acc[t] = fmaf(g, ld_any(x, dt, xo + (int64_t)y2 * W + x2), acc[t]);
+    }
+    acc[9] += g;
+  }
+  __shared__ float red[8][10];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const float v = warp_sum(acc[i]);
+    if (lane == 0) red[warp][i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 10) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
+    parts[((size_t)b * C + c) * 10 + threadIdx.x] = s;
+  }
+}
+
+// =====================================================================================================
+// GDFN gate backward (recomputes the depthwise conv): a = dw(t)+bias, y[c] = gelu(a[c])*a[c+Hd]
+//   da[c] = dg[c]*a[c+Hd]*gelu'(a[c]),   da[c+Hd] = dg[c]*gelu(a[c])       (Restormer.py:90-91)
+// grid (ceil(HW/256), Hd, B)
+// =====================================================================================================
+__device__ __forceinline__ float dw3x3_at(const void* t, int dt, int64_t base, const float* w, int yy, int xx, int H,
+                                          int W) {
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    const int y2 = yy + k / 3 - 1, x2 = xx + k % 3 - 1;
+    if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) s = fmaf(w[k], ld_any(t, dt, base + (int64_t)y2 * W + x2), s);
+  }
+  return s;
+}
+
+__global__ void __launch_bounds__(256)
+gelu_gate_bwd_kernel(const void* __restrict__ t, int64_t t_bs, const float* __restrict__ w,
+                     const float* __restrict__ bias, const void* __restrict__ dg, int64_t dg_bs,
+                     void* __restrict__ da, int64_t da_bs, int dt, int Hd, int H, int W) {
+  const int c = blockIdx.y, b = blockIdx.z;
+  const int64_t HW = (int64_t)H * W;
+  const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (p >= HW) return;
+  const int yy = (int)(p / W), xx = (int)(p % W);
+  float w1[9], w2[9];
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    w1[k] = w[c * 9 + k];
+    w2[k] = w[(c + Hd) * 9 + k];
+  }
+  const float a1 = dw3x3_at(t, dt, (int64_t)b * t_bs + (int64_t)c * HW, w1, yy, xx, H, W) + (bias ? bias[c] : 0.f);
+  const float a2 =
+      dw3x3_at(t, dt, (int64_t)b * t_bs + (int64_t)(c + Hd) * HW, w2, yy, xx, H, W) + (bias ? bias[c + Hd] : 0.f);
+  const float g = ld_any(dg, dt, (int64_t)b * dg_bs + (int64_t)c * HW + p);
+  const float cdf = 0.5f * (1.0f + erff(a1 * 0.70710678118654752440f));
+  const float pdf = 0.39894228040143267794f * expf(-0.5f * a1 * a1);
+  st_any(da, dt, (int64_t)b * da_bs + (int64_t)c * HW + p, g * a2 * (cdf + a1 * pdf));
+  st_any(da, dt, (int64_t)b * da_bs + (int64_t)(c + Hd) * HW + p, g * a1 * cdf);
+}
+
+// =====================================================================================================
+// MDTA small backward, one CTA per (head, sample).  Inputs: Gram partials (forward), attn, temperature, W_out and
+// dM_b = dout_b . v_b^T  [B,C,C].  With G^ = G/(a b^T) (a_i = max(|q_i|,eps), b_j likewise), S = temp*G^,
+// attn = softmax(S), M_b = W_out . blockdiag(attn):
+//   dattn = W_out[:,h]^T . dM[:,h],  dW_out[:,h] (per sample) = dM[:,h] . attn^T
+//   dS = attn o (dattn - rowsum(dattn o attn)),  dtemp = sum dS o G^,  dG^ = temp*dS
+//   P = dG^/(a b^T),  r_i = sum_j dG^_ij G^_ij / a_i^2,  s_j = sum_i dG^_ij G^_ij / b_j^2
+//   dq = P.k - diag(r).q,  dk = P^T.q - diag(s).k      -> mqk[b] (2C x 2C) so that d[q;k] = mqk[b] . [q;k]
+//   mt[b] = M_b^T                                      -> dv = mt[b] . dout
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
+                const float* __restrict__ temperature, const float* __restrict__ w_out, const float* __restrict__ dM,
+                float* __restrict__ mt, float* __restrict__ mqk, float* __restrict__ dw_out_part,
+                float* __restrict__ dtemp_part, int C, int d) {
+  extern __shared__ float sm[];
+  const int D1 = d + 1;
+  float* at = sm;                        // attn  [d][d+1]
+  float* gh = at + (size_t)d * D1;       // G^    [d][d+1]
+  float* da = gh + (size_t)d * D1;       // dattn -> dG^ [d][d+1]
+  float* na = da + (size_t)d * D1;       // a [d]
+  float* nb = na + d;                    // b [d]
+  float* rs = nb + d;                    // rowsum / r [d]
+  float* cs = rs + d;                    // s [d]
+  __shared__ float red[8];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int h = blockIdx.x, b = blockIdx.y, heads = gridDim.x;
+  const size_t per = (size_t)d * d + 2 * d;
+  const float* base = partials + ((size_t)b * heads + h) * nslab * per;
+  const float* a_g = attn + ((size_t)b * heads + h) * d * d;
+  const float* dMb = dM + (size_t)b * C * C;
+  const float temp = temperature[h];
+
+  for (int j = tid; j < 2 * d; j += 256) {
+    float s = 0.f;
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + j];
+    na[j] = fmaxf(sqrtf(s), 1e-12f);  // na[d..2d) aliases nb
+  }
+  __syncthreads();
+  for (int e = tid; e < d * d; e += 256) {
+    const int i = e / d, j = e % d;
+    float s = 0.f;
+    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];
+    gh[i * D1 + j] = s / (na[i] * nb[j]);
+    at[i * D1 + j] = a_g[e];
+    // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
+    float acc = 0.f;
+    for (int o = 0; o < C; ++o) acc = fmaf(w_out[(size_t)o * C + h * d + i], dMb[(size_t)o * C + h * d + j], acc);
+    da[i * D1 + j] = acc;
+  }
+  __syncthreads();
+  // per-sample dW_out[o][hd+i] = sum_j dM[o][hd+j]*attn[i][j];  mt[b][hd+j][o] = sum_i W[o][hd+i]*attn[i][j]
+  for (int e = tid; e < C * d; e += 256) {
+    const int o = e / d, i = e % d;
+    float s1 = 0.f, s2 = 0.f;
+    for (int j = 0; j < d; ++j) {
+      s1 = fmaf(dMb[(size_t)o * C + h * d + j], at[i * D1 + j], s1);
+      s2 = fmaf(w_out[(size_t)o * C + h * d + j], at[j * D1 + i], s2);   // here "i" plays the role of column j
+    }
+    dw_out_part[((size_t)b * C + o) * C + h * d + i] = s1;
+    mt[((size_t)b * C + h * d + i) * C + o] = s2;
+  }
+  // row sums of dattn o attn
+  for (int i = warp; i < d; i += 8) {
+    float s = 0.f;
+    for (int j = lane; j < d; j += 32) s += da[i * D1 + j] * at[i * D1 + j];
+    s = warp_sum(s);
+    if (lane == 0) rs[i] = s;
+  }
+  __syncthreads();
+  float tsum = 0.f;
+  for (int e = tid; e < d * d; e += 256) {
+    const int i = e / d, j = e % d;
+    const float dS = at[i * D1 + j] * (da[i * D1 + j] - rs[i]);
+    tsum += dS * gh[i * D1 + j];
+    da[i * D1 + j] = temp * dS;  // dG^
+  }
+  tsum = warp_sum(tsum);
+  if (lane == 0) red[warp] = tsum;
+  __syncthreads();
+  if (tid == 0) {
+    float s = 0.f;
+    for (int w = 0; w < 8; ++w) s += red[w];
+    dtemp_part[(size_t)b * heads + h] = s;
+  }
+  // r_i, s_j
+  for (int i = warp; i < d; i += 8) {
+    float s = 0.f, s2 = 0.f;
+    for (int j = lane; j < d; j += 32) {
+      s += da[i * D1 + j] * gh[i * D1 + j];
+      s2 += da[j * D1 + i] * gh[j * D1 + i];
+    }
+    s = warp_sum(s);
+    s2 = warp_sum(s2);
+    if (lane == 0) {
+      rs[i] = s / (na[i] * na[i]);
+      cs[i] = s2 / (nb[i] * nb[i]);
+    }
+  }
+  __syncthreads();
+  // mqk rows of this head: [hd+i] (dq) and [C+hd+j] (dk), full 2C columns
+  const int C2 = 2 * C;
+  float* mq = mqk + (size_t)b * C2 * C2;
+  for (int e = tid; e < d * C2; e += 256) {
+    const int i = e / C2, col = e % C2;
+    float vq = 0.f, vk = 0.f;
+    if (col < C) {
+      const int jj = col - h * d;
+      if (jj == i) vq = -rs[i];                                              // dq_i <- -r_i q_i
+      if (jj >= 0 && jj < d) vk = da[jj * D1 + i] / (na[jj] * nb[i]);        // dk_i <- sum_jj P[jj][i] q_jj
+    } else {
+      const int jj = col - C - h * d;
+      if (jj >= 0 && jj < d) vq = da[i * D1 + jj] / (na[i] * nb[jj]);        // dq_i <- sum_jj P[i][jj] k_jj
+      if (jj == i) vk = -cs[i];                                              // dk_i <- -s_i k_i
+    }
+    mq[(size_t)(h * d + i) * C2 + col] = vq;
+    mq[(size_t)(C + h * d + i) * C2 + col] = vk;
+  }
+}
+
+// =====================================================================================================
+// PixelShuffle(2) / PixelUnshuffle(2) as a copy (gradients of Upsample / Downsample, Restormer.py:171-189).
+// x [B,C,H,W].  SHUFFLE2: y [B,C/4,2H,2W], y[c,2h+i,2w+j] = x[4c+2i+j,h,w].  UNSHUFFLE2: the inverse,
+// y [B,4C,H/2,W/2].  One thread per input element.
+// =====================================================================================================
+__global__ void pixel_shuffle_kernel(const void* __restrict__ x, int64_t x_bs, void* __restrict__ y, int64_t y_bs,
+                                     int dt, int C, int H, int W, int mode) {
+  const int b = blockIdx.y;
+  const int64_t HW = (int64_t)H * W, n = (int64_t)C * HW;
+  for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(e / HW);
+    const int64_t p = e % HW;
+    const int hh = (int)(p / W), ww = (int)(p % W);
+    int64_t off;
+    if (mode == B200IR_SHUFFLE2) {
+      const int oc = c >> 2, i = (c >> 1) & 1, j = c & 1;
+      off = (int64_t)oc * (HW * 4) + (int64_t)(2 * hh + i) * (2 * W) + (2 * ww + j);
+    } else {
+      const int oc = c * 4 + (hh & 1) * 2 + (ww & 1);
+      off = (int64_t)oc * (HW / 4) + (int64_t)(hh >> 1) * (W / 2) + (ww >> 1);
+    }
+    st_any(y, dt, (int64_t)b * y_bs + off, ld_any(x, dt, (int64_t)b * x_bs + e));
+  }
+}
+
+// =====================================================================================================
+// L1 loss (nn.L1Loss, MoCE-IR-main/src/train.py:51,65): parts[blk] = sum |pred-target| ; loss = sum(parts)/n.
+// Backward: grad = sign(pred-target) * gscale[0] / n.
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+l1_loss_fwd_kernel(const void* __restrict__ pred, int p_dt, const void* __restrict__ target, int t_dt, int64_t n,
+                   float* __restrict__ parts) {
+  float s = 0.f;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256)
+    s += fabsf(ld_any(pred, p_dt, i) - ld_any(target, t_dt, i));
+  __shared__ float red[8];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    parts[blockIdx.x] = t;
+  }
+}
+__global__ void l1_loss_finish_kernel(const float* __restrict__ parts, int nparts, float inv_n, float* __restrict__ loss) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    float s = 0.f;
+    for (int i = 0; i < nparts; ++i) s += parts[i];
+    loss[0] = s * inv_n;
+  }
+}
+__global__ void l1_loss_bwd_kernel(const void* __restrict__ pred, int p_dt, const void* __restrict__ target, int t_dt,
+                                   int64_t n, const float* __restrict__ gscale, float inv_n, void* __restrict__ grad,
+                                   int g_dt) {
+  const float gs = gscale[0] * inv_n;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float d = ld_any(pred, p_dt, i) - ld_any(target, t_dt, i);
+    st_any(grad, g_dt, i, d > 0.f ? gs : (d < 0.f ? -gs : 0.f));
+  }
+}
+
+// =====================================================================================================
+// AdamW (torch.optim.AdamW semantics, MoCE-IR-main/src/train.py:83: decoupled weight decay, bias-corrected
+// moments, eps added after the sqrt / sqrt(bias_correction2)); one launch per flat fp32 buffer.
+// =====================================================================================================
+__global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                             float* __restrict__ v, int64_t n, float lr, float beta1, float beta2, float eps, float wd,
+                             float bc1, float bc2_sqrt, float gscale) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gscale;
+    float pi = p[i];
+    pi *= 1.0f - lr * wd;
+    const float mi = m[i] + (1.0f - beta1) * (gi - m[i]);       // lerp, as torch's _single_tensor_adamw
+    const float vi = beta2 * v[i] + (1.0f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = pi - (lr / bc1) * (mi / denom);
+  }
+}
+
+static inline int grid_1d(int64_t n, int threads, int cap) {
+  int64_t g = (n + threads - 1) / threads;
+  if (g > cap) g = cap;
+  if (g < 1) g = 1;
+  return (int)g;
+}
+
+}  // namespace b200ir
+
+using namespace b200ir;
+
+extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int ln_type, const float* ln_w,
+                             const float* ln_b, void* y, int64_t y_bstride, int y_dtype, int B, int C, int64_t HW,
+                             b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && y && ln_w && B > 0 && C > 0 && HW > 0, "ln_fwd: bad args");
+  B200IR_CHECK_ARG(ln_type == B200IR_LN_WITHBIAS || ln_type == B200IR_LN_BIASFREE, "ln_fwd: bad ln_type %d", ln_type);
+  B200IR_CHECK_ARG(ln_type != B200IR_LN_WITHBIAS || ln_b, "ln_fwd: ln_b missing");
+  B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(y_dtype), "ln_fwd: bad dtype");
+  const int tps = (int)((HW + 127) / 128);
+  const int64_t ntiles = (int64_t)B * tps;
+  ln_fwd_kernel<<<grid_1d(ntiles, 1, 148 * 16), 128, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w,
+                                                                               ln_b, y, y_bstride, y_dtype, C, HW, tps,
+                                                                               ntiles);
+  return check_launch("ln_fwd");
+}
+
+extern "C" int b200ir_ln_bwd_nparts(int B, int64_t HW) {
+  if (B <= 0 || HW <= 0) return B200IR_E_BADARG;
+  const int64_t ntiles = (int64_t)B * ((HW + 127) / 128);
+  return grid_1d(ntiles, 1, 148 * 8);
+}
+
+extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride,
+                             int g_dtype, int ln_type, const float* ln_w, const void* res, int64_t res_bstride,
+                             int res_dtype, void* dx, int64_t dx_bstride, int dx_dtype, float* parts, int nparts,
+                             int B, int C, int64_t HW, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && g && dx && ln_w && parts && B > 0 && C > 0 && HW > 0, "ln_bwd: bad args");
+  B200IR_CHECK_ARG(ln_type == B200IR_LN_WITHBIAS || ln_type == B200IR_LN_BIASFREE, "ln_bwd: bad ln_type %d", ln_type);
+  B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(g_dtype) && dtype_ok(dx_dtype) && (!res || dtype_ok(res_dtype)),
+                   "ln_bwd: bad dtype");
+  B200IR_CHECK_ARG(nparts == b200ir_ln_bwd_nparts(B, HW), "ln_bwd: nparts=%d, expected %d", nparts,
+                   b200ir_ln_bwd_nparts(B, HW));
+  B200IR_UNSUPPORTED(C <= 1024, "ln_bwd: C=%d > 1024 unsupported", C);
+  const int tps = (int)((HW + 127) / 128);
+  const int64_t ntiles = (int64_t)B * tps;
+  ln_bwd_kernel<<<nparts, 128, (size_t)8 * C * sizeof(float), (cudaStream_t)stream>>>(
+      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride, dx_dtype,
+      parts, C, HW, tps, ntiles);
+  return check_launch("ln_bwd");
+}
+
+extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride,
+                                      b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(in && out && n > 0 && K > 0 && stride >= K, "reduce_partials: bad args");
+  reduce_partials_kernel<<<grid_1d(K, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
+  return check_launch("reduce_partials");
+}
+
+namespace b200ir {
+static void wgrad_split(int B, int M, int N, int64_t HW, int per_sample, int* nsplit, int* cps, int* cpsplit,
+                        int* ctotal) {
+  const int chunks_per_sample = (int)((HW + WK - 1) / WK);
+  const int total = per_sample ? chunks_per_sample : B * chunks_per_sample;
+  const int64_t tiles = (int64_t)((M + WM - 1) / WM) * ((N + WN - 1) / WN) * (per_sample ? B : 1);
+  int64_t want = (4 * 148 + tiles - 1) / tiles;
+  if (want > 64) want = 64;
+  if (want > total) want = total;
+  if (want < 1) want = 1;
+  const int per = (int)((total + want - 1) / want);
+  *nsplit = (total + per - 1) / per;
+  *cps = chunks_per_sample;
+  *cpsplit = per;
+  *ctotal = total;
+}
+}  // namespace b200ir
+
+extern "C" int b200ir_conv_wgrad_nsplit(int B, int Cout, int Cin, int taps, int64_t HW, int per_sample) {
+  if (B <= 0 || Cout <= 0 || Cin <= 0 || HW <= 0 || (taps != 1 && taps != 9)) return B200IR_E_BADARG;
+  int ns, a, b, c;
+  wgrad_split(B, Cout, Cin * taps, HW, per_sample, &ns, &a, &b, &c);
+  return ns;
+}
+
+extern "C" int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtype, const void* x, int64_t x_bstride,
+                                 int x_dtype, float* parts_w, float* parts_b, int nsplit, int B, int Cout, int Cin,
+                                 int H, int W, int taps, int per_sample, int impl, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(dy && x && parts_w && B > 0 && Cout > 0 && Cin > 0 && H > 0 && W > 0, "conv_wgrad: bad args");
+  B200IR_CHECK_ARG(taps == 1 || taps == 9, "conv_wgrad: taps must be 1 or 9");
+  B200IR_CHECK_ARG(dtype_ok(dy_dtype) && dtype_ok(x_dtype), "conv_wgrad: bad dtype");
+  int ns, cps, cpsplit, ctotal;
+  wgrad_split(B, Cout, Cin * taps, (int64_t)H * W, per_sample, &ns, &cps, &cpsplit, &ctotal);
+  B200IR_CHECK_ARG(ns == nsplit, "conv_wgrad: nsplit=%d, expected %d (b200ir_conv_wgrad_nsplit)", nsplit, ns);
+  const int G = per_sample ? B : 1;
+  B200IR_CHECK_ARG((int64_t)G * ns <= 65535, "conv_wgrad: grid too large");
+  dim3 grid((unsigned)((Cin * taps + WN - 1) / WN), (unsigned)((Cout + WM - 1) / WM), (unsigned)(G * ns));
+  wgrad_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dy, dy_bstride, dy_dtype, x, x_bstride, x_dtype, parts_w,
+                                                            parts_b, Cout, Cin, taps, H, W, ns, cps, cpsplit, ctotal,
+                                                            per_sample);
+  return check_launch("conv_wgrad_simt");
+}
+
+extern "C" int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
+                                      float* parts, int B, int C, int H, int W, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(dy && x && parts && B > 0 && C > 0 && H > 0 && W > 0 && B <= 65535, "dwconv3x3_wgrad: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_wgrad: bad dtype");
+  dwconv_wgrad_kernel<<<dim3((unsigned)C, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(dy, dy_bstride, x, x_bstride,
+                                                                                        dtype, parts, C, H, W);
+  return check_launch("dwconv3x3_wgrad");
+}
+
+extern "C" int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias,
+                                              const void* dg, int64_t dg_bstride, void* da, int64_t da_bstride,
+                                              int dtype, int B, int Hd, int H, int W, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(t && w && dg && da && B > 0 && Hd > 0 && H > 0 && W > 0, "gelu_gate_bwd: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype) && B <= 65535 && Hd <= 65535, "gelu_gate_bwd: bad dtype / grid");
+  dim3 grid((unsigned)(((int64_t)H * W + 255) / 256), (unsigned)Hd, (unsigned)B);
+  gelu_gate_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride,
+                                                               dtype, Hd, H, W);
+  return check_launch("gelu_gate_bwd");
+}
+
+extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const float* temperature,
+                               const float* w_out, const float* dM, float* mt, float* mqk, float* dw_out_part,
+                               float* dtemp_part, int B, int C, int heads, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(partials && attn && temperature && w_out && dM && mt && mqk && dw_out_part && dtemp_part,
+                   "mdta_bwd: null pointer");
+  B200IR_CHECK_ARG(nslab > 0 && B > 0 && C > 0 && heads > 0 && C % heads == 0 && B <= 65535, "mdta_bwd: bad shape");
+  const int d = C / heads;
+  B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
+  const size_t smem = (3 * (size_t)d * (d + 1) + 4 * (size_t)d) * sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(mdta_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    attr_set = true;
+  }
+  mdta_bwd_kernel<<<dim3((unsigned)heads, (unsigned)B), 256, smem, (cudaStream_t)stream>>>(
+      partials, nslab, attn, temperature, w_out, dM, mt, mqk, dw_out_part, dtemp_part, C, d);
+  return check_launch("mdta_bwd");
+}
+
+extern "C" int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B,
+                                    int C, int H, int W, int mode, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && y && B > 0 && C > 0 && H > 0 && W > 0 && B <= 65535, "pixel_shuffle: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "pixel_shuffle: bad dtype");
+  B200IR_CHECK_ARG(mode == B200IR_SHUFFLE2 || mode == B200IR_UNSHUFFLE2, "pixel_shuffle: bad mode %d", mode);
+  B200IR_CHECK_ARG(mode != B200IR_SHUFFLE2 || C % 4 == 0, "pixel_shuffle: PixelShuffle(2) needs C%%4==0");
+  B200IR_CHECK_ARG(mode != B200IR_UNSHUFFLE2 || (H % 2 == 0 && W % 2 == 0), "pixel_shuffle: needs even H,W");
+  const int64_t n = (int64_t)C * H * W;
+  pixel_shuffle_kernel<<<dim3((unsigned)grid_1d(n, 256, 148 * 8), (unsigned)B), 256, 0, (cudaStream_t)stream>>>(
+      x, x_bstride, y, y_bstride, dtype, C, H, W, mode);
+  return check_launch("pixel_shuffle");
+}
+
+extern "C" int b200ir_l1_loss_fwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
+                                  float* parts, int nparts, float* loss, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(pred && target && parts && loss && n > 0 && nparts > 0 && nparts <= 4096, "l1_loss_fwd: bad args");
+  B200IR_CHECK_ARG(dtype_ok(pred_dtype) && dtype_ok(target_dtype), "l1_loss_fwd: bad dtype");
+  l1_loss_fwd_kernel<<<nparts, 256, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, target_dtype, n, parts);
+  int rc = check_launch("l1_loss_fwd");
+  if (rc) return rc;
+  l1_loss_finish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(parts, nparts, 1.0f / (float)n, loss);
+  return check_launch("l1_loss_finish");
+}
+
+extern "C" int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
+                                  const float* gscale, void* grad, int grad_dtype, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(pred && target && gscale && grad && n > 0, "l1_loss_bwd: bad args");
+  B200IR_CHECK_ARG(dtype_ok(pred_dtype) && dtype_ok(target_dtype) && dtype_ok(grad_dtype), "l1_loss_bwd: bad dtype");
+  l1_loss_bwd_kernel<<<grid_1d(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, target_dtype,
+                                                                                n, gscale, 1.0f / (float)n, grad,
+                                                                                grad_dtype);
+  return check_launch("l1_loss_bwd");
+}
+
+extern "C" int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                                 float beta2, float eps, float weight_decay, int step, float grad_scale,
+                                 b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw_step: bad args");
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  adamw_kernel<<<grid_1d(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(
+      p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
+  return check_launch("adamw_step");
+}

@@ -363,3 +363,175 @@ def conv3x3_tc(x, packed, Cout, shuffle=L.SHUFFLE_NONE, out=None, out_dtype=None
                                        Cout, H, W_, shuffle, _stream())
     L.check(rc, "b200ir_conv3x3_tc_fwd")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# backward / training-step kernels (csrc/backward.cu)
+# ---------------------------------------------------------------------------------------------------
+def reduce_partials(parts, n, K, stride=None, out=None):
+    """out[k] = sum_{i<n} parts.flat[i*stride + k]  (fixed order; fp32)."""
+    if out is None:
+        out = torch.empty((K,), device=parts.device, dtype=torch.float32)
+    with _timed("reduce_partials", n, K):
+        L.check(lib.b200ir_reduce_partials(parts.data_ptr(), out.data_ptr(), n, K, K if stride is None else stride,
+                                           _stream()), "b200ir_reduce_partials")
+    return out
+
+
+def ln_fwd(x, ln_type, ln_w, ln_b, out_dtype=None):
+    """LN(x) materialised (only the backward needs it as a tensor)."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    y = torch.empty((B, C, H, W_), device=x.device, dtype=out_dtype or x.dtype)
+    yp, ybs, ydt = _act(y, "y")
+    with _timed("ln_fwd", B, C, H * W_, xdt):
+        rc = lib.b200ir_ln_fwd(xp, xbs, xdt, ln_type, _par(ln_w, "ln_w", C),
+                               _par(ln_b, "ln_b", C if ln_type == L.LN_WITHBIAS else None), yp, ybs, ydt, B, C, H * W_,
+                               _stream())
+    L.check(rc, "b200ir_ln_fwd")
+    return y
+
+
+def ln_bwd(x, g, ln_type, ln_w, res=None):
+    """-> (dx, dweight[C], dbias[C])."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    gp, gbs, gdt = _act(g, "g")
+    dx = torch.empty((B, C, H, W_), device=x.device, dtype=x.dtype)
+    dp, dbs, ddt = _act(dx, "dx")
+    rp, rbs, rdt = (None, 0, 0)
+    if res is not None:
+        rp, rbs, rdt = _act(res, "res")
+    nparts = lib.b200ir_ln_bwd_nparts(B, H * W_)
+    parts = torch.empty((nparts, 2, C), device=x.device, dtype=torch.float32)
+    with _timed("ln_bwd", B, C, H * W_, xdt):
+        rc = lib.b200ir_ln_bwd(xp, xbs, xdt, gp, gbs, gdt, ln_type, _par(ln_w, "ln_w", C), rp, rbs, rdt, dp, dbs, ddt,
+                               parts.data_ptr(), nparts, B, C, H * W_, _stream())
+    L.check(rc, "b200ir_ln_bwd")
+    d = reduce_partials(parts, nparts, 2 * C)
+    return dx, d[:C], d[C:]
+
+
+def conv_wgrad(dy, x, taps=1, per_sample=False, want_bias=False, impl=L.IMPL_AUTO):
+    """Weight (and bias) gradient of a 1x1 / dense 3x3 conv: (dW [G,Cout,Cin*taps] or [Cout,Cin*taps], db or None)."""
+    B, Cout, H, W_ = dy.shape
+    Cin = x.shape[1]
+    if x.shape[0] != B or tuple(x.shape[2:]) != (H, W_):
+        raise ValueError("conv_wgrad: dy / x shape mismatch")
+    dp, dbs, ddt = _act(dy, "dy")
+    xp, xbs, xdt = _act(x, "x")
+    ns = lib.b200ir_conv_wgrad_nsplit(B, Cout, Cin, taps, H * W_, int(per_sample))
+    if ns <= 0:
+        raise RuntimeError("b200ir_conv_wgrad_nsplit failed")
+    G = B if per_sample else 1
+    N = Cin * taps
+    pw = torch.empty((ns, G, Cout, N), device=dy.device, dtype=torch.float32)
+    pb = torch.empty((ns, G, Cout), device=dy.device, dtype=torch.float32) if want_bias else None
+    with _timed("conv_wgrad", B, Cout, Cin, H * W_, taps, int(per_sample), ddt, xdt):
+        rc = lib.b200ir_conv_wgrad(dp, dbs, ddt, xp, xbs, xdt, pw.data_ptr(), pb.data_ptr() if want_bias else None, ns,
+                                   B, Cout, Cin, H, W_, taps, int(per_sample), impl, _stream())
+    L.check(rc, "b200ir_conv_wgrad")
+    dw = pw[0] if ns == 1 else reduce_partials(pw, ns, G * Cout * N).view(G, Cout, N)
+    db = None
+    if want_bias:  # the bias of a per-sample weight is still shared: sum over samples and splits
+        db = pb.view(Cout) if ns * G == 1 else reduce_partials(pb, ns * G, Cout)
+    return (dw if per_sample else dw[0]), db
+
+
+def dwconv3x3_wgrad(dy, x, want_bias=False):
+    """-> (dw [C,1,3,3], db [C] or None)."""
+    B, C, H, W_ = x.shape
+    dp, dbs, ddt = _act(dy, "dy")
+    xp, xbs, xdt = _act(x, "x")
+    if ddt != xdt:
+        raise ValueError("dwconv3x3_wgrad: dtype mismatch")
+    parts = torch.empty((B, C, 10), device=x.device, dtype=torch.float32)
+    with _timed("dwconv3x3_wgrad", B, C, H, W_, xdt):
+        L.check(lib.b200ir_dwconv3x3_wgrad(dp, dbs, xp, xbs, xdt, parts.data_ptr(), B, C, H, W_, _stream()),
+                "b200ir_dwconv3x3_wgrad")
+    d = parts.view(C, 10) if B == 1 else reduce_partials(parts, B, C * 10).view(C, 10)
+    return d[:, :9].reshape(C, 1, 3, 3), (d[:, 9] if want_bias else None)
+
+
+def dwconv3x3_gelu_gate_bwd(t, w, bias, dg):
+    """Gradient w.r.t. the depthwise-conv output (2Hd channels) of the fused dwconv+GELU gate."""
+    B, C2, H, W_ = t.shape
+    Hd = C2 // 2
+    tp, tbs, tdt = _act(t, "t")
+    gp, gbs, gdt = _act(dg, "dg")
+    if gdt != tdt:
+        raise ValueError("dwconv3x3_gelu_gate_bwd: dtype mismatch")
+    da = torch.empty((B, C2, H, W_), device=t.device, dtype=t.dtype)
+    ap, abs_, adt = _act(da, "da")
+    with _timed("dwconv3x3_gelu_gate_bwd", B, Hd, H, W_, tdt):
+        rc = lib.b200ir_dwconv3x3_gelu_gate_bwd(tp, tbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), gp, gbs, ap, abs_,
+                                                tdt, B, Hd, H, W_, _stream())
+    L.check(rc, "b200ir_dwconv3x3_gelu_gate_bwd")
+    return da
+
+
+def mdta_bwd(partials, attn, temperature, w_out, dM):
+    """-> (mt [B,C,C], mqk [B,2C,2C], dW_out [C,C], dtemperature [heads])."""
+    B, heads, nslab, per = partials.shape
+    C = w_out.shape[0]
+    dev = partials.device
+    mt = torch.empty((B, C, C), device=dev, dtype=torch.float32)
+    mqk = torch.empty((B, 2 * C, 2 * C), device=dev, dtype=torch.float32)
+    dwp = torch.empty((B, C, C), device=dev, dtype=torch.float32)
+    dtp = torch.empty((B, heads), device=dev, dtype=torch.float32)
+    with _timed("mdta_bwd", B, C, heads):
+        rc = lib.b200ir_mdta_bwd(partials.data_ptr(), nslab, attn.data_ptr(), _par(temperature, "temperature", heads),
+                                 _par(w_out, "w_out", C * C), _par(dM, "dM", B * C * C), mt.data_ptr(), mqk.data_ptr(),
+                                 dwp.data_ptr(), dtp.data_ptr(), B, C, heads, _stream())
+    L.check(rc, "b200ir_mdta_bwd")
+    dw = dwp.view(C, C) if B == 1 else reduce_partials(dwp, B, C * C).view(C, C)
+    dt = dtp.view(heads) if B == 1 else reduce_partials(dtp, B, heads)
+    return mt, mqk, dw, dt
+
+
+def pixel_shuffle(x, mode):
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if mode == L.SHUFFLE2:
+        y = torch.empty((B, C // 4, H * 2, W_ * 2), device=x.device, dtype=x.dtype)
+    else:
+        y = torch.empty((B, C * 4, H // 2, W_ // 2), device=x.device, dtype=x.dtype)
+    yp, ybs, ydt = _act(y, "y")
+    with _timed("pixel_shuffle", B, C, H, W_, mode, xdt):
+        L.check(lib.b200ir_pixel_shuffle(xp, xbs, yp, ybs, xdt, B, C, H, W_, mode, _stream()), "b200ir_pixel_shuffle")
+    return y
+
+
+def l1_loss_fwd(pred, target):
+    if pred.shape != target.shape or not (pred.is_contiguous() and target.is_contiguous()):
+        raise ValueError("l1_loss: pred/target must be contiguous tensors of the same shape")
+    n = pred.numel()
+    nparts = min(1024, max(1, (n + 4095) // 4096))
+    parts = torch.empty((nparts,), device=pred.device, dtype=torch.float32)
+    loss = torch.empty((), device=pred.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("l1_loss_fwd", n):
+        rc = lib.b200ir_l1_loss_fwd(pred.data_ptr(), _DT[pred.dtype], target.data_ptr(), _DT[target.dtype], n,
+                                    parts.data_ptr(), nparts, loss.data_ptr(), _stream())
+    L.check(rc, "b200ir_l1_loss_fwd")
+    return loss
+
+
+def l1_loss_bwd(pred, target, gscale):
+    grad = torch.empty_like(pred)
+    with _timed("l1_loss_bwd", pred.numel()):
+        rc = lib.b200ir_l1_loss_bwd(pred.data_ptr(), _DT[pred.dtype], target.data_ptr(), _DT[target.dtype], pred.numel(),
+                                    gscale.data_ptr(), grad.data_ptr(), _DT[grad.dtype], _stream())
+    L.check(rc, "b200ir_l1_loss_bwd")
+    return grad
+
+
+def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
+    for t in (p, g, m, v):
+        if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda or t.numel() != p.numel():
+            raise ValueError("adamw_step: flat contiguous float32 CUDA buffers of equal size expected")
+    with _timed("adamw_step", p.numel()):
+        rc = lib.b200ir_adamw_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr, beta1, beta2,
+                                   eps, weight_decay, step, grad_scale, _stream())
+    L.check(rc, "b200ir_adamw_step")

@@ -124,6 +124,59 @@ int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, cons
                           int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int H, int W, int shuffle_mode,
                           b200ir_stream_t stream);
 
+/* ---- backward / training step (autograd backward of the ops above, nn.L1Loss, AdamW) -------------
+ * Input gradients of the 1x1 / depthwise / dense 3x3 convs reuse the forward entry points with transposed / flipped
+ * weights.  The entry points below are the reductions over pixels and the non-linear pieces.  All reductions write
+ * fixed-order partial sums that b200ir_reduce_partials folds: results are bitwise reproducible. */
+
+/* y = LN(x) materialised (operand of the weight gradient of the fused LN + 1x1 conv; Restormer.py:37-39,54-57). */
+int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int ln_type, const float* ln_w, const float* ln_b,
+                  void* y, int64_t y_bstride, int y_dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
+/* LayerNorm backward: dx = res + dLN(x)^T g;  parts fp32 [nparts][2][C] = partial (dweight | dbias), nparts from
+ * b200ir_ln_bwd_nparts.  res (optional) = gradient arriving through the residual add (Restormer.py:147-148). */
+int b200ir_ln_bwd_nparts(int B, int64_t HW);
+int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride, int g_dtype,
+                  int ln_type, const float* ln_w, const void* res, int64_t res_bstride, int res_dtype, void* dx,
+                  int64_t dx_bstride, int dx_dtype, float* parts, int nparts, int B, int C, int64_t HW,
+                  b200ir_stream_t stream);
+/* out[k] = sum_{i<n} in[i*stride+k], fixed order. */
+int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride, b200ir_stream_t stream);
+/* Weight (+bias) gradient of a 1x1 (taps=1) or dense 3x3 pad-1 (taps=9) conv = reduction over pixels:
+ *   parts_w[split][g][o][c*taps+t] = partial sum_p dy[b,o,p]*x[b,c,p+shift(t)],  parts_b[split][g][o] = partial sum_p dy
+ * g = sample if per_sample (MDTA: dM_b = dout_b.v_b^T, gradient of the folded per-sample weight) else the whole batch
+ * (G=1).  nsplit from b200ir_conv_wgrad_nsplit.  parts_b may be NULL.  impl: B200IR_IMPL_* (TC: bf16 tcgen05). */
+int b200ir_conv_wgrad_nsplit(int B, int Cout, int Cin, int taps, int64_t HW, int per_sample);
+int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtype, const void* x, int64_t x_bstride, int x_dtype,
+                      float* parts_w, float* parts_b, int nsplit, int B, int Cout, int Cin, int H, int W, int taps,
+                      int per_sample, int impl, b200ir_stream_t stream);
+/* Depthwise 3x3 weight/bias gradient: parts fp32 [B][C][10] (9 taps + bias), reduce over B with reduce_partials. */
+int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
+                           float* parts, int B, int C, int H, int W, b200ir_stream_t stream);
+/* Backward of b200ir_dwconv3x3_gelu_gate_fwd w.r.t. the depthwise-conv OUTPUT (recomputed from t): da [B,2Hd,H,W]
+ * from t [B,2Hd,H,W] and dg [B,Hd,H,W]; dt / dw then follow from b200ir_dwconv3x3_fwd (flipped w) / _wgrad. */
+int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
+                                   int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, int B, int Hd, int H,
+                                   int W, b200ir_stream_t stream);
+/* MDTA backward, small per-(sample, head) part (softmax, temperature, F.normalize; Restormer.py:121-131).
+ * In: Gram partials + attn of the forward, dM [B,C,C] (= conv_wgrad(dout, v, per_sample)).
+ * Out: mt [B,C,C] = M_b^T (dv = mt_b.dout), mqk [B,2C,2C] (d[q;k] = mqk_b.[q;k]), dw_out_part [B,C,C] and
+ * dtemp_part [B,heads] (sum over B = dW_out, dtemperature). */
+int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const float* temperature, const float* w_out,
+                    const float* dM, float* mt, float* mqk, float* dw_out_part, float* dtemp_part, int B, int C,
+                    int heads, b200ir_stream_t stream);
+/* nn.PixelShuffle(2) / nn.PixelUnshuffle(2) as a copy (x [B,C,H,W]; gradients of Upsample / Downsample). */
+int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B, int C, int H,
+                         int W, int mode, b200ir_stream_t stream);
+/* nn.L1Loss (mean) forward / backward (MoCE-IR-main/src/train.py:51,65).  parts: fp32 [nparts] scratch. */
+int b200ir_l1_loss_fwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n, float* parts,
+                       int nparts, float* loss, b200ir_stream_t stream);
+int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
+                       const float* gscale, void* grad, int grad_dtype, b200ir_stream_t stream);
+/* torch.optim.AdamW step on one flat fp32 buffer (MoCE-IR-main/src/train.py:83); g is scaled by grad_scale first
+ * (1/world_size after a sum all-reduce). */
+int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                      float eps, float weight_decay, int step, float grad_scale, b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -279,3 +279,55 @@ def synth_image(b: int, h: int, w: int, seed: int = 1234, c: int = 3, dtype=torc
 def psnr(a: Tensor, b: Tensor, peak: float = 1.0) -> float:
     mse = torch.mean((a.double() - b.double()) ** 2).item()
     return float("inf") if mse == 0 else 10.0 * math.log10(peak * peak / mse)
+
+
+# --------------------------------------------------------------------------------------
+# training step                                       (MoCE-IR-main/src/train.py:51-88)
+# --------------------------------------------------------------------------------------
+def l1_loss(pred: Tensor, target: Tensor) -> Tensor:
+    """``nn.L1Loss()`` with the default mean reduction (MoCE-IR-main/src/train.py:51,65)."""
+    return (pred - target).abs().mean()
+
+
+def block_grads(x: Tensor, p: Dict[str, Tensor], num_heads: int, gy: Tensor):
+    """Gradients of ``sum(transformer_block(x) * gy)`` w.r.t. x and every parameter — what torch autograd gives the
+    reference inside ``loss.backward()``.  Returns (y, dx, {name: dparam})."""
+    x = x.detach().clone().requires_grad_(True)
+    q = {k: v.detach().clone().requires_grad_(True) for k, v in p.items()}
+    y = transformer_block(x, q, "", num_heads)
+    names = sorted(q)
+    gs = torch.autograd.grad(y, [x] + [q[n] for n in names], gy)
+    return y.detach(), gs[0], dict(zip(names, gs[1:]))
+
+
+def adamw_reference(p: Tensor, g: Tensor, m: Tensor, v: Tensor, step: int, lr=2e-4, betas=(0.9, 0.999), eps=1e-8,
+                    weight_decay=1e-2):
+    """One ``torch.optim.AdamW`` update (defaults of ``optim.AdamW(lr=2e-4)``, MoCE-IR-main/src/train.py:83) restated
+    on flat tensors: decoupled decay, bias-corrected moments, eps outside sqrt(v_hat).  Returns (p, m, v)."""
+    b1, b2 = betas
+    p = p * (1 - lr * weight_decay)
+    m = m + (1 - b1) * (g - m)
+    v = b2 * v + (1 - b2) * g * g
+    bc1, bc2 = 1 - b1 ** step, 1 - b2 ** step
+    p = p - (lr / bc1) * m / (v.sqrt() / math.sqrt(bc2) + eps)
+    return p, m, v
+
+
+def train_step_reference(sd: Dict[str, Tensor], cfg: Optional[dict], degraded: Tensor, clean: Tensor, steps: int = 1,
+                         lr: float = 2e-4):
+    """``training_step`` + ``configure_optimizers`` of the reference driver as a plain loop (Lightning is not
+    installed): restored = net(degrad); loss = L1(restored, clean); AdamW(lr=2e-4) step
+    (MoCE-IR-main/src/train.py:59-88; the LinearWarmupCosine scheduler is left out — lr is constant here).
+    Returns (losses, grads of the last step, updated state_dict)."""
+    q = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    names = sorted(q)
+    opt = torch.optim.AdamW([q[n] for n in names], lr=lr)
+    losses, grads = [], None
+    for _ in range(steps):
+        opt.zero_grad(set_to_none=True)
+        loss = l1_loss(restormer_forward(q, degraded, cfg), clean)
+        loss.backward()
+        grads = {n: q[n].grad.detach().clone() for n in names}
+        opt.step()
+        losses.append(loss.item())
+    return losses, grads, {n: q[n].detach().clone() for n in names}

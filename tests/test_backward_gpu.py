@@ -1,0 +1,250 @@
+"""GPU parity of the backward (training) kernels, through the C ABI, against torch autograd over the CPU oracle —
+the same gradients ``loss.backward()`` gives the reference (MoCE-IR-main/src/train.py:59-72).
+
+Tolerances: fp32 path — every gradient within 1e-4 of the oracle's relative to that gradient's max-abs (the
+BASELINE.json fp32 bar applied to gradients); bf16 path — relative L2 error <= 3e-2 per gradient tensor."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+from oracle import restormer_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def b200ir():
+    import b200ir as m
+    return m
+
+
+def close32(a, ref, tol=1e-4):
+    a, ref = a.detach().double().cpu(), ref.detach().double().cpu()
+    assert a.shape == ref.shape, (a.shape, ref.shape)
+    scale = ref.abs().max().clamp_min(1e-6).item()
+    err = (a - ref).abs().max().item()
+    assert err <= tol * scale, f"max-abs {err:.3e} vs scale {scale:.3e}"
+
+
+def rel(a, ref):
+    a, ref = a.detach().double().cpu(), ref.detach().double().cpu()
+    return ((a - ref).norm() / ref.norm().clamp_min(1e-30)).item()
+
+
+def leaf(t, dtype=None):
+    t = t.cuda()
+    if dtype is not None:
+        t = t.to(dtype)
+    return t.detach().requires_grad_(True)
+
+
+@pytest.mark.parametrize("ln", ["none", "WithBias", "BiasFree"])
+@pytest.mark.parametrize("Cin,Cout,H,W,bias,res", [(48, 144, 16, 16, False, False), (30, 17, 9, 13, True, True),
+                                                   (96, 96, 24, 8, True, False), (127, 48, 16, 8, False, True)])
+def test_ln_conv1x1_backward(b200ir, ln, Cin, Cout, H, W, bias, res):
+    from b200ir import autograd_ops as A, _lib as L
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(2, Cin, H, W, generator=g)
+    w = torch.randn(Cout, Cin, 1, 1, generator=g) * 0.2
+    b = torch.randn(Cout, generator=g) if bias else None
+    lw = torch.rand(Cin, generator=g) + 0.5
+    lb = torch.randn(Cin, generator=g) * 0.1
+    r = torch.randn(2, Cout, H, W, generator=g) if res else None
+    gy = torch.randn(2, Cout, H, W, generator=g)
+
+    ins = [t.clone().requires_grad_(True) if t is not None else None for t in (x, w, b, lw, lb, r)]
+    xr, wr, br, lwr, lbr, rr = ins
+    n = xr if ln == "none" else O.layernorm(xr, lwr, lbr if ln == "WithBias" else None)
+    y = F.conv2d(n, wr, br)
+    if res:
+        y = y + rr
+    used = [t for t in ins if t is not None]
+    refg = dict(zip([id(t) for t in used], torch.autograd.grad(y, used, gy, allow_unused=True)))
+
+    lt = {"none": L.LN_NONE, "WithBias": L.LN_WITHBIAS, "BiasFree": L.LN_BIASFREE}[ln]
+    xs, ws, bs, lws, lbs, rs = [leaf(t) if t is not None else None for t in (x, w, b, lw, lb, r)]
+    out = A.ln_conv1x1(xs, ws, bs, lt, lws if ln != "none" else None, lbs if ln == "WithBias" else None, rs)
+    close32(out, y, 1e-5)
+    out.backward(gy.cuda())
+    close32(xs.grad, refg[id(xr)])
+    close32(ws.grad, refg[id(wr)])
+    if bias:
+        close32(bs.grad, refg[id(br)])
+    if res:
+        close32(rs.grad, refg[id(rr)])
+    if ln != "none":
+        close32(lws.grad, refg[id(lwr)])
+    if ln == "WithBias":
+        close32(lbs.grad, refg[id(lbr)])
+
+
+@pytest.mark.parametrize("C,H,W,bias", [(24, 16, 16, False), (30, 7, 13, True), (96, 40, 24, True)])
+def test_dwconv_backward(b200ir, C, H, W, bias):
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, C, H, W, generator=g)
+    w = torch.randn(C, 1, 3, 3, generator=g) * 0.3
+    b = torch.randn(C, generator=g) if bias else None
+    gy = torch.randn(2, C, H, W, generator=g)
+    ins = [t.clone().requires_grad_(True) for t in (x, w) + ((b,) if bias else ())]
+    y = F.conv2d(ins[0], ins[1], ins[2] if bias else None, padding=1, groups=C)
+    refg = torch.autograd.grad(y, ins, gy)
+    xs, ws = leaf(x), leaf(w)
+    bs = leaf(b) if bias else None
+    A.dwconv3x3(xs, ws, bs).backward(gy.cuda())
+    close32(xs.grad, refg[0])
+    close32(ws.grad, refg[1])
+    if bias:
+        close32(bs.grad, refg[2])
+
+
+@pytest.mark.parametrize("Hd,H,W,bias", [(31, 16, 16, False), (20, 9, 7, True), (127, 24, 16, True)])
+def test_gelu_gate_backward(b200ir, Hd, H, W, bias):
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 2 * Hd, H, W, generator=g)
+    w = torch.randn(2 * Hd, 1, 3, 3, generator=g) * 0.3
+    b = torch.randn(2 * Hd, generator=g) * 0.2 if bias else None
+    gy = torch.randn(2, Hd, H, W, generator=g)
+    ins = [t.clone().requires_grad_(True) for t in (x, w) + ((b,) if bias else ())]
+    t = F.conv2d(ins[0], ins[1], ins[2] if bias else None, padding=1, groups=2 * Hd)
+    x1, x2 = t.chunk(2, dim=1)
+    y = F.gelu(x1) * x2
+    refg = torch.autograd.grad(y, ins, gy)
+    xs, ws = leaf(x), leaf(w)
+    bs = leaf(b) if bias else None
+    A.dwconv3x3_gelu_gate(xs, ws, bs).backward(gy.cuda())
+    close32(xs.grad, refg[0])
+    close32(ws.grad, refg[1])
+    if bias:
+        close32(bs.grad, refg[2])
+
+
+@pytest.mark.parametrize("C,heads,H,W,bias", [(48, 1, 16, 16, False), (64, 2, 8, 24, True), (96, 2, 16, 8, True),
+                                              (96, 1, 16, 16, False)])
+def test_mdta_core_backward(b200ir, C, heads, H, W, bias):
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(6)
+    qkv = torch.randn(2, 3 * C, H, W, generator=g)
+    temp = torch.rand(heads, 1, 1, generator=g) + 0.5
+    wo = torch.randn(C, C, 1, 1, generator=g) * 0.2
+    bo = torch.randn(C, generator=g) if bias else None
+    r = torch.randn(2, C, H, W, generator=g)
+    gy = torch.randn(2, C, H, W, generator=g)
+
+    ins = [t.clone().requires_grad_(True) for t in (qkv, temp, wo, r) + ((bo,) if bias else ())]
+    q, k, v = ins[0].chunk(3, dim=1)
+    d = C // heads
+    sh = lambda t: t.reshape(2, heads, d, H * W)
+    attn = ((F.normalize(sh(q), dim=-1) @ F.normalize(sh(k), dim=-1).transpose(-2, -1)) * ins[1]).softmax(dim=-1)
+    y = ins[3] + F.conv2d((attn @ sh(v)).reshape(2, C, H, W), ins[2], ins[4] if bias else None)
+    refg = torch.autograd.grad(y, ins, gy)
+
+    qs, ts, wos, rs = leaf(qkv), leaf(temp), leaf(wo), leaf(r)
+    bos = leaf(bo) if bias else None
+    out = A.mdta_core(qs, ts, wos, bos, heads, rs)
+    close32(out, y, 1e-5)
+    out.backward(gy.cuda())
+    close32(qs.grad, refg[0])
+    close32(ts.grad, refg[1])
+    close32(wos.grad, refg[2])
+    close32(rs.grad, refg[3])
+    if bias:
+        close32(bos.grad, refg[4])
+
+
+@pytest.mark.parametrize("Cin,Cout,H,W,shuffle,bias,res", [(3, 48, 16, 16, "none", False, False),
+                                                           (48, 24, 16, 24, "unshuffle", False, False),
+                                                           (96, 192, 8, 8, "shuffle", False, False),
+                                                           (32, 3, 16, 8, "none", True, True)])
+def test_conv3x3_backward(b200ir, Cin, Cout, H, W, shuffle, bias, res):
+    from b200ir import autograd_ops as A, _lib as L
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(2, Cin, H, W, generator=g)
+    w = torch.randn(Cout, Cin, 3, 3, generator=g) * 0.1
+    b = torch.randn(Cout, generator=g) if bias else None
+    ins = [t.clone().requires_grad_(True) for t in (x, w) + ((b,) if bias else ())]
+    y = F.conv2d(ins[0], ins[1], ins[2] if bias else None, padding=1)
+    if shuffle == "unshuffle":
+        y = O.pixel_unshuffle2(y)
+    elif shuffle == "shuffle":
+        y = O.pixel_shuffle2(y)
+    r = torch.randn(y.shape, generator=g) if res else None
+    if res:
+        rr = r.clone().requires_grad_(True)
+        y = y + rr
+        ins.append(rr)
+    gy = torch.randn(y.shape, generator=g)
+    refg = torch.autograd.grad(y, ins, gy)
+    mode = {"none": L.SHUFFLE_NONE, "unshuffle": L.UNSHUFFLE2, "shuffle": L.SHUFFLE2}[shuffle]
+    xs, ws = leaf(x), leaf(w)
+    bs = leaf(b) if bias else None
+    rs = leaf(r) if res else None
+    out = A.conv3x3(xs, ws, bs, rs, mode)
+    close32(out, y, 1e-5)
+    out.backward(gy.cuda())
+    close32(xs.grad, refg[0])
+    close32(ws.grad, refg[1])
+    if bias:
+        close32(bs.grad, refg[2])
+    if res:
+        close32(rs.grad, refg[-1])
+
+
+BLOCKS = [(48, 1, 2.66, False, "WithBias", 16, 16), (96, 2, 2.66, True, "BiasFree", 16, 8),
+          (64, 2, 2.0, True, "WithBias", 8, 24), (96, 1, 2.66, False, "WithBias", 16, 16)]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("C,heads,f,bias,ln,H,W", BLOCKS)
+def test_block_backward(b200ir, dtype, C, heads, f, bias, ln, H, W):
+    p = O.synth_block_params(C, heads, f, bias, ln, 21)
+    x = O.synth_image(2, H, W, seed=9, c=C) * 2 - 1
+    gy = torch.randn(2, C, H, W, generator=torch.Generator().manual_seed(10))
+    y, dx, dp = O.block_grads(x, p, heads, gy)
+    blk = b200ir.TransformerBlock(C, heads, f, bias, ln).cuda()
+    blk.load_state_dict(p, strict=True)
+    xs = leaf(x, dtype)
+    out = blk(xs)
+    out.backward(gy.cuda().to(dtype))
+    got = dict(blk.named_parameters())
+    assert set(got) == set(dp)
+    if dtype == torch.float32:
+        close32(out, y, 1e-5)
+        close32(xs.grad, dx)
+        for n in dp:
+            close32(got[n].grad, dp[n])
+    else:
+        assert rel(xs.grad.float(), dx) < 3e-2
+        for n in dp:
+            assert got[n].grad is not None and got[n].grad.dtype == torch.float32
+            assert rel(got[n].grad, dp[n]) < 3e-2, n
+
+
+def test_l1_loss_and_adamw(b200ir):
+    from b200ir import autograd_ops as A, ops
+    g = torch.Generator().manual_seed(11)
+    pred, tgt = torch.rand(2, 3, 16, 24, generator=g), torch.rand(2, 3, 16, 24, generator=g)
+    pr = pred.clone().requires_grad_(True)
+    lr_ = O.l1_loss(pr, tgt)
+    (gr,) = torch.autograd.grad(lr_ * 3.0, pr)
+    ps = leaf(pred)
+    ls = A.l1_loss(ps, tgt.cuda())
+    (ls * 3.0).backward()
+    assert abs(ls.item() - lr_.item()) < 1e-6
+    close32(ps.grad, gr, 1e-6)
+    # AdamW: three steps against torch.optim.AdamW itself and the oracle restatement
+    n = 10007
+    p0, m0, v0 = torch.randn(n, generator=g), torch.zeros(n), torch.zeros(n)
+    pt = p0.clone().requires_grad_(True)
+    opt = torch.optim.AdamW([pt], lr=2e-4)
+    pc, mc, vc = p0.cuda(), m0.cuda(), v0.cuda()
+    po, mo, vo = p0.clone(), m0.clone(), v0.clone()
+    for step in range(1, 4):
+        gg = torch.randn(n, generator=g)
+        pt.grad = gg.clone()
+        opt.step()
+        ops.adamw_step(pc, gg.cuda(), mc, vc, 2e-4, 0.9, 0.999, 1e-8, 1e-2, step)
+        po, mo, vo = O.adamw_reference(po, gg, mo, vo, step)
+    assert (pc.cpu() - pt.detach()).abs().max() <= 1e-6
+    assert (po - pt.detach()).abs().max() <= 1e-6
