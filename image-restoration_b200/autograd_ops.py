@@ -29,8 +29,16 @@ def _p(t):
     return t.contiguous()
 
 
+PARAM_EPOCH = 0  # bumped by b200ir.AdamW.step(): its kernel updates parameters in place without touching _version
+
+
+def bump_param_epoch():
+    global PARAM_EPOCH
+    PARAM_EPOCH += 1
+
+
 def _sig(*ts):
-    return tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
+    return (PARAM_EPOCH,) + tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
 
 
 def packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b):
@@ -111,7 +119,7 @@ _ST_CACHE = {}
 
 def _bias_st(bias, C, nrows, device):
     """(s, t) epilogue vectors of the per-sample GEMM: s unused (no LayerNorm), t = project_out bias."""
-    key = (None if bias is None else (bias.data_ptr(), bias._version), C, nrows, str(device))
+    key = (PARAM_EPOCH, None if bias is None else (bias.data_ptr(), bias._version), C, nrows, str(device))
     st = _ST_CACHE.get(key)
     if st is None:
         if len(_ST_CACHE) > 4096:

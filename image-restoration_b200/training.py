@@ -1,0 +1,131 @@
+"""Training-step pieces around the block path, mirroring what the reference driver uses:
+``nn.L1Loss()`` (MoCE-IR-main/src/train.py:51), ``optim.AdamW(self.parameters(), lr=2e-4)`` (:83) and DDP gradient
+averaging (:131).  Everything numeric runs in hand-written kernels (csrc/backward.cu); torch only owns the buffers.
+
+``AdamW`` keeps parameters, gradients and both moments in four flat fp32 buffers (the module's ``nn.Parameter``s become
+views of the first), so one optimizer step is ONE kernel launch over 26 M elements and the DDP all-reduce is ONE NCCL
+call on the flat gradient buffer.
+"""
+from __future__ import annotations
+
+from typing import Iterable, Optional
+
+import torch
+import torch.nn as nn
+
+from . import autograd_ops as A
+from . import ops
+
+
+class L1Loss(nn.Module):
+    """Drop-in for ``nn.L1Loss()`` (mean reduction only, as the reference uses it)."""
+
+    def __init__(self, reduction: str = "mean"):
+        super().__init__()
+        if reduction != "mean":
+            raise ValueError("b200ir.L1Loss supports reduction='mean' only")
+
+    def forward(self, pred, target):
+        if pred.shape != target.shape:
+            raise ValueError("L1Loss: shape mismatch")
+        return A.l1_loss(pred, target)
+
+
+class AdamW:
+    """``torch.optim.AdamW`` semantics (decoupled weight decay, bias correction, eps outside the sqrt) on flat buffers.
+
+    Constructor signature follows ``torch.optim.AdamW(params, lr, betas, eps, weight_decay)``.  Parameters must be
+    fp32 CUDA tensors; after construction each ``p.data`` is a view into ``self.flat_p``.
+    """
+
+    def __init__(self, params: Iterable[nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2):
+        self.params = [p for p in params if p.requires_grad]
+        if not self.params:
+            raise ValueError("AdamW: no trainable parameters")
+        dev = self.params[0].device
+        for p in self.params:
+            if not p.is_cuda or p.dtype != torch.float32 or p.device != dev:
+                raise ValueError("AdamW: parameters must be float32 CUDA tensors on one device (no CPU fallback)")
+        self.lr, self.betas, self.eps, self.weight_decay = lr, tuple(betas), eps, weight_decay
+        self.offsets, n = [], 0
+        for p in self.params:
+            self.offsets.append(n)
+            n += (p.numel() + 3) // 4 * 4          # keep every view 16-byte aligned
+        self.numel = n
+        self.flat_p = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.flat_g = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.exp_avg = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.grad_views = []
+        with torch.no_grad():
+            for p, o in zip(self.params, self.offsets):
+                view = self.flat_p[o:o + p.numel()].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                self.grad_views.append(self.flat_g[o:o + p.numel()].view(p.shape))
+        self.step_count = 0
+
+    def zero_grad(self, set_to_none: bool = True):
+        for p in self.params:
+            p.grad = None
+
+    def gather_grads(self):
+        """Collect ``p.grad`` into the flat gradient buffer (no-op for gradients that already live there)."""
+        src, dst = [], []
+        for p, gv in zip(self.params, self.grad_views):
+            if p.grad is None:
+                gv.zero_()
+            elif p.grad.data_ptr() != gv.data_ptr():
+                src.append(p.grad)
+                dst.append(gv)
+        if src:
+            torch._foreach_copy_(dst, src)
+        return self.flat_g
+
+    @torch.no_grad()
+    def step(self, grad_scale: float = 1.0, gathered: bool = False):
+        if not gathered:
+            self.gather_grads()
+        self.step_count += 1
+        ops.adamw_step(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0], self.betas[1],
+                       self.eps, self.weight_decay, self.step_count, grad_scale)
+        A.bump_param_epoch()   # packed bf16 weight caches key on this (the kernel does not bump tensor versions)
+
+    def state_dict(self):
+        return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "lr": self.lr,
+                "betas": self.betas, "eps": self.eps, "weight_decay": self.weight_decay}
+
+    def load_state_dict(self, sd):
+        self.step_count = int(sd["step"])
+        self.exp_avg.copy_(sd["exp_avg"])
+        self.exp_avg_sq.copy_(sd["exp_avg_sq"])
+        self.lr, self.betas, self.eps, self.weight_decay = sd["lr"], tuple(sd["betas"]), sd["eps"], sd["weight_decay"]
+
+
+def allreduce_flat_grads(flat_g: torch.Tensor, group=None) -> float:
+    """DDP gradient averaging (MoCE-IR-main/src/train.py:131): ONE sum all-reduce of the flat gradient buffer; returns
+    the 1/world_size factor to hand to ``AdamW.step(grad_scale=...)`` (the division is fused into the update kernel)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return 1.0
+    world = dist.get_world_size(group)
+    if world == 1:
+        return 1.0
+    dist.all_reduce(flat_g, op=dist.ReduceOp.SUM, group=group)
+    return 1.0 / world
+
+
+def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.Tensor, loss_fn: Optional[nn.Module] = None,
+               group=None) -> torch.Tensor:
+    """``training_step`` of the reference driver (MoCE-IR-main/src/train.py:59-72) + optimizer step:
+    restored = net(degrad); loss = L1(restored, clean); backward; (all-reduce); AdamW.  Returns the loss (device scalar)."""
+    loss_fn = loss_fn or L1Loss()
+    opt.zero_grad()
+    restored = net(degraded)
+    loss = loss_fn(restored, clean)
+    loss.backward()
+    flat_g = opt.gather_grads()
+    scale = allreduce_flat_grads(flat_g, group)
+    opt.step(grad_scale=scale, gathered=True)
+    return loss.detach()
