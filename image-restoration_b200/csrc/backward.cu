@@ -138,10 +138,10 @@ __global__ void reduce_partials_kernel(const float* __restrict__ in, float* __re
 // =====================================================================================================
 // Weight gradient of a 1x1 conv (taps=1) or a dense 3x3 conv (taps=9): reduction over pixels
 //   dW[g][o][c*taps+t] = sum_{b in g} sum_p dy[b,o,p] * x[b,c,p+shift(t)],   db[g][o] = sum dy[b,o,p]
-// g = sample (per_sample, MDTA dM_b = dout_b . v_b^T) or the whole batch.  Split-K over 32-pixel chunks.
+// g = sample (per_sample, MDTA dM_b = dout_b . v_b^T) or the whole batch.  Split-K over 64-pixel chunks.
 // CUDA-core fp32 FMA version (exact path); grid (n-tiles, m-tiles, G*nsplit).
 // =====================================================================================================
-constexpr int WM = 64, WN = 64, WK = 32;
+constexpr int WM = 64, WN = 64, WK = 64;   // WK = pixels per split-K chunk (same chunking as wgrad_tc.cu)
 
 __global__ void __launch_bounds__(256)
 wgrad_simt_kernel(const void* __restrict__ A, int64_t a_bs, int a_dt, const void* __restrict__ X, int64_t x_bs, int x_dt,
@@ -167,9 +167,9 @@ wgrad_simt_kernel(const void* __restrict__ A, int64_t a_bs, int a_dt, const void
     const int b = per_sample ? g : ch / chunks_per_sample;
     const int64_t p0 = (int64_t)(ch % chunks_per_sample) * WK;
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
+    for (int i = 0; i < 16; ++i) {
       const int e = tid + i * 256;
-      const int r = e >> 5, cpx = e & 31;
+      const int r = e >> 6, cpx = e & 63;
       const int64_t p = p0 + cpx;
       float av = 0.f, xv = 0.f;
       if (p < HW) {
@@ -562,12 +562,23 @@ extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_
 }
 
 namespace b200ir {
+bool wgrad_tc_supported(const void* dy, int64_t dy_bs, int dy_dt, const void* x, int64_t x_bs, int x_dt, int taps,
+                        int64_t HW);                                                    // wgrad_tc.cu
+void wgrad_tc_tiles(int M, int N, int* mtiles, int* ntiles, int* Ntile);
+int wgrad_tc_launch(const void* dy, int64_t dy_bs, int dy_dt, const void* x, int64_t x_bs, float* pw, float* pb, int B,
+                    int M, int N, int64_t HW, int per_sample, int nsplit, int chunks_per_sample, int chunks_per_split,
+                    int chunks_total, cudaStream_t st);
+
+// split-K plan shared by the CUDA-core and the tcgen05 kernels (depends on the shape only, so the caller can size the
+// partial buffers before knowing which kernel runs): ~2 waves of 148 SMs worth of 128 x <=256 tiles, <= 64 splits.
 static void wgrad_split(int B, int M, int N, int64_t HW, int per_sample, int* nsplit, int* cps, int* cpsplit,
                         int* ctotal) {
   const int chunks_per_sample = (int)((HW + WK - 1) / WK);
   const int total = per_sample ? chunks_per_sample : B * chunks_per_sample;
-  const int64_t tiles = (int64_t)((M + WM - 1) / WM) * ((N + WN - 1) / WN) * (per_sample ? B : 1);
-  int64_t want = (4 * 148 + tiles - 1) / tiles;
+  int mt, nt, ntile;
+  wgrad_tc_tiles(M, N, &mt, &nt, &ntile);
+  const int64_t tiles = (int64_t)mt * nt * (per_sample ? B : 1);
+  int64_t want = (2 * 148 + tiles - 1) / tiles;
   if (want > 64) want = 64;
   if (want > total) want = total;
   if (want < 1) want = 1;
@@ -597,6 +608,12 @@ extern "C" int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtyp
   B200IR_CHECK_ARG(ns == nsplit, "conv_wgrad: nsplit=%d, expected %d (b200ir_conv_wgrad_nsplit)", nsplit, ns);
   const int G = per_sample ? B : 1;
   B200IR_CHECK_ARG((int64_t)G * ns <= 65535, "conv_wgrad: grid too large");
+  B200IR_CHECK_ARG(impl >= 0 && impl <= 2, "conv_wgrad: bad impl %d", impl);
+  if (impl != B200IR_IMPL_SIMT &&
+      wgrad_tc_supported(dy, dy_bstride, dy_dtype, x, x_bstride, x_dtype, taps, (int64_t)H * W))
+    return wgrad_tc_launch(dy, dy_bstride, dy_dtype, x, x_bstride, parts_w, parts_b, B, Cout, Cin, (int64_t)H * W,
+                           per_sample, ns, cps, cpsplit, ctotal, (cudaStream_t)stream);
+  B200IR_UNSUPPORTED(impl != B200IR_IMPL_TC, "conv_wgrad: tcgen05 path unsupported for this shape/dtype");
   dim3 grid((unsigned)((Cin * taps + WN - 1) / WN), (unsigned)((Cout + WM - 1) / WM), (unsigned)(G * ns));
   wgrad_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(dy, dy_bstride, dy_dtype, x, x_bstride, x_dtype, parts_w,
                                                             parts_b, Cout, Cin, taps, H, W, ns, cps, cpsplit, ctotal,

@@ -287,3 +287,34 @@ def test_restormer_train_steps(b200ir, dtype):
         assert len(bad) <= len(grads) // 20, bad     # bf16 activations: >=95% of the 100+ gradient tensors within 10%
     # loss must go down on a repeated batch
     assert got[-1] < got[0]
+
+
+@pytest.mark.parametrize("B,Cout,Cin,H,W,per_sample,bias", [(2, 144, 48, 16, 16, False, False), (3, 48, 127, 8, 24, False, True),
+                                                            (2, 510, 96, 32, 32, False, True), (2, 96, 96, 16, 16, True, True),
+                                                            (1, 2042, 384, 8, 8, False, False), (2, 17, 255, 24, 24, False, False),
+                                                            (4, 288, 300, 8, 16, True, False)])
+def test_conv_wgrad_tc_vs_exact(b200ir, B, Cout, Cin, H, W, per_sample, bias):
+    """tcgen05 weight-gradient GEMM (bf16 operands, fp32 accumulate) against the fp64 sum over the same bf16 values and
+    against the CUDA-core kernel."""
+    from b200ir import ops, _lib as L
+    g = torch.Generator().manual_seed(31)
+    dy = torch.randn(B, Cout + 5, H, W, generator=g).bfloat16().cuda()[:, 2:2 + Cout]   # channel slice of a wider buffer
+    x = torch.randn(B, Cin, H, W, generator=g).bfloat16().cuda()
+    if (dy.data_ptr() % 16) or (H * W * 2) % 16:
+        pytest.skip("slice not 16B aligned")
+    dw_tc, db_tc = ops.conv_wgrad(dy, x, 1, per_sample=per_sample, want_bias=bias, impl=L.IMPL_TC)
+    dw_si, db_si = ops.conv_wgrad(dy, x, 1, per_sample=per_sample, want_bias=bias, impl=L.IMPL_SIMT)
+    a = dy.double().reshape(B, Cout, -1).cpu()
+    b = x.double().reshape(B, Cin, -1).cpu()
+    ref = torch.einsum("bop,bcp->boc", a, b)
+    if not per_sample:
+        ref = ref.sum(0)
+    close32(dw_tc, ref, 2e-5)
+    close32(dw_si, ref, 2e-5)
+    if bias:
+        refb = a.sum((0, 2))
+        close32(db_tc, refb, 2e-5)
+        close32(db_si, refb, 2e-5)
+    # determinism
+    dw2, _ = ops.conv_wgrad(dy, x, 1, per_sample=per_sample, want_bias=bias, impl=L.IMPL_TC)
+    assert torch.equal(dw2, dw_tc)
