@@ -3,7 +3,7 @@ from . import _lib, ops  # noqa: F401  (fails loudly if libb200ir.so is missing)
 from .modules import (Attention, BiasFree_LayerNorm, Downsample, FeedForward, LayerNorm, OverlapPatchEmbed,  # noqa: F401
                       Restormer, TransformerBlock, Upsample, WithBias_LayerNorm)
 
-from .training import AdamW, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
+from .training import AdamW, GraphedTrainStep, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
 
-__all__ = ["AdamW", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "Downsample", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+__all__ = ["AdamW", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "Downsample", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
            "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -42,13 +42,15 @@ SIGNATURES = {
     "b200ir_reduce_partials": [_vp, _vp, _i, _i64, _i64, _vp],
     "b200ir_conv_wgrad_nsplit": [_i, _i, _i, _i, _i64, _i],
     "b200ir_conv_wgrad": [_vp, _i64, _i, _vp, _i64, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
-    "b200ir_dwconv3x3_wgrad": [_vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _vp],
-    "b200ir_dwconv3x3_gelu_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _vp],
+    "b200ir_im2col3x3": [_vp, _i64, _i, _vp, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_bwd_nparts": [_i, _i, _i, _i],
+    "b200ir_dwconv3x3_wgrad": [_vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_gelu_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "b200ir_mdta_bwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
     "b200ir_l1_loss_bwd": [_vp, _i, _vp, _i, _i64, _vp, _vp, _i, _vp],
-    "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _f, _vp],
+    "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],
 }
 
 

@@ -232,9 +232,8 @@ class _DwGate(torch.autograd.Function):
     def backward(ctx, dg):
         t, w, bias = ctx.saved_tensors
         dg = _cg(dg)
-        da = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg)
+        da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None)
         dt = ops.dwconv3x3(da, _flip_dw(w), None) if ctx.needs_input_grad[0] else None
-        dw, db = ops.dwconv3x3_wgrad(da, t, want_bias=bias is not None)
         return dt, dw.to(w.dtype), db
 
 

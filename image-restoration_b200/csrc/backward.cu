@@ -13,73 +13,91 @@
 namespace b200ir {
 
 // =====================================================================================================
-// LayerNorm materialised: y = LN(x)   (operand of the weight-gradient GEMM of the fused LN+1x1 conv)
+// LayerNorm kernels.  CTA = 32 pixels x 8 warps; lane = pixel (coalesced along HW), warp w owns channels w, w+8, ...
+// Per-pixel sums over C are combined across the 8 warps through shared memory in fixed order.
 // =====================================================================================================
-__global__ void __launch_bounds__(128)
+constexpr int LN_PX = 32;
+
+__device__ __forceinline__ float ln_cross_warp(float v, float (*red)[LN_PX], int warp, int lane) {
+  __syncthreads();            // previous use of red is over
+  red[warp][lane] = v;
+  __syncthreads();
+  float s = 0.f;
+#pragma unroll
+  for (int w = 0; w < 8; ++w) s += red[w][lane];
+  return s;
+}
+
+// y = LN(x) materialised (operand of the weight-gradient GEMM of the fused LN + 1x1 conv)
+__global__ void __launch_bounds__(256)
 ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, const float* __restrict__ lw,
               const float* __restrict__ lb, void* __restrict__ y, int64_t y_bs, int y_dt, int C, int64_t HW, int tps,
               int64_t ntiles) {
+  __shared__ float red[8][LN_PX];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float invC = 1.0f / (float)C;
   for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int b = (int)(t / tps);
-    const int64_t p = (t % tps) * 128 + threadIdx.x;
-    if (p >= HW) continue;
+    const int64_t p = (t % tps) * LN_PX + lane;
+    const bool valid = p < HW;
     const int64_t xo = (int64_t)b * x_bs + p, yo = (int64_t)b * y_bs + p;
     float s = 0.f;
-    for (int c = 0; c < C; ++c) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
-    const float mu = s / (float)C;
+    if (valid)
+      for (int c = warp; c < C; c += 8) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
+    const float mu = ln_cross_warp(s, red, warp, lane) * invC;
     float v = 0.f;
-    for (int c = 0; c < C; ++c) {
-      const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
-      v += d * d;
-    }
-    const float rstd = 1.0f / sqrtf(v / (float)C + 1e-5f);
-    for (int c = 0; c < C; ++c) {
-      const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
-      float n;
-      if (ln_type == B200IR_LN_WITHBIAS) n = (xv - mu) * rstd * lw[c] + lb[c];   // Restormer.py:57
-      else n = xv * rstd * lw[c];                                                // Restormer.py:39
-      st_any(y, y_dt, yo + (int64_t)c * HW, n);
-    }
+    if (valid)
+      for (int c = warp; c < C; c += 8) {
+        const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
+        v += d * d;
+      }
+    const float rstd = 1.0f / sqrtf(ln_cross_warp(v, red, warp, lane) * invC + 1e-5f);
+    if (valid)
+      for (int c = warp; c < C; c += 8) {
+        const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
+        float n;
+        if (ln_type == B200IR_LN_WITHBIAS) n = (xv - mu) * rstd * lw[c] + lb[c];   // Restormer.py:57
+        else n = xv * rstd * lw[c];                                                // Restormer.py:39
+        st_any(y, y_dt, yo + (int64_t)c * HW, n);
+      }
   }
 }
 
-// =====================================================================================================
 // LayerNorm backward.  g = dL/dLN(x), h = g*gamma, xh = (x-mu)*rstd:
 //   WithBias: dx = rstd*(h - mean(h) - xh*mean(h*xh)),  dgamma = sum_p g*xh,  dbeta = sum_p g
 //   BiasFree: dx = rstd*h - rstd^3*(x-mu)*sum_c(h*x)/C,  dgamma = sum_p g*x*rstd
 // dx (+)= res (gradient arriving through the residual path of TransformerBlock, Restormer.py:147-148).
-// parts: fp32 [gridDim.x][2][C] partial dgamma / dbeta (fixed order inside a CTA: per-warp accumulators).
-// =====================================================================================================
-__global__ void __launch_bounds__(128)
+// parts: fp32 [gridDim.x][2][C] partial dgamma / dbeta; a channel is only ever touched by one warp of the CTA, which
+// accumulates it tile after tile in shared memory: fixed order, deterministic.
+__global__ void __launch_bounds__(256)
 ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __restrict__ g, int64_t g_bs, int g_dt,
               int ln_type, const float* __restrict__ lw, const void* __restrict__ res, int64_t res_bs, int res_dt,
               void* __restrict__ dx, int64_t dx_bs, int dx_dt, float* __restrict__ parts, int C, int64_t HW, int tps,
               int64_t ntiles) {
-  extern __shared__ float acc[];  // [4 warps][2][C]
+  extern __shared__ float acc[];  // [2][C]
+  __shared__ float red[8][LN_PX];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < 8 * C; i += 128) acc[i] = 0.f;
+  for (int i = threadIdx.x; i < 2 * C; i += 256) acc[i] = 0.f;
   __syncthreads();
-  float* wacc = acc + (size_t)warp * 2 * C;
   const float invC = 1.0f / (float)C;
   for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
     const int b = (int)(t / tps);
-    const int64_t p = (t % tps) * 128 + threadIdx.x;
+    const int64_t p = (t % tps) * LN_PX + lane;
     const bool valid = p < HW;
     const int64_t xo = (int64_t)b * x_bs + p, go = (int64_t)b * g_bs + p;
-    float mu = 0.f, rstd = 0.f;
-    if (valid) {
-      float s = 0.f;
-      for (int c = 0; c < C; ++c) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
-      mu = s * invC;
-      float v = 0.f;
-      for (int c = 0; c < C; ++c) {
+    float s = 0.f;
+    if (valid)
+      for (int c = warp; c < C; c += 8) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
+    const float mu = ln_cross_warp(s, red, warp, lane) * invC;
+    float v = 0.f;
+    if (valid)
+      for (int c = warp; c < C; c += 8) {
         const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
         v += d * d;
       }
-      rstd = 1.0f / sqrtf(v * invC + 1e-5f);
-    }
+    const float rstd = 1.0f / sqrtf(ln_cross_warp(v, red, warp, lane) * invC + 1e-5f);
     float s1 = 0.f, s2 = 0.f;
-    for (int c = 0; c < C; ++c) {
+    for (int c = warp; c < C; c += 8) {
       float xv = 0.f, gv = 0.f;
       if (valid) {
         xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
@@ -99,21 +117,23 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
       dgam = warp_sum(dgam);
       dbet = warp_sum(dbet);
       if (lane == 0) {
-        wacc[c] += dgam;
-        wacc[C + c] += dbet;
+        acc[c] += dgam;
+        acc[C + c] += dbet;
       }
     }
+    s1 = ln_cross_warp(s1, red, warp, lane) * invC;
+    s2 = ln_cross_warp(s2, red, warp, lane) * invC;
     if (valid) {
       const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p;
-      for (int c = 0; c < C; ++c) {
+      for (int c = warp; c < C; c += 8) {
         const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
         const float h = ld_any(g, g_dt, go + (int64_t)c * HW) * lw[c];
         float d;
         if (ln_type == B200IR_LN_WITHBIAS) {
           const float xh = (xv - mu) * rstd;
-          d = rstd * (h - s1 * invC - xh * s2 * invC);
+          d = rstd * (h - s1 - xh * s2);
         } else {
-          d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2 * invC;
+          d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2;
         }
         if (res) d += ld_any(res, res_dt, ro + (int64_t)c * HW);
         st_any(dx, dx_dt, dxo + (int64_t)c * HW, d);
@@ -122,16 +142,29 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
   }
   __syncthreads();
   float* out = parts + (size_t)blockIdx.x * 2 * C;
-  for (int i = threadIdx.x; i < 2 * C; i += 128) out[i] = acc[i] + acc[2 * C + i] + acc[4 * C + i] + acc[6 * C + i];
+  for (int i = threadIdx.x; i < 2 * C; i += 256) out[i] = acc[i];
 }
 
-// out[k] = sum_{i<n} in[i*stride + k]   (fixed order)
-__global__ void reduce_partials_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int64_t K,
-                                       int64_t stride) {
-  for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < K; k += (int64_t)gridDim.x * blockDim.x) {
+// out[k] = sum_{i<n} in[i*stride + k].  CTA = 32 outputs x 8 slices of the partial index; each slice is summed
+// sequentially, the 8 slice sums are combined in fixed order (deterministic).
+__global__ void __launch_bounds__(256)
+reduce_partials_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int64_t K, int64_t stride) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  for (int64_t k0 = (int64_t)blockIdx.x * 32; k0 < K; k0 += (int64_t)gridDim.x * 32) {
+    const int64_t k = k0 + lane;
     float s = 0.f;
-    for (int i = 0; i < n; ++i) s += in[(size_t)i * stride + k];
-    out[k] = s;
+    if (k < K)
+      for (int i = sl; i < n; i += 8) s += in[(size_t)i * stride + k];
+    __syncthreads();
+    red[sl][lane] = s;
+    __syncthreads();
+    if (sl == 0 && k < K) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][lane];
+      out[k] = t;
+    }
   }
 }
 
@@ -223,85 +256,6 @@ wgrad_simt_kernel(const void* __restrict__ A, int64_t a_bs, int a_dt, const void
 }
 
 // =====================================================================================================
-// Depthwise 3x3 weight / bias gradient: parts[b][c][t] = sum_p dy[b,c,p]*x[b,c,p+shift(t)] (t<9), [9] = sum dy.
-// grid (C, B); one CTA per plane.
-// =====================================================================================================
-__global__ void __launch_bounds__(256)
-dwconv_wgrad_kernel(const void* __restrict__ dy, int64_t dy_bs, const void* __restrict__ x, int64_t x_bs, int dt,
-                    float* __restrict__ parts, int C, int H, int W) {
-  const int c = blockIdx.x, b = blockIdx.y;
-  const int64_t HW = (int64_t)H * W;
-  const int64_t dyo = (int64_t)b * dy_bs + (int64_t)c * HW, xo = (int64_t)b * x_bs + (int64_t)c * HW;
-  float acc[10];
-#pragma unroll
-  for (int i = 0; i < 10; ++i) acc[i] = 0.f;
-  for (int64_t p = threadIdx.x; p < HW; p += 256) {
-    const float g = ld_any(dy, dt, dyo + p);
-    const int yy = (int)(p / W), xx = (int)(p % W);
-#pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      const int y2 = yy + t / 3 - 1, x2 = xx + t % 3 - 1;
-      if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) acc[t] = fmaf(g, ld_any(x, dt, xo + (int64_t)y2 * W + x2), acc[t]);
-    }
-    acc[9] += g;
-  }
-  __shared__ float red[8][10];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-#pragma unroll
-  for (int i = 0; i < 10; ++i) {
-    const float v = warp_sum(acc[i]);
-    if (lane == 0) red[warp][i] = v;
-  }
-  __syncthreads();
-  if (threadIdx.x < 10) {
-    float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
-    parts[((size_t)b * C + c) * 10 + threadIdx.x] = s;
-  }
-}
-
-// =====================================================================================================
-// GDFN gate backward (recomputes the depthwise conv): a = dw(t)+bias, y[c] = gelu(a[c])*a[c+Hd]
-//   da[c] = dg[c]*a[c+Hd]*gelu'(a[c]),   da[c+Hd] = dg[c]*gelu(a[c])       (Restormer.py:90-91)
-// grid (ceil(HW/256), Hd, B)
-// =====================================================================================================
-__device__ __forceinline__ float dw3x3_at(const void* t, int dt, int64_t base, const float* w, int yy, int xx, int H,
-                                          int W) {
-  float s = 0.f;
-#pragma unroll
-  for (int k = 0; k < 9; ++k) {
-    const int y2 = yy + k / 3 - 1, x2 = xx + k % 3 - 1;
-    if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) s = fmaf(w[k], ld_any(t, dt, base + (int64_t)y2 * W + x2), s);
-  }
-  return s;
-}
-
-__global__ void __launch_bounds__(256)
-gelu_gate_bwd_kernel(const void* __restrict__ t, int64_t t_bs, const float* __restrict__ w,
-                     const float* __restrict__ bias, const void* __restrict__ dg, int64_t dg_bs,
-                     void* __restrict__ da, int64_t da_bs, int dt, int Hd, int H, int W) {
-  const int c = blockIdx.y, b = blockIdx.z;
-  const int64_t HW = (int64_t)H * W;
-  const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (p >= HW) return;
-  const int yy = (int)(p / W), xx = (int)(p % W);
-  float w1[9], w2[9];
-#pragma unroll
-  for (int k = 0; k < 9; ++k) {
-    w1[k] = w[c * 9 + k];
-    w2[k] = w[(c + Hd) * 9 + k];
-  }
-  const float a1 = dw3x3_at(t, dt, (int64_t)b * t_bs + (int64_t)c * HW, w1, yy, xx, H, W) + (bias ? bias[c] : 0.f);
-  const float a2 =
-      dw3x3_at(t, dt, (int64_t)b * t_bs + (int64_t)(c + Hd) * HW, w2, yy, xx, H, W) + (bias ? bias[c + Hd] : 0.f);
-  const float g = ld_any(dg, dt, (int64_t)b * dg_bs + (int64_t)c * HW + p);
-  const float cdf = 0.5f * (1.0f + erff(a1 * 0.70710678118654752440f));
-  const float pdf = 0.39894228040143267794f * expf(-0.5f * a1 * a1);
-  st_any(da, dt, (int64_t)b * da_bs + (int64_t)c * HW + p, g * a2 * (cdf + a1 * pdf));
-  st_any(da, dt, (int64_t)b * da_bs + (int64_t)(c + Hd) * HW + p, g * a1 * cdf);
-}
-
-// =====================================================================================================
 // MDTA small backward, one CTA per (head, sample).  Inputs: Gram partials (forward), attn, temperature, W_out and
 // dM_b = dout_b . v_b^T  [B,C,C].  With G^ = G/(a b^T) (a_i = max(|q_i|,eps), b_j likewise), S = temp*G^,
 // attn = softmax(S), M_b = W_out . blockdiag(attn):
@@ -311,11 +265,15 @@ gelu_gate_bwd_kernel(const void* __restrict__ t, int64_t t_bs, const float* __re
 //   dq = P.k - diag(r).q,  dk = P^T.q - diag(s).k      -> mqk[b] (2C x 2C) so that d[q;k] = mqk[b] . [q;k]
 //   mt[b] = M_b^T                                      -> dv = mt[b] . dout
 // =====================================================================================================
-__global__ void __launch_bounds__(256)
-mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
-                const float* __restrict__ temperature, const float* __restrict__ w_out, const float* __restrict__ dM,
-                float* __restrict__ mt, float* __restrict__ mqk, float* __restrict__ dw_out_part,
-                float* __restrict__ dtemp_part, int C, int d) {
+// Kernel 1 (chain): grid (heads, B), 1024 threads: dattn, softmax / temperature / normalise backward -> mqk, dtemp.
+// Kernel 2 (fold):  grid (ceil(C/32), heads, B), 256 threads: per-sample dW_out and mt for 32 output channels.
+constexpr int MB_THREADS = 1024;
+
+__global__ void __launch_bounds__(MB_THREADS)
+mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
+                      const float* __restrict__ temperature, const float* __restrict__ w_out,
+                      const float* __restrict__ dM, float* __restrict__ mqk, float* __restrict__ dtemp_part, int C,
+                      int d) {
   extern __shared__ float sm[];
   const int D1 = d + 1;
   float* at = sm;                        // attn  [d][d+1]
@@ -325,8 +283,9 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
   float* nb = na + d;                    // b [d]
   float* rs = nb + d;                    // rowsum / r [d]
   float* cs = rs + d;                    // s [d]
-  __shared__ float red[8];
+  __shared__ float red[MB_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  constexpr int NW = MB_THREADS / 32;
   const int h = blockIdx.x, b = blockIdx.y, heads = gridDim.x;
   const size_t per = (size_t)d * d + 2 * d;
   const float* base = partials + ((size_t)b * heads + h) * nslab * per;
@@ -334,13 +293,13 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
   const float* dMb = dM + (size_t)b * C * C;
   const float temp = temperature[h];
 
-  for (int j = tid; j < 2 * d; j += 256) {
+  for (int j = tid; j < 2 * d; j += MB_THREADS) {
     float s = 0.f;
     for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + j];
     na[j] = fmaxf(sqrtf(s), 1e-12f);  // na[d..2d) aliases nb
   }
   __syncthreads();
-  for (int e = tid; e < d * d; e += 256) {
+  for (int e = tid; e < d * d; e += MB_THREADS) {
     const int i = e / d, j = e % d;
     float s = 0.f;
     for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];
@@ -348,23 +307,12 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
     at[i * D1 + j] = a_g[e];
     // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
     float acc = 0.f;
+#pragma unroll 4
     for (int o = 0; o < C; ++o) acc = fmaf(w_out[(size_t)o * C + h * d + i], dMb[(size_t)o * C + h * d + j], acc);
     da[i * D1 + j] = acc;
   }
   __syncthreads();
-  // per-sample dW_out[o][hd+i] = sum_j dM[o][hd+j]*attn[i][j];  mt[b][hd+j][o] = sum_i W[o][hd+i]*attn[i][j]
-  for (int e = tid; e < C * d; e += 256) {
-    const int o = e / d, i = e % d;
-    float s1 = 0.f, s2 = 0.f;
-    for (int j = 0; j < d; ++j) {
-      s1 = fmaf(dMb[(size_t)o * C + h * d + j], at[i * D1 + j], s1);
-      s2 = fmaf(w_out[(size_t)o * C + h * d + j], at[j * D1 + i], s2);   // here "i" plays the role of column j
-    }
-    dw_out_part[((size_t)b * C + o) * C + h * d + i] = s1;
-    mt[((size_t)b * C + h * d + i) * C + o] = s2;
-  }
-  // row sums of dattn o attn
-  for (int i = warp; i < d; i += 8) {
+  for (int i = warp; i < d; i += NW) {  // row sums of dattn o attn
     float s = 0.f;
     for (int j = lane; j < d; j += 32) s += da[i * D1 + j] * at[i * D1 + j];
     s = warp_sum(s);
@@ -372,7 +320,7 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
   }
   __syncthreads();
   float tsum = 0.f;
-  for (int e = tid; e < d * d; e += 256) {
+  for (int e = tid; e < d * d; e += MB_THREADS) {
     const int i = e / d, j = e % d;
     const float dS = at[i * D1 + j] * (da[i * D1 + j] - rs[i]);
     tsum += dS * gh[i * D1 + j];
@@ -383,11 +331,10 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
   __syncthreads();
   if (tid == 0) {
     float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += red[w];
+    for (int w = 0; w < NW; ++w) s += red[w];
     dtemp_part[(size_t)b * heads + h] = s;
   }
-  // r_i, s_j
-  for (int i = warp; i < d; i += 8) {
+  for (int i = warp; i < d; i += NW) {  // r_i, s_j
     float s = 0.f, s2 = 0.f;
     for (int j = lane; j < d; j += 32) {
       s += da[i * D1 + j] * gh[i * D1 + j];
@@ -401,10 +348,10 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
     }
   }
   __syncthreads();
-  // mqk rows of this head: [hd+i] (dq) and [C+hd+j] (dk), full 2C columns
+  // mqk rows of this head: [hd+i] (dq) and [C+hd+i] (dk), full 2C columns
   const int C2 = 2 * C;
   float* mq = mqk + (size_t)b * C2 * C2;
-  for (int e = tid; e < d * C2; e += 256) {
+  for (int e = tid; e < d * C2; e += MB_THREADS) {
     const int i = e / C2, col = e % C2;
     float vq = 0.f, vk = 0.f;
     if (col < C) {
@@ -418,6 +365,65 @@ mdta_bwd_kernel(const float* __restrict__ partials, int nslab, const float* __re
     }
     mq[(size_t)(h * d + i) * C2 + col] = vq;
     mq[(size_t)(C + h * d + i) * C2 + col] = vk;
+  }
+}
+
+// per-sample dW_out[o][hd+i] = sum_j dM[o][hd+j]*attn[i][j];  mt[b][hd+j][o] = sum_i W[o][hd+i]*attn[i][j]
+__global__ void __launch_bounds__(256)
+mdta_bwd_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out, const float* __restrict__ dM,
+                     float* __restrict__ mt, float* __restrict__ dw_out_part, int C, int d) {
+  extern __shared__ float sm[];
+  const int D1 = d + 1;
+  float* at = sm;                          // attn [d][d+1]
+  float* ws = at + (size_t)d * D1;         // W_out[o0..o0+32)[hd..hd+d)   [32][d+1]
+  float* ds = ws + (size_t)32 * D1;        // dM   [o0..o0+32)[hd..hd+d)   [32][d+1]
+  const int tid = threadIdx.x;
+  const int o0 = blockIdx.x * 32, h = blockIdx.y, b = blockIdx.z, heads = gridDim.y;
+  const float* a_g = attn + ((size_t)b * heads + h) * d * d;
+  const float* dMb = dM + (size_t)b * C * C;
+  for (int e = tid; e < d * d; e += 256) at[(e / d) * D1 + e % d] = a_g[e];
+  for (int e = tid; e < 32 * d; e += 256) {
+    const int ol = e / d, i = e % d, o = o0 + ol;
+    ws[ol * D1 + i] = o < C ? w_out[(size_t)o * C + h * d + i] : 0.f;
+    ds[ol * D1 + i] = o < C ? dMb[(size_t)o * C + h * d + i] : 0.f;
+  }
+  __syncthreads();
+  for (int e = tid; e < 32 * d; e += 256) {   // dW_out: threads along i (contiguous in the output row)
+    const int ol = e / d, i = e % d, o = o0 + ol;
+    if (o >= C) continue;
+    float s = 0.f;
+    for (int j = 0; j < d; ++j) s = fmaf(ds[ol * D1 + j], at[i * D1 + j], s);
+    dw_out_part[((size_t)b * C + o) * C + h * d + i] = s;
+  }
+  for (int e = tid; e < 32 * d; e += 256) {   // mt: threads along o (contiguous in the output row)
+    const int j = e / 32, ol = e % 32, o = o0 + ol;
+    if (o >= C) continue;
+    float s = 0.f;
+    for (int i = 0; i < d; ++i) s = fmaf(ws[ol * D1 + i], at[i * D1 + j], s);
+    mt[((size_t)b * C + h * d + j) * C + o] = s;
+  }
+}
+
+// =====================================================================================================
+// im2col for the dense 3x3 weight gradient on tensor cores: y[b][c*9+t][p] = x[b][c][p + shift(t)] (zero padded),
+// bf16 output, so that dW[o][c*9+t] = sum_p dy[o,p]*y[c*9+t,p] is a plain K-major GEMM (wgrad_tc.cu).
+// grid (ceil(HW/256), Cin, B)
+// =====================================================================================================
+__global__ void __launch_bounds__(256)
+im2col3x3_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, bf16* __restrict__ y, int Cin, int H, int W) {
+  const int c = blockIdx.y, b = blockIdx.z;
+  const int64_t HW = (int64_t)H * W;
+  const int64_t p = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (p >= HW) return;
+  const int yy = (int)(p / W), xx = (int)(p % W);
+  const int64_t xo = (int64_t)b * x_bs + (int64_t)c * HW;
+  bf16* yo = y + ((int64_t)b * Cin + c) * 9 * HW + p;
+#pragma unroll
+  for (int t = 0; t < 9; ++t) {
+    const int y2 = yy + t / 3 - 1, x2 = xx + t % 3 - 1;
+    float v = 0.f;
+    if (y2 >= 0 && y2 < H && x2 >= 0 && x2 < W) v = ld_any(x, x_dt, xo + (int64_t)y2 * W + x2);
+    yo[(int64_t)t * HW] = __float2bfloat16_rn(v);
   }
 }
 
@@ -489,7 +495,12 @@ __global__ void l1_loss_bwd_kernel(const void* __restrict__ pred, int p_dt, cons
 // =====================================================================================================
 __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                              float* __restrict__ v, int64_t n, float lr, float beta1, float beta2, float eps, float wd,
-                             float bc1, float bc2_sqrt, float gscale) {
+                             float bc1, float bc2_sqrt, float gscale, const int* __restrict__ step_dev) {
+  if (step_dev) {  // CUDA-graph replay: the step count lives on the device (b200ir_adamw_step, step_dev != NULL)
+    const double st = (double)step_dev[0];
+    bc1 = (float)(1.0 - pow((double)beta1, st));
+    bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, st));
+  }
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const float gi = g[i] * gscale;
     float pi = p[i];
@@ -501,6 +512,9 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
     const float denom = sqrtf(vi) / bc2_sqrt + eps;
     p[i] = pi - (lr / bc1) * (mi / denom);
   }
+}
+__global__ void counter_inc_kernel(int* c) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) c[0] += 1;
 }
 
 static inline int grid_1d(int64_t n, int threads, int cap) {
@@ -521,9 +535,9 @@ extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int 
   B200IR_CHECK_ARG(ln_type == B200IR_LN_WITHBIAS || ln_type == B200IR_LN_BIASFREE, "ln_fwd: bad ln_type %d", ln_type);
   B200IR_CHECK_ARG(ln_type != B200IR_LN_WITHBIAS || ln_b, "ln_fwd: ln_b missing");
   B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(y_dtype), "ln_fwd: bad dtype");
-  const int tps = (int)((HW + 127) / 128);
+  const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
-  ln_fwd_kernel<<<grid_1d(ntiles, 1, 148 * 16), 128, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w,
+  ln_fwd_kernel<<<grid_1d(ntiles, 1, 148 * 16), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w,
                                                                                ln_b, y, y_bstride, y_dtype, C, HW, tps,
                                                                                ntiles);
   return check_launch("ln_fwd");
@@ -531,8 +545,8 @@ extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int 
 
 extern "C" int b200ir_ln_bwd_nparts(int B, int64_t HW) {
   if (B <= 0 || HW <= 0) return B200IR_E_BADARG;
-  const int64_t ntiles = (int64_t)B * ((HW + 127) / 128);
-  return grid_1d(ntiles, 1, 148 * 8);
+  const int64_t ntiles = (int64_t)B * ((HW + LN_PX - 1) / LN_PX);
+  return grid_1d(ntiles, 1, 148 * 4);
 }
 
 extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride,
@@ -545,10 +559,10 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
                    "ln_bwd: bad dtype");
   B200IR_CHECK_ARG(nparts == b200ir_ln_bwd_nparts(B, HW), "ln_bwd: nparts=%d, expected %d", nparts,
                    b200ir_ln_bwd_nparts(B, HW));
-  B200IR_UNSUPPORTED(C <= 1024, "ln_bwd: C=%d > 1024 unsupported", C);
-  const int tps = (int)((HW + 127) / 128);
+  B200IR_UNSUPPORTED(C <= 4096, "ln_bwd: C=%d > 4096 unsupported", C);
+  const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
-  ln_bwd_kernel<<<nparts, 128, (size_t)8 * C * sizeof(float), (cudaStream_t)stream>>>(
+  ln_bwd_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
       x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride, dx_dtype,
       parts, C, HW, tps, ntiles);
   return check_launch("ln_bwd");
@@ -557,7 +571,7 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
 extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride,
                                       b200ir_stream_t stream) {
   B200IR_CHECK_ARG(in && out && n > 0 && K > 0 && stride >= K, "reduce_partials: bad args");
-  reduce_partials_kernel<<<grid_1d(K, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
+  reduce_partials_kernel<<<grid_1d(K, 32, 148 * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
   return check_launch("reduce_partials");
 }
 
@@ -621,26 +635,6 @@ extern "C" int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtyp
   return check_launch("conv_wgrad_simt");
 }
 
-extern "C" int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
-                                      float* parts, int B, int C, int H, int W, b200ir_stream_t stream) {
-  B200IR_CHECK_ARG(dy && x && parts && B > 0 && C > 0 && H > 0 && W > 0 && B <= 65535, "dwconv3x3_wgrad: bad args");
-  B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_wgrad: bad dtype");
-  dwconv_wgrad_kernel<<<dim3((unsigned)C, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(dy, dy_bstride, x, x_bstride,
-                                                                                        dtype, parts, C, H, W);
-  return check_launch("dwconv3x3_wgrad");
-}
-
-extern "C" int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias,
-                                              const void* dg, int64_t dg_bstride, void* da, int64_t da_bstride,
-                                              int dtype, int B, int Hd, int H, int W, b200ir_stream_t stream) {
-  B200IR_CHECK_ARG(t && w && dg && da && B > 0 && Hd > 0 && H > 0 && W > 0, "gelu_gate_bwd: bad args");
-  B200IR_CHECK_ARG(dtype_ok(dtype) && B <= 65535 && Hd <= 65535, "gelu_gate_bwd: bad dtype / grid");
-  dim3 grid((unsigned)(((int64_t)H * W + 255) / 256), (unsigned)Hd, (unsigned)B);
-  gelu_gate_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride,
-                                                               dtype, Hd, H, W);
-  return check_launch("gelu_gate_bwd");
-}
-
 extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const float* temperature,
                                const float* w_out, const float* dM, float* mt, float* mqk, float* dw_out_part,
                                float* dtemp_part, int B, int C, int heads, b200ir_stream_t stream) {
@@ -650,14 +644,29 @@ extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* at
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
   const size_t smem = (3 * (size_t)d * (d + 1) + 4 * (size_t)d) * sizeof(float);
+  const size_t smem2 = ((size_t)d * (d + 1) + 64 * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(mdta_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(mdta_bwd_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    cudaFuncSetAttribute(mdta_bwd_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     attr_set = true;
   }
-  mdta_bwd_kernel<<<dim3((unsigned)heads, (unsigned)B), 256, smem, (cudaStream_t)stream>>>(
-      partials, nslab, attn, temperature, w_out, dM, mt, mqk, dw_out_part, dtemp_part, C, d);
+  mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
+      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d);
+  int rc = check_launch("mdta_bwd_chain");
+  if (rc) return rc;
+  mdta_bwd_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem2,
+                         (cudaStream_t)stream>>>(attn, w_out, dM, mt, dw_out_part, C, d);
   return check_launch("mdta_bwd");
+}
+
+extern "C" int b200ir_im2col3x3(const void* x, int64_t x_bstride, int x_dtype, void* y, int B, int Cin, int H, int W,
+                                b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && y && B > 0 && Cin > 0 && H > 0 && W > 0 && B <= 65535 && Cin <= 65535, "im2col3x3: bad args");
+  B200IR_CHECK_ARG(dtype_ok(x_dtype), "im2col3x3: bad dtype");
+  dim3 grid((unsigned)(((int64_t)H * W + 255) / 256), (unsigned)Cin, (unsigned)B);
+  im2col3x3_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, (bf16*)y, Cin, H, W);
+  return check_launch("im2col3x3");
 }
 
 extern "C" int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B,
@@ -695,12 +704,19 @@ extern "C" int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* 
 }
 
 extern "C" int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
-                                 float beta2, float eps, float weight_decay, int step, float grad_scale,
+                                 float beta2, float eps, float weight_decay, int step, int* step_dev, float grad_scale,
                                  b200ir_stream_t stream) {
-  B200IR_CHECK_ARG(p && g && m && v && n > 0 && step >= 1, "adamw_step: bad args");
-  const double bc1 = 1.0 - pow((double)beta1, (double)step);
-  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  B200IR_CHECK_ARG(p && g && m && v && n > 0 && (step >= 1 || step_dev), "adamw_step: bad args");
+  double bc1 = 1.0, bc2 = 1.0;
+  if (step_dev) {  // ++*step_dev on the stream, then the update reads it: replayable inside a CUDA graph
+    counter_inc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(step_dev);
+    int rc = check_launch("adamw_tick");
+    if (rc) return rc;
+  } else {
+    bc1 = 1.0 - pow((double)beta1, (double)step);
+    bc2 = 1.0 - pow((double)beta2, (double)step);
+  }
   adamw_kernel<<<grid_1d(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(
-      p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale);
+      p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale, step_dev);
   return check_launch("adamw_step");
 }

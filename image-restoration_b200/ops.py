@@ -418,6 +418,16 @@ def conv_wgrad(dy, x, taps=1, per_sample=False, want_bias=False, impl=L.IMPL_AUT
     Cin = x.shape[1]
     if x.shape[0] != B or tuple(x.shape[2:]) != (H, W_):
         raise ValueError("conv_wgrad: dy / x shape mismatch")
+    if (taps == 9 and impl != L.IMPL_SIMT and torch.bfloat16 in (dy.dtype, x.dtype) and (H * W_) % 8 == 0
+            and H * W_ >= 64 and B * Cin * 9 * H * W_ * 2 <= (4 << 30)):
+        # bf16 training path: im2col (bf16) + the tcgen05 GEMM over Cin*9 "channels"
+        x9 = torch.empty((B, Cin * 9, H, W_), device=x.device, dtype=torch.bfloat16)
+        xp, xbs, xdt = _act(x, "x")
+        with _timed("im2col3x3", B, Cin, H, W_, xdt):
+            L.check(lib.b200ir_im2col3x3(xp, xbs, xdt, x9.data_ptr(), B, Cin, H, W_, _stream()), "b200ir_im2col3x3")
+        if dy.dtype != torch.bfloat16:
+            dy = copy_cast(dy, torch.empty(dy.shape, device=dy.device, dtype=torch.bfloat16))
+        return conv_wgrad(dy, x9, 1, per_sample, want_bias, impl)
     dp, dbs, ddt = _act(dy, "dy")
     xp, xbs, xdt = _act(x, "x")
     ns = lib.b200ir_conv_wgrad_nsplit(B, Cout, Cin, taps, H * W_, int(per_sample))
@@ -445,16 +455,18 @@ def dwconv3x3_wgrad(dy, x, want_bias=False):
     xp, xbs, xdt = _act(x, "x")
     if ddt != xdt:
         raise ValueError("dwconv3x3_wgrad: dtype mismatch")
-    parts = torch.empty((B, C, 10), device=x.device, dtype=torch.float32)
+    nparts = lib.b200ir_dwconv3x3_bwd_nparts(B, C, H, W_)
+    parts = torch.empty((nparts, C, 10), device=x.device, dtype=torch.float32)
     with _timed("dwconv3x3_wgrad", B, C, H, W_, xdt):
-        L.check(lib.b200ir_dwconv3x3_wgrad(dp, dbs, xp, xbs, xdt, parts.data_ptr(), B, C, H, W_, _stream()),
+        L.check(lib.b200ir_dwconv3x3_wgrad(dp, dbs, xp, xbs, xdt, parts.data_ptr(), nparts, B, C, H, W_, _stream()),
                 "b200ir_dwconv3x3_wgrad")
-    d = parts.view(C, 10) if B == 1 else reduce_partials(parts, B, C * 10).view(C, 10)
+    d = parts.view(C, 10) if nparts == 1 else reduce_partials(parts, nparts, C * 10).view(C, 10)
     return d[:, :9].reshape(C, 1, 3, 3), (d[:, 9] if want_bias else None)
 
 
-def dwconv3x3_gelu_gate_bwd(t, w, bias, dg):
-    """Gradient w.r.t. the depthwise-conv output (2Hd channels) of the fused dwconv+GELU gate."""
+def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False):
+    """Backward of the fused dwconv+GELU gate: (da [B,2Hd,H,W] = gradient w.r.t. the depthwise-conv output,
+    dw [2Hd,1,3,3], db [2Hd] or None)."""
     B, C2, H, W_ = t.shape
     Hd = C2 // 2
     tp, tbs, tdt = _act(t, "t")
@@ -463,11 +475,14 @@ def dwconv3x3_gelu_gate_bwd(t, w, bias, dg):
         raise ValueError("dwconv3x3_gelu_gate_bwd: dtype mismatch")
     da = torch.empty((B, C2, H, W_), device=t.device, dtype=t.dtype)
     ap, abs_, adt = _act(da, "da")
+    nparts = lib.b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W_)
+    parts = torch.empty((nparts, C2, 10), device=t.device, dtype=torch.float32)
     with _timed("dwconv3x3_gelu_gate_bwd", B, Hd, H, W_, tdt):
         rc = lib.b200ir_dwconv3x3_gelu_gate_bwd(tp, tbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), gp, gbs, ap, abs_,
-                                                tdt, B, Hd, H, W_, _stream())
+                                                tdt, parts.data_ptr(), nparts, B, Hd, H, W_, _stream())
     L.check(rc, "b200ir_dwconv3x3_gelu_gate_bwd")
-    return da
+    d = parts.view(C2, 10) if nparts == 1 else reduce_partials(parts, nparts, C2 * 10).view(C2, 10)
+    return da, d[:, :9].reshape(C2, 1, 3, 3), (d[:, 9] if want_bias else None)
 
 
 def mdta_bwd(partials, attn, temperature, w_out, dM):
@@ -527,11 +542,18 @@ def l1_loss_bwd(pred, target, gscale):
     return grad
 
 
-def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0):
+def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, step_dev=None):
+    """One AdamW update of a flat buffer.  `step_dev` (int32 CUDA tensor [1]) replaces the host `step`: the call
+    increments it on the stream and the kernel derives the bias corrections from it (CUDA-graph replayable)."""
     for t in (p, g, m, v):
         if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda or t.numel() != p.numel():
             raise ValueError("adamw_step: flat contiguous float32 CUDA buffers of equal size expected")
+    if step_dev is not None and (step_dev.dtype != torch.int32 or not step_dev.is_cuda):
+        raise ValueError("adamw_step: step_dev must be an int32 CUDA tensor")
+    global LAUNCHES
+    LAUNCHES += 1 if step_dev is not None else 0
     with _timed("adamw_step", p.numel()):
         rc = lib.b200ir_adamw_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr, beta1, beta2,
-                                   eps, weight_decay, step, grad_scale, _stream())
+                                   eps, weight_decay, step, step_dev.data_ptr() if step_dev is not None else None,
+                                   grad_scale, _stream())
     L.check(rc, "b200ir_adamw_step")

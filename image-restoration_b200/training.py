@@ -65,6 +65,9 @@ class AdamW:
                 p.data = view
                 self.grad_views.append(self.flat_g[o:o + p.numel()].view(p.shape))
         self.step_count = 0
+        # the step count also lives on the device: the update kernel increments and reads it there, so that a captured
+        # CUDA graph of the whole training step replays with the right bias corrections
+        self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
 
     def zero_grad(self, set_to_none: bool = True):
         for p in self.params:
@@ -89,7 +92,7 @@ class AdamW:
             self.gather_grads()
         self.step_count += 1
         ops.adamw_step(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0], self.betas[1],
-                       self.eps, self.weight_decay, self.step_count, grad_scale)
+                       self.eps, self.weight_decay, self.step_count, grad_scale, step_dev=self.step_dev)
         A.bump_param_epoch()   # packed bf16 weight caches key on this (the kernel does not bump tensor versions)
 
     def state_dict(self):
@@ -98,6 +101,7 @@ class AdamW:
 
     def load_state_dict(self, sd):
         self.step_count = int(sd["step"])
+        self.step_dev.fill_(self.step_count)
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
         self.lr, self.betas, self.eps, self.weight_decay = sd["lr"], tuple(sd["betas"]), sd["eps"], sd["weight_decay"]
@@ -129,3 +133,68 @@ def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.
     scale = allreduce_flat_grads(flat_g, group)
     opt.step(grad_scale=scale, gathered=True)
     return loss.detach()
+
+
+class GraphedTrainStep:
+    """The whole training step (forward, L1, backward, gradient gather, [all-reduce], AdamW) captured ONCE in a CUDA
+    graph and replayed per batch: ~2000 kernel launches become one graph launch, which removes the CPU launch bound of
+    small-patch training (cfg4: 128x128 patches).  Shapes are fixed by the example batch.
+
+    With a process group of more than one rank the gradient all-reduce stays outside the graphs (two graphs: everything
+    up to the flat gradient buffer, then AdamW) so that NCCL is called eagerly between them.
+    """
+
+    def __init__(self, net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.Tensor,
+                 loss_fn: Optional[nn.Module] = None, group=None, warmup: int = 2):
+        import torch.distributed as dist
+        self.net, self.opt, self.group = net, opt, group
+        self.loss_fn = loss_fn or L1Loss()
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.degraded = degraded.detach().clone()
+        self.clean = clean.detach().clone()
+        # warm up eagerly on a side stream (lazy inits, cudaFuncSetAttribute, allocator), then restore the state
+        snap = [t.clone() for t in (opt.flat_p, opt.exp_avg, opt.exp_avg_sq, opt.step_dev)]
+        steps0 = opt.step_count
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                train_step(net, opt, self.degraded, self.clean, self.loss_fn, group)
+        torch.cuda.current_stream().wait_stream(side)
+        for dst, src in zip((opt.flat_p, opt.exp_avg, opt.exp_avg_sq, opt.step_dev), snap):
+            dst.copy_(src)
+        opt.step_count = steps0
+        opt.zero_grad()
+        A.bump_param_epoch()
+        torch.cuda.synchronize()
+        self.g1 = torch.cuda.CUDAGraph()
+        self.g2 = None
+        launches0 = ops.LAUNCHES
+        with torch.cuda.graph(self.g1):
+            restored = net(self.degraded)
+            loss = self.loss_fn(restored, self.clean)
+            loss.backward()
+            opt.gather_grads()
+            self.loss = loss.detach()
+            if self.world == 1:
+                opt.step(grad_scale=1.0, gathered=True)
+        if self.world > 1:
+            self.g2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.g2):
+                opt.step(grad_scale=1.0 / self.world, gathered=True)
+        # the capture itself did not execute anything: undo the host-side step bookkeeping of the captured step()
+        opt.step_count = steps0
+        self.launches_per_step = ops.LAUNCHES - launches0   # libb200ir kernels inside the graph(s)
+
+    def __call__(self, degraded: torch.Tensor, clean: torch.Tensor) -> torch.Tensor:
+        self.degraded.copy_(degraded, non_blocking=True)
+        self.clean.copy_(clean, non_blocking=True)
+        self.g1.replay()
+        if self.g2 is not None:
+            import torch.distributed as dist
+            dist.all_reduce(self.opt.flat_g, op=dist.ReduceOp.SUM, group=self.group)
+            self.g2.replay()
+        self.opt.step_count += 1
+        ops.LAUNCHES += self.launches_per_step
+        A.bump_param_epoch()   # parameters changed under the packed-weight caches
+        return self.loss

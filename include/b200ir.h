@@ -149,14 +149,21 @@ int b200ir_conv_wgrad_nsplit(int B, int Cout, int Cin, int taps, int64_t HW, int
 int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtype, const void* x, int64_t x_bstride, int x_dtype,
                       float* parts_w, float* parts_b, int nsplit, int B, int Cout, int Cin, int H, int W, int taps,
                       int per_sample, int impl, b200ir_stream_t stream);
-/* Depthwise 3x3 weight/bias gradient: parts fp32 [B][C][10] (9 taps + bias), reduce over B with reduce_partials. */
+/* y bf16 [B,Cin*9,H*W]: y[b][c*9+t][p] = x[b][c][p+shift(t)] (zero padded) — turns the dense 3x3 weight gradient into
+ * b200ir_conv_wgrad(taps=1) over Cin*9 channels so that it runs on the tcgen05 kernel. */
+int b200ir_im2col3x3(const void* x, int64_t x_bstride, int x_dtype, void* y, int B, int Cin, int H, int W,
+                     b200ir_stream_t stream);
+/* Depthwise 3x3 weight/bias gradient (csrc/dw_backward.cu): parts fp32 [nparts][C][10] (9 taps + bias) with
+ * nparts = b200ir_dwconv3x3_bwd_nparts(B, C, H, W); fold with b200ir_reduce_partials. */
+int b200ir_dwconv3x3_bwd_nparts(int B, int C, int H, int W);
 int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
-                           float* parts, int B, int C, int H, int W, b200ir_stream_t stream);
-/* Backward of b200ir_dwconv3x3_gelu_gate_fwd w.r.t. the depthwise-conv OUTPUT (recomputed from t): da [B,2Hd,H,W]
- * from t [B,2Hd,H,W] and dg [B,Hd,H,W]; dt / dw then follow from b200ir_dwconv3x3_fwd (flipped w) / _wgrad. */
+                           float* parts, int nparts, int B, int C, int H, int W, b200ir_stream_t stream);
+/* Backward of b200ir_dwconv3x3_gelu_gate_fwd w.r.t. the depthwise-conv OUTPUT (recomputed from t) fused with the
+ * depthwise weight/bias gradient: da [B,2Hd,H,W] from t [B,2Hd,H,W] and dg [B,Hd,H,W]; parts fp32 [nparts][2Hd][10]
+ * with nparts = b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W).  dt then follows from b200ir_dwconv3x3_fwd (flipped w). */
 int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
-                                   int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, int B, int Hd, int H,
-                                   int W, b200ir_stream_t stream);
+                                   int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, float* parts,
+                                   int nparts, int B, int Hd, int H, int W, b200ir_stream_t stream);
 /* MDTA backward, small per-(sample, head) part (softmax, temperature, F.normalize; Restormer.py:121-131).
  * In: Gram partials + attn of the forward, dM [B,C,C] (= conv_wgrad(dout, v, per_sample)).
  * Out: mt [B,C,C] = M_b^T (dv = mt_b.dout), mqk [B,2C,2C] (d[q;k] = mqk_b.[q;k]), dw_out_part [B,C,C] and
@@ -173,9 +180,12 @@ int b200ir_l1_loss_fwd(const void* pred, int pred_dtype, const void* target, int
 int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
                        const float* gscale, void* grad, int grad_dtype, b200ir_stream_t stream);
 /* torch.optim.AdamW step on one flat fp32 buffer (MoCE-IR-main/src/train.py:83); g is scaled by grad_scale first
- * (1/world_size after a sum all-reduce). */
+ * (1/world_size after a sum all-reduce).  The step count (bias correction) is either the host value `step` (>= 1,
+ * step_dev NULL) or a device counter `step_dev` that this call increments on the stream before the update — the form
+ * that can be captured in a CUDA graph and replayed. */
 int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
-                      float eps, float weight_decay, int step, float grad_scale, b200ir_stream_t stream);
+                      float eps, float weight_decay, int step, int* step_dev, float grad_scale,
+                      b200ir_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -18,6 +18,7 @@ def main():
     ap.add_argument("--dtype", default="bf16")
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--breakdown", action="store_true")
+    ap.add_argument("--graph", action="store_true")
     a = ap.parse_args()
     torch.manual_seed(0)
     net = b200ir.Restormer().cuda()
@@ -27,14 +28,15 @@ def main():
     clean = torch.rand(a.batch, 3, a.size, a.size, generator=g)
     deg = (clean + 25 / 255 * torch.randn(clean.shape, generator=g)).clamp(0, 1).cuda()
     clean = clean.cuda()
+    step = b200ir.GraphedTrainStep(net, opt, deg, clean) if a.graph else (lambda d, c: b200ir.train_step(net, opt, d, c))
     for _ in range(2):
-        loss = b200ir.train_step(net, opt, deg, clean)
+        loss = step(deg, clean)
     torch.cuda.synchronize()
     l0 = ops.LAUNCHES
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(a.steps):
-        loss = b200ir.train_step(net, opt, deg, clean)
+        loss = step(deg, clean)
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / a.steps
