@@ -191,13 +191,43 @@ static int dw_nsplit(int B, int C, int H, int W) {
   return (int)want;
 }
 
+// dw_backward_tma.cu (bf16 fast path)
+bool dw_bwd_tma_shape_ok(int H, int W);
+int dw_bwd_tma_tiles_per_plane(int H, int W);
+template <bool GATE>
+int dw_bwd_tma_launch(const void* x, int64_t x_bs, const void* g, int64_t g_bs, void* da, int64_t da_bs, const float* w,
+                      const float* bias, float* parts, int B, int Cout, int H, int W, cudaStream_t st);
+
+static bool dw_tma_ok(int dtype, int H, int W, const void* a, int64_t a_bs, const void* b, int64_t b_bs, const void* c,
+                      int64_t c_bs) {
+  auto al = [](const void* p, int64_t bs) { return !p || (((uintptr_t)p % 16) == 0 && bs % 8 == 0); };
+  return dtype == B200IR_BF16 && dw_bwd_tma_shape_ok(H, W) && al(a, a_bs) && al(b, b_bs) && al(c, c_bs);
+}
+
+// parts beyond the ones the chosen kernel writes are zeroed, so the caller always folds `nparts` parts
+static int zero_tail(float* parts, int nparts, int used, int64_t per_part, cudaStream_t st) {
+  if (nparts > used) {
+    cudaError_t e = cudaMemsetAsync(parts + (size_t)used * per_part, 0, (size_t)(nparts - used) * per_part * sizeof(float), st);
+    if (e != cudaSuccess) {
+      set_error("dw backward: cudaMemsetAsync: %s", cudaGetErrorString(e));
+      return (int)e;
+    }
+  }
+  return 0;
+}
+
 }  // namespace b200ir
 
 using namespace b200ir;
 
 extern "C" int b200ir_dwconv3x3_bwd_nparts(int B, int C, int H, int W) {
   if (B <= 0 || C <= 0 || H <= 0 || W <= 0) return B200IR_E_BADARG;
-  return B * dw_nsplit(B, C, H, W);
+  int n = dw_nsplit(B, C, H, W);
+  if (dw_bwd_tma_shape_ok(H, W)) {
+    const int t = dw_bwd_tma_tiles_per_plane(H, W);
+    if (t > n) n = t;
+  }
+  return B * n;   // capacity: whichever kernel runs writes <= this many parts and zero-fills the rest
 }
 
 extern "C" int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
@@ -205,11 +235,20 @@ extern "C" int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const 
   B200IR_CHECK_ARG(dy && x && parts && B > 0 && C > 0 && H > 0 && W > 0 && B <= 65535 && C <= 65535,
                    "dwconv3x3_wgrad: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_wgrad: bad dtype");
+  B200IR_CHECK_ARG(nparts == b200ir_dwconv3x3_bwd_nparts(B, C, H, W),
+                   "dwconv3x3_wgrad: nparts=%d, expected %d (b200ir_dwconv3x3_bwd_nparts)", nparts,
+                   b200ir_dwconv3x3_bwd_nparts(B, C, H, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dw_tma_ok(dtype, H, W, dy, dy_bstride, x, x_bstride, nullptr, 0)) {
+    int rc = zero_tail(parts, nparts, B * dw_bwd_tma_tiles_per_plane(H, W), (int64_t)C * 10, st);
+    if (rc) return rc;
+    return dw_bwd_tma_launch<false>(x, x_bstride, dy, dy_bstride, nullptr, 0, nullptr, nullptr, parts, B, C, H, W, st);
+  }
   const int ns = dw_nsplit(B, C, H, W);
-  B200IR_CHECK_ARG(nparts == B * ns, "dwconv3x3_wgrad: nparts=%d, expected %d (b200ir_dwconv3x3_bwd_nparts)", nparts,
-                   B * ns);
-  dwconv_wgrad_tile_kernel<<<dim3((unsigned)ns, (unsigned)C, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(
-      dy, dy_bstride, x, x_bstride, dtype, parts, C, H, W);
+  int rc = zero_tail(parts, nparts, B * ns, (int64_t)C * 10, st);
+  if (rc) return rc;
+  dwconv_wgrad_tile_kernel<<<dim3((unsigned)ns, (unsigned)C, (unsigned)B), 256, 0, st>>>(dy, dy_bstride, x, x_bstride,
+                                                                                         dtype, parts, C, H, W);
   return check_launch("dwconv3x3_wgrad");
 }
 
@@ -219,10 +258,19 @@ extern "C" int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, 
                                               b200ir_stream_t stream) {
   B200IR_CHECK_ARG(t && w && dg && da && parts && B > 0 && Hd > 0 && H > 0 && W > 0, "gelu_gate_bwd: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype) && B <= 65535 && Hd <= 65535, "gelu_gate_bwd: bad dtype / grid");
+  B200IR_CHECK_ARG(nparts == b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W),
+                   "gelu_gate_bwd: nparts=%d, expected %d (b200ir_dwconv3x3_bwd_nparts with C=Hd)", nparts,
+                   b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dw_tma_ok(dtype, H, W, t, t_bstride, dg, dg_bstride, da, da_bstride)) {
+    int rc = zero_tail(parts, nparts, B * dw_bwd_tma_tiles_per_plane(H, W), (int64_t)Hd * 20, st);
+    if (rc) return rc;
+    return dw_bwd_tma_launch<true>(t, t_bstride, dg, dg_bstride, da, da_bstride, w, bias, parts, B, Hd, H, W, st);
+  }
   const int ns = dw_nsplit(B, Hd, H, W);
-  B200IR_CHECK_ARG(nparts == B * ns, "gelu_gate_bwd: nparts=%d, expected %d (b200ir_dwconv3x3_bwd_nparts with C=Hd)",
-                   nparts, B * ns);
-  gelu_gate_bwd_tile_kernel<<<dim3((unsigned)ns, (unsigned)Hd, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(
+  int rc = zero_tail(parts, nparts, B * ns, (int64_t)Hd * 20, st);
+  if (rc) return rc;
+  gelu_gate_bwd_tile_kernel<<<dim3((unsigned)ns, (unsigned)Hd, (unsigned)B), 256, 0, st>>>(
       t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride, dtype, parts, Hd, H, W);
   return check_launch("gelu_gate_bwd");
 }

@@ -346,3 +346,46 @@ def test_graphed_train_step_matches_eager(b200ir):
     # eval forward after graphed training sees the updated weights (packed-weight caches are invalidated)
     with torch.no_grad():
         assert torch.equal(net_e(deg), net_g(deg))
+
+
+@pytest.mark.parametrize("Hd,H,W,bias", [(31, 64, 64, False), (20, 24, 136, True), (8, 130, 256, True), (127, 16, 72, False)])
+def test_gelu_gate_backward_bf16_tma(b200ir, Hd, H, W, bias):
+    """bf16 fast path (TMA-staged tiles, fitted cdf) of the gate backward + fused depthwise weight gradient against
+    fp32 autograd on the same bf16-rounded inputs."""
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(15)
+    x = torch.randn(2, 2 * Hd, H, W, generator=g).bfloat16()
+    w = torch.randn(2 * Hd, 1, 3, 3, generator=g) * 0.3
+    b = torch.randn(2 * Hd, generator=g) * 0.2 if bias else None
+    gy = torch.randn(2, Hd, H, W, generator=g).bfloat16()
+    ins = [x.float().requires_grad_(True), w.clone().requires_grad_(True)] + ([b.clone().requires_grad_(True)] if bias else [])
+    t = F.conv2d(ins[0], ins[1], ins[2] if bias else None, padding=1, groups=2 * Hd)
+    x1, x2 = t.chunk(2, dim=1)
+    refg = torch.autograd.grad(F.gelu(x1) * x2, ins, gy.float())
+    xs, ws = leaf(x), leaf(w)
+    bs = leaf(b) if bias else None
+    A.dwconv3x3_gelu_gate(xs, ws, bs).backward(gy.cuda())
+    assert rel(xs.grad.float(), refg[0]) < 1e-2
+    assert rel(ws.grad, refg[1]) < 1e-2
+    if bias:
+        assert rel(bs.grad, refg[2]) < 1e-2
+
+
+@pytest.mark.parametrize("C,H,W,bias", [(24, 64, 64, False), (30, 24, 136, True), (9, 130, 256, True)])
+def test_dwconv_backward_bf16_tma(b200ir, C, H, W, bias):
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(16)
+    x = torch.randn(2, C, H, W, generator=g).bfloat16()
+    w = torch.randn(C, 1, 3, 3, generator=g) * 0.3
+    b = torch.randn(C, generator=g) if bias else None
+    gy = torch.randn(2, C, H, W, generator=g).bfloat16()
+    ins = [x.float().requires_grad_(True), w.clone().requires_grad_(True)] + ([b.clone().requires_grad_(True)] if bias else [])
+    y = F.conv2d(ins[0], ins[1], ins[2] if bias else None, padding=1, groups=C)
+    refg = torch.autograd.grad(y, ins, gy.float())
+    xs, ws = leaf(x), leaf(w)
+    bs = leaf(b) if bias else None
+    A.dwconv3x3(xs, ws, bs).backward(gy.cuda())
+    assert rel(xs.grad.float(), refg[0]) < 1e-2
+    assert rel(ws.grad, refg[1]) < 2e-3
+    if bias:
+        assert rel(bs.grad, refg[2]) < 2e-3
