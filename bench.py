@@ -135,6 +135,7 @@ def main():
     ap.add_argument("--batch", type=int, default=BATCH)
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-train", action="store_true", help="skip the cfg4 training-step leg")
     ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -214,6 +215,35 @@ def main():
             torch.cuda.synchronize()
             table = ops.timing_stop()
 
+    # ---- training-step leg (BASELINE configs[3]): L1 + AdamW, 128x128 patches, batch 8 per GPU, DDP all-reduce --------
+    train = None
+    if not args.no_train:
+        del dev_in
+        torch.cuda.empty_cache()
+        TB, TS = 8, 128
+        tnet = b200ir.Restormer().to(dev).set_compute_dtype(cd)
+        tnet.load_state_dict(O.synth_state_dict({}, seed=0), strict=True)
+        opt = b200ir.AdamW(tnet.parameters(), lr=2e-4)
+        tg = torch.Generator().manual_seed(4321 + rank)
+        cleans = [torch.rand(TB, 3, TS, TS, generator=tg).to(dev) for _ in range(4)]
+        degs = [(c + 25.0 / 255.0 * torch.randn(c.shape, generator=tg).to(dev)).clamp(0, 1) for c in cleans]
+        step = b200ir.GraphedTrainStep(tnet, opt, degs[0], cleans[0])
+        for i in range(args.warmup):
+            step(degs[i % 4], cleans[i % 4])
+        barrier()
+        e0.record()
+        for i in range(args.steps):
+            loss = step(degs[i % 4], cleans[i % 4])
+        e1.record()
+        barrier()
+        ms_tr = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        train = {"workload": f"Restormer training step (L1 + AdamW lr=2e-4), {TS}x{TS} patches, batch {TB}/GPU, "
+                             f"{'DDP sum all-reduce of the flat fp32 gradient buffer (NCCL)' if world > 1 else 'single GPU'}"
+                             f"; BASELINE configs[3]; whole step replayed from one CUDA graph",
+                 "value": world * TB * TS * TS / 1e6 / (ms_tr * 1e-3), "unit": "MP/s", "ms_per_step": ms_tr,
+                 "gpu_launches_per_step": step.launches_per_step, "loss": float(loss.item()),
+                 "allreduce_bytes_per_step": opt.numel * 4 if world > 1 else 0}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -242,6 +272,8 @@ def main():
                 "h2d_bytes_per_step": B * 3 * H * W * 4, "d2h_bytes_per_step": B * 3 * H * W * 4},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline,
     }
+    if train is not None:
+        out["train_step"] = train
     if not args.no_cpu_baseline:
         v, dt, cores, sample = cpu_reference_run(2, 1)
         out["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample,

@@ -83,11 +83,11 @@ def dwconv3x3_gelu_gate(x, w, bias):
     return ops.dwconv3x3_gelu_gate(x, _p(w), _p(bias))
 
 
-def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None):
+def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None, cache=None):
     """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147)."""
     if _needs_grad(qkv, temperature, w_out, b_out, res):
-        return _MdtaCore.apply(qkv, temperature, w_out, b_out, res, heads)
-    return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out)[0]
+        return _MdtaCore.apply(qkv, temperature, w_out, b_out, res, heads, cache)
+    return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out, cache)[0]
 
 
 def _per_sample_gemm(x, m, bias, res, out=None):
@@ -99,7 +99,7 @@ def _per_sample_gemm(x, m, bias, res, out=None):
     return ops.ln_conv1x1(x, m, bias, L.LN_NONE, None, None, res, out=out, per_sample_w=True)
 
 
-def _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out=None, want_saved=False):
+def _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out=None, cache=None):
     B, C3, H, W = qkv.shape
     C = C3 // 3
     partials = ops.mdta_gram(qkv, heads)
@@ -107,28 +107,26 @@ def _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out=None, want_sa
     if USE_TC and ops.gemm_tc_usable(v, C):
         mp, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), packed=True,
                                          want_attn=True)
-        y = ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device)), C, L.LN_NONE, res, out=out)
+        y = ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device, cache)), C, L.LN_NONE, res, out=out)
     else:
         m, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), want_attn=True)
         y = ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
     return y, partials, attn
 
 
-_ST_CACHE = {}
-
-
-def _bias_st(bias, C, nrows, device):
-    """(s, t) epilogue vectors of the per-sample GEMM: s unused (no LayerNorm), t = project_out bias."""
-    key = (PARAM_EPOCH, None if bias is None else (bias.data_ptr(), bias._version), C, nrows, str(device))
-    st = _ST_CACHE.get(key)
-    if st is None:
-        if len(_ST_CACHE) > 4096:
-            _ST_CACHE.clear()
+def _bias_st(bias, C, nrows, device, cache=None):
+    """(s, t) epilogue vectors of the per-sample GEMM: s unused (no LayerNorm), t = project_out bias.  Cached only in
+    the owning module's cache (a tensor's address alone does not identify it once it has been freed)."""
+    sig = _sig(bias) + (C, nrows)
+    ent = cache.get("bias_st") if cache is not None else None
+    if ent is None or ent[0] != sig:
         st = torch.zeros((2, nrows), device=device, dtype=torch.float32)
         if bias is not None:
             st[1, :C] = bias.detach().float()
-        _ST_CACHE[key] = st
-    return st
+        ent = (sig, st)
+        if cache is not None:
+            cache["bias_st"] = ent
+    return ent[1]
 
 
 def conv3x3(x, w, bias, res, shuffle, out=None, out_dtype=None, cache=None, key=None):
@@ -241,8 +239,8 @@ class _MdtaCore(torch.autograd.Function):
     """F.normalize + q.k^T*temperature + softmax + attn.v + project_out + residual (Restormer.py:117-131,147)."""
 
     @staticmethod
-    def forward(ctx, qkv, temperature, w_out, b_out, res, heads):
-        y, partials, attn = _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res)
+    def forward(ctx, qkv, temperature, w_out, b_out, res, heads, cache=None):
+        y, partials, attn = _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, None, cache)
         ctx.save_for_backward(qkv, temperature, w_out, partials, attn)
         ctx.has_bias, ctx.has_res, ctx.heads = b_out is not None, res is not None, heads
         return y
@@ -261,7 +259,7 @@ class _MdtaCore(torch.autograd.Function):
         _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
         _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])
         return (dqkv, dtemp.view(temperature.shape).to(temperature.dtype), dw.view(w_out.shape).to(w_out.dtype), db,
-                dout if ctx.has_res else None, None)
+                dout if ctx.has_res else None, None, None)
 
 
 class _Conv3x3(torch.autograd.Function):

@@ -122,7 +122,7 @@ class Attention(nn.Module):
         qkv = A.dwconv3x3(t, self.qkv_dwconv.weight, self.qkv_dwconv.bias)
         del t
         return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
-                           res, out=out)
+                           res, out=out, cache=cache)
 
     def forward(self, x):
         return self._run(x)
