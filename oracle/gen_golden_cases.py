@@ -18,3 +18,13 @@ NET_CASES = [
 ]
 
 
+
+# backward / training-step fixtures (oracle/gen_golden_train.py)
+# (name, dim, heads, ffn_factor, bias, ln_type, B, H, W, seed)
+TRAIN_BLOCK_CASES = [
+    ("train_blk_c48_h1", 48, 1, 2.66, False, "WithBias", 2, 8, 16, 31),
+    ("train_blk_c32_h2_bias_biasfree", 32, 2, 2.0, True, "BiasFree", 1, 8, 8, 32),
+]
+# (name, cfg-overrides, B, H, W, weight seed, image seed, steps)
+TRAIN_NET_CASE = ("train_net_dim8_16", dict(dim=8, num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, heads=[1, 2, 4, 8]),
+                  2, 16, 16, 9, 41, 3)

@@ -389,3 +389,44 @@ def test_dwconv_backward_bf16_tma(b200ir, C, H, W, bias):
     assert rel(ws.grad, refg[1]) < 2e-3
     if bias:
         assert rel(bs.grad, refg[2]) < 2e-3
+
+
+def test_train_steps_match_reference_golden(b200ir):
+    """fp32 CUDA path vs the stored outputs of the REFERENCE's own training loop (tests/golden/train_net_*.npz, made by
+    oracle/gen_golden_train.py from /root/reference/Restormer.py + torch.optim.AdamW)."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle.gen_golden_cases import TRAIN_NET_CASE
+    name, cfgo, b, h, w, wseed, iseed, steps = TRAIN_NET_CASE
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    cfg = dict(O.DEFAULT_CFG)
+    cfg.update(cfgo)
+    clean = O.synth_image(b, h, w, seed=iseed)
+    noise = torch.randn(clean.shape, generator=torch.Generator().manual_seed(iseed + 1)) * (25.0 / 255.0)
+    degraded = (clean + noise).clamp(0, 1)
+    net = b200ir.Restormer(**cfg).cuda()
+    net.load_state_dict(O.synth_state_dict(cfgo, seed=wseed), strict=True)
+    opt = b200ir.AdamW(net.parameters(), lr=2e-4)
+    losses = [b200ir.train_step(net, opt, degraded.cuda(), clean.cuda()).item() for _ in range(steps)]
+    assert np.allclose(losses, gold["losses"], rtol=0, atol=1e-5), (losses, gold["losses"])
+    for n, q in net.named_parameters():
+        close32(q.grad, torch.from_numpy(gold["g_" + n]), 1e-3)
+        assert (q.detach().cpu() - torch.from_numpy(gold["p_" + n])).abs().max() <= 2 * 2e-4 + 1e-6, n
+
+
+def test_block_grads_match_reference_golden(b200ir):
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle.gen_golden_cases import TRAIN_BLOCK_CASES
+    for name, dim, heads, f, bias, ln, b, h, w, seed in TRAIN_BLOCK_CASES:
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+        blk = b200ir.TransformerBlock(dim, heads, f, bias, ln).cuda()
+        blk.load_state_dict(O.synth_block_params(dim, heads, f, bias, ln, seed), strict=True)
+        xs = leaf(O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1)
+        gy = torch.randn(b, dim, h, w, generator=torch.Generator().manual_seed(seed + 200))
+        blk(xs).backward(gy.cuda())
+        close32(xs.grad, torch.from_numpy(gold["dx"]))
+        for n, q in blk.named_parameters():
+            close32(q.grad, torch.from_numpy(gold["d_" + n]))

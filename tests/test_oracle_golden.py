@@ -69,3 +69,37 @@ def test_fp64_oracle_close_to_fp32():
     y32 = O.transformer_block(x, p, "", 1)
     y64 = O.transformer_block(x.double(), {k: v.double() for k, v in p.items()}, "", 1)
     assert (y32.double() - y64).abs().max() < 1e-5
+
+
+# ---- backward / training-step oracle pinned against the reference's own autograd + torch.optim.AdamW ----------------
+def test_oracle_block_grads_match_reference():
+    import numpy as np
+    from oracle.gen_golden_cases import TRAIN_BLOCK_CASES
+    for name, dim, heads, f, bias, ln, b, h, w, seed in TRAIN_BLOCK_CASES:
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+        p = O.synth_block_params(dim, heads, f, bias, ln, seed)
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        gy = torch.randn(b, dim, h, w, generator=torch.Generator().manual_seed(seed + 200))
+        _, dx, dp = O.block_grads(x, p, heads, gy)
+        ref = torch.from_numpy(gold["dx"])
+        assert (dx - ref).abs().max() <= 1e-5 * ref.abs().max().clamp_min(1)
+        assert {"d_" + n for n in dp} == {k for k in gold.files if k != "dx"}
+        for n, g in dp.items():
+            ref = torch.from_numpy(gold["d_" + n])
+            assert (g - ref).abs().max() <= 2e-5 * ref.abs().max().clamp_min(1e-3), (name, n)
+
+
+def test_oracle_train_step_matches_reference():
+    import numpy as np
+    from oracle.gen_golden_cases import TRAIN_NET_CASE
+    name, cfg, b, h, w, wseed, iseed, steps = TRAIN_NET_CASE
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    clean = O.synth_image(b, h, w, seed=iseed)
+    noise = torch.randn(clean.shape, generator=torch.Generator().manual_seed(iseed + 1)) * (25.0 / 255.0)
+    degraded = (clean + noise).clamp(0, 1)
+    losses, grads, new_sd = O.train_step_reference(O.synth_state_dict(cfg, seed=wseed), cfg, degraded, clean, steps=steps)
+    assert np.allclose(losses, gold["losses"], rtol=0, atol=1e-6)
+    for n in grads:
+        ref = torch.from_numpy(gold["g_" + n])
+        assert (grads[n] - ref).abs().max() <= 1e-4 * ref.abs().max().clamp_min(1e-6), n
+        assert (new_sd[n] - torch.from_numpy(gold["p_" + n])).abs().max() <= 1e-6, n
