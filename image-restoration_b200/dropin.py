@@ -1,0 +1,206 @@
+"""``accelerate(model)``: swap the Restormer-family pieces of an EXISTING reference model for the B200 kernels, in place.
+
+The reference repo holds ~70 copies of the same block under different wrappers (Restormer.py, moce_ir.py / MoCE-IR-main,
+AdaIR-main/net/model.py, the experiment/*Rectiformer variants — SURVEY.md §2.3).  Instead of mirroring every wrapper,
+this walks any ``nn.Module`` tree and replaces, by STRUCTURE (attribute names + parameter shapes, never by class
+identity, so nothing of the reference is imported here):
+
+  * blocks  ``norm1, attn, norm2, ffn``          (Restormer.TransformerBlock, Restormer.py:137-150)
+  * blocks  ``norms[0..1], mixer, ffn``          (moce_ir.EncoderBlock, moce_ir.py:805-834)
+  * MDTA    ``temperature, qkv, qkv_dwconv, project_out``   (Attention, Restormer.py:99-132)
+  * GDFN    ``project_in, dwconv, project_out``             (FeedForward, Restormer.py:76-93)
+  * LayerNorm wrappers with a ``body`` holding ``weight`` (and ``bias``)   (Restormer.py:60-70)
+  * ``Downsample`` / ``Upsample`` = Sequential(conv3x3 no-bias, PixelUnshuffle/PixelShuffle(2))  (Restormer.py:171-189)
+
+The replacement adopts the reference's own ``nn.Conv2d`` / LayerNorm-body sub-modules, so ``state_dict()`` keys, the
+optimizer's parameter objects and checkpoints are unchanged.  Variants that carry the same attribute names but a
+different forward (gates, dynamic temperature ...) are caught by ``verify=True``: every candidate is run against the
+original on a random input (fp32, on the model's CUDA device) and only swapped if the outputs agree.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Tuple
+
+import torch
+import torch.nn as nn
+
+from . import modules as M
+
+
+def _conv_ok(c, k, groups=None):
+    return (isinstance(c, nn.Conv2d) and c.kernel_size == (k, k) and c.stride == (1, 1) and c.dilation == (1, 1)
+            and c.padding == (k // 2, k // 2) and c.padding_mode == "zeros"
+            and (groups is None or c.groups == groups))
+
+
+def _is_ln(m) -> bool:
+    body = getattr(m, "body", None)
+    if body is None or not isinstance(body, nn.Module) or isinstance(body, nn.Sequential):
+        return False
+    names = {n for n, _ in body.named_parameters()}
+    w = getattr(body, "weight", None)
+    return names in ({"weight"}, {"weight", "bias"}) and w is not None and w.dim() == 1 and \
+        {n for n, _ in m.named_parameters()} == {"body." + n for n in names}
+
+
+def _is_mdta(m) -> bool:
+    need = ("temperature", "qkv", "qkv_dwconv", "project_out", "num_heads")
+    if not all(hasattr(m, a) for a in need):
+        return False
+    pn = {n.split(".")[0] for n, _ in m.named_parameters()}
+    if pn != {"temperature", "qkv", "qkv_dwconv", "project_out"}:
+        return False
+    c3 = m.qkv.out_channels
+    return (_conv_ok(m.qkv, 1, 1) and _conv_ok(m.qkv_dwconv, 3, c3) and _conv_ok(m.project_out, 1, 1)
+            and c3 == 3 * m.qkv.in_channels and m.qkv_dwconv.in_channels == c3
+            and m.project_out.in_channels == m.qkv.in_channels == m.project_out.out_channels
+            and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and m.qkv.in_channels % m.num_heads == 0)
+
+
+def _is_gdfn(m) -> bool:
+    if not all(hasattr(m, a) for a in ("project_in", "dwconv", "project_out")):
+        return False
+    pn = {n.split(".")[0] for n, _ in m.named_parameters()}
+    if pn != {"project_in", "dwconv", "project_out"}:
+        return False
+    h2 = m.project_in.out_channels
+    return (_conv_ok(m.project_in, 1, 1) and _conv_ok(m.dwconv, 3, h2) and _conv_ok(m.project_out, 1, 1)
+            and h2 % 2 == 0 and m.dwconv.in_channels == h2 and m.project_out.in_channels == h2 // 2
+            and m.project_out.out_channels == m.project_in.in_channels)
+
+
+def _is_resize(m):
+    """Sequential(conv3x3 (no bias), PixelUnshuffle(2) | PixelShuffle(2)) wrapped as `.body` -> 'down' | 'up' | None."""
+    body = getattr(m, "body", None)
+    if not isinstance(body, nn.Sequential) or len(body) != 2 or not _conv_ok(body[0], 3, 1) or body[0].bias is not None:
+        return None
+    if {n for n, _ in m.named_parameters()} != {"body.0.weight"}:
+        return None
+    if isinstance(body[1], nn.PixelUnshuffle) and body[1].downscale_factor == 2:
+        return "down"
+    if isinstance(body[1], nn.PixelShuffle) and body[1].upscale_factor == 2:
+        return "up"
+    return None
+
+
+def _bare(cls):
+    obj = cls.__new__(cls)
+    nn.Module.__init__(obj)
+    return obj
+
+
+def _adopt_ln(m):
+    ln = _bare(M.LayerNorm)
+    ln.body = m.body
+    ln._eye = None
+    return ln
+
+
+def _adopt_mdta(m):
+    a = _bare(M.Attention)
+    a.num_heads = m.num_heads
+    a.temperature = m.temperature
+    a.qkv, a.qkv_dwconv, a.project_out = m.qkv, m.qkv_dwconv, m.project_out
+    return a
+
+
+def _adopt_gdfn(m):
+    f = _bare(M.FeedForward)
+    f.project_in, f.dwconv, f.project_out = m.project_in, m.dwconv, m.project_out
+    return f
+
+
+def _adopt(m):
+    """-> (replacement, kind) or (None, None)."""
+    if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.FeedForward, M.LayerNorm, M.Downsample,
+                      M.Upsample)):
+        return None, None
+    kids = dict(m.named_children())
+    if set(kids) == {"norm1", "attn", "norm2", "ffn"} and _is_ln(m.norm1) and _is_ln(m.norm2) and _is_mdta(m.attn) \
+            and _is_gdfn(m.ffn) and not list(m.named_parameters(recurse=False)):
+        b = _bare(M.TransformerBlock)
+        b.norm1, b.attn, b.norm2, b.ffn = _adopt_ln(m.norm1), _adopt_mdta(m.attn), _adopt_ln(m.norm2), _adopt_gdfn(m.ffn)
+        return b, "block"
+    if set(kids) == {"norms", "mixer", "ffn"} and isinstance(m.norms, nn.ModuleList) and len(m.norms) == 2 \
+            and all(_is_ln(n) for n in m.norms) and _is_mdta(m.mixer) and _is_gdfn(m.ffn) \
+            and not list(m.named_parameters(recurse=False)):
+        b = _bare(M.EncoderBlock)
+        b.norms = nn.ModuleList([_adopt_ln(m.norms[0]), _adopt_ln(m.norms[1])])
+        b.mixer, b.ffn = _adopt_mdta(m.mixer), _adopt_gdfn(m.ffn)
+        return b, "encoder_block"
+    if _is_mdta(m):
+        return _adopt_mdta(m), "attention"
+    if _is_gdfn(m):
+        return _adopt_gdfn(m), "feedforward"
+    if _is_ln(m):
+        return _adopt_ln(m), "layernorm"
+    rz = _is_resize(m)
+    if rz:
+        r = _bare(M.Downsample if rz == "down" else M.Upsample)
+        r.body = m.body
+        return r, rz + "sample"
+    return None, None
+
+
+def _in_channels(new, kind):
+    if kind in ("block",):
+        return new.attn.qkv.in_channels
+    if kind == "encoder_block":
+        return new.mixer.qkv.in_channels
+    if kind == "attention":
+        return new.qkv.in_channels
+    if kind == "feedforward":
+        return new.project_in.in_channels
+    if kind == "layernorm":
+        return new.body.weight.numel()
+    return new.body[0].in_channels
+
+
+@torch.no_grad()
+def _agrees(old, new, kind, tol):
+    p = next(new.parameters())
+    if not p.is_cuda or p.dtype != torch.float32:
+        raise ValueError("accelerate(verify=True) needs the model on a CUDA device in float32")
+    g = torch.Generator(device="cpu").manual_seed(1234)
+    x = (torch.rand(2, _in_channels(new, kind), 16, 24, generator=g) * 2 - 1).to(p.device)
+    # the ORIGINAL runs through cuDNN / cuBLAS here: keep it in true fp32 for the comparison (TF32 is on by default for
+    # cuDNN convolutions and would differ from either exact implementation by ~1e-3)
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        ref = old(x)
+        got = new(x)
+    except Exception:
+        return False
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+    return ref.shape == got.shape and float((ref - got).abs().max()) <= tol * max(1.0, float(ref.abs().max()))
+
+
+def accelerate(model: nn.Module, verify: bool = True, tol: float = 1e-4) -> Tuple[nn.Module, Dict[str, int]]:
+    """Replace every structurally matching sub-module of `model` in place.  Returns (model, {kind: count}); modules that
+    match by structure but not by behaviour (verify) are counted under 'rejected' and left untouched."""
+    stats: Dict[str, int] = {}
+    work: List[Tuple[nn.Module, str, nn.Module]] = []
+
+    def walk(parent):
+        for name, child in list(parent.named_children()):
+            new, kind = _adopt(child)
+            if new is None:
+                walk(child)
+                continue
+            new.train(child.training)
+            if verify and not _agrees(child, new, kind, tol):
+                stats["rejected"] = stats.get("rejected", 0) + 1
+                walk(child)
+                continue
+            work.append((parent, name, new))
+            stats[kind] = stats.get(kind, 0) + 1
+
+    walk(model)
+    for parent, name, new in work:
+        if isinstance(parent, (nn.Sequential, nn.ModuleList)) and name.isdigit():
+            parent[int(name)] = new
+        else:
+            setattr(parent, name, new)
+    return model, stats

@@ -28,8 +28,8 @@ def _w2d(conv: nn.Conv2d) -> torch.Tensor:
 
 
 def _ln_args(norm: "LayerNorm"):
-    body = norm.body
-    if isinstance(body, WithBias_LayerNorm):
+    body = norm.body  # ours, or a reference LayerNorm body adopted by dropin.accelerate(): told apart by its parameters
+    if getattr(body, "bias", None) is not None:
         return L.LN_WITHBIAS, body.weight, body.bias
     return L.LN_BIASFREE, body.weight, None
 
@@ -144,6 +144,36 @@ class TransformerBlock(nn.Module):
     def forward(self, x, out=None):
         x = self.attn._run(x, norm=self.norm1, res=x)
         x = self.ffn._run(x, norm=self.norm2, res=x, out=out)
+        return x
+
+
+##########################################################################
+## MoCE-IR flavour of the same block (moce_ir.py:805-834, 903-932): identical math, different attribute names
+## (`norms.0`, `norms.1`, `mixer`, `ffn`) — those names are the checkpoint contract of MoCE-IR models.
+class EncoderBlock(nn.Module):
+    def __init__(self, dim, num_heads, ffn_expansion_factor, bias, LayerNorm_type):
+        super().__init__()
+        self.norms = nn.ModuleList([LayerNorm(dim, LayerNorm_type), LayerNorm(dim, LayerNorm_type)])
+        self.mixer = Attention(dim, num_heads, bias)
+        self.ffn = FeedForward(dim, ffn_expansion_factor, bias)
+
+    def forward(self, x, out=None):
+        x = self.mixer._run(x, norm=self.norms[0], res=x)            # x + mixer(norms[0](x))   moce_ir.py:826
+        return self.ffn._run(x, norm=self.norms[1], res=x, out=out)  # x + ffn(norms[1](x))     moce_ir.py:830
+
+
+class EncoderResidualGroup(nn.Module):
+    def __init__(self, dim, num_heads, num_blocks, ffn_expansion, LayerNorm_type, bias):
+        super().__init__()
+        self.loss = None
+        self.num_blocks = num_blocks
+        self.layers = nn.ModuleList([EncoderBlock(dim, num_heads, ffn_expansion, bias, LayerNorm_type)
+                                     for _ in range(num_blocks)])
+
+    def forward(self, x):
+        self.loss = 0                                                # moce_ir.py:926 (no auxiliary loss in the encoder)
+        for blk in self.layers:
+            x = blk(x)
         return x
 
 

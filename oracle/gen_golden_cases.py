@@ -28,3 +28,22 @@ TRAIN_BLOCK_CASES = [
 # (name, cfg-overrides, B, H, W, weight seed, image seed, steps)
 TRAIN_NET_CASE = ("train_net_dim8_16", dict(dim=8, num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, heads=[1, 2, 4, 8]),
                   2, 16, 16, 9, 41, 3)
+
+# MoCE-IR encoder groups (oracle/gen_golden_moce.py): (name, dim, heads, ffn_factor, bias, ln, blocks, B, H, W, seed)
+MOCE_CASES = [
+    ("moce_encgrp_c32_h2", 32, 2, 2, True, "WithBias", 2, 2, 8, 16, 51),
+    ("moce_encgrp_c48_h1_biasfree", 48, 1, 2, True, "BiasFree", 1, 1, 8, 8, 52),
+]
+
+
+def moce_block_params(dim, heads, f, bias, ln, nblk, seed):
+    """Seeded synthetic state_dict of an EncoderResidualGroup: Restormer block parameters renamed to the MoCE-IR
+    attribute names (norm1 -> norms.0, norm2 -> norms.1, attn -> mixer; moce_ir.py:817-823) under ``layers.{i}.``."""
+    from oracle import restormer_oracle as O
+    sd = {}
+    for i in range(nblk):
+        p = O.synth_block_params(dim, heads, float(f), bias, ln, seed + i)
+        for k, v in p.items():
+            k = k.replace("norm1.", "norms.0.").replace("norm2.", "norms.1.").replace("attn.", "mixer.")
+            sd[f"layers.{i}.{k}"] = v
+    return sd

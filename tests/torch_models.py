@@ -1,0 +1,131 @@
+"""TEST INFRASTRUCTURE: plain-PyTorch nn.Modules shaped like the reference's classes (same attribute / parameter names
+as Restormer.py:60-150 and moce_ir.py:805-834), whose forwards call the CPU oracle's functional restatement.  They stand
+in for "an existing reference model" in the tests of b200ir.accelerate(); nothing in the product imports this file."""
+import torch
+import torch.nn as nn
+
+from oracle import restormer_oracle as O
+
+
+class _Body(nn.Module):
+    def __init__(self, dim, with_bias):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(dim))
+        if with_bias:
+            self.bias = nn.Parameter(torch.zeros(dim))
+
+
+class RefLayerNorm(nn.Module):
+    def __init__(self, dim, LayerNorm_type):
+        super().__init__()
+        self.body = _Body(dim, LayerNorm_type != "BiasFree")
+
+    def forward(self, x):
+        return O.layernorm(x, self.body.weight, getattr(self.body, "bias", None))
+
+
+class RefFeedForward(nn.Module):
+    def __init__(self, dim, f, bias):
+        super().__init__()
+        hd = int(dim * f)
+        self.project_in = nn.Conv2d(dim, hd * 2, 1, bias=bias)
+        self.dwconv = nn.Conv2d(hd * 2, hd * 2, 3, 1, 1, groups=hd * 2, bias=bias)
+        self.project_out = nn.Conv2d(hd, dim, 1, bias=bias)
+
+    def forward(self, x):
+        return O.feedforward(x, dict(self.named_parameters()), "")
+
+
+class RefAttention(nn.Module):
+    def __init__(self, dim, num_heads, bias):
+        super().__init__()
+        self.num_heads = num_heads
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.qkv = nn.Conv2d(dim, dim * 3, 1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(dim * 3, dim * 3, 3, 1, 1, groups=dim * 3, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, 1, bias=bias)
+
+    def forward(self, x):
+        return O.attention(x, dict(self.named_parameters()), "", self.num_heads)
+
+
+class RefGatedAttention(RefAttention):
+    """Same attribute names, different forward (sigmoid output gate, as the experiment/*gate* variants do):
+    accelerate(verify=True) must leave it alone."""
+
+    def forward(self, x):
+        return torch.sigmoid(x) * super().forward(x)
+
+
+class RefTransformerBlock(nn.Module):
+    def __init__(self, dim, heads, f, bias, ln, attn_cls=RefAttention):
+        super().__init__()
+        self.norm1 = RefLayerNorm(dim, ln)
+        self.attn = attn_cls(dim, heads, bias)
+        self.norm2 = RefLayerNorm(dim, ln)
+        self.ffn = RefFeedForward(dim, f, bias)
+
+    def forward(self, x):
+        x = x + self.attn(self.norm1(x))
+        return x + self.ffn(self.norm2(x))
+
+
+class RefEncoderBlock(nn.Module):
+    def __init__(self, dim, heads, f, bias, ln):
+        super().__init__()
+        self.norms = nn.ModuleList([RefLayerNorm(dim, ln), RefLayerNorm(dim, ln)])
+        self.mixer = RefAttention(dim, heads, bias)
+        self.ffn = RefFeedForward(dim, f, bias)
+
+    def forward(self, x):
+        x = x + self.mixer(self.norms[0](x))
+        return x + self.ffn(self.norms[1](x))
+
+
+class RefDown(nn.Module):
+    def __init__(self, n):
+        super().__init__()
+        self.body = nn.Sequential(nn.Conv2d(n, n // 2, 3, 1, 1, bias=False), nn.PixelUnshuffle(2))
+
+    def forward(self, x):
+        return self.body(x)
+
+
+class RefUp(nn.Module):
+    def __init__(self, n):
+        super().__init__()
+        self.body = nn.Sequential(nn.Conv2d(n, n * 2, 3, 1, 1, bias=False), nn.PixelShuffle(2))
+
+    def forward(self, x):
+        return self.body(x)
+
+
+class RefMiniNet(nn.Module):
+    """A small U-shaped model mixing every pattern accelerate() knows, a decoder that uses Attention / FeedForward /
+    LayerNorm separately (like moce_ir.DecoderBlock) and one gated variant."""
+
+    def __init__(self, dim=16):
+        super().__init__()
+        self.embed = nn.Conv2d(3, dim, 3, 1, 1, bias=False)
+        self.enc = nn.Sequential(RefTransformerBlock(dim, 1, 2.66, False, "WithBias"),
+                                 RefEncoderBlock(dim, 2, 2.0, True, "BiasFree"))
+        self.down = RefDown(dim)
+        self.mid = nn.ModuleList([RefEncoderBlock(dim * 2, 2, 2.0, True, "WithBias")])
+        self.gated = RefTransformerBlock(dim * 2, 2, 2.0, False, "WithBias", attn_cls=RefGatedAttention)
+        self.up = RefUp(dim * 2)
+        self.dec_norm = RefLayerNorm(dim, "WithBias")
+        self.dec_attn = RefAttention(dim, 1, True)
+        self.dec_ffn = RefFeedForward(dim, 2.0, True)
+        self.out = nn.Conv2d(dim, 3, 3, 1, 1, bias=True)
+
+    def forward(self, img):
+        x = self.enc(self.embed(img))
+        y = self.down(x)
+        for m in self.mid:
+            y = m(y)
+        y = self.gated(y)
+        x = x + self.up(y)
+        n = self.dec_norm(x)
+        x = x + self.dec_attn(n)
+        x = x + self.dec_ffn(n)
+        return self.out(x) + img
