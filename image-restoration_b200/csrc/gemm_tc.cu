@@ -782,6 +782,12 @@ extern "C" int b200ir_pack_conv3x3(const float* w, const float* bias, int Cin, i
   return check_launch("pack_conv3x3");
 }
 
+namespace b200ir {
+int conv3x3_stream_launch(const void* x, int64_t x_bs, const void* wp, const float* st, int Nrows, int Kpad, int kpt,
+                          void* y, int64_t y_bs, int y_dt, int B, int Cin, int Cout, int H, int W, int mode,
+                          cudaStream_t stream);  // conv3x3_stream_tc.cu
+}
+
 extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, const float* st, void* y,
                                      int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int H, int W,
                                      int shuffle_mode, b200ir_stream_t stream) {
@@ -794,6 +800,9 @@ extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const voi
                      "conv3x3_tc: needs Cin%%8==0 and 16B-aligned NHWC activations");
   B200IR_CHECK_ARG(shuffle_mode != B200IR_UNSHUFFLE2 || (H % 2 == 0 && W % 2 == 0), "conv3x3_tc: odd H/W");
   B200IR_CHECK_ARG(shuffle_mode != B200IR_SHUFFLE2 || Cout % 4 == 0, "conv3x3_tc: Cout%%4 != 0");
+  if (g.nslices >= 2)  // the weight matrix does not fit in shared memory: stream both operands (conv3x3_stream_tc.cu)
+    return conv3x3_stream_launch(x, x_bstride, wp, st, g.Nrows, g.Kpad, g.kpt, y, y_bstride, y_dtype, B, Cin, Cout, H,
+                                 W, shuffle_mode, (cudaStream_t)stream);
   int TWs = 0;
   while ((1 << TWs) < W && TWs < 7) ++TWs;
   const int TW = 1 << TWs, TH = 128 / TW;

@@ -22,6 +22,9 @@ def rel_err(a, b):
     ("none", 48, 48, 2, 10, 40, True),
     ("none", 32, 16, 1, 6, 200, True),
     ("unshuffle", 64, 32, 3, 12, 136, False),
+    ("none", 256, 320, 1, 16, 32, True),        # streamed-weights kernel (conv3x3_stream_tc.cu), bias, Cout > 256
+    ("shuffle", 384, 768, 1, 32, 32, False),
+    ("unshuffle", 200, 96, 2, 20, 48, True),     # Cin not a multiple of 64, ragged tiles
 ])
 def test_conv3x3_tc(mode, Cin, Cout, B, H, W, bias):
     import b200ir
