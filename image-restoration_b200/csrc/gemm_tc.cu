@@ -20,6 +20,8 @@
 //   LayerNorm is folded algebraically: W.LN(x) = rstd*(W.diag(g).x - mu*s) + t with s[o]=sum_c bf16(W g)[o,c],
 //   t[o] = bias[o] + sum_c W[o,c] b[c], so the tensor core consumes the raw bf16 activations.
 //   TMEM: 2 accumulator stages x 256 columns; the epilogue of chunk i overlaps the MMAs of chunk i+1.
+#include <stdlib.h>
+
 #include <mutex>
 #include <type_traits>
 
@@ -45,6 +47,11 @@ PFN_encodeTiled get_encode_tiled() {
 
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, bool swizzle128) {
+  return make_tmap_bf16_sw(m, base, rank, dims, strides_bytes, box, swizzle128 ? 128 : 0);
+}
+
+int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle_bytes) {
   PFN_encodeTiled enc = get_encode_tiled();
   if (!enc) {
     set_error("cuTensorMapEncodeTiled entry point unavailable");
@@ -59,7 +66,9 @@ int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* d
     if (i > 0) gs[i - 1] = strides_bytes[i];
   }
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), gd, gs, bx, es,
-                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                        : (swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_NONE),
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -132,6 +141,34 @@ bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1, bool has_res
     if (S >= need) return true;
   }
   return false;
+}
+
+// geometry of the channels-on-lanes variant (MODE 4): same packing / slicing, but the out-channel slice of a CTA is cut
+// in 128-row MMA tiles and 32-row store boxes (so slices must be multiples of 32 rows when there are several), and the
+// epilogue staging is two 2 KB tiles per warp (bf16 output) instead of per-group buffers.
+bool gemm_tc_geometry_t(int Cin, int Cout, bool out16, GemmGeom* g) {
+  if (!gemm_tc_geometry(Cin, Cout, g, 1, false, false)) return false;
+  if (g->nslices > 1 && g->Nslice % 32) {
+    g->Nslice = ceil_to(g->Nslice, 32);
+    g->nslices = (g->Nrows + g->Nslice - 1) / g->Nslice;
+    g->nbox = 16;
+    for (int nb = 256; nb >= 16; nb -= 16)
+      if (g->Nslice % nb == 0) {
+        g->nbox = nb;
+        break;
+      }
+  }
+  if (g->Nslice > 512) return false;
+  const size_t wbytes = (size_t)(g->Kpad / 64) * g->Nslice * 128;
+  g->epi_warp_bytes = out16 ? 4096 : 0;
+  const size_t fixed = 1024 + 16 * g->epi_warp_bytes;
+  const long avail = 227 * 1024 - 8 * 1024 - (long)wbytes - (long)fixed;
+  int S = avail > 0 ? (int)(avail / 16384) : 0;
+  if (S > 8) S = 8;
+  if (S < 3) return false;
+  g->S = S;
+  g->smem = wbytes + (size_t)S * 16384 + fixed;
+  return true;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -220,6 +257,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                const GemmTcParams P) {
   using namespace tc;
   constexpr bool HAS_RES = !std::is_same<TRES, void>::value;
+  constexpr bool ONE = MODE == 0 || MODE == 4;   // 1x1 conv over flattened HW (MODE 4: channels-on-lanes epilogue)
   typedef typename std::conditional<HAS_RES, TRES, float>::type TR;
   // bf16 NCHW output (and bf16 residual) of the 1x1 path goes through shared memory + TMA (see epilogue)
   constexpr bool TMA_EPI = MODE == 0 && std::is_same<TOUT, bf16>::value &&
@@ -230,10 +268,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   uint8_t* Wsm = smem;
   uint8_t* ring = smem + wbytes;
   uint8_t* epi_smem = ring + (size_t)P.S * kStageBytes;   // [16 warps][epi_warp_bytes]
-  __shared__ uint64_t bar_full[8], bar_empty[8], bar_wfull[1], bar_wempty[1], bar_accfull[2], bar_accempty[2],
+  __shared__ uint64_t bar_full[8], bar_empty[8], bar_wfull[1], bar_wempty[1], bar_accfull[4], bar_accempty[4],
       bar_stfull[2], bar_stempty[2], bar_res[2 * kEpiWarps];
   __shared__ uint32_t tmem_slot[1];
-  __shared__ float s_mu[256], s_rstd[256];   // [2][128]: (-rstd*mu, rstd) per pixel, double buffered
+  __shared__ __align__(16) float s_mu[256], s_rstd[256];   // [2][128]: (-rstd*mu, rstd) per pixel, double buffered
   __shared__ __align__(16) float2 s_st[512];               // (s, t) of this CTA's out-channel slice
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -248,9 +286,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     mbar_init(bar_wfull, 1);
     mbar_init(bar_wempty, 1);
     for (int i = 0; i < 2 * kEpiWarps; ++i) mbar_init(&bar_res[i], 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 4; ++i) {
       mbar_init(&bar_accfull[i], 1);
       mbar_init(&bar_accempty[i], kEpiWarps);
+    }
+    for (int i = 0; i < 2; ++i) {
       mbar_init(&bar_stfull[i], 128);
       mbar_init(&bar_stempty[i], kEpiWarps);
     }
@@ -262,7 +302,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     if (lane == 0) {
       tma_prefetch_desc(&tmX);
       tma_prefetch_desc(&tmW);
-      if (TMA_EPI) tma_prefetch_desc(&tmY);
+      if (TMA_EPI || MODE == 4) tma_prefetch_desc(&tmY);
       if (TMA_EPI && HAS_RES) tma_prefetch_desc(&tmR);
     }
     tmem_alloc(tmem_slot, 512);
@@ -283,7 +323,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       uint32_t it = 0, wload = 0;
       int cur = -1;
       for (int tile = t_begin; tile < t_end; ++tile) {
-        const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
+        const int b = ONE ? tile / P.tiles_per_sample : 0;
         const int p0 = (tile - b * P.tiles_per_sample) * 128;
         if (cur < 0 || (P.per_sample_w && b != cur)) {
           if (wload > 0) mbar_wait(bar_wempty, (wload - 1) & 1);
@@ -296,7 +336,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           cur = b;
         }
         int cx0 = 0, cy0 = 0, cb = 0;
-        if (MODE != 0) {
+        if (!ONE) {
           const int tpi = P.tiles_x * P.tiles_y;
           cb = tile / tpi;
           const int r = tile - cb * tpi;
@@ -306,9 +346,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_empty[stage], ph ^ 1);
-          mbar_arrive_expect_tx(&bar_full[stage], MODE == 0 ? 2u * P.BK * 128u : (uint32_t)kStageBytes);
+          mbar_arrive_expect_tx(&bar_full[stage], ONE ? 2u * P.BK * 128u : (uint32_t)kStageBytes);
           uint8_t* dst = ring + (size_t)stage * kStageBytes;
-          if (MODE == 0) {
+          if (ONE) {
             tma_load_3d(dst, &tmX, &bar_full[stage], p0, kc * P.BK, b);
             tma_load_3d(dst + P.BK * 128, &tmX, &bar_full[stage], p0 + 64, kc * P.BK, b);
           } else {
@@ -325,6 +365,47 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
       uint32_t it = 0, acc_it = 0, wload = 0;
       int cur = -1;
       const uint32_t ring_addr = smem_u32(ring), w_addr = smem_u32(Wsm);
+      if (MODE == 4) {
+        // D[128 out-channels (lanes)][128 pixels (columns)] = W[128 x K] (K-major, resident) . X[K x 128 px] (MN-major
+        // activation tile): four 128-column accumulators rotate over (pixel tile, channel tile) items.
+        const int mtiles = (P.Nslice + 127) >> 7;
+        const uint32_t idesc = make_idesc_bf16(128, 128, 0, 1);
+        for (int tile = t_begin; tile < t_end; ++tile) {
+          const int b = tile / P.tiles_per_sample;
+          if (cur < 0 || (P.per_sample_w && b != cur)) {
+            mbar_wait(bar_wfull, wload & 1);
+            ++wload;
+            cur = b;
+          }
+          for (int mt = 0; mt < mtiles; ++mt, ++acc_it) {
+            const uint32_t as = acc_it & 3, aph = (acc_it >> 2) & 1;
+            mbar_wait(&bar_accempty[as], aph ^ 1);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + as * 128;
+            for (int kc = 0; kc < P.kchunks; ++kc) {
+              const uint32_t cit = it + kc, stage = cit % P.S, ph = (cit / P.S) & 1;
+              if (mt == 0) {
+                mbar_wait(&bar_full[stage], ph);
+                tc_fence_after();
+              }
+              const int rows = min(P.BK, P.Cin - kc * P.BK);
+              const int ksteps = (rows + 15) >> 4;
+              for (int ks = 0; ks < ksteps; ++ks) {
+                const int kglob = kc * P.BK + ks * 16;
+                const uint64_t adesc = make_smem_desc_sw128(
+                    w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)mt * 16384u + (kglob & 63) * 2u, 16u, 1024u);
+                const uint64_t bdesc = make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048,
+                                                            (uint32_t)P.BK * 128u, 1024u);
+                umma_bf16(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
+              }
+              if (mt == mtiles - 1) umma_commit(&bar_empty[stage]);
+            }
+            umma_commit(&bar_accfull[as]);
+          }
+          it += P.kchunks;
+          if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit(bar_wempty);
+        }
+      } else
       for (int tile = t_begin; tile < t_end; ++tile) {
         const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
         if (cur < 0 || (P.per_sample_w && b != cur)) {
@@ -401,6 +482,113 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         mbar_arrive(&bar_stfull[sp]);
       }
     }
+  } else if (MODE == 4) {
+    // ===== epilogue, channels on lanes: warp w <-> TMEM lane quadrant w%4 (32 out-channels) x pixel columns
+    // [32*(w/4), +32).  A thread owns 32 consecutive pixels of ONE output channel: (s,t) live in registers, the per-pixel
+    // (-rstd*mu, rstd) come as broadcast LDS.128, results are packed pairwise to bf16 and written as four 16-byte
+    // chunks into the warp's private [32 ch][64 B] staging tile (SWIZZLE_64B pattern: conflict-free), which one TMA
+    // store box {32 px, 32 ch} sends to the NCHW output (rows / pixels past the tensor are clipped by TMA).
+    const int quad = warp & 3, wq = warp >> 2;
+    const int mtiles = (P.Nslice + 127) >> 7;
+    constexpr bool OUT16 = std::is_same<TOUT, bf16>::value;
+    TOUT* yout = reinterpret_cast<TOUT*>(P.y);
+    const TR* rin = reinterpret_cast<const TR*>(P.res);
+    uint8_t* stg = epi_smem + (size_t)warp * P.epi_warp_bytes;   // [2][32 ch][64 B]
+    uint32_t acc_it = 0, tcount = 0, st_it = 0;
+    for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
+      const int b = tile / P.tiles_per_sample;
+      const int64_t p0 = (int64_t)(tile - b * P.tiles_per_sample) * 128 + wq * 32;
+      const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+      if (has_ln) mbar_wait(&bar_stfull[sp], sph);
+      const float4* nm4 = reinterpret_cast<const float4*>(&s_mu[sp * 128 + wq * 32]);
+      const float4* rs4 = reinterpret_cast<const float4*>(&s_rstd[sp * 128 + wq * 32]);
+      for (int mt = 0; mt < mtiles; ++mt, ++acc_it) {
+        const uint32_t as = acc_it & 3, aph = (acc_it >> 2) & 1;
+        const int rowbase = mt * 128 + quad * 32;              // rows of this CTA's out-channel slice
+        const int row = rowbase + lane, co = n_lo + row;
+        const bool wok = rowbase < P.Nslice && n_lo + rowbase < P.Cout;   // warp-uniform
+        const bool cok = row < P.Nslice && co < P.Cout;
+        const float2 stv = cok ? s_st[row] : make_float2(0.f, 0.f);
+        mbar_wait(&bar_accfull[as], aph);
+        tc_fence_after();
+        const uint32_t tb = tmem_base + as * 128 + wq * 32 + ((uint32_t)(quad * 32) << 16);
+        uint8_t* sbuf = stg + (st_it & 1) * 2048;
+        if (OUT16 && wok) {
+          if (lane == 0) bulk_wait_read<1>();   // the store that used this buffer two items ago has read it
+          __syncwarp();
+        }
+        if (wok) {
+          uint32_t r[32];
+          tmem_ld_32x16(tb, r);             // both halves in flight before the single wait
+          tmem_ld_32x16(tb + 16, r + 16);
+          tmem_ld_wait();
+          tc_fence_before();                 // accumulator is in registers: hand the TMEM slot back right away
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar_accempty[as]);
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {   // 8 pixels at a time: few live registers
+            float v[8];
+            if (has_ln) {
+              const float4 a0 = nm4[g8 * 2], a1 = nm4[g8 * 2 + 1], c0 = rs4[g8 * 2], c1 = rs4[g8 * 2 + 1];
+              const float nmv[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+              const float rsv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+#pragma unroll
+              for (int j = 0; j < 8; ++j)
+                v[j] = fmaf(__uint_as_float(r[g8 * 8 + j]), rsv[j], fmaf(nmv[j], stv.x, stv.y));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[g8 * 8 + j]) + stv.y;
+            }
+            const int64_t pp = p0 + g8 * 8;
+            const bool pok = pp < P.HW;          // HW % 8 == 0: an 8-pixel group is entirely in or out
+            if (HAS_RES && cok && pok) {
+              const TR* rp = rin + (int64_t)b * P.res_bs + (int64_t)co * P.HW + pp;
+              if (std::is_same<TR, bf16>::value) {
+                const uint4 u = __ldg(reinterpret_cast<const uint4*>(rp));
+                const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  v[2 * k] += __uint_as_float(uu[k] << 16);
+                  v[2 * k + 1] += __uint_as_float(uu[k] & 0xffff0000u);
+                }
+              } else {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) v[k] += ldf<TR>(rp + k);
+              }
+            }
+            if (OUT16) {
+              uint32_t pk[4];
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * k], v[2 * k + 1]);
+                pk[k] = *reinterpret_cast<uint32_t*>(&h);
+              }
+              const uint32_t chunk = (uint32_t)g8 ^ (((uint32_t)lane >> 1) & 3u);
+              *reinterpret_cast<uint4*>(sbuf + lane * 64 + chunk * 16) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            } else if (cok && pok) {
+              float4* d4 = reinterpret_cast<float4*>(yout + (int64_t)b * P.y_bs + (int64_t)co * P.HW + pp);
+              d4[0] = make_float4(v[0], v[1], v[2], v[3]);
+              d4[1] = make_float4(v[4], v[5], v[6], v[7]);
+            }
+          }
+        }
+        if (OUT16 && wok) fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (!wok) mbar_arrive(&bar_accempty[as]);
+          if (OUT16 && wok) {
+            tma_store_3d(&tmY, sbuf, (int)p0, n_lo + rowbase, b);
+            bulk_commit();
+          }
+        }
+        if (OUT16 && wok) ++st_it;
+      }
+      if (has_ln) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar_stempty[sp]);
+      }
+    }
+    if (lane == 0) bulk_wait<0>();
   } else if (TMA_EPI) {
     // ===== epilogue (bf16 NCHW via TMA): warp w <-> TMEM lane quadrant w%4 and a contiguous quarter of the chunk's
     // 16-column groups.  Each warp is self-contained: tcgen05.ld -> fp32 math -> bf16 into its private staging
@@ -662,7 +850,16 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
                        ((uintptr_t)y % 16) == 0 && (!res || (res_bstride % 8 == 0 && ((uintptr_t)res % 16) == 0));
   B200IR_UNSUPPORTED(tma_epi || y_dtype == B200IR_F32,
                      "gemm_tc: bf16 output / residual must be 16B-aligned with batch strides %% 8 == 0");
-  B200IR_UNSUPPORTED(gemm_tc_geometry(Cin, Cout, &g, 1, res != nullptr, tma_epi),
+  // Two epilogues.  Default: pixels on the TMEM lanes (MODE 0).  B200IR_GEMM_EPI=ch selects the channels-on-lanes
+  // variant (MODE 4: D = W.X, a thread owns 32 pixels of one channel, 2.4x fewer instructions).  Measured on B200 it is
+  // not faster (K4 352 vs 334 us, K6 191 vs 193 us): these GEMMs sit at the HBM WRITE roof (3.95 TB/s write-only vs
+  // 6.6 TB/s copy, tools/bw_probe.py), not at the issue limit, so MODE 0 stays the default.
+  const char* epi_env = getenv("B200IR_GEMM_EPI");
+  const bool force_px = !(epi_env && epi_env[0] == 'c');
+  const bool al16 = ((uintptr_t)y % 16) == 0 && y_bstride % 8 == 0 &&
+                    (!res || (((uintptr_t)res % 16) == 0 && res_bstride % 8 == 0));
+  bool mode4 = !force_px && al16 && gemm_tc_geometry_t(Cin, Cout, y_dtype == B200IR_BF16, &g);
+  B200IR_UNSUPPORTED(mode4 || gemm_tc_geometry(Cin, Cout, &g, 1, res != nullptr, tma_epi),
                      "gemm_tc: unsupported Cin=%d Cout=%d", Cin, Cout);
   B200IR_UNSUPPORTED(HW % 8 == 0 && HW >= 64 && x_bstride % 8 == 0 && ((uintptr_t)x % 16) == 0,
                      "gemm_tc: needs HW%%8==0, HW>=64 and 16B-aligned activations (HW=%lld)", (long long)HW);
@@ -684,7 +881,15 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
     if (rc) return rc;
   }
   CUtensorMap tmY = tmX, tmR = tmX;
-  if (tma_epi) {
+  if (mode4) {
+    if (y_dtype == B200IR_BF16) {   // one {32 px, 32 ch} box per warp item, SWIZZLE_64B staging
+      const uint64_t dims[3] = {(uint64_t)HW, (uint64_t)Cout, (uint64_t)B};
+      const uint32_t box[3] = {32, 32, 1};
+      const uint64_t stry[3] = {2, (uint64_t)HW * 2, (uint64_t)y_bstride * 2};
+      int rc = make_tmap_bf16_sw(&tmY, y, 3, dims, stry, box, 64);
+      if (rc) return rc;
+    }
+  } else if (tma_epi) {
     const uint64_t dims[3] = {(uint64_t)HW, (uint64_t)Cout, (uint64_t)B};
     const uint32_t box[3] = {32, 16, 1};
     const uint64_t stry[3] = {2, (uint64_t)HW * 2, (uint64_t)y_bstride * 2};
@@ -722,7 +927,12 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
     std::call_once(once, [] {                                                                                   \
       cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
     });                                                                                                         \
-    gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);                      \
+    static std::once_flag once4;                                                                                \
+    std::call_once(once4, [] {                                                                                  \
+      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
+    });                                                                                                         \
+    if (mode4) gemm_tc_kernel<TRES, TOUT, 4><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);           \
+    else gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);                 \
   } while (0)
   const bool ob = y_dtype == B200IR_BF16;
   if (!res) {

@@ -180,5 +180,8 @@ PFN_encodeTiled get_encode_tiled();  // gemm_tc.cu
 // rank-N bf16 tensor map with 128B swizzle, OOB -> zeros.  dims/strides innermost first; strides[0] implied.
 int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                    const uint32_t* box, bool swizzle128 = true);
+// same with an explicit swizzle span in bytes (0 | 64 | 128)
+int make_tmap_bf16_sw(CUtensorMap* m, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                      const uint32_t* box, int swizzle_bytes);
 
 }  // namespace b200ir

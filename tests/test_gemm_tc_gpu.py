@@ -90,3 +90,33 @@ def test_gemm_tc_large_tail_and_multi_cta():
     packed = ops.pack_conv1x1(w.cuda(), None, L.LN_WITHBIAS, lw.cuda(), lb.cuda())
     y = ops.gemm_tc(x.cuda(), packed, Cout, L.LN_WITHBIAS).float().cpu()
     assert rel_err(y, ref) < 6e-3
+
+
+def test_gemm_tc_channels_on_lanes_epilogue_matches_default():
+    """The opt-in channels-on-lanes epilogue (B200IR_GEMM_EPI=ch, gemm_tc_kernel MODE 4) gives the same bf16 results as
+    the default pixels-on-lanes epilogue (identical fp32 accumulators, identical rounding point)."""
+    import os
+    import torch
+    import b200ir
+    from b200ir import ops
+    L = b200ir._lib
+    g = torch.Generator().manual_seed(77)
+    for (B, Cin, Cout, H, W, ln, res) in [(2, 96, 510, 16, 24, L.LN_WITHBIAS, False), (1, 255, 96, 16, 16, L.LN_NONE, True),
+                                          (3, 48, 144, 8, 40, L.LN_BIASFREE, False), (2, 384, 1152, 8, 8, L.LN_WITHBIAS, False)]:
+        x = (torch.rand(B, Cin, H, W, generator=g) * 2 - 1).bfloat16().cuda()
+        w = ((torch.rand(Cout, Cin, generator=g) - 0.5) / Cin ** 0.5).cuda()
+        bias = (torch.rand(Cout, generator=g) - 0.5).cuda()
+        lw, lb = (torch.rand(Cin, generator=g) + 0.5).cuda(), (torch.rand(Cin, generator=g) - 0.5).cuda()
+        r = (torch.rand(B, Cout, H, W, generator=g) - 0.5).bfloat16().cuda() if res else None
+        packed = ops.pack_conv1x1(w, bias, ln, lw if ln else None, lb if ln == L.LN_WITHBIAS else None)
+        os.environ.pop("B200IR_GEMM_EPI", None)
+        y0 = ops.gemm_tc(x, packed, Cout, ln, r)
+        os.environ["B200IR_GEMM_EPI"] = "ch"
+        try:
+            y1 = ops.gemm_tc(x, packed, Cout, ln, r)
+            y1f = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
+        finally:
+            os.environ.pop("B200IR_GEMM_EPI", None)
+        torch.cuda.synchronize()
+        assert (y0.float() - y1.float()).abs().max() <= 2e-2 * y0.float().abs().max()
+        assert ((y1f - y0.float()).norm() / y0.float().norm()) < 4e-3
