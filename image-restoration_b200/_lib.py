@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200ir.so")
+LIB_PATH = os.environ.get("B200IR_LIB") or os.path.join(_HERE, "libb200ir.so")   # B200IR_LIB: A/B builds (tools/)
 
 F32, BF16 = 0, 1
 LN_NONE, LN_WITHBIAS, LN_BIASFREE = 0, 1, 2

@@ -15,6 +15,11 @@
 
 namespace b200ir {
 
+#ifndef B200IR_DW_BW_RS
+#define B200IR_DW_BW_RS 4   // measured: 64x64 planes 82 -> 49 us, 128x128 unchanged (more resident CTAs)
+#endif
+constexpr int BW_RS = B200IR_DW_BW_RS;   // output rows per thread
+
 struct DwBwdParams {
   const bf16* g;     // dg [B,Hd,H,W] (GATE) or dy [B,C,H,W]
   int64_t g_bs;
@@ -85,11 +90,11 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
 
     if (tid < nthreads) {
       const int gx = x0 + xg * 8;
-      const int64_t poff = (int64_t)(y0 + strip * DW_RS) * P.W + gx;
+      const int64_t poff = (int64_t)(y0 + strip * BW_RS) * P.W + gx;
       const bf16* grow = P.g + (int64_t)b * P.g_bs + (int64_t)c * HWp + poff;
       const bool xok = gx < P.W;
-      const int yrem = P.H - (y0 + strip * DW_RS);
-      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * DW_RS) * pitch +
+      const int yrem = P.H - (y0 + strip * BW_RS);
+      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * BW_RS) * pitch +
                             (uint32_t)(DW_XP + xg * 8) * 2u;
       if (GATE) {
         bf16* a1row = P.da + (int64_t)b * P.da_bs + (int64_t)c * HWp + poff;
@@ -106,7 +111,7 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
         dw_load_row2(base, base + plane_bytes, win[0]);
         dw_load_row2(base + pitch, base + plane_bytes + pitch, win[1]);
 #pragma unroll
-        for (int j = 0; j < DW_RS; ++j) {
+        for (int j = 0; j < BW_RS; ++j) {
           const uint32_t ra = base + (uint32_t)(j + 2) * pitch;
           dw_load_row2(ra, ra + plane_bytes, win[(j + 2) % 3]);
           const bool ok = xok && j < yrem;
@@ -163,7 +168,7 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
         dw_load_row(base, win[0]);
         dw_load_row(base + pitch, win[1]);
 #pragma unroll
-        for (int j = 0; j < DW_RS; ++j) {
+        for (int j = 0; j < BW_RS; ++j) {
           dw_load_row(base + (uint32_t)(j + 2) * pitch, win[(j + 2) % 3]);
           const bool ok = xok && j < yrem;
           float gv[8];
@@ -208,9 +213,9 @@ void dw_bwd_tma_tiles(int H, int W, int* TW, int* TH, int* nxg, int* nstrips, in
   *TW = W >= 128 ? 128 : 64;
   *nxg = *TW / 8;
   *nstrips = 128 / *nxg;
-  const int maxstrips = (H + DW_RS - 1) / DW_RS;
+  const int maxstrips = (H + BW_RS - 1) / BW_RS;
   if (*nstrips > maxstrips) *nstrips = maxstrips;
-  *TH = *nstrips * DW_RS;
+  *TH = *nstrips * BW_RS;
   *tiles_x = (W + *TW - 1) / *TW;
   *tiles_y = (H + *TH - 1) / *TH;
 }

@@ -16,10 +16,25 @@
 
 namespace b200ir {
 
+// forward geometry: FW_THREADS threads, each sliding its window down RS output rows (tile = TW x (threads/(TW/8))*RS).
+// Measured on B200 (tools/bench_ops.py, C=96 level): plain dwconv is fastest with RS=8 (fewer window refills, 87 % of
+// HBM); the gated kernel is issue/latency-bound and gains 22 % from RS=4 (smaller tiles -> twice the resident CTAs).
+#ifndef B200IR_DW_GATE_RS
+#define B200IR_DW_GATE_RS 4
+#endif
+#ifndef B200IR_DW_GATE_STAGES
+#define B200IR_DW_GATE_STAGES 2
+#endif
+#ifndef B200IR_DW_FW_THREADS
+#define B200IR_DW_FW_THREADS 128
+#endif
+constexpr int FW_THREADS = B200IR_DW_FW_THREADS;
+
 template <bool GATE>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(FW_THREADS)
 dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) {
   using namespace tc;
+  constexpr int FW_RS = GATE ? B200IR_DW_GATE_RS : 8;
   constexpr int NIN = GATE ? 2 : 1;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
@@ -65,11 +80,11 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
 
     if (tid < nthreads) {
       const int gx = x0 + xg * 8;
-      bf16* orow = P.y + (int64_t)b * P.y_bs + (int64_t)c * HWp + (int64_t)(y0 + strip * DW_RS) * P.W + gx;
+      bf16* orow = P.y + (int64_t)b * P.y_bs + (int64_t)c * HWp + (int64_t)(y0 + strip * FW_RS) * P.W + gx;
       const bool xok = gx < P.W;
-      const int yrem = P.H - (y0 + strip * DW_RS);
+      const int yrem = P.H - (y0 + strip * FW_RS);
       // staged row r <-> image row y0-1+r ; staged col 8+i <-> image col x0+i
-      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * DW_RS) * pitch +
+      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * FW_RS) * pitch +
                             (uint32_t)(DW_XP + xg * 8) * 2u;
       if (GATE) {
         float2 wk[9];
@@ -81,7 +96,7 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
         dw_load_row2(base, base + plane_bytes, win[0]);
         dw_load_row2(base + pitch, base + plane_bytes + pitch, win[1]);
 #pragma unroll
-        for (int j = 0; j < DW_RS; ++j) {
+        for (int j = 0; j < FW_RS; ++j) {
           const uint32_t ra = base + (uint32_t)(j + 2) * pitch;
           dw_load_row2(ra, ra + plane_bytes, win[(j + 2) % 3]);
           uint32_t pk[4];
@@ -110,7 +125,7 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
         dw_load_row(base, win[0]);
         dw_load_row(base + pitch, win[1]);
 #pragma unroll
-        for (int j = 0; j < DW_RS; ++j) {
+        for (int j = 0; j < FW_RS; ++j) {
           dw_load_row(base + (uint32_t)(j + 2) * pitch, win[(j + 2) % 3]);
           float o[8];
 #pragma unroll
@@ -151,14 +166,15 @@ bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, c
 template <bool GATE>
 int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs, int B,
                       int Cout, int H, int W, cudaStream_t st) {
+  constexpr int FW_RS = GATE ? B200IR_DW_GATE_RS : 8;
   DwTmaParams P;
   P.y = (bf16*)y; P.y_bs = y_bs; P.w = w; P.bias = bias; P.Cout = Cout; P.H = H; P.W = W;
   P.TW = W >= 128 ? 128 : 64;
   P.nxg = P.TW / 8;
-  P.nstrips = 128 / P.nxg;                       // 8 (TW=128) or 16 (TW=64)
-  const int maxstrips = (H + DW_RS - 1) / DW_RS;
+  P.nstrips = FW_THREADS / P.nxg;                       // 8 (TW=128) or 16 (TW=64)
+  const int maxstrips = (H + FW_RS - 1) / FW_RS;
   if (P.nstrips > maxstrips) P.nstrips = maxstrips;
-  P.TH = P.nstrips * DW_RS;
+  P.TH = P.nstrips * FW_RS;
   P.tiles_x = (W + P.TW - 1) / P.TW;
   P.tiles_y = (H + P.TH - 1) / P.TH;
   const int64_t nitems64 = (int64_t)B * Cout * P.tiles_x * P.tiles_y;
@@ -177,7 +193,7 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
   const size_t pitch = (size_t)(P.TW + 2 * DW_XP) * 2;
   const size_t plane = ((size_t)(P.TH + 2) * pitch + 127) & ~(size_t)127;
   const size_t stage = plane * (GATE ? 2 : 1);
-  P.S = GATE ? 2 : 3;
+  P.S = GATE ? B200IR_DW_GATE_STAGES : 3;
   const size_t smem = stage * P.S + 256;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -188,7 +204,7 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
   if (ctas_per_sm < 1) ctas_per_sm = 1;
   int64_t grid = 148ll * ctas_per_sm;
   if (grid > P.nitems) grid = P.nitems;
-  dwconv_tma_kernel<GATE><<<(unsigned)grid, 128, smem, st>>>(tm, P);
+  dwconv_tma_kernel<GATE><<<(unsigned)grid, FW_THREADS, smem, st>>>(tm, P);
   return check_launch(GATE ? "dwconv3x3_gelu_gate_tma" : "dwconv3x3_tma");
 }
 
