@@ -299,6 +299,15 @@ mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float
     na[j] = fmaxf(sqrtf(s), 1e-12f);  // na[d..2d) aliases nb
   }
   __syncthreads();
+  // stage this head's column blocks W_out[:, hd:hd+d] and dM_b[:, hd:hd+d] (C x d each) in shared memory
+  float* wsm = cs + d;                   // [C][d]
+  float* dsm = wsm + (size_t)C * d;      // [C][d]
+  for (int e = tid; e < C * d; e += MB_THREADS) {
+    const int o = e / d, i = e - o * d;
+    wsm[e] = w_out[(size_t)o * C + h * d + i];
+    dsm[e] = dMb[(size_t)o * C + h * d + i];
+  }
+  __syncthreads();
   for (int e = tid; e < d * d; e += MB_THREADS) {
     const int i = e / d, j = e % d;
     float s = 0.f;
@@ -307,8 +316,8 @@ mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float
     at[i * D1 + j] = a_g[e];
     // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
     float acc = 0.f;
-#pragma unroll 4
-    for (int o = 0; o < C; ++o) acc = fmaf(w_out[(size_t)o * C + h * d + i], dMb[(size_t)o * C + h * d + j], acc);
+#pragma unroll 8
+    for (int o = 0; o < C; ++o) acc = fmaf(wsm[o * d + i], dsm[o * d + j], acc);
     da[i * D1 + j] = acc;
   }
   __syncthreads();
@@ -562,7 +571,7 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   B200IR_UNSUPPORTED(C <= 4096, "ln_bwd: C=%d > 4096 unsupported", C);
   const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
-  ln_bwd_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
+ln_bwd_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
       x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride, dx_dtype,
       parts, C, HW, tps, ntiles);
   return check_launch("ln_bwd");
@@ -643,7 +652,8 @@ extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* at
   B200IR_CHECK_ARG(nslab > 0 && B > 0 && C > 0 && heads > 0 && C % heads == 0 && B <= 65535, "mdta_bwd: bad shape");
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
-  const size_t smem = (3 * (size_t)d * (d + 1) + 4 * (size_t)d) * sizeof(float);
+  const size_t smem = (3 * (size_t)d * (d + 1) + 4 * (size_t)d + 2 * (size_t)C * d) * sizeof(float);
+  B200IR_UNSUPPORTED(smem <= 220 * 1024, "mdta_bwd: C=%d head dim %d needs %zu B of shared memory", C, d, smem);
   const size_t smem2 = ((size_t)d * (d + 1) + 64 * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
