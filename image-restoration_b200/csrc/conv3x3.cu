@@ -88,6 +88,10 @@ conv3x3_simt_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const fl
   }
 }
 
+int conv3x3_thin_launch(const void* x, int64_t x_bs, int x_dt, const float* w, const float* bias, const void* res,
+                        int64_t res_bs, int res_dt, void* y, int64_t y_bs, int y_dt, int B, int Cin, int Cout, int H,
+                        int W, cudaStream_t st);  // conv3x3_thin.cu
+
 }  // namespace b200ir
 
 using namespace b200ir;
@@ -103,6 +107,11 @@ extern "C" int b200ir_conv3x3_fwd(const void* x, int64_t x_bstride, int x_dtype,
                    "conv3x3: PixelUnshuffle(2) needs even H,W (got %dx%d)", H, W);
   B200IR_CHECK_ARG(shuffle_mode != B200IR_SHUFFLE2 || Cout % 4 == 0, "conv3x3: PixelShuffle(2) needs Cout%%4==0");
   B200IR_CHECK_ARG(B <= 65535 && (Cout + COT - 1) / COT <= 65535, "conv3x3: grid too large");
+  if (shuffle_mode == B200IR_SHUFFLE_NONE) {  // patch-embed / output conv: one side of the channel pair is tiny
+    const int rc = conv3x3_thin_launch(x, x_bstride, x_dtype, w, bias, res, res_bstride, res_dtype, y, y_bstride,
+                                       y_dtype, B, Cin, Cout, H, W, (cudaStream_t)stream);
+    if (rc >= 0) return rc;   // -1: not a thin shape
+  }
   const int tiles_x = (W + CT - 1) / CT, tiles_y = (H + CT - 1) / CT;
   dim3 grid((unsigned)(tiles_x * tiles_y), (unsigned)((Cout + COT - 1) / COT), (unsigned)B);
   conv3x3_simt_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, w, bias, res, res_bstride,

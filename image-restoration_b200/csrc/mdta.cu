@@ -80,6 +80,27 @@ gram_simt_kernel(const void* __restrict__ qkv, int64_t bs, int dt, int C, int d,
   if (tid < 2 * d) out[d * d + tid] = nrm;
 }
 
+// sum of n values spaced `stride` apart, in index order (bitwise reproducible), with the loads of each group of 8 issued
+// together so the chain is not one DRAM/L2 latency per term
+__device__ __forceinline__ float ordered_sum(const float* __restrict__ p, size_t stride, int n) {
+  float s = 0.f;
+  int i = 0;
+  for (; i + 8 <= n; i += 8) {
+    float v[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) v[k] = __ldg(p + (size_t)(i + k) * stride);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += v[k];
+  }
+  float v[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) v[k] = i + k < n ? __ldg(p + (size_t)(i + k) * stride) : 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (i + k < n) s += v[k];
+  return s;
+}
+
 // ---- stage 2a: slab reduce + normalise + temperature + row softmax.  grid (ceil(d/8), heads, B), 256 threads:
 // one warp per attention row (8 rows per block), so B*heads*d/8 blocks share the slab reduction.
 __global__ void __launch_bounds__(256)
@@ -93,8 +114,7 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
   const size_t per = (size_t)d * d + 2 * d;
   const float* base = partials + ((size_t)b * heads + h) * nslab * per;
   for (int j = tid; j < d; j += 256) {
-    float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + d + j];  // fixed order
+    const float s = ordered_sum(base + (size_t)d * d + d + j, per, nslab);  // fixed order
     nk[j] = fmaxf(sqrtf(s), 1e-12f);                                                          // (:122)
   }
   __syncthreads();
@@ -102,8 +122,7 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
   if (i >= d) return;
   float nq = 0.f;
   if (lane == 0) {
-    float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + i];
+    const float s = ordered_sum(base + (size_t)d * d + i, per, nslab);
     nq = fmaxf(sqrtf(s), 1e-12f);                                                             // (:121)
   }
   nq = __shfl_sync(0xffffffffu, nq, 0);
@@ -111,8 +130,7 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
   float* row = rowbuf + warp * d;
   float mx = -INFINITY;
   for (int j = lane; j < d; j += 32) {
-    float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)i * d + j];       // fixed order
+    const float s = ordered_sum(base + (size_t)i * d + j, per, nslab);  // fixed order
     const float v = s / (nq * nk[j]) * temp;                                                  // (:124)
     row[j] = v;
     mx = fmaxf(mx, v);
@@ -131,25 +149,25 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
 }
 
 // ---- stage 2b: fold project_out into the attention matrix: m[b][o][h*d+j] = sum_i w_out[o][h*d+i] attn[b,h][i][j]
-// grid (ceil(C/32), heads, B), 256 threads.  Writes fp32 m [B,C,C] and/or the bf16 operand of the tcgen05 GEMM
+// grid (ceil(C/kFoldRows), heads, B), 256 threads; kFoldRows = 32 or 8 (launcher).  Writes fp32 m [B,C,C] and/or the bf16 operand of the tcgen05 GEMM
 // mp [B][nrows][kpad] (zero padded) so that no separate packing launch is needed.
 __global__ void __launch_bounds__(256)
 mdta_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out, float* __restrict__ m,
-                 bf16* __restrict__ mp, int kpad, int nrows, int C, int d) {
+                 bf16* __restrict__ mp, int kpad, int nrows, int C, int d, int kFoldRows) {
   extern __shared__ float sm[];
   float* at = sm;                    // [d][d+1]
-  float* ws = sm + (size_t)d * (d + 1);  // [32][d+1]
+  float* ws = sm + (size_t)d * (d + 1);  // [kFoldRows][d+1]
   const int tid = threadIdx.x;
   const int h = blockIdx.y, b = blockIdx.z, heads = gridDim.y;
-  const int o0 = blockIdx.x * 32;
+  const int o0 = blockIdx.x * kFoldRows;
   const float* a = attn + ((size_t)b * heads + h) * d * d;
   for (int e = tid; e < d * d; e += 256) at[(e / d) * (d + 1) + (e % d)] = a[e];
-  for (int e = tid; e < 32 * d; e += 256) {
+  for (int e = tid; e < kFoldRows * d; e += 256) {
     const int o = o0 + e / d, i = e % d;
     ws[(e / d) * (d + 1) + i] = o < C ? w_out[(size_t)o * C + h * d + i] : 0.f;
   }
   __syncthreads();
-  for (int e = tid; e < 32 * d; e += 256) {
+  for (int e = tid; e < kFoldRows * d; e += 256) {
     const int ol = e / d, j = e % d, o = o0 + ol;
     if (o >= C) continue;
     float s = 0.f;
@@ -159,7 +177,7 @@ mdta_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out
   }
   if (mp) {  // zero padding: columns [C,kpad) of valid rows (head 0 blocks) and whole rows [C,nrows) (last row block)
     if (h == 0)
-      for (int e = tid; e < 32 * (kpad - C); e += 256) {
+      for (int e = tid; e < kFoldRows * (kpad - C); e += 256) {
         const int o = o0 + e / (kpad - C), c = C + e % (kpad - C);
         if (o < C) mp[((size_t)b * nrows + o) * kpad + c] = __float2bfloat16_rn(0.f);
       }
@@ -241,13 +259,15 @@ extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, co
                         st>>>(partials, nslab, temperature, attn, d);
   int rc = check_launch("mdta_softmax");
   if (rc) return rc;
-  const size_t smem = ((size_t)d * (d + 1) + 32 * (size_t)(d + 1)) * sizeof(float);
+  // output rows per block: 32 when that already fills the GPU, else 8 (few heads / small batch)
+  const int kFoldRows = (int64_t)((C + 31) / 32) * heads * B >= 2 * 148 ? 32 : 8;
+  const size_t smem = ((size_t)d * (d + 1) + kFoldRows * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(mdta_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
     attr_set = true;
   }
-  mdta_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem, st>>>(
-      attn, w_out, m, (bf16*)mp, kpad, nrows, C, d);
+  mdta_fold_kernel<<<dim3((unsigned)((C + kFoldRows - 1) / kFoldRows), (unsigned)heads, (unsigned)B), 256, smem, st>>>(
+      attn, w_out, m, (bf16*)mp, kpad, nrows, C, d, kFoldRows);
   return check_launch("mdta_fold");
 }

@@ -148,6 +148,35 @@ def test_conv3x3(b200ir, dtype, mode, Cin, Cout, H, W):
         assert rel_err(y, ref) < 6e-3
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("Cin,Cout,B,H,W,bias,res", [
+    (3, 48, 2, 9, 13, True, False),      # patch embed, odd width (scalar stores), ragged tile
+    (3, 48, 1, 24, 128, False, False),   # two column tiles, vector stores
+    (1, 20, 2, 10, 66, True, True),      # grey input, Cout not a multiple of 8
+    (96, 3, 2, 16, 256, False, True),    # output conv, 16-byte staging path + `+ inp_img`
+    (50, 3, 1, 11, 130, True, True),     # ragged channels / width: scalar staging
+    (48, 1, 2, 8, 128, True, False),     # grey output
+])
+def test_conv3x3_thin(b200ir, dtype, Cin, Cout, B, H, W, bias, res):
+    """The thin-input / thin-output kernels (conv3x3_thin.cu) behind b200ir_conv3x3_fwd, Restormer.py:220,257,306."""
+    L = b200ir._lib
+    g = torch.Generator().manual_seed(11)
+    x = (torch.rand(B, Cin, H, W, generator=g) * 2 - 1).to(dtype)
+    w = (torch.rand(Cout, Cin, 3, 3, generator=g) - 0.5) / (Cin * 9) ** 0.5
+    bv = torch.rand(Cout, generator=g) - 0.5 if bias else None
+    ref = F.conv2d(x.float(), w, bv, padding=1)
+    r = None
+    if res:
+        r = (torch.rand(ref.shape, generator=g) - 0.5).to(dtype)
+        ref = ref + r.float()
+    y = b200ir.ops.conv3x3(dev(x), dev(w), dev(bv) if bias else None, dev(r) if res else None, L.SHUFFLE_NONE)
+    y = y.float().cpu()
+    if dtype == torch.float32:
+        assert (y - ref).abs().max() <= 2e-5
+    else:
+        assert rel_err(y, ref) < 6e-3
+
+
 @pytest.mark.parametrize("case", BLOCK_CASES, ids=[c[0] for c in BLOCK_CASES])
 def test_block_vs_golden_fp32(b200ir, case):
     """TransformerBlock on the GPU (fp32 path) against the reference's stored output."""
