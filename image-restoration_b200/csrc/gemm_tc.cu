@@ -838,6 +838,12 @@ extern "C" int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, co
   return check_launch("pack_conv1x1");
 }
 
+namespace b200ir {
+int gemm_stream_launch(const void* x, int64_t x_bs, const void* wp, int Bw, const float* st, int ln_type,
+                       const void* res, int64_t res_bs, int res_dt, void* y, int64_t y_bs, int y_dt, int B, int Cin,
+                       int Cout, int64_t HW, int Kpad, int Nrows, cudaStream_t stream);  // gemm_stream_tc.cu
+}
+
 extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st,
                                   int ln_type, const void* res, int64_t res_bstride, int res_dtype, void* y,
                                   int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int64_t HW,
@@ -865,6 +871,18 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
                      "gemm_tc: needs HW%%8==0, HW>=64 and 16B-aligned activations (HW=%lld)", (long long)HW);
   B200IR_UNSUPPORTED(HW < (1ll << 31) && (int64_t)B * ((HW + 127) / 128) < (1ll << 31), "gemm_tc: too many tiles");
 
+  // Deep levels (Cin >= 384: level 4 and the level-3/4 project_out): the weight matrix needs 3..15 resident slices, every
+  // slice re-reads the activations and issues narrow MMAs -> stream both operands instead (gemm_stream_tc.cu; measured
+  // 384->2042 103 -> 62 us, 1021->384 84 -> 39 us).  With short K the streamed weights cost more L2 traffic than the
+  // output is worth, so everything else stays on the resident-weight kernel.  B200IR_GEMM_STREAM=0 / 1 forces never /
+  // always (tests, A/B runs).
+  {
+    const char* se = getenv("B200IR_GEMM_STREAM");
+    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && g.nslices >= 2);
+    if (!mode4 && want && Cin >= 64)
+      return gemm_stream_launch(x, x_bstride, wp, Bw, st, ln_type, res, res_bstride, res_dtype, y, y_bstride, y_dtype,
+                                B, Cin, Cout, HW, g.Kpad, g.Nrows, (cudaStream_t)stream);
+  }
   CUtensorMap tmX, tmW;
   {
     const uint64_t dims[3] = {(uint64_t)HW, (uint64_t)Cin, (uint64_t)B};

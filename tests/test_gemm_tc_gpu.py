@@ -120,3 +120,41 @@ def test_gemm_tc_channels_on_lanes_epilogue_matches_default():
         torch.cuda.synchronize()
         assert (y0.float() - y1.float()).abs().max() <= 2e-2 * y0.float().abs().max()
         assert ((y1f - y0.float()).norm() / y0.float().norm()) < 4e-3
+
+
+def test_gemm_stream_matches_resident_weights_kernel():
+    """Deep-level shapes go to the streamed-operand kernel (gemm_stream_tc.cu); B200IR_GEMM_STREAM=0 forces the
+    resident-weight kernel.  Same packed operands, same fp32 accumulation -> results agree to bf16 rounding; ragged pixel
+    tiles, several items per CTA, per-sample weights, all LayerNorm kinds, residual, both output dtypes."""
+    import os
+    import b200ir
+    from b200ir import ops
+    L = b200ir._lib
+    g = torch.Generator().manual_seed(99)
+    cases = [(3, 384, 2042, 40, 40, L.LN_WITHBIAS, False, False), (2, 1021, 384, 24, 40, L.LN_NONE, True, False),
+             (2, 384, 1152, 25, 40, L.LN_BIASFREE, False, False), (3, 384, 384, 32, 32, L.LN_NONE, True, True),
+             (1, 192, 1020, 64, 72, L.LN_WITHBIAS, False, False)]
+    for (B, Cin, Cout, H, W, ln, res, per_sample) in cases:
+        x = (torch.rand(B, Cin, H, W, generator=g) * 2 - 0.5).bfloat16().cuda()
+        wshape = (B, Cout, Cin) if per_sample else (Cout, Cin)
+        w = ((torch.rand(wshape, generator=g) - 0.5) / Cin ** 0.5).cuda()
+        bias = (torch.rand(Cout, generator=g) - 0.5).cuda()
+        lw, lb = (torch.rand(Cin, generator=g) + 0.5).cuda(), (torch.rand(Cin, generator=g) - 0.5).cuda()
+        r = (torch.rand(B, Cout, H, W, generator=g) - 0.5).bfloat16().cuda() if res else None
+        packed = ops.pack_conv1x1(w, bias, ln, lw if ln else None, lb if ln == L.LN_WITHBIAS else None,
+                                  per_sample=per_sample)
+        os.environ["B200IR_GEMM_STREAM"] = "0"
+        try:
+            y0 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
+        finally:
+            os.environ.pop("B200IR_GEMM_STREAM", None)
+        os.environ["B200IR_GEMM_STREAM"] = "1"
+        try:
+            y1 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
+            y1b = ops.gemm_tc(x, packed, Cout, ln, r)
+        finally:
+            os.environ.pop("B200IR_GEMM_STREAM", None)
+        torch.cuda.synchronize()
+        scale = y0.abs().max()
+        assert (y0 - y1).abs().max() <= 1e-4 * scale, (Cin, Cout, float((y0 - y1).abs().max()), float(scale))
+        assert (y1b.float() - y1).abs().max() <= 1e-2 * scale
