@@ -18,22 +18,26 @@ namespace b200ir {
 // =====================================================================================================
 constexpr int LN_PX = 32;
 
-__device__ __forceinline__ float ln_cross_warp(float v, float (*red)[LN_PX], int warp, int lane) {
-  __syncthreads();            // previous use of red is over
-  red[warp][lane] = v;
-  __syncthreads();
-  float s = 0.f;
-#pragma unroll
-  for (int w = 0; w < 8; ++w) s += red[w][lane];
-  return s;
+// DT: compile-time activation dtype of ALL tensors of the launch (B200IR_F32 / B200IR_BF16), or -1 = per-tensor runtime
+// dtype (then every load is a branch and the loads of an unrolled channel loop cannot be issued together).
+template <int DT> __device__ __forceinline__ float ldt(const void* p, int dt, int64_t i) {
+  if (DT == B200IR_BF16) return __bfloat162float(((const bf16*)p)[i]);
+  if (DT == B200IR_F32) return ((const float*)p)[i];
+  return ld_any(p, dt, i);
+}
+template <int DT> __device__ __forceinline__ void stt(void* p, int dt, int64_t i, float v) {
+  if (DT == B200IR_BF16) ((bf16*)p)[i] = __float2bfloat16_rn(v);
+  else if (DT == B200IR_F32) ((float*)p)[i] = v;
+  else st_any(p, dt, i, v);
 }
 
 // y = LN(x) materialised (operand of the weight-gradient GEMM of the fused LN + 1x1 conv)
+template <int DT>
 __global__ void __launch_bounds__(256)
 ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, const float* __restrict__ lw,
               const float* __restrict__ lb, void* __restrict__ y, int64_t y_bs, int y_dt, int C, int64_t HW, int tps,
               int64_t ntiles) {
-  __shared__ float red[8][LN_PX];
+  __shared__ float red2[8][2][LN_PX];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const float invC = 1.0f / (float)C;
   for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -41,25 +45,38 @@ ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, c
     const int64_t p = (t % tps) * LN_PX + lane;
     const bool valid = p < HW;
     const int64_t xo = (int64_t)b * x_bs + p, yo = (int64_t)b * y_bs + p;
-    float s = 0.f;
-    if (valid)
-      for (int c = warp; c < C; c += 8) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
-    const float mu = ln_cross_warp(s, red, warp, lane) * invC;
-    float v = 0.f;
-    if (valid)
+    const float x0 = valid ? ldt<DT>(x, x_dt, xo) : 0.f;   // shift: keeps E[d^2] - E[d]^2 well conditioned
+    float S1 = 0.f, S2 = 0.f;
+    if (valid) {
+#pragma unroll 4
       for (int c = warp; c < C; c += 8) {
-        const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
-        v += d * d;
+        const float d = ldt<DT>(x, x_dt, xo + (int64_t)c * HW) - x0;
+        S1 += d;
+        S2 = fmaf(d, d, S2);
       }
-    const float rstd = 1.0f / sqrtf(ln_cross_warp(v, red, warp, lane) * invC + 1e-5f);
-    if (valid)
+    }
+    __syncthreads();
+    red2[warp][0][lane] = S1;
+    red2[warp][1][lane] = S2;
+    __syncthreads();
+    S1 = S2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      S1 += red2[w][0][lane];
+      S2 += red2[w][1][lane];
+    }
+    const float md = S1 * invC, mu = x0 + md;
+    const float rstd = 1.0f / sqrtf(fmaxf(S2 * invC - md * md, 0.f) + 1e-5f);
+    if (valid) {
+#pragma unroll 4
       for (int c = warp; c < C; c += 8) {
-        const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
+        const float xv = ldt<DT>(x, x_dt, xo + (int64_t)c * HW);
         float n;
-        if (ln_type == B200IR_LN_WITHBIAS) n = (xv - mu) * rstd * lw[c] + lb[c];   // Restormer.py:57
-        else n = xv * rstd * lw[c];                                                // Restormer.py:39
-        st_any(y, y_dt, yo + (int64_t)c * HW, n);
+        if (ln_type == B200IR_LN_WITHBIAS) n = (xv - mu) * rstd * __ldg(lw + c) + __ldg(lb + c);   // Restormer.py:57
+        else n = xv * rstd * __ldg(lw + c);                                                       // Restormer.py:39
+        stt<DT>(y, y_dt, yo + (int64_t)c * HW, n);
       }
+    }
   }
 }
 
@@ -69,13 +86,14 @@ ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, c
 // dx (+)= res (gradient arriving through the residual path of TransformerBlock, Restormer.py:147-148).
 // parts: fp32 [gridDim.x][2][C] partial dgamma / dbeta; a channel is only ever touched by one warp of the CTA, which
 // accumulates it tile after tile in shared memory: fixed order, deterministic.
+template <int DT>
 __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __restrict__ g, int64_t g_bs, int g_dt,
               int ln_type, const float* __restrict__ lw, const void* __restrict__ res, int64_t res_bs, int res_dt,
               void* __restrict__ dx, int64_t dx_bs, int dx_dt, float* __restrict__ parts, int C, int64_t HW, int tps,
               int64_t ntiles) {
   extern __shared__ float acc[];  // [2][C]
-  __shared__ float red[8][LN_PX];
+  __shared__ float red4[8][4][LN_PX];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < 2 * C; i += 256) acc[i] = 0.f;
   __syncthreads();
@@ -85,35 +103,61 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
     const int64_t p = (t % tps) * LN_PX + lane;
     const bool valid = p < HW;
     const int64_t xo = (int64_t)b * x_bs + p, go = (int64_t)b * g_bs + p;
-    float s = 0.f;
-    if (valid)
-      for (int c = warp; c < C; c += 8) s += ld_any(x, x_dt, xo + (int64_t)c * HW);
-    const float mu = ln_cross_warp(s, red, warp, lane) * invC;
-    float v = 0.f;
-    if (valid)
+    // pass A (one trip over x and g): shifted sums S1 = sum(x-x0), S2 = sum((x-x0)^2), H1 = sum(h), H2 = sum(h*(x-x0))
+    const float x0 = valid ? ldt<DT>(x, x_dt, xo) : 0.f;
+    float S1 = 0.f, S2 = 0.f, H1 = 0.f, H2 = 0.f;
+    if (valid) {
+#pragma unroll 4
       for (int c = warp; c < C; c += 8) {
-        const float d = ld_any(x, x_dt, xo + (int64_t)c * HW) - mu;
-        v += d * d;
+        const float d = ldt<DT>(x, x_dt, xo + (int64_t)c * HW) - x0;
+        const float h = ldt<DT>(g, g_dt, go + (int64_t)c * HW) * __ldg(lw + c);
+        S1 += d;
+        S2 = fmaf(d, d, S2);
+        H1 += h;
+        H2 = fmaf(h, d, H2);
       }
-    const float rstd = 1.0f / sqrtf(ln_cross_warp(v, red, warp, lane) * invC + 1e-5f);
-    float s1 = 0.f, s2 = 0.f;
+    }
+    __syncthreads();   // previous tile's readers of red4 are done
+    red4[warp][0][lane] = S1;
+    red4[warp][1][lane] = S2;
+    red4[warp][2][lane] = H1;
+    red4[warp][3][lane] = H2;
+    __syncthreads();
+    S1 = S2 = H1 = H2 = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      S1 += red4[w][0][lane];
+      S2 += red4[w][1][lane];
+      H1 += red4[w][2][lane];
+      H2 += red4[w][3][lane];
+    }
+    const float md = S1 * invC;                       // mu - x0
+    const float mu = x0 + md;
+    const float rstd = 1.0f / sqrtf(fmaxf(S2 * invC - md * md, 0.f) + 1e-5f);
+    const float s1 = H1 * invC;                       // mean(h)
+    // WithBias: s2 = mean(h*xh) = rstd*(mean(h*(x-x0)) - md*mean(h));  BiasFree: s2 = mean(h*x)
+    const float s2 = ln_type == B200IR_LN_WITHBIAS ? rstd * (H2 * invC - md * s1) : (H2 * invC + x0 * s1);
+    // pass B: dx, and this tile's contribution to dgamma / dbeta
+    const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p;
+#pragma unroll 2
     for (int c = warp; c < C; c += 8) {
-      float xv = 0.f, gv = 0.f;
+      float xv = 0.f, gv = 0.f, rv = 0.f;
       if (valid) {
-        xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
-        gv = ld_any(g, g_dt, go + (int64_t)c * HW);
+        xv = ldt<DT>(x, x_dt, xo + (int64_t)c * HW);
+        gv = ldt<DT>(g, g_dt, go + (int64_t)c * HW);
+        if (res) rv = ldt<DT>(res, res_dt, ro + (int64_t)c * HW);
       }
-      const float h = gv * lw[c];
-      float dgam, dbet = gv;
+      const float h = gv * __ldg(lw + c);
+      float d, dgam, dbet = gv;
       if (ln_type == B200IR_LN_WITHBIAS) {
         const float xh = (xv - mu) * rstd;
-        s1 += h;
-        s2 += h * xh;
+        d = rstd * (h - s1 - xh * s2);
         dgam = gv * xh;
       } else {
-        s2 += h * xv;
+        d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2;
         dgam = gv * xv * rstd;
       }
+      if (valid) stt<DT>(dx, dx_dt, dxo + (int64_t)c * HW, d + rv);
       dgam = warp_sum(dgam);
       dbet = warp_sum(dbet);
       if (lane == 0) {
@@ -121,22 +165,109 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
         acc[C + c] += dbet;
       }
     }
-    s1 = ln_cross_warp(s1, red, warp, lane) * invC;
-    s2 = ln_cross_warp(s2, red, warp, lane) * invC;
+  }
+  __syncthreads();
+  float* out = parts + (size_t)blockIdx.x * 2 * C;
+  for (int i = threadIdx.x; i < 2 * C; i += 256) out[i] = acc[i];
+}
+
+// bf16 fast path of ln_bwd_kernel: a lane owns TWO adjacent pixels (bf16x2 accesses: 128 B per warp instruction, half the
+// instructions and half the dgamma/dbeta shuffles per byte), channel pointers advance by 8*HW instead of being
+// recomputed.  Needs HW even, even batch strides and 4-byte aligned bases.  Same two-pass math as above.
+__global__ void __launch_bounds__(256)
+ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __restrict__ g, int64_t g_bs, int ln_type,
+                     const float* __restrict__ lw, const bf16* __restrict__ res, int64_t res_bs, bf16* __restrict__ dx,
+                     int64_t dx_bs, float* __restrict__ parts, int C, int64_t HW, int tps, int64_t ntiles) {
+  extern __shared__ float acc[];  // [2][C]
+  __shared__ float2 red4[8][4][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 2 * C; i += 256) acc[i] = 0.f;
+  __syncthreads();
+  const float invC = 1.0f / (float)C;
+  const int64_t cstep = 8 * HW;
+  auto ld2 = [](const bf16* p) {
+    return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+  };
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int b = (int)(t / tps);
+    const int64_t p = (t % tps) * 64 + 2 * lane;
+    const bool valid = p < HW;
+    const bf16* xw = x + (int64_t)b * x_bs + p + (int64_t)warp * HW;
+    const bf16* gw = g + (int64_t)b * g_bs + p + (int64_t)warp * HW;
+    const float2 x0 = valid ? ld2(x + (int64_t)b * x_bs + p) : make_float2(0.f, 0.f);
+    float2 S1 = {0.f, 0.f}, S2 = {0.f, 0.f}, H1 = {0.f, 0.f}, H2 = {0.f, 0.f};
     if (valid) {
-      const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p;
-      for (int c = warp; c < C; c += 8) {
-        const float xv = ld_any(x, x_dt, xo + (int64_t)c * HW);
-        const float h = ld_any(g, g_dt, go + (int64_t)c * HW) * lw[c];
-        float d;
+      const bf16 *xp = xw, *gp = gw;
+#pragma unroll 4
+      for (int c = warp; c < C; c += 8, xp += cstep, gp += cstep) {
+        const float2 xv = ld2(xp), gv = ld2(gp);
+        const float gam = __ldg(lw + c);
+        const float d0 = xv.x - x0.x, d1 = xv.y - x0.y, h0 = gv.x * gam, h1 = gv.y * gam;
+        S1.x += d0; S1.y += d1;
+        S2.x = fmaf(d0, d0, S2.x); S2.y = fmaf(d1, d1, S2.y);
+        H1.x += h0; H1.y += h1;
+        H2.x = fmaf(h0, d0, H2.x); H2.y = fmaf(h1, d1, H2.y);
+      }
+    }
+    __syncthreads();
+    red4[warp][0][lane] = S1;
+    red4[warp][1][lane] = S2;
+    red4[warp][2][lane] = H1;
+    red4[warp][3][lane] = H2;
+    __syncthreads();
+    S1 = S2 = H1 = H2 = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const float2 a = red4[w][0][lane], bq = red4[w][1][lane], cq = red4[w][2][lane], dq = red4[w][3][lane];
+      S1.x += a.x; S1.y += a.y; S2.x += bq.x; S2.y += bq.y;
+      H1.x += cq.x; H1.y += cq.y; H2.x += dq.x; H2.y += dq.y;
+    }
+    float mu[2], rstd[2], s1[2], s2[2];
+    {
+      const float S1v[2] = {S1.x, S1.y}, S2v[2] = {S2.x, S2.y}, H1v[2] = {H1.x, H1.y}, H2v[2] = {H2.x, H2.y};
+      const float x0v[2] = {x0.x, x0.y};
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float md = S1v[k] * invC;
+        mu[k] = x0v[k] + md;
+        rstd[k] = 1.0f / sqrtf(fmaxf(S2v[k] * invC - md * md, 0.f) + 1e-5f);
+        s1[k] = H1v[k] * invC;
+        s2[k] = ln_type == B200IR_LN_WITHBIAS ? rstd[k] * (H2v[k] * invC - md * s1[k]) : (H2v[k] * invC + x0v[k] * s1[k]);
+      }
+    }
+    const bf16 *xp = xw, *gp = gw;
+    const bf16* rp = res ? res + (int64_t)b * res_bs + p + (int64_t)warp * HW : nullptr;
+    bf16* dp = dx + (int64_t)b * dx_bs + p + (int64_t)warp * HW;
+#pragma unroll 2
+    for (int c = warp; c < C; c += 8, xp += cstep, gp += cstep, dp += cstep) {
+      float2 xv = {0.f, 0.f}, gv = {0.f, 0.f}, rv = {0.f, 0.f};
+      if (valid) {
+        xv = ld2(xp);
+        gv = ld2(gp);
+        if (rp) rv = ld2(rp);
+      }
+      if (rp) rp += cstep;
+      const float gam = __ldg(lw + c);
+      const float xs[2] = {xv.x, xv.y}, gs[2] = {gv.x, gv.y};
+      float d[2], dgam = 0.f;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float h = gs[k] * gam;
         if (ln_type == B200IR_LN_WITHBIAS) {
-          const float xh = (xv - mu) * rstd;
-          d = rstd * (h - s1 - xh * s2);
+          const float xh = (xs[k] - mu[k]) * rstd[k];
+          d[k] = rstd[k] * (h - s1[k] - xh * s2[k]);
+          dgam = fmaf(gs[k], xh, dgam);
         } else {
-          d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2;
+          d[k] = rstd[k] * h - rstd[k] * rstd[k] * rstd[k] * (xs[k] - mu[k]) * s2[k];
+          dgam = fmaf(gs[k] * xs[k], rstd[k], dgam);
         }
-        if (res) d += ld_any(res, res_dt, ro + (int64_t)c * HW);
-        st_any(dx, dx_dt, dxo + (int64_t)c * HW, d);
+      }
+      if (valid) *reinterpret_cast<__nv_bfloat162*>(dp) = __floats2bfloat162_rn(d[0] + rv.x, d[1] + rv.y);
+      dgam = warp_sum(dgam);
+      const float dbet = warp_sum(gv.x + gv.y);
+      if (lane == 0) {
+        acc[c] += dgam;
+        acc[C + c] += dbet;
       }
     }
   }
@@ -546,9 +677,14 @@ extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int 
   B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(y_dtype), "ln_fwd: bad dtype");
   const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
-  ln_fwd_kernel<<<grid_1d(ntiles, 1, 148 * 16), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w,
-                                                                               ln_b, y, y_bstride, y_dtype, C, HW, tps,
-                                                                               ntiles);
+#define B200IR_LN_FWD(DT)                                                                                        \
+  ln_fwd_kernel<DT><<<grid_1d(ntiles, 1, 148 * 16), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w, \
+                                                                                   ln_b, y, y_bstride, y_dtype, C, HW,  \
+                                                                                   tps, ntiles)
+  if (x_dtype == y_dtype && x_dtype == B200IR_BF16) B200IR_LN_FWD(B200IR_BF16);
+  else if (x_dtype == y_dtype) B200IR_LN_FWD(B200IR_F32);
+  else B200IR_LN_FWD(-1);
+#undef B200IR_LN_FWD
   return check_launch("ln_fwd");
 }
 
@@ -571,9 +707,25 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   B200IR_UNSUPPORTED(C <= 4096, "ln_bwd: C=%d > 4096 unsupported", C);
   const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
-ln_bwd_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
-      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride, dx_dtype,
-      parts, C, HW, tps, ntiles);
+#define B200IR_LN_BWD(DT)                                                                                   \
+  ln_bwd_kernel<DT><<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(                          \
+      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride,     \
+      dx_dtype, parts, C, HW, tps, ntiles)
+  const bool same = x_dtype == g_dtype && x_dtype == dx_dtype && (!res || res_dtype == x_dtype);
+  auto even = [](const void* q, int64_t bs) { return !q || (((uintptr_t)q & 3) == 0 && (bs & 1) == 0); };
+  // (tiny planes keep the 32-pixel tiles: twice as many CTAs to spread the channel loop over)
+  if (same && x_dtype == B200IR_BF16 && (HW & 1) == 0 && (int64_t)B * ((HW + 63) / 64) >= 2 * 148 && even(x, x_bstride) && even(g, g_bstride) &&
+      even(res, res_bstride) && even(dx, dx_bstride)) {
+    const int tps2 = (int)((HW + 63) / 64);
+    ln_bwd_bf16x2_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
+        (const bf16*)x, x_bstride, (const bf16*)g, g_bstride, ln_type, ln_w, (const bf16*)res, res_bstride, (bf16*)dx,
+        dx_bstride, parts, C, HW, tps2, (int64_t)B * tps2);
+    return check_launch("ln_bwd_bf16x2");
+  }
+  if (same && x_dtype == B200IR_BF16) B200IR_LN_BWD(B200IR_BF16);
+  else if (same) B200IR_LN_BWD(B200IR_F32);
+  else B200IR_LN_BWD(-1);
+#undef B200IR_LN_BWD
   return check_launch("ln_bwd");
 }
 
