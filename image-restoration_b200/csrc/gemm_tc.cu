@@ -878,7 +878,7 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   // always (tests, A/B runs).
   {
     const char* se = getenv("B200IR_GEMM_STREAM");
-    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && g.nslices >= 2);
+    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && (g.nslices >= 3 || (!res && g.nslices >= 2)));
     if (!mode4 && want && Cin >= 64)
       return gemm_stream_launch(x, x_bstride, wp, Bw, st, ln_type, res, res_bstride, res_dtype, y, y_bstride, y_dtype,
                                 B, Cin, Cout, HW, g.Kpad, g.Nrows, (cudaStream_t)stream);
