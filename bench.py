@@ -136,6 +136,7 @@ def main():
     ap.add_argument("--dtype", default="bf16", choices=["bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the cfg4 training-step leg")
+    ap.add_argument("--no-hires", action="store_true", help="skip the cfg5 1024x1024 leg")
     ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -215,6 +216,25 @@ def main():
             torch.cuda.synchronize()
             table = ops.timing_stop()
 
+    # ---- high-resolution leg (BASELINE configs[4]): 1024x1024 full frame, batch 1 per GPU ----------------------------
+    hires = None
+    if not args.no_hires:
+        HR = 1024
+        hin = [O.synth_image(1, HR, HR, seed=777 + 10 * rank + i).to(dev) for i in range(3)]
+        with torch.no_grad():
+            for i in range(args.warmup):
+                net(hin[i % 3])
+            barrier()
+            e0.record()
+            for i in range(args.steps):
+                net(hin[i % 3])
+            e1.record()
+            barrier()
+        ms_hr = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        hires = {"workload": f"Restormer forward, one {HR}x{HR} RGB frame per GPU, {args.dtype}; BASELINE configs[4]",
+                 "value": world * HR * HR / 1e6 / (ms_hr * 1e-3), "unit": "MP/s", "ms_per_step": ms_hr}
+        del hin
+
     # ---- training-step leg (BASELINE configs[3]): L1 + AdamW, 128x128 patches, batch 8 per GPU, DDP all-reduce --------
     train = None
     if not args.no_train:
@@ -274,6 +294,8 @@ def main():
     }
     if train is not None:
         out["train_step"] = train
+    if hires is not None:
+        out["hires"] = hires
     if not args.no_cpu_baseline:
         v, dt, cores, sample = cpu_reference_run(2, 1)
         out["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample,
