@@ -187,9 +187,12 @@ mdta_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out
   }
 }
 
-int gram_slab_len(int B, int heads, int64_t HW, int* nslab_out) {
-  // enough (b, head, slab) work items for ~2 waves of 148 SMs; slabs are multiples of 256 pixels
-  int64_t want = (2 * 148 + (int64_t)B * heads - 1) / ((int64_t)B * heads);
+int gram_slab_len(int B, int d, int heads, int64_t HW, int* nslab_out) {
+  // (b, head, slab) work items = CTAs: as many as run CONCURRENTLY on 148 SMs and no more, so that there is no
+  // nearly-empty last wave (19 slabs x 16 samples = 304 CTAs on 148 resident slots ran as 2.05 -> 3 waves).  Head dims
+  // <= 64 fit two CTAs per SM (TMEM columns and shared memory), larger ones one.  Slabs are multiples of 256 pixels.
+  const int64_t cap = d <= 64 ? 2 * 148 : 148;
+  int64_t want = cap / ((int64_t)B * heads);
   int64_t maxslab = (HW + 255) / 256;
   if (want > maxslab) want = maxslab;
   if (want < 1) want = 1;
@@ -207,7 +210,7 @@ using namespace b200ir;
 extern "C" int b200ir_mdta_gram_nslab(int B, int C, int heads, int64_t HW) {
   if (B <= 0 || C <= 0 || heads <= 0 || HW <= 0) return B200IR_E_BADARG;
   int n = 0;
-  gram_slab_len(B, heads, HW, &n);
+  gram_slab_len(B, C / heads, heads, HW, &n);
   return n;
 }
 
@@ -225,7 +228,7 @@ extern "C" int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype,
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_gram: head dim %d > 128 unsupported", d);
   int want = 0;
-  const int64_t slab_len = gram_slab_len(B, heads, HW, &want);
+  const int64_t slab_len = gram_slab_len(B, d, heads, HW, &want);
   B200IR_CHECK_ARG(nslab == want, "mdta_gram: nslab=%d, expected %d (b200ir_mdta_gram_nslab)", nslab, want);
   B200IR_CHECK_ARG(B <= 65535 && heads <= 65535, "mdta_gram: grid too large");
   cudaStream_t st = (cudaStream_t)stream;
