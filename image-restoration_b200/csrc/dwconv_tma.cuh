@@ -17,16 +17,30 @@ struct DwTmaParams {
 constexpr int DW_RS = 8;   // output rows per thread
 constexpr int DW_XP = 8;   // left/right padding of the staged tile in pixels (keeps TMA coordinates 16B aligned)
 
+#ifndef B200IR_GELU_TANH
+#define B200IR_GELU_TANH 1
+#endif
 __device__ __forceinline__ float gelu_fast(float x) {
-  // x * sigmoid(x * q(min(x^2, 64))): clamping x^2 keeps the odd polynomial monotone outside the fitted range
-  // (|x| > 8 -> exact 0 / x in fp32 anyway); coefficients pre-multiplied by -log2(e) for ex2
+  // x * sigmoid(x * q(min(x^2, 64))), q = degree-2 fit in x^2 (max abs err 2.5e-5 vs erf GELU); clamping x^2 keeps the
+  // odd polynomial monotone outside the fitted range (|x| > 8 -> exact 0 / x in fp32 anyway).
   const float x2 = fminf(x * x, 64.f);
+#if B200IR_GELU_TANH
+  // sigmoid(z) = 0.5 + 0.5 tanh(z/2): ONE MUFU op (tanh.approx) instead of ex2 + rcp -- the XU pipe was the busiest
+  // pipe of the gate kernel (ncu r1j: 33.7 %).  Coefficients are q/2.
+  float t = fmaf(-3.5151753375e-4f, x2, 3.7005650955e-2f);
+  t = fmaf(t, x2, 0.79750787845f);
+  float th;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(t * x));
+  const float hx = 0.5f * x;
+  return fmaf(hx, th, hx);
+#else
   float t = fmaf(1.0142652e-3f, x2, -1.0677574e-1f);   // -log2e * (-7.030350675e-4, 7.401130191e-2)
   t = fmaf(t, x2, -2.3011213f);                        // -log2e * 1.5950157569
   float e, r;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t * x));
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
   return x * r;
+#endif
 }
 
 // packed fp32x2 FMA (sm_100): d = a * b + c on both halves, one issue slot

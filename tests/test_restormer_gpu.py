@@ -41,6 +41,7 @@ def test_net_bf16_psnr(case):
         y = net.set_compute_dtype(torch.bfloat16)(x.cuda()).cpu()
     gold = torch.from_numpy(np.load(os.path.join(GOLDEN, name + ".npz"))["y"])
     assert y.dtype == torch.float32
+    print("PSNR", name, O.psnr(y, gold))
     assert O.psnr(y, gold) >= 50.0, O.psnr(y, gold)
 
 
