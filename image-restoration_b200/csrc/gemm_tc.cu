@@ -140,6 +140,14 @@ bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1, bool has_res
     const int need = g->nchunks > 1 ? g->kchunks + 1 : 3;
     if (S >= need) return true;
   }
+  if (taps != 1) {
+    // no resident weight slice fits (e.g. 768 -> 384: one 16-row slice is already 221 KB): the 3x3 path then streams
+    // both operands (conv3x3_stream_tc.cu), which only needs the packing geometry (Kpad, Nrows, kpt)
+    g->Nslice = 16;
+    g->nslices = Npad / 16 > 2 ? Npad / 16 : 2;
+    g->NC = 16; g->nchunks = 1; g->nbox = 16; g->S = 0; g->gpw = 1; g->epi_warp_bytes = 0; g->smem = 0;
+    return true;
+  }
   return false;
 }
 

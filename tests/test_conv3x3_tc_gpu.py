@@ -25,6 +25,8 @@ def rel_err(a, b):
     ("none", 256, 320, 1, 16, 32, True),        # streamed-weights kernel (conv3x3_stream_tc.cu), bias, Cout > 256
     ("shuffle", 384, 768, 1, 32, 32, False),
     ("unshuffle", 200, 96, 2, 20, 48, True),     # Cin not a multiple of 64, ragged tiles
+    ("none", 768, 384, 2, 16, 16, False),        # backward of Upsample 384->768: no resident slice fits, stream-only
+    ("none", 384, 192, 1, 32, 32, True),
 ])
 def test_conv3x3_tc(mode, Cin, Cout, B, H, W, bias):
     import b200ir
