@@ -31,6 +31,7 @@ SIGNATURES = {
     "b200ir_copy_cast": [_vp, _i64, _i, _vp, _i64, _i, _i, _i64, _vp],
     "b200ir_gemm_tc_geometry": [_i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "b200ir_pack_conv1x1": [_vp, _i64, _i, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp],
+    "b200ir_pack_conv1x1_t": [_vp, _i, _i, _vp, _vp, _vp],
     "b200ir_conv3x3_tc_geometry": [_i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "b200ir_nchw_to_nhwc": [_vp, _i64, _vp, _i, _i, _i64, _vp],
     "b200ir_pack_conv3x3": [_vp, _vp, _i, _i, _vp, _vp, _vp],

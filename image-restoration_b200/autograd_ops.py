@@ -181,10 +181,11 @@ class _LnConv1x1(torch.autograd.Function):
         del xn
         dx = dlw = dlb = None
         if need[0] or ctx.ln_type != L.LN_NONE:
-            wt = _p(w).reshape(cout, cin).t().contiguous()
             if USE_TC and ops.gemm_tc_usable(dy, cin) and x.dtype == torch.bfloat16:
-                dn = ops.gemm_tc(dy, ops.pack_conv1x1(wt), cin, L.LN_NONE, None, out_dtype=x.dtype)
+                dn = ops.gemm_tc(dy, ops.pack_conv1x1_t(_p(w).reshape(cout, cin)), cin, L.LN_NONE, None,
+                                 out_dtype=x.dtype)
             else:
+                wt = _p(w).reshape(cout, cin).t().contiguous()
                 dn = ops.ln_conv1x1(dy, wt, None, L.LN_NONE, None, None, None, out_dtype=x.dtype)
             if ctx.ln_type != L.LN_NONE:
                 dx, dlw, dlb = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w))

@@ -217,6 +217,31 @@ __global__ void pack_conv1x1_kernel(const float* __restrict__ w, int64_t w_bs, c
   }
 }
 
+// wp[c][o] = bf16(w[o][c]) for c < Cin (rows), o < Cout (k), zero padded to [Nrows][Kpad]; st = 0.
+// 32x32 tiles through shared memory: coalesced fp32 reads along c, coalesced bf16 writes along o.
+__global__ void __launch_bounds__(256)
+pack_conv1x1_t_kernel(const float* __restrict__ w, int Cin, int Cout, int Kpad, int Nrows, bf16* __restrict__ wp,
+                      float* __restrict__ st) {
+  __shared__ float tile[32][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int k0 = blockIdx.x * 32, r0 = blockIdx.y * 32;   // k = o (source row), r = c (source column)
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int o = k0 + ty + 8 * i, c = r0 + tx;
+    tile[ty + 8 * i][tx] = (o < Cout && c < Cin) ? w[(size_t)o * Cin + c] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = r0 + ty + 8 * i, k = k0 + tx;
+    if (r < Nrows && k < Kpad) wp[(size_t)r * Kpad + k] = __float2bfloat16_rn(tile[tx][ty + 8 * i]);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 32 && r0 + threadIdx.x < Nrows) {
+    st[r0 + threadIdx.x] = 0.f;
+    st[Nrows + r0 + threadIdx.x] = 0.f;
+  }
+}
+
 }  // namespace b200ir
 
 namespace b200ir {
@@ -844,6 +869,15 @@ extern "C" int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, co
   pack_conv1x1_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, w_bstride, bias, ln_type, ln_w, ln_b, Cin, Cout,
                                                               g.Kpad, g.Nrows, (bf16*)wp, st);
   return check_launch("pack_conv1x1");
+}
+
+extern "C" int b200ir_pack_conv1x1_t(const float* w, int Cin, int Cout, void* wp, float* st, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(w && wp && st && Cin > 0 && Cout > 0, "pack_conv1x1_t: bad args");
+  GemmGeom g;
+  B200IR_UNSUPPORTED(gemm_tc_geometry(Cout, Cin, &g), "pack_conv1x1_t: unsupported Cin=%d Cout=%d", Cin, Cout);
+  dim3 grid((unsigned)((g.Kpad + 31) / 32), (unsigned)((g.Nrows + 31) / 32));
+  pack_conv1x1_t_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, Cin, Cout, g.Kpad, g.Nrows, (bf16*)wp, st);
+  return check_launch("pack_conv1x1_t");
 }
 
 namespace b200ir {

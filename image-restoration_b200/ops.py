@@ -271,6 +271,21 @@ def pack_conv1x1(w, bias=None, ln_type=L.LN_NONE, ln_w=None, ln_b=None, per_samp
     return wp, st
 
 
+def pack_conv1x1_t(w):
+    """Operand of the input-gradient GEMM dx = W^T.dy: same result as pack_conv1x1(w.t()), packed from w [Cout,Cin]."""
+    Cout, Cin = w.shape
+    geo = gemm_tc_geometry(Cout, Cin)
+    if geo is None:
+        raise ValueError(f"pack_conv1x1_t: ({Cout},{Cin}) unsupported by the tcgen05 GEMM")
+    kpad, nrows = geo
+    wp = torch.empty((1, nrows, kpad), device=w.device, dtype=torch.bfloat16)
+    st = torch.empty((2, nrows), device=w.device, dtype=torch.float32)
+    with _timed("pack_conv1x1", 1, Cout, Cin):
+        rc = lib.b200ir_pack_conv1x1_t(_par(w, "w", Cout * Cin), Cin, Cout, wp.data_ptr(), st.data_ptr(), _stream())
+    L.check(rc, "b200ir_pack_conv1x1_t")
+    return wp, st
+
+
 def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=None):
     """y = res + W.LN(x) + bias on tcgen05 tensor cores; `packed` = pack_conv1x1(...)."""
     wp, st = packed

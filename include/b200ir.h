@@ -107,6 +107,11 @@ int b200ir_gemm_tc_geometry(int Cin, int Cout, int* kpad, int* nrows);
 int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, const float* bias, int ln_type,
                         const float* ln_w, const float* ln_b, int Cin, int Cout, void* wp, float* st,
                         b200ir_stream_t stream);
+/* Operand of the INPUT-gradient GEMM dx = W^T.dy of a 1x1 conv (autograd of nn.Conv2d(Cin,Cout,1), Restormer.py:80,86,
+ * 103,107): packs w^T straight from w fp32 [Cout][Cin] (tiled shared-memory transpose), i.e. the result equals
+ * b200ir_pack_conv1x1(w^T, ln NONE, no bias) for a GEMM with Cin' = Cout, Cout' = Cin; sizes from
+ * b200ir_gemm_tc_geometry(Cout, Cin). */
+int b200ir_pack_conv1x1_t(const float* w, int Cin, int Cout, void* wp, float* st, b200ir_stream_t stream);
 int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st, int ln_type,
                        const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
                        int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);

@@ -158,3 +158,18 @@ def test_gemm_stream_matches_resident_weights_kernel():
         scale = y0.abs().max()
         assert (y0 - y1).abs().max() <= 1e-4 * scale, (Cin, Cout, float((y0 - y1).abs().max()), float(scale))
         assert (y1b.float() - y1).abs().max() <= 1e-2 * scale
+
+
+@pytest.mark.parametrize("Cout,Cin", [(288, 96), (510, 96), (96, 255), (2042, 384), (384, 1021), (48, 127), (144, 48)])
+def test_pack_conv1x1_t_equals_pack_of_transpose(Cout, Cin):
+    """b200ir_pack_conv1x1_t (operand of dx = W^T.dy, packed straight from w) == b200ir_pack_conv1x1(w^T), bit for bit,
+    including the zero padding."""
+    from b200ir import ops
+    g = torch.Generator().manual_seed(Cout + Cin)
+    w = (torch.rand(Cout, Cin, generator=g) - 0.5).cuda()
+    wp0, st0 = ops.pack_conv1x1(w.t().contiguous())
+    wp1, st1 = ops.pack_conv1x1_t(w)
+    torch.cuda.synchronize()
+    assert wp0.shape == wp1.shape
+    assert torch.equal(wp0.view(torch.int16), wp1.view(torch.int16))
+    assert torch.equal(st0[1], st1[1])   # t = 0 (no bias); s (row sums) is only read by the LayerNorm epilogue
