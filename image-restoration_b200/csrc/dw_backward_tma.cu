@@ -9,6 +9,7 @@
 // Per item the 10 (20) accumulators are reduced over the CTA in fixed order and written to
 //   parts[b * tiles + tile][channel][10]   (b200ir_reduce_partials folds the parts: deterministic).
 // Reference: autograd of FeedForward.forward Restormer.py:90-91 and Attention.forward :114.
+#include <cstdlib>
 #include <mutex>
 
 #include "dwconv_tma.cuh"
@@ -29,6 +30,7 @@ struct DwBwdParams {
   const float* bias;
   float* parts;
   int Cout, Ctot, H, W, TW, TH, nxg, nstrips, tiles_x, tiles_y, S, nitems;
+  int ncg;   // channels per work item: 1, or 128 / (nxg*nstrips) for small planes (W = 16 | 32), see dw_bwd_tma_tiles
 };
 
 __device__ __forceinline__ void unpack8(const uint4 v, float* o) {
@@ -47,9 +49,11 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
   __shared__ uint64_t bar_full[4];
   __shared__ float red[2][4][NV];
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int nthreads = P.nxg * P.nstrips;
+  const int tpc = P.nxg * P.nstrips;          // threads per channel plane
+  const int nthreads = tpc * P.ncg;
   const uint32_t pitch = (uint32_t)(P.TW + 2 * DW_XP) * 2u;
-  const uint32_t plane_bytes = ((uint32_t)(P.TH + 2) * pitch + 127u) & ~127u;
+  const uint32_t cplane = (uint32_t)(P.TH + 2) * pitch;                        // one channel of a box (dense)
+  const uint32_t plane_bytes = ((uint32_t)P.ncg * cplane + 127u) & ~127u;      // one TMA box = ncg channels
   const uint32_t stage_bytes = plane_bytes * NIN;
 
   if (tid == 0) {
@@ -60,11 +64,12 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
   __syncthreads();
 
   const int tiles = P.tiles_x * P.tiles_y;
+  const uint32_t cgroups = (uint32_t)((P.Cout + P.ncg - 1) / P.ncg);
   auto issue = [&](uint32_t item, int stage) {   // thread 0
     const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int c = (int)(pc % cgroups) * P.ncg, b = (int)(pc / cgroups);
     const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
-    mbar_arrive_expect_tx(&bar_full[stage], (uint32_t)(P.TH + 2) * pitch * NIN);
+    mbar_arrive_expect_tx(&bar_full[stage], cplane * (uint32_t)P.ncg * NIN);
 #pragma unroll
     for (int k = 0; k < NIN; ++k)
       tma_load_4d(smem + (size_t)stage * stage_bytes + (size_t)k * plane_bytes, &tmX, &bar_full[stage], x0 - DW_XP,
@@ -76,26 +81,27 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
     for (int s = 0; s < P.S; ++s)
       if (first + s * step < (uint32_t)P.nitems) issue(first + s * step, s);
 
-  const int xg = tid % P.nxg, strip = tid / P.nxg;
+  const int cs = tid / tpc, rr = tid - cs * tpc;      // channel of the group, thread within the channel plane
+  const int xg = rr % P.nxg, strip = rr / P.nxg;
   const int64_t HWp = (int64_t)P.H * P.W;
   uint32_t it = 0;
   for (uint32_t item = first; item < (uint32_t)P.nitems; item += step, ++it) {
     const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
     const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int cb = (int)(pc % cgroups) * P.ncg, c = cb + cs, b = (int)(pc / cgroups);
     const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
     float acc[NV];
 #pragma unroll
     for (int i = 0; i < NV; ++i) acc[i] = 0.f;
 
-    if (tid < nthreads) {
+    if (tid < nthreads && c < P.Cout) {
       const int gx = x0 + xg * 8;
       const int64_t poff = (int64_t)(y0 + strip * BW_RS) * P.W + gx;
       const bf16* grow = P.g + (int64_t)b * P.g_bs + (int64_t)c * HWp + poff;
       const bool xok = gx < P.W;
       const int yrem = P.H - (y0 + strip * BW_RS);
-      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * BW_RS) * pitch +
-                            (uint32_t)(DW_XP + xg * 8) * 2u;
+      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)cs * cplane +
+                            (uint32_t)(strip * BW_RS) * pitch + (uint32_t)(DW_XP + xg * 8) * 2u;
       if (GATE) {
         bf16* a1row = P.da + (int64_t)b * P.da_bs + (int64_t)c * HWp + poff;
         bf16* a2row = a1row + (int64_t)P.Cout * HWp;
@@ -186,6 +192,32 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
     } else {
       mbar_wait(&bar_full[stage], ph);   // keep every thread's view of the barrier phase in step
     }
+    if (P.ncg > 1) {
+      // small planes: the tpc (power of two <= 32) threads of a channel are consecutive lanes of one warp: butterfly
+      // within that lane group (fixed order), its first lane writes the channel's sums
+#pragma unroll
+      for (int i = 0; i < NV; ++i) {
+        float v = acc[i];
+        for (int o = tpc >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        acc[i] = v;
+      }
+      if (tid < nthreads && c < P.Cout && rr == 0) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const int plane = (GATE && i >= 10) ? c + P.Cout : c;
+          P.parts[(((size_t)b * tiles + t) * P.Ctot + plane) * 10 + (i % 10)] = acc[i];
+        }
+      }
+      __syncthreads();   // every thread is done reading this stage
+      if (tid == 0) {
+        const uint32_t nxt = item + (uint32_t)P.S * step;
+        if (nxt < (uint32_t)P.nitems) {
+          fence_proxy_async();
+          issue(nxt, stage);
+        }
+      }
+      continue;
+    }
     // fixed-order CTA reduction of the per-item sums
     float (*rb)[NV] = red[it & 1];
 #pragma unroll
@@ -196,7 +228,7 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
     __syncthreads();   // every thread is done reading this stage; rb complete
     if (tid < NV) {
       const float s = rb[0][tid] + rb[1][tid] + rb[2][tid] + rb[3][tid];
-      const int plane = (GATE && tid >= 10) ? c + P.Cout : c;
+      const int plane = (GATE && tid >= 10) ? cb + P.Cout : cb;   // ncg == 1 here
       P.parts[(((size_t)b * tiles + t) * P.Ctot + plane) * 10 + (tid % 10)] = s;
     }
     if (tid == 0) {
@@ -209,22 +241,38 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
   }
 }
 
-void dw_bwd_tma_tiles(int H, int W, int* TW, int* TH, int* nxg, int* nstrips, int* tiles_x, int* tiles_y) {
-  *TW = W >= 128 ? 128 : 64;
-  *nxg = *TW / 8;
-  *nstrips = 128 / *nxg;
+// Small planes (W = 16 or 32: the two deep levels at 128x128 training patches) would leave most of the 128 threads
+// idle with one plane per item, so an item then carries ncg = 128 / tpc channels (one TMA box with ncg channels), where
+// tpc = nxg * nstrips threads (a power of two <= 32) cover one channel plane tile.
+void dw_bwd_tma_tiles(int H, int W, int* TW, int* TH, int* nxg, int* nstrips, int* tiles_x, int* tiles_y, int* ncg) {
   const int maxstrips = (H + BW_RS - 1) / BW_RS;
-  if (*nstrips > maxstrips) *nstrips = maxstrips;
+  if (W < 64) {
+    *TW = W;
+    *nxg = W / 8;
+    int ns = 1;
+    while (ns < maxstrips && ns * 2 * *nxg <= 32) ns *= 2;
+    *nstrips = ns;
+    *ncg = 128 / (*nxg * ns);
+  } else {
+    *TW = W >= 128 ? 128 : 64;
+    *nxg = *TW / 8;
+    *nstrips = 128 / *nxg;
+    if (*nstrips > maxstrips) *nstrips = maxstrips;
+    *ncg = 1;
+  }
   *TH = *nstrips * BW_RS;
   *tiles_x = (W + *TW - 1) / *TW;
   *tiles_y = (H + *TH - 1) / *TH;
 }
 
-bool dw_bwd_tma_shape_ok(int H, int W) { return W % 8 == 0 && W >= 64 && H >= 8; }
+bool dw_bwd_tma_shape_ok(int H, int W) {
+  static const bool small_ok = !(getenv("B200IR_DW_SMALL") && getenv("B200IR_DW_SMALL")[0] == '0');   // A/B switch
+  return (((W == 16 || W == 32) && small_ok) || (W % 8 == 0 && W >= 64)) && H >= 8;
+}
 
 int dw_bwd_tma_tiles_per_plane(int H, int W) {
-  int TW, TH, nxg, ns, tx, ty;
-  dw_bwd_tma_tiles(H, W, &TW, &TH, &nxg, &ns, &tx, &ty);
+  int TW, TH, nxg, ns, tx, ty, ncg;
+  dw_bwd_tma_tiles(H, W, &TW, &TH, &nxg, &ns, &tx, &ty, &ncg);
   return tx * ty;
 }
 
@@ -235,8 +283,8 @@ int dw_bwd_tma_launch(const void* x, int64_t x_bs, const void* g, int64_t g_bs, 
   DwBwdParams P;
   P.g = (const bf16*)g; P.g_bs = g_bs; P.da = (bf16*)da; P.da_bs = da_bs; P.w = w; P.bias = bias; P.parts = parts;
   P.Cout = Cout; P.Ctot = GATE ? 2 * Cout : Cout; P.H = H; P.W = W;
-  dw_bwd_tma_tiles(H, W, &P.TW, &P.TH, &P.nxg, &P.nstrips, &P.tiles_x, &P.tiles_y);
-  const int64_t nitems64 = (int64_t)B * Cout * P.tiles_x * P.tiles_y;
+  dw_bwd_tma_tiles(H, W, &P.TW, &P.TH, &P.nxg, &P.nstrips, &P.tiles_x, &P.tiles_y, &P.ncg);
+  const int64_t nitems64 = (int64_t)B * ((Cout + P.ncg - 1) / P.ncg) * P.tiles_x * P.tiles_y;
   if (nitems64 >= (1ll << 30)) {
     set_error("dw_bwd_tma: too many work items");
     return B200IR_E_UNSUPPORTED;
@@ -245,11 +293,11 @@ int dw_bwd_tma_launch(const void* x, int64_t x_bs, const void* g, int64_t g_bs, 
   CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)W, (uint64_t)H, (uint64_t)P.Ctot, (uint64_t)B};
   const uint64_t str[4] = {2, (uint64_t)W * 2, (uint64_t)H * W * 2, (uint64_t)x_bs * 2};
-  const uint32_t box[4] = {(uint32_t)(P.TW + 2 * DW_XP), (uint32_t)(P.TH + 2), 1, 1};
+  const uint32_t box[4] = {(uint32_t)(P.TW + 2 * DW_XP), (uint32_t)(P.TH + 2), (uint32_t)P.ncg, 1};
   int rc = make_tmap_bf16(&tm, x, 4, dims, str, box, false);
   if (rc) return rc;
   const size_t pitch = (size_t)(P.TW + 2 * DW_XP) * 2;
-  const size_t plane = ((size_t)(P.TH + 2) * pitch + 127) & ~(size_t)127;
+  const size_t plane = ((size_t)P.ncg * (P.TH + 2) * pitch + 127) & ~(size_t)127;
   const size_t stage = plane * (GATE ? 2 : 1);
   P.S = GATE ? 2 : 3;
   const size_t smem = stage * P.S + 256;
