@@ -40,9 +40,11 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 127) & ~(uintptr_t)127);
   __shared__ uint64_t bar_full[4];
   const int tid = threadIdx.x;
-  const int nthreads = P.nxg * P.nstrips;
+  const int tpc = P.nxg * P.nstrips;                                   // threads per channel plane tile
+  const int nthreads = tpc * P.ncg;
   const uint32_t pitch = (uint32_t)(P.TW + 2 * DW_XP) * 2u;            // bytes per staged row
-  const uint32_t plane_bytes = ((uint32_t)(P.TH + 2) * pitch + 127u) & ~127u;
+  const uint32_t cplane = (uint32_t)(P.TH + 2) * pitch;                // one channel of a box (dense)
+  const uint32_t plane_bytes = ((uint32_t)P.ncg * cplane + 127u) & ~127u;   // one TMA box = ncg channels
   const uint32_t stage_bytes = plane_bytes * NIN;
 
   if (tid == 0) {
@@ -53,11 +55,12 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
   __syncthreads();
 
   const int tiles = P.tiles_x * P.tiles_y;
+  const uint32_t cgroups = (uint32_t)((P.Cout + P.ncg - 1) / P.ncg);
   auto issue = [&](uint32_t item, int stage) {   // thread 0
     const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int c = (int)(pc % cgroups) * P.ncg, b = (int)(pc / cgroups);
     const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
-    mbar_arrive_expect_tx(&bar_full[stage], (uint32_t)(P.TH + 2) * pitch * NIN);
+    mbar_arrive_expect_tx(&bar_full[stage], cplane * (uint32_t)P.ncg * NIN);
 #pragma unroll
     for (int k = 0; k < NIN; ++k)
       tma_load_4d(smem + (size_t)stage * stage_bytes + (size_t)k * plane_bytes, &tmX, &bar_full[stage], x0 - DW_XP,
@@ -69,23 +72,24 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
     for (int s = 0; s < P.S; ++s)
       if (first + s * step < (uint32_t)P.nitems) issue(first + s * step, s);
 
-  const int xg = tid % P.nxg, strip = tid / P.nxg;
+  const int cs = tid / tpc, rr = tid - cs * tpc;       // channel within the group, thread within the plane tile
+  const int xg = rr % P.nxg, strip = rr / P.nxg;
   const int64_t HWp = (int64_t)P.H * P.W;
   uint32_t it = 0;
   for (uint32_t item = first; item < (uint32_t)P.nitems; item += step, ++it) {
     const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
     const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int c = (int)(pc % (uint32_t)P.Cout), b = (int)(pc / (uint32_t)P.Cout);
+    const int c = (int)(pc % cgroups) * P.ncg + cs, b = (int)(pc / cgroups);
     const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
 
-    if (tid < nthreads) {
+    if (tid < nthreads && c < P.Cout) {
       const int gx = x0 + xg * 8;
       bf16* orow = P.y + (int64_t)b * P.y_bs + (int64_t)c * HWp + (int64_t)(y0 + strip * FW_RS) * P.W + gx;
       const bool xok = gx < P.W;
       const int yrem = P.H - (y0 + strip * FW_RS);
       // staged row r <-> image row y0-1+r ; staged col 8+i <-> image col x0+i
-      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)(strip * FW_RS) * pitch +
-                            (uint32_t)(DW_XP + xg * 8) * 2u;
+      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)cs * cplane +
+                            (uint32_t)(strip * FW_RS) * pitch + (uint32_t)(DW_XP + xg * 8) * 2u;
       if (GATE) {
         float2 wk[9];
 #pragma unroll
@@ -159,7 +163,7 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
 }
 
 bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, const void* x, const void* y) {
-  return dtype == B200IR_BF16 && W % 8 == 0 && W >= 64 && H >= 8 && x_bs % 8 == 0 && y_bs % 8 == 0 &&
+  return dtype == B200IR_BF16 && W % 8 == 0 && W >= 16 && H >= 8 && x_bs % 8 == 0 && y_bs % 8 == 0 &&
          ((uintptr_t)x % 16) == 0 && ((uintptr_t)y % 16) == 0;
 }
 
@@ -169,15 +173,18 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
   constexpr int FW_RS = GATE ? B200IR_DW_GATE_RS : 8;
   DwTmaParams P;
   P.y = (bf16*)y; P.y_bs = y_bs; P.w = w; P.bias = bias; P.Cout = Cout; P.H = H; P.W = W;
-  P.TW = W >= 128 ? 128 : 64;
+  P.TW = W >= 128 ? 128 : (W >= 64 ? 64 : W);           // planes narrower than 64 pixels: the whole width
   P.nxg = P.TW / 8;
   P.nstrips = FW_THREADS / P.nxg;                       // 8 (TW=128) or 16 (TW=64)
   const int maxstrips = (H + FW_RS - 1) / FW_RS;
   if (P.nstrips > maxstrips) P.nstrips = maxstrips;
+  // narrow planes would leave most threads idle: carry several channels per item (one TMA box with ncg channels)
+  P.ncg = W < 64 ? FW_THREADS / (P.nxg * P.nstrips) : 1;
+  if (P.ncg > Cout) P.ncg = Cout;
   P.TH = P.nstrips * FW_RS;
   P.tiles_x = (W + P.TW - 1) / P.TW;
   P.tiles_y = (H + P.TH - 1) / P.TH;
-  const int64_t nitems64 = (int64_t)B * Cout * P.tiles_x * P.tiles_y;
+  const int64_t nitems64 = (int64_t)B * ((Cout + P.ncg - 1) / P.ncg) * P.tiles_x * P.tiles_y;
   if (nitems64 >= (1ll << 30)) {
     set_error("dwconv_tma: too many work items");
     return B200IR_E_UNSUPPORTED;
@@ -187,11 +194,11 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
   CUtensorMap tm;
   const uint64_t dims[4] = {(uint64_t)W, (uint64_t)H, (uint64_t)Ctot, (uint64_t)B};
   const uint64_t str[4] = {2, (uint64_t)W * 2, (uint64_t)H * W * 2, (uint64_t)x_bs * 2};
-  const uint32_t box[4] = {(uint32_t)(P.TW + 2 * DW_XP), (uint32_t)(P.TH + 2), 1, 1};
+  const uint32_t box[4] = {(uint32_t)(P.TW + 2 * DW_XP), (uint32_t)(P.TH + 2), (uint32_t)P.ncg, 1};
   int rc = make_tmap_bf16(&tm, x, 4, dims, str, box, false);
   if (rc) return rc;
   const size_t pitch = (size_t)(P.TW + 2 * DW_XP) * 2;
-  const size_t plane = ((size_t)(P.TH + 2) * pitch + 127) & ~(size_t)127;
+  const size_t plane = ((size_t)P.ncg * (P.TH + 2) * pitch + 127) & ~(size_t)127;
   const size_t stage = plane * (GATE ? 2 : 1);
   P.S = GATE ? B200IR_DW_GATE_STAGES : 3;
   const size_t smem = stage * P.S + 256;

@@ -12,6 +12,7 @@ struct DwTmaParams {
   const float* bias;
   int Cout, H, W, TW, TH, nxg, nstrips, tiles_x, tiles_y, S;
   int nitems;
+  int ncg;   // channels per work item (> 1 for planes narrower than 64 pixels: one TMA box carries ncg channels)
 };
 
 constexpr int DW_RS = 8;   // output rows per thread

@@ -34,7 +34,9 @@ def b200ir():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("C,H,W,bias", [(144, 16, 24, False), (48, 8, 8, True), (30, 7, 13, True), (96, 40, 64, False),
-                                        (48, 33, 200, True), (24, 128, 128, False), (16, 70, 264, False)])
+                                        (48, 33, 200, True), (24, 128, 128, False), (16, 70, 264, False),
+                                        # narrow planes on the TMA path: several channels per work item, ragged groups
+                                        (1152, 32, 32, False), (50, 16, 16, True), (7, 24, 40, True), (3, 9, 56, False)])
 def test_dwconv3x3(b200ir, dtype, C, H, W, bias):
     g = torch.Generator().manual_seed(1)
     x = (torch.rand(2, C, H, W, generator=g) * 2 - 1).to(dtype)
@@ -50,7 +52,8 @@ def test_dwconv3x3(b200ir, dtype, C, H, W, bias):
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("Hd,H,W,bias", [(127, 16, 16, False), (64, 8, 24, True), (255, 9, 7, True),
-                                         (127, 72, 136, True), (32, 64, 64, False), (15, 130, 256, False)])
+                                         (127, 72, 136, True), (32, 64, 64, False), (15, 130, 256, False),
+                                         (1021, 32, 32, False), (31, 16, 16, True), (5, 20, 48, True)])
 def test_dwconv3x3_gelu_gate(b200ir, dtype, Hd, H, W, bias):
     g = torch.Generator().manual_seed(2)
     x = (torch.rand(2, 2 * Hd, H, W, generator=g) * 4 - 2).to(dtype)
