@@ -39,7 +39,8 @@ SIGNATURES = {
     "b200ir_gemm_tc_fwd": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _vp],
     "b200ir_ln_fwd": [_vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_ln_bwd_nparts": [_i, _i64],
-    "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i, _i, _i, _i64, _vp],
+    "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i64, _vp, _i, _i, _i,
+                      _i64, _vp],
     "b200ir_reduce_partials": [_vp, _vp, _i, _i64, _i64, _vp],
     "b200ir_conv_wgrad_nsplit": [_i, _i, _i, _i, _i64, _i],
     "b200ir_conv_wgrad": [_vp, _i64, _i, _vp, _i64, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],

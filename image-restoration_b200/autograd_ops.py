@@ -176,10 +176,8 @@ class _LnConv1x1(torch.autograd.Function):
         dy = _cg(dy)
         cout, cin = w.shape[0], w.shape[1]
         need = ctx.needs_input_grad
-        xn = ops.ln_fwd(x, ctx.ln_type, _p(ln_w), _p(ln_b)) if ctx.ln_type != L.LN_NONE else x
-        dw, db = ops.conv_wgrad(dy, xn, 1, want_bias=ctx.has_bias)
-        del xn
         dx = dlw = dlb = None
+        xn = x if ctx.ln_type == L.LN_NONE else None
         if need[0] or ctx.ln_type != L.LN_NONE:
             if USE_TC and ops.gemm_tc_usable(dy, cin) and x.dtype == torch.bfloat16:
                 dn = ops.gemm_tc(dy, ops.pack_conv1x1_t(_p(w).reshape(cout, cin)), cin, L.LN_NONE, None,
@@ -188,11 +186,14 @@ class _LnConv1x1(torch.autograd.Function):
                 wt = _p(w).reshape(cout, cin).t().contiguous()
                 dn = ops.ln_conv1x1(dy, wt, None, L.LN_NONE, None, None, None, out_dtype=x.dtype)
             if ctx.ln_type != L.LN_NONE:
-                dx, dlw, dlb = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w))
+                # one pass over (x, dn): dx, dgamma/dbeta and LN(x) itself (operand of the weight gradient below)
+                dx, dlw, dlb, xn = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w), None, _p(ln_b), want_xn=True)
                 if ctx.ln_type != L.LN_WITHBIAS:
                     dlb = None
             else:
                 dx = dn
+        dw, db = ops.conv_wgrad(dy, xn, 1, want_bias=ctx.has_bias)
+        del xn
         dres = dy if ctx.has_res else None
         return (dx, dw.view(w.shape).to(w.dtype), db, dlw, dlb, dres, None, None, None, None)
 

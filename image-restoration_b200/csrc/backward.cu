@@ -89,9 +89,9 @@ ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, c
 template <int DT>
 __global__ void __launch_bounds__(256)
 ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __restrict__ g, int64_t g_bs, int g_dt,
-              int ln_type, const float* __restrict__ lw, const void* __restrict__ res, int64_t res_bs, int res_dt,
-              void* __restrict__ dx, int64_t dx_bs, int dx_dt, float* __restrict__ parts, int C, int64_t HW, int tps,
-              int64_t ntiles) {
+              int ln_type, const float* __restrict__ lw, const float* __restrict__ lb, const void* __restrict__ res,
+              int64_t res_bs, int res_dt, void* __restrict__ dx, int64_t dx_bs, int dx_dt, void* __restrict__ xn,
+              int64_t xn_bs, float* __restrict__ parts, int C, int64_t HW, int tps, int64_t ntiles) {
   extern __shared__ float acc[];  // [2][C]
   __shared__ float red4[8][4][LN_PX];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -138,7 +138,7 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
     // WithBias: s2 = mean(h*xh) = rstd*(mean(h*(x-x0)) - md*mean(h));  BiasFree: s2 = mean(h*x)
     const float s2 = ln_type == B200IR_LN_WITHBIAS ? rstd * (H2 * invC - md * s1) : (H2 * invC + x0 * s1);
     // pass B: dx, and this tile's contribution to dgamma / dbeta
-    const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p;
+    const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p, no = (int64_t)b * xn_bs + p;
 #pragma unroll 2
     for (int c = warp; c < C; c += 8) {
       float xv = 0.f, gv = 0.f, rv = 0.f;
@@ -147,17 +147,21 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
         gv = ldt<DT>(g, g_dt, go + (int64_t)c * HW);
         if (res) rv = ldt<DT>(res, res_dt, ro + (int64_t)c * HW);
       }
-      const float h = gv * __ldg(lw + c);
-      float d, dgam, dbet = gv;
+      const float gam = __ldg(lw + c);
+      const float h = gv * gam;
+      float d, dgam, dbet = gv, nv;
       if (ln_type == B200IR_LN_WITHBIAS) {
         const float xh = (xv - mu) * rstd;
         d = rstd * (h - s1 - xh * s2);
         dgam = gv * xh;
+        nv = xn ? fmaf(xh, gam, __ldg(lb + c)) : 0.f;
       } else {
         d = rstd * h - rstd * rstd * rstd * (xv - mu) * s2;
         dgam = gv * xv * rstd;
+        nv = xv * rstd * gam;
       }
       if (valid) stt<DT>(dx, dx_dt, dxo + (int64_t)c * HW, d + rv);
+      if (valid && xn) stt<DT>(xn, dx_dt, no + (int64_t)c * HW, nv);
       dgam = warp_sum(dgam);
       dbet = warp_sum(dbet);
       if (lane == 0) {
@@ -176,8 +180,9 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
 // recomputed.  Needs HW even, even batch strides and 4-byte aligned bases.  Same two-pass math as above.
 __global__ void __launch_bounds__(256)
 ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __restrict__ g, int64_t g_bs, int ln_type,
-                     const float* __restrict__ lw, const bf16* __restrict__ res, int64_t res_bs, bf16* __restrict__ dx,
-                     int64_t dx_bs, float* __restrict__ parts, int C, int64_t HW, int tps, int64_t ntiles) {
+                     const float* __restrict__ lw, const float* __restrict__ lb, const bf16* __restrict__ res,
+                     int64_t res_bs, bf16* __restrict__ dx, int64_t dx_bs, bf16* __restrict__ xn, int64_t xn_bs,
+                     float* __restrict__ parts, int C, int64_t HW, int tps, int64_t ntiles) {
   extern __shared__ float acc[];  // [2][C]
   __shared__ float2 red4[8][4][32];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -238,6 +243,7 @@ ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __res
     const bf16 *xp = xw, *gp = gw;
     const bf16* rp = res ? res + (int64_t)b * res_bs + p + (int64_t)warp * HW : nullptr;
     bf16* dp = dx + (int64_t)b * dx_bs + p + (int64_t)warp * HW;
+    bf16* np = xn ? xn + (int64_t)b * xn_bs + p + (int64_t)warp * HW : nullptr;
 #pragma unroll 2
     for (int c = warp; c < C; c += 8, xp += cstep, gp += cstep, dp += cstep) {
       float2 xv = {0.f, 0.f}, gv = {0.f, 0.f}, rv = {0.f, 0.f};
@@ -249,7 +255,8 @@ ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __res
       if (rp) rp += cstep;
       const float gam = __ldg(lw + c);
       const float xs[2] = {xv.x, xv.y}, gs[2] = {gv.x, gv.y};
-      float d[2], dgam = 0.f;
+      float d[2], nv[2], dgam = 0.f;
+      const float bet = (np && ln_type == B200IR_LN_WITHBIAS) ? __ldg(lb + c) : 0.f;
 #pragma unroll
       for (int k = 0; k < 2; ++k) {
         const float h = gs[k] * gam;
@@ -257,12 +264,18 @@ ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __res
           const float xh = (xs[k] - mu[k]) * rstd[k];
           d[k] = rstd[k] * (h - s1[k] - xh * s2[k]);
           dgam = fmaf(gs[k], xh, dgam);
+          nv[k] = fmaf(xh, gam, bet);
         } else {
           d[k] = rstd[k] * h - rstd[k] * rstd[k] * rstd[k] * (xs[k] - mu[k]) * s2[k];
           dgam = fmaf(gs[k] * xs[k], rstd[k], dgam);
+          nv[k] = xs[k] * rstd[k] * gam;
         }
       }
       if (valid) *reinterpret_cast<__nv_bfloat162*>(dp) = __floats2bfloat162_rn(d[0] + rv.x, d[1] + rv.y);
+      if (np) {
+        if (valid) *reinterpret_cast<__nv_bfloat162*>(np) = __floats2bfloat162_rn(nv[0], nv[1]);
+        np += cstep;
+      }
       dgam = warp_sum(dgam);
       const float dbet = warp_sum(gv.x + gv.y);
       if (lane == 0) {
@@ -695,9 +708,11 @@ extern "C" int b200ir_ln_bwd_nparts(int B, int64_t HW) {
 }
 
 extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride,
-                             int g_dtype, int ln_type, const float* ln_w, const void* res, int64_t res_bstride,
-                             int res_dtype, void* dx, int64_t dx_bstride, int dx_dtype, float* parts, int nparts,
-                             int B, int C, int64_t HW, b200ir_stream_t stream) {
+                             int g_dtype, int ln_type, const float* ln_w, const float* ln_b, const void* res,
+                             int64_t res_bstride, int res_dtype, void* dx, int64_t dx_bstride, int dx_dtype, void* xn,
+                             int64_t xn_bstride, float* parts, int nparts, int B, int C, int64_t HW,
+                             b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(!xn || ln_type != B200IR_LN_WITHBIAS || ln_b, "ln_bwd: xn output needs ln_b");
   B200IR_CHECK_ARG(x && g && dx && ln_w && parts && B > 0 && C > 0 && HW > 0, "ln_bwd: bad args");
   B200IR_CHECK_ARG(ln_type == B200IR_LN_WITHBIAS || ln_type == B200IR_LN_BIASFREE, "ln_bwd: bad ln_type %d", ln_type);
   B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(g_dtype) && dtype_ok(dx_dtype) && (!res || dtype_ok(res_dtype)),
@@ -709,17 +724,17 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   const int64_t ntiles = (int64_t)B * tps;
 #define B200IR_LN_BWD(DT)                                                                                   \
   ln_bwd_kernel<DT><<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(                          \
-      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, res, res_bstride, res_dtype, dx, dx_bstride,     \
-      dx_dtype, parts, C, HW, tps, ntiles)
+      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, ln_b, res, res_bstride, res_dtype, dx,           \
+      dx_bstride, dx_dtype, xn, xn_bstride, parts, C, HW, tps, ntiles)
   const bool same = x_dtype == g_dtype && x_dtype == dx_dtype && (!res || res_dtype == x_dtype);
   auto even = [](const void* q, int64_t bs) { return !q || (((uintptr_t)q & 3) == 0 && (bs & 1) == 0); };
   // (tiny planes keep the 32-pixel tiles: twice as many CTAs to spread the channel loop over)
   if (same && x_dtype == B200IR_BF16 && (HW & 1) == 0 && (int64_t)B * ((HW + 63) / 64) >= 2 * 148 && even(x, x_bstride) && even(g, g_bstride) &&
-      even(res, res_bstride) && even(dx, dx_bstride)) {
+      even(res, res_bstride) && even(dx, dx_bstride) && even(xn, xn_bstride)) {
     const int tps2 = (int)((HW + 63) / 64);
     ln_bwd_bf16x2_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
-        (const bf16*)x, x_bstride, (const bf16*)g, g_bstride, ln_type, ln_w, (const bf16*)res, res_bstride, (bf16*)dx,
-        dx_bstride, parts, C, HW, tps2, (int64_t)B * tps2);
+        (const bf16*)x, x_bstride, (const bf16*)g, g_bstride, ln_type, ln_w, ln_b, (const bf16*)res, res_bstride,
+        (bf16*)dx, dx_bstride, (bf16*)xn, xn_bstride, parts, C, HW, tps2, (int64_t)B * tps2);
     return check_launch("ln_bwd_bf16x2");
   }
   if (same && x_dtype == B200IR_BF16) B200IR_LN_BWD(B200IR_BF16);

@@ -407,8 +407,9 @@ def ln_fwd(x, ln_type, ln_w, ln_b, out_dtype=None):
     return y
 
 
-def ln_bwd(x, g, ln_type, ln_w, res=None):
-    """-> (dx, dweight[C], dbias[C])."""
+def ln_bwd(x, g, ln_type, ln_w, res=None, ln_b=None, want_xn=False):
+    """-> (dx, dweight[C], dbias[C]) or, with want_xn, (dx, dweight, dbias, LN(x)): the normalised tensor is a by-product
+    of the same pass (operand of the following weight-gradient GEMM)."""
     B, C, H, W_ = x.shape
     xp, xbs, xdt = _act(x, "x")
     gp, gbs, gdt = _act(g, "g")
@@ -417,13 +418,20 @@ def ln_bwd(x, g, ln_type, ln_w, res=None):
     rp, rbs, rdt = (None, 0, 0)
     if res is not None:
         rp, rbs, rdt = _act(res, "res")
+    xn, np_, nbs = None, None, 0
+    if want_xn:
+        xn = torch.empty((B, C, H, W_), device=x.device, dtype=x.dtype)
+        np_, nbs, _ = _act(xn, "xn")
     nparts = lib.b200ir_ln_bwd_nparts(B, H * W_)
     parts = torch.empty((nparts, 2, C), device=x.device, dtype=torch.float32)
     with _timed("ln_bwd", B, C, H * W_, xdt):
-        rc = lib.b200ir_ln_bwd(xp, xbs, xdt, gp, gbs, gdt, ln_type, _par(ln_w, "ln_w", C), rp, rbs, rdt, dp, dbs, ddt,
-                               parts.data_ptr(), nparts, B, C, H * W_, _stream())
+        rc = lib.b200ir_ln_bwd(xp, xbs, xdt, gp, gbs, gdt, ln_type, _par(ln_w, "ln_w", C),
+                               _par(ln_b, "ln_b", C) if ln_type == L.LN_WITHBIAS and ln_b is not None else None,
+                               rp, rbs, rdt, dp, dbs, ddt, np_, nbs, parts.data_ptr(), nparts, B, C, H * W_, _stream())
     L.check(rc, "b200ir_ln_bwd")
     d = reduce_partials(parts, nparts, 2 * C)
+    if want_xn:
+        return dx, d[:C], d[C:], xn
     return dx, d[:C], d[C:]
 
 

@@ -138,12 +138,14 @@ int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, cons
 int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int ln_type, const float* ln_w, const float* ln_b,
                   void* y, int64_t y_bstride, int y_dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
 /* LayerNorm backward: dx = res + dLN(x)^T g;  parts fp32 [nparts][2][C] = partial (dweight | dbias), nparts from
- * b200ir_ln_bwd_nparts.  res (optional) = gradient arriving through the residual add (Restormer.py:147-148). */
+ * b200ir_ln_bwd_nparts.  res (optional) = gradient arriving through the residual add (Restormer.py:147-148).
+ * xn (optional, dtype/layout of dx, needs ln_b for WithBias) receives LN(x) as a by-product: the operand of the
+ * following weight-gradient GEMM, so that no separate b200ir_ln_fwd pass over x is needed. */
 int b200ir_ln_bwd_nparts(int B, int64_t HW);
 int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride, int g_dtype,
-                  int ln_type, const float* ln_w, const void* res, int64_t res_bstride, int res_dtype, void* dx,
-                  int64_t dx_bstride, int dx_dtype, float* parts, int nparts, int B, int C, int64_t HW,
-                  b200ir_stream_t stream);
+                  int ln_type, const float* ln_w, const float* ln_b, const void* res, int64_t res_bstride,
+                  int res_dtype, void* dx, int64_t dx_bstride, int dx_dtype, void* xn, int64_t xn_bstride,
+                  float* parts, int nparts, int B, int C, int64_t HW, b200ir_stream_t stream);
 /* out[k] = sum_{i<n} in[i*stride+k], fixed order. */
 int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride, b200ir_stream_t stream);
 /* Weight (+bias) gradient of a 1x1 (taps=1) or dense 3x3 pad-1 (taps=9) conv = reduction over pixels:

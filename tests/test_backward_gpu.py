@@ -437,3 +437,32 @@ def test_block_grads_match_reference_golden(b200ir):
         close32(xs.grad, torch.from_numpy(gold["dx"]))
         for n, q in blk.named_parameters():
             close32(q.grad, torch.from_numpy(gold["d_" + n]))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("ln", ["WithBias", "BiasFree"])
+@pytest.mark.parametrize("B,C,H,W", [(2, 48, 16, 24), (8, 96, 64, 64), (1, 30, 7, 13), (2, 384, 8, 8)])
+def test_ln_bwd_with_normalised_byproduct(b200ir, dtype, ln, B, C, H, W):
+    """b200ir_ln_bwd: dx (+ residual gradient), dgamma, dbeta and the LN(x) by-product against autograd of the oracle's
+    LayerNorm (Restormer.py:37-39,54-57) on the same (rounded) inputs; covers the generic and the bf16x2 kernels."""
+    from b200ir import ops
+    L = b200ir._lib
+    g = torch.Generator().manual_seed(B * C + H)
+    x = (torch.randn(B, C, H, W, generator=g) + 0.5).to(dtype)
+    gy = torch.randn(B, C, H, W, generator=g).to(dtype)
+    r = torch.randn(B, C, H, W, generator=g).to(dtype)
+    lw = torch.rand(C, generator=g) + 0.5
+    lb = torch.rand(C, generator=g) - 0.5
+    xr = x.float().requires_grad_(True)
+    lwr, lbr = lw.clone().requires_grad_(True), lb.clone().requires_grad_(True)
+    y = O.layernorm(xr, lwr, lbr if ln == "WithBias" else None)
+    y.backward(gy.float())
+    code = L.LN_WITHBIAS if ln == "WithBias" else L.LN_BIASFREE
+    dx, dlw, dlb, xn = ops.ln_bwd(x.cuda(), gy.cuda(), code, lw.cuda(), r.cuda(), lb.cuda() if ln == "WithBias" else None,
+                                  want_xn=True)
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
+    assert rel(dx.float(), xr.grad + r.float()) < tol
+    assert rel(xn.float(), y.detach()) < tol
+    assert rel(dlw, lwr.grad) < (1e-5 if dtype == torch.float32 else 2e-3)
+    if ln == "WithBias":
+        assert rel(dlb, lbr.grad) < (1e-5 if dtype == torch.float32 else 2e-3)
