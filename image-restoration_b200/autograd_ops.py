@@ -198,10 +198,6 @@ class _LnConv1x1(torch.autograd.Function):
         return (dx, dw.view(w.shape).to(w.dtype), db, dlw, dlb, dres, None, None, None, None)
 
 
-def _flip_dw(w):
-    return _p(w).flip(2, 3).contiguous()
-
-
 class _DwConv(torch.autograd.Function):
     """Depthwise 3x3 (Restormer.py:106,114)."""
 
@@ -215,7 +211,7 @@ class _DwConv(torch.autograd.Function):
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
         dy = _cg(dy)
-        dx = ops.dwconv3x3(dy, _flip_dw(w), None) if ctx.needs_input_grad[0] else None
+        dx = ops.dwconv3x3_bwd_input(dy, _p(w)) if ctx.needs_input_grad[0] else None
         dw, db = ops.dwconv3x3_wgrad(dy, x, want_bias=ctx.has_bias)
         return dx, dw.to(w.dtype), db
 
@@ -233,7 +229,7 @@ class _DwGate(torch.autograd.Function):
         t, w, bias = ctx.saved_tensors
         dg = _cg(dg)
         da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None)
-        dt = ops.dwconv3x3(da, _flip_dw(w), None) if ctx.needs_input_grad[0] else None
+        dt = ops.dwconv3x3_bwd_input(da, _p(w)) if ctx.needs_input_grad[0] else None
         return dt, dw.to(w.dtype), db
 
 

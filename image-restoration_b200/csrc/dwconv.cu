@@ -60,7 +60,7 @@ template <typename T, bool GATE>
 __global__ void __launch_bounds__(256)
 dwconv3x3_vec_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restrict__ w,
                      const float* __restrict__ bias, T* __restrict__ y, int64_t y_bs, int Cout, int H, int W,
-                     int nxg, int nstrip, int64_t total) {
+                     int nxg, int nstrip, int64_t total, int flip) {
   constexpr int N = Vec<T>::N;
   constexpr int NIN = GATE ? 2 : 1;
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,7 +81,7 @@ dwconv3x3_vec_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restr
   for (int k = 0; k < NIN; ++k) {
     const int cin = c + k * Cout;
 #pragma unroll
-    for (int i = 0; i < 9; ++i) wk[k][i] = __ldg(w + cin * 9 + i);
+    for (int i = 0; i < 9; ++i) wk[k][i] = __ldg(w + cin * 9 + (flip ? 8 - i : i));
     bs[k] = bias ? __ldg(bias + cin) : 0.f;
     plane[k] = x + (int64_t)b * x_bs + (int64_t)cin * HWp;
   }
@@ -125,7 +125,7 @@ template <typename T, bool GATE>
 __global__ void __launch_bounds__(256)
 dwconv3x3_scalar_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restrict__ w,
                         const float* __restrict__ bias, T* __restrict__ y, int64_t y_bs, int Cout, int H, int W,
-                        int64_t total) {
+                        int64_t total, int flip) {
   const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (idx >= total) return;
   const int xx = (int)(idx % W);
@@ -147,7 +147,8 @@ dwconv3x3_scalar_kernel(const T* __restrict__ x, int64_t x_bs, const float* __re
       for (int s = -1; s <= 1; ++s) {
         const int yr = yy + r, xs = xx + s;
         if (yr >= 0 && yr < H && xs >= 0 && xs < W)
-          a = fmaf(w[cin * 9 + (r + 1) * 3 + (s + 1)], to_f<T>(plane[(int64_t)yr * W + xs]), a);
+          a = fmaf(w[cin * 9 + (flip ? 8 - ((r + 1) * 3 + (s + 1)) : (r + 1) * 3 + (s + 1))],
+                   to_f<T>(plane[(int64_t)yr * W + xs]), a);
       }
     o[k] = a;
   }
@@ -156,7 +157,7 @@ dwconv3x3_scalar_kernel(const T* __restrict__ x, int64_t x_bs, const float* __re
 
 template <typename T, bool GATE>
 static int launch_dwconv(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs,
-                         int B, int Cout, int H, int W, cudaStream_t st) {
+                         int B, int Cout, int H, int W, cudaStream_t st, int flip = 0) {
   constexpr int N = Vec<T>::N;
   const bool vec_ok = (W % N == 0) && (x_bs % N == 0) && (y_bs % N == 0) && ((uintptr_t)x % 16 == 0) &&
                       ((uintptr_t)y % 16 == 0);
@@ -165,12 +166,12 @@ static int launch_dwconv(const void* x, int64_t x_bs, const float* w, const floa
     const int64_t total = (int64_t)B * Cout * nstrip * nxg;
     const int64_t blocks = (total + 255) / 256;
     dwconv3x3_vec_kernel<T, GATE><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, x_bs, w, bias, (T*)y, y_bs, Cout, H,
-                                                                    W, nxg, nstrip, total);
+                                                                    W, nxg, nstrip, total, flip);
   } else {
     const int64_t total = (int64_t)B * Cout * H * W;
     const int64_t blocks = (total + 255) / 256;
     dwconv3x3_scalar_kernel<T, GATE><<<(unsigned)blocks, 256, 0, st>>>((const T*)x, x_bs, w, bias, (T*)y, y_bs, Cout,
-                                                                       H, W, total);
+                                                                       H, W, total, flip);
   }
   return check_launch(GATE ? "dwconv3x3_gelu_gate" : "dwconv3x3");
 }
@@ -179,7 +180,7 @@ static int launch_dwconv(const void* x, int64_t x_bs, const float* w, const floa
 bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, const void* x, const void* y);
 template <bool GATE>
 int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs, int B,
-                      int Cout, int H, int W, cudaStream_t st);
+                      int Cout, int H, int W, cudaStream_t st, int flip = 0);
 
 }  // namespace b200ir
 
@@ -195,6 +196,18 @@ extern "C" int b200ir_dwconv3x3_fwd(const void* x, int64_t x_bstride, const floa
   if (dtype == B200IR_BF16)
     return launch_dwconv<bf16, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
   return launch_dwconv<float, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
+}
+
+extern "C" int b200ir_dwconv3x3_bwd_input(const void* dy, int64_t dy_bstride, const float* w, void* dx,
+                                          int64_t dx_bstride, int dtype, int B, int C, int H, int W,
+                                          b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(dy && w && dx && B > 0 && C > 0 && H > 0 && W > 0, "dwconv3x3_bwd_input: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_bwd_input: bad dtype %d", dtype);
+  if (dwconv_tma_supported(dtype, H, W, dy_bstride, dx_bstride, dy, dx))
+    return dwconv_tma_launch<false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
+  if (dtype == B200IR_BF16)
+    return launch_dwconv<bf16, false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
+  return launch_dwconv<float, false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
 }
 
 extern "C" int b200ir_dwconv3x3_gelu_gate_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias,

@@ -122,7 +122,7 @@ dwconv_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwTmaParams P) 
       } else {
         float wk[9];
 #pragma unroll
-        for (int i = 0; i < 9; ++i) wk[i] = __ldg(P.w + c * 9 + i);
+        for (int i = 0; i < 9; ++i) wk[i] = __ldg(P.w + c * 9 + (P.flip ? 8 - i : i));
         const float bs = P.bias ? __ldg(P.bias + c) : 0.f;
         mbar_wait(&bar_full[stage], ph);
         float win[3][10];
@@ -169,10 +169,10 @@ bool dwconv_tma_supported(int dtype, int H, int W, int64_t x_bs, int64_t y_bs, c
 
 template <bool GATE>
 int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs, int B,
-                      int Cout, int H, int W, cudaStream_t st) {
+                      int Cout, int H, int W, cudaStream_t st, int flip) {
   constexpr int FW_RS = GATE ? B200IR_DW_GATE_RS : 8;
   DwTmaParams P;
-  P.y = (bf16*)y; P.y_bs = y_bs; P.w = w; P.bias = bias; P.Cout = Cout; P.H = H; P.W = W;
+  P.y = (bf16*)y; P.y_bs = y_bs; P.w = w; P.bias = bias; P.Cout = Cout; P.H = H; P.W = W; P.flip = flip;
   P.TW = W >= 128 ? 128 : (W >= 64 ? 64 : W);           // planes narrower than 64 pixels: the whole width
   P.nxg = P.TW / 8;
   P.nstrips = FW_THREADS / P.nxg;                       // 8 (TW=128) or 16 (TW=64)
@@ -216,8 +216,8 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
 }
 
 template int dwconv_tma_launch<false>(const void*, int64_t, const float*, const float*, void*, int64_t, int, int, int,
-                                      int, cudaStream_t);
+                                      int, cudaStream_t, int);
 template int dwconv_tma_launch<true>(const void*, int64_t, const float*, const float*, void*, int64_t, int, int, int,
-                                     int, cudaStream_t);
+                                     int, cudaStream_t, int);
 
 }  // namespace b200ir

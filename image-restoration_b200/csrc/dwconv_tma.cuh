@@ -12,6 +12,7 @@ struct DwTmaParams {
   const float* bias;
   int Cout, H, W, TW, TH, nxg, nstrips, tiles_x, tiles_y, S;
   int nitems;
+  int flip;  // 1: taps read in reverse order (= input gradient of the depthwise conv)
   int ncg;   // channels per work item (> 1 for planes narrower than 64 pixels: one TMA box carries ncg channels)
 };
 

@@ -127,6 +127,18 @@ def dwconv3x3(x, w, bias=None, out=None):
     return out
 
 
+def dwconv3x3_bwd_input(dy, w):
+    """Input gradient of the depthwise 3x3 conv: depthwise conv of dy with w's taps in reverse order."""
+    B, C, H, W_ = dy.shape
+    gp, gbs, gdt = _act(dy, "dy")
+    dx = torch.empty_like(dy, memory_format=torch.contiguous_format)
+    dp, dbs, _ = _act(dx, "dx")
+    with _timed("dwconv3x3", B, C, H, W_, gdt):
+        rc = lib.b200ir_dwconv3x3_bwd_input(gp, gbs, _par(w, "w", C * 9), dp, dbs, gdt, B, C, H, W_, _stream())
+    L.check(rc, "b200ir_dwconv3x3_bwd_input")
+    return dx
+
+
 def dwconv3x3_gelu_gate(x, w, bias=None, out=None):
     B, C2, H, W_ = x.shape
     if C2 % 2:

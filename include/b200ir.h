@@ -134,6 +134,10 @@ int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const void* wp, cons
  * weights.  The entry points below are the reductions over pixels and the non-linear pieces.  All reductions write
  * fixed-order partial sums that b200ir_reduce_partials folds: results are bitwise reproducible. */
 
+/* Input gradient of the depthwise 3x3 conv (autograd of nn.Conv2d(C,C,3,padding=1,groups=C), Restormer.py:84,106):
+ * dx = depthwise conv of dy with the taps of w [C,1,3,3] read in reverse order (no flipped copy of w needed). */
+int b200ir_dwconv3x3_bwd_input(const void* dy, int64_t dy_bstride, const float* w, void* dx, int64_t dx_bstride,
+                               int dtype, int B, int C, int H, int W, b200ir_stream_t stream);
 /* y = LN(x) materialised (operand of the weight gradient of the fused LN + 1x1 conv; Restormer.py:37-39,54-57). */
 int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int ln_type, const float* ln_w, const float* ln_b,
                   void* y, int64_t y_bstride, int y_dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
