@@ -23,6 +23,7 @@ SIGNATURES = {
     "b200ir_ln_conv1x1_fwd": [_vp, _i64, _i, _vp, _i64, _vp, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i,
                               _i, _i, _i, _i64, _vp],
     "b200ir_dwconv3x3_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv_kxk_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_dwconv3x3_bwd_input": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
     "b200ir_dwconv3x3_gelu_gate_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
     "b200ir_mdta_gram_nslab": [_i, _i, _i, _i64],

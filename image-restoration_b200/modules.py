@@ -129,6 +129,41 @@ class Attention(nn.Module):
 
 
 ##########################################################################
+## MoCE-IR decoder mixer (moce_ir.py:325-368): MDTA with q from one tensor and k, v from another.
+class CrossAttention(nn.Module):
+    """q = q_dwconv(q(x)) (1x1 + depthwise 3x3), k, v = kv_dwconv(kv(y)).chunk(2) (1x1 + depthwise 7x7); the two
+    depthwise kernels write the channel slices [0,C) and [C,3C) of ONE buffer, which is exactly the qkv layout the MDTA
+    kernels (Gram+norms, softmax+fold, attn.v+project_out) already take.  Forward only: the 7x7 depthwise backward is
+    not built yet, so a call that needs gradients fails loudly instead of silently leaving this library."""
+
+    def __init__(self, dim, num_heads, bias):
+        super().__init__()
+        self.num_heads = num_heads
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.q = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
+        self.q_dwconv = nn.Conv2d(dim, dim, kernel_size=3, stride=1, padding=1, groups=dim, bias=bias)
+        self.kv = nn.Conv2d(dim, dim * 2, kernel_size=1, bias=bias)
+        self.kv_dwconv = nn.Conv2d(dim * 2, dim * 2, kernel_size=7, stride=1, padding=7 // 2, groups=dim * 2, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
+
+    def forward(self, x, y):
+        if torch.is_grad_enabled() and (x.requires_grad or y.requires_grad or
+                                        any(p.requires_grad for p in self.parameters())):
+            raise NotImplementedError("b200ir.CrossAttention: backward (depthwise 7x7 gradient) is not built; "
+                                      "call under torch.no_grad()")
+        B, C, H, W = x.shape
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        tq = A.ln_conv1x1(x, self.q.weight, self.q.bias, L.LN_NONE, None, None, None, cache=cache, key="q")
+        tkv = A.ln_conv1x1(y, self.kv.weight, self.kv.bias, L.LN_NONE, None, None, None, cache=cache, key="kv")
+        qkv = torch.empty((B, 3 * C, H, W), device=x.device, dtype=tq.dtype)
+        ops.dwconv3x3(tq, A._p(self.q_dwconv.weight), A._p(self.q_dwconv.bias), out=qkv[:, :C])
+        ops.dwconv_kxk(tkv, A._p(self.kv_dwconv.weight), A._p(self.kv_dwconv.bias), out=qkv[:, C:])
+        del tq, tkv
+        return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
+                           None, cache=cache)
+
+
+##########################################################################
 class TransformerBlock(nn.Module):
     """x = x + attn(norm1(x)); x = x + ffn(norm2(x))   (Restormer.py:137-150), as 8 kernel launches:
     LN+qkv | dw3x3 | Gram+norms | softmax+fold | attn.v+proj+res | LN+project_in | dw3x3+GELU gate |

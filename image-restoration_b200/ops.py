@@ -127,6 +127,23 @@ def dwconv3x3(x, w, bias=None, out=None):
     return out
 
 
+def dwconv_kxk(x, w, bias=None, out=None):
+    """Depthwise K x K conv (K = 3, 5, 7; stride 1, zero padding K//2)."""
+    B, C, H, W_ = x.shape
+    K = w.shape[-1]
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        out = torch.empty_like(x, memory_format=torch.contiguous_format)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != xdt:
+        raise ValueError("dwconv_kxk: in/out dtype mismatch")
+    with _timed("dwconv_kxk", B, C, H, W_, K, xdt):
+        rc = lib.b200ir_dwconv_kxk_fwd(xp, xbs, _par(w, "w", C * K * K), _par(bias, "bias", C), yp, ybs, xdt, B, C, H, W_,
+                                       K, _stream())
+    L.check(rc, "b200ir_dwconv_kxk_fwd")
+    return out
+
+
 def dwconv3x3_bwd_input(dy, w):
     """Input gradient of the depthwise 3x3 conv: depthwise conv of dy with w's taps in reverse order."""
     B, C, H, W_ = dy.shape

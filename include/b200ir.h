@@ -94,6 +94,11 @@ int b200ir_conv3x3_fwd(const void* x, int64_t x_bstride, int x_dtype, const floa
 int b200ir_copy_cast(const void* x, int64_t x_bstride, int x_dtype, void* y, int64_t y_bstride, int y_dtype,
                      int B, int64_t CHW, b200ir_stream_t stream);
 
+/* Depthwise K x K conv, stride 1, zero padding K/2, K in {3,5,7}: the kv_dwconv (7x7) of MoCE-IR's CrossAttention
+ * (moce_ir.py:341-342).  w fp32 [C,1,K,K], bias fp32 [C] or NULL; x/y share `dtype`. */
+int b200ir_dwconv_kxk_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias, void* y,
+                          int64_t y_bstride, int dtype, int B, int C, int H, int W, int K, b200ir_stream_t stream);
+
 /* ---- tcgen05 / TMEM / TMA path (bf16 activations) -------------------------------------------------
  * Same math as b200ir_ln_conv1x1_fwd, as a persistent tensor-core GEMM (csrc/gemm_tc.cu).  Weights are
  * first packed once per parameter update:

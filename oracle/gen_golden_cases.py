@@ -36,6 +36,13 @@ MOCE_CASES = [
 ]
 
 
+# CrossAttention of the MoCE-IR decoder (moce_ir.py:325-368): name, dim, heads, bias, batch, H, W, seed
+CROSS_CASES = [
+    ("moce_cross_c32_h2", 32, 2, True, 2, 12, 20, 61),
+    ("moce_cross_c48_h1_nobias", 48, 1, False, 1, 8, 8, 62),
+]
+
+
 def moce_block_params(dim, heads, f, bias, ln, nblk, seed):
     """Seeded synthetic state_dict of an EncoderResidualGroup: Restormer block parameters renamed to the MoCE-IR
     attribute names (norm1 -> norms.0, norm2 -> norms.1, attn -> mixer; moce_ir.py:817-823) under ``layers.{i}.``."""

@@ -1,4 +1,4 @@
-"""Generate tests/golden/moce_encblk_*.npz from the UNMODIFIED reference moce_ir.py (build container only).
+"""Generate tests/golden/moce_encgrp_*.npz and moce_cross_*.npz from the UNMODIFIED reference moce_ir.py (build container only).
 
 Pins the MoCE-IR flavour of the block (``EncoderBlock`` / ``EncoderResidualGroup``, moce_ir.py:805-834, 903-932: same
 math as Restormer's TransformerBlock under the names ``norms.0``, ``norms.1``, ``mixer``, ``ffn``; bias=True as the
@@ -22,7 +22,7 @@ fv.nn = fvnn
 sys.modules["fvcore"], sys.modules["fvcore.nn"] = fv, fvnn
 
 from oracle import restormer_oracle as O  # noqa: E402
-from oracle.gen_golden_cases import MOCE_CASES, moce_block_params  # noqa: E402
+from oracle.gen_golden_cases import CROSS_CASES, MOCE_CASES, moce_block_params  # noqa: E402
 
 import moce_ir as MR  # noqa: E402  (the reference)
 
@@ -45,6 +45,18 @@ def main():
             out["d_" + n] = q.grad.numpy()
         np.savez_compressed(os.path.join(GOLD, name + ".npz"), **out)
         print(name, tuple(y.shape), len(out))
+    # CrossAttention (decoder mixer): outputs of the reference module for seeded parameters and two seeded inputs
+    for name, dim, heads, bias, b, h, w, seed in CROSS_CASES:
+        mod = MR.CrossAttention(dim, heads, bias)
+        sd = O.synth_cross_attention_params(dim, heads, bias, seed)
+        assert set(sd) == set(mod.state_dict()), sorted(set(sd) ^ set(mod.state_dict()))
+        mod.load_state_dict(sd, strict=True)
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        y = O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1
+        with torch.no_grad():
+            out = mod(x, y)
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=out.numpy())
+        print(name, tuple(out.shape))
 
 
 if __name__ == "__main__":

@@ -76,6 +76,43 @@ def attention(x: Tensor, p: Dict[str, Tensor], prefix: str, num_heads: int) -> T
     return F.conv2d(out, g("project_out.weight"), g("project_out.bias"))           # :131
 
 
+def cross_attention(x: Tensor, y: Tensor, p: Dict[str, Tensor], prefix: str, num_heads: int) -> Tensor:
+    """MoCE-IR ``CrossAttention.forward`` (moce_ir.py:345-368): MDTA whose q comes from ``x`` (1x1 + depthwise 3x3) and
+    whose k, v come from ``y`` (1x1 + depthwise 7x7, padding 3); no LayerNorm, no residual inside."""
+    b, c, h, w = x.shape
+    g = lambda k: p.get(prefix + k)
+    q = F.conv2d(x, g("q.weight"), g("q.bias"))                                               # :348 1x1
+    q = F.conv2d(q, g("q_dwconv.weight"), g("q_dwconv.bias"), padding=1, groups=c)            # :348 dw3x3
+    kv = F.conv2d(y, g("kv.weight"), g("kv.bias"))                                            # :349 1x1
+    kk = g("kv_dwconv.weight").shape[-1]
+    kv = F.conv2d(kv, g("kv_dwconv.weight"), g("kv_dwconv.bias"), padding=kk // 2, groups=2 * c)   # :349 dw7x7
+    k, v = kv.chunk(2, dim=1)                                                                 # :350
+    d = c // num_heads
+    q = F.normalize(q.reshape(b, num_heads, d, h * w), dim=-1)                                # :352,356
+    k = F.normalize(k.reshape(b, num_heads, d, h * w), dim=-1)                                # :353,357
+    v = v.reshape(b, num_heads, d, h * w)                                                     # :354
+    attn = ((q @ k.transpose(-2, -1)) * g("temperature")).softmax(dim=-1)                     # :359-361
+    out = (attn @ v).reshape(b, c, h, w)                                                      # :363-365
+    return F.conv2d(out, g("project_out.weight"), g("project_out.bias"))                      # :367
+
+
+def synth_cross_attention_params(dim: int, heads: int, bias: bool, seed: int, kv_kernel: int = 7) -> Dict[str, Tensor]:
+    """Seeded synthetic state_dict of a CrossAttention module (names of moce_ir.py:334-343)."""
+    gen = torch.Generator().manual_seed(seed)
+    sd = {"temperature": 0.5 + torch.rand(heads, 1, 1, generator=gen)}
+    def conv(name, cout, cin, k, groups=1):
+        fan = (cin // groups) * k * k
+        sd[name + ".weight"] = (torch.rand(cout, cin // groups, k, k, generator=gen) - 0.5) * (2.0 / fan ** 0.5)
+        if bias:
+            sd[name + ".bias"] = (torch.rand(cout, generator=gen) - 0.5) * 0.2
+    conv("q", dim, dim, 1)
+    conv("q_dwconv", dim, dim, 3, groups=dim)
+    conv("kv", 2 * dim, dim, 1)
+    conv("kv_dwconv", 2 * dim, 2 * dim, kv_kernel, groups=2 * dim)
+    conv("project_out", dim, dim, 1)
+    return sd
+
+
 # --------------------------------------------------------------------------------------
 # GDFN feed-forward                                   (Restormer.py:76-93)
 # --------------------------------------------------------------------------------------

@@ -103,3 +103,20 @@ def test_oracle_train_step_matches_reference():
         ref = torch.from_numpy(gold["g_" + n])
         assert (grads[n] - ref).abs().max() <= 1e-4 * ref.abs().max().clamp_min(1e-6), n
         assert (new_sd[n] - torch.from_numpy(gold["p_" + n])).abs().max() <= 1e-6, n
+
+
+def test_cross_attention_oracle_vs_reference_golden():
+    """oracle.cross_attention (restated from moce_ir.py:345-368) against outputs of the reference's own CrossAttention
+    module stored by oracle/gen_golden_moce.py."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle import restormer_oracle as O
+    from oracle.gen_golden_cases import CROSS_CASES
+    for name, dim, heads, bias, b, h, w, seed in CROSS_CASES:
+        p = O.synth_cross_attention_params(dim, heads, bias, seed)
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        y = O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1
+        out = O.cross_attention(x, y, p, "", heads)
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))["y"]
+        assert np.abs(out.numpy() - gold).max() <= 1e-6
