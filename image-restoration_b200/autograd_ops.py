@@ -216,6 +216,28 @@ class _DwConv(torch.autograd.Function):
         return dx, dw.to(w.dtype), db
 
 
+class _DwConvKxK(torch.autograd.Function):
+    """Depthwise K x K (K = 3, 5, 7), e.g. CrossAttention.kv_dwconv (moce_ir.py:341)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias):
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = bias is not None
+        return ops.dwconv_kxk(x, _p(w), _p(bias))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dx, dw, db = ops.dwconv_kxk_bwd(_cg(dy), x, _p(w), want_bias=ctx.has_bias, want_input=ctx.needs_input_grad[0])
+        return dx, dw.to(w.dtype), db
+
+
+def dwconv_kxk(x, w, bias):
+    if _needs_grad(x, w, bias):
+        return _DwConvKxK.apply(x, w, bias)
+    return ops.dwconv_kxk(x, _p(w), _p(bias))
+
+
 class _DwGate(torch.autograd.Function):
     """dwconv + chunk + gelu(x1)*x2 (Restormer.py:84,90-91); the conv output is recomputed in backward."""
 

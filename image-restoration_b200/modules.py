@@ -133,8 +133,8 @@ class Attention(nn.Module):
 class CrossAttention(nn.Module):
     """q = q_dwconv(q(x)) (1x1 + depthwise 3x3), k, v = kv_dwconv(kv(y)).chunk(2) (1x1 + depthwise 7x7); the two
     depthwise kernels write the channel slices [0,C) and [C,3C) of ONE buffer, which is exactly the qkv layout the MDTA
-    kernels (Gram+norms, softmax+fold, attn.v+project_out) already take.  Forward only: the 7x7 depthwise backward is
-    not built yet, so a call that needs gradients fails loudly instead of silently leaving this library."""
+    kernels (Gram+norms, softmax+fold, attn.v+project_out) already take.  With gradients the two halves are produced by
+    the autograd functions and concatenated (one extra copy) before the same MDTA core."""
 
     def __init__(self, dim, num_heads, bias):
         super().__init__()
@@ -147,17 +147,17 @@ class CrossAttention(nn.Module):
         self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
 
     def forward(self, x, y):
-        if torch.is_grad_enabled() and (x.requires_grad or y.requires_grad or
-                                        any(p.requires_grad for p in self.parameters())):
-            raise NotImplementedError("b200ir.CrossAttention: backward (depthwise 7x7 gradient) is not built; "
-                                      "call under torch.no_grad()")
         B, C, H, W = x.shape
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         tq = A.ln_conv1x1(x, self.q.weight, self.q.bias, L.LN_NONE, None, None, None, cache=cache, key="q")
         tkv = A.ln_conv1x1(y, self.kv.weight, self.kv.bias, L.LN_NONE, None, None, None, cache=cache, key="kv")
-        qkv = torch.empty((B, 3 * C, H, W), device=x.device, dtype=tq.dtype)
-        ops.dwconv3x3(tq, A._p(self.q_dwconv.weight), A._p(self.q_dwconv.bias), out=qkv[:, :C])
-        ops.dwconv_kxk(tkv, A._p(self.kv_dwconv.weight), A._p(self.kv_dwconv.bias), out=qkv[:, C:])
+        if torch.is_grad_enabled() and (tq.requires_grad or tkv.requires_grad):
+            qkv = torch.cat([A.dwconv3x3(tq, self.q_dwconv.weight, self.q_dwconv.bias),
+                             A.dwconv_kxk(tkv, self.kv_dwconv.weight, self.kv_dwconv.bias)], dim=1)
+        else:
+            qkv = torch.empty((B, 3 * C, H, W), device=x.device, dtype=tq.dtype)
+            ops.dwconv3x3(tq, A._p(self.q_dwconv.weight), A._p(self.q_dwconv.bias), out=qkv[:, :C])
+            ops.dwconv_kxk(tkv, A._p(self.kv_dwconv.weight), A._p(self.kv_dwconv.bias), out=qkv[:, C:])
         del tq, tkv
         return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
                            None, cache=cache)

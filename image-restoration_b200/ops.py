@@ -144,6 +144,32 @@ def dwconv_kxk(x, w, bias=None, out=None):
     return out
 
 
+def dwconv_kxk_bwd(dy, x, w, want_bias=False, want_input=True):
+    """Backward of dwconv_kxk: (dx or None, dw [C,1,K,K], db [C] or None)."""
+    B, C, H, W_ = dy.shape
+    K = w.shape[-1]
+    gp, gbs, gdt = _act(dy, "dy")
+    xp, xbs, xdt = _act(x, "x")
+    if gdt != xdt:
+        raise ValueError("dwconv_kxk_bwd: dtype mismatch")
+    dx = None
+    if want_input:
+        dx = torch.empty_like(dy, memory_format=torch.contiguous_format)
+        dp, dbs, _ = _act(dx, "dx")
+        with _timed("dwconv_kxk", B, C, H, W_, K, gdt):
+            rc = lib.b200ir_dwconv_kxk_bwd_input(gp, gbs, _par(w, "w", C * K * K), dp, dbs, gdt, B, C, H, W_, K, _stream())
+        L.check(rc, "b200ir_dwconv_kxk_bwd_input")
+    nparts = lib.b200ir_dwconv_kxk_wgrad_nparts(B, H, W_)
+    nv = K * K + 1
+    parts = torch.empty((nparts, C, nv), device=dy.device, dtype=torch.float32)
+    with _timed("dwconv_kxk_wgrad", B, C, H, W_, K, gdt):
+        rc = lib.b200ir_dwconv_kxk_wgrad(gp, gbs, xp, xbs, gdt, parts.data_ptr(), nparts, B, C, H, W_, K, _stream())
+    L.check(rc, "b200ir_dwconv_kxk_wgrad")
+    d = reduce_partials(parts, nparts, C * nv).view(C, nv)
+    dw = d[:, :K * K].reshape(C, 1, K, K)
+    return dx, dw, (d[:, K * K].contiguous() if want_bias else None)
+
+
 def dwconv3x3_bwd_input(dy, w):
     """Input gradient of the depthwise 3x3 conv: depthwise conv of dy with w's taps in reverse order."""
     B, C, H, W_ = dy.shape

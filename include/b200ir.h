@@ -98,6 +98,14 @@ int b200ir_copy_cast(const void* x, int64_t x_bstride, int x_dtype, void* y, int
  * (moce_ir.py:341-342).  w fp32 [C,1,K,K], bias fp32 [C] or NULL; x/y share `dtype`. */
 int b200ir_dwconv_kxk_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias, void* y,
                           int64_t y_bstride, int dtype, int B, int C, int H, int W, int K, b200ir_stream_t stream);
+/* Its backward: input gradient (the same conv with the taps read in reverse order) and the weight/bias gradient as
+ * fixed-order partial sums parts fp32 [nparts][C][K*K+1] (last entry = bias gradient), folded by
+ * b200ir_reduce_partials; nparts from b200ir_dwconv_kxk_wgrad_nparts. */
+int b200ir_dwconv_kxk_bwd_input(const void* dy, int64_t dy_bstride, const float* w, void* dx, int64_t dx_bstride,
+                                int dtype, int B, int C, int H, int W, int K, b200ir_stream_t stream);
+int b200ir_dwconv_kxk_wgrad_nparts(int B, int H, int W);
+int b200ir_dwconv_kxk_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
+                            float* parts, int nparts, int B, int C, int H, int W, int K, b200ir_stream_t stream);
 
 /* ---- tcgen05 / TMEM / TMA path (bf16 activations) -------------------------------------------------
  * Same math as b200ir_ln_conv1x1_fwd, as a persistent tensor-core GEMM (csrc/gemm_tc.cu).  Weights are

@@ -51,12 +51,16 @@ def main():
         sd = O.synth_cross_attention_params(dim, heads, bias, seed)
         assert set(sd) == set(mod.state_dict()), sorted(set(sd) ^ set(mod.state_dict()))
         mod.load_state_dict(sd, strict=True)
-        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
-        y = O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1
-        with torch.no_grad():
-            out = mod(x, y)
-        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=out.numpy())
-        print(name, tuple(out.shape))
+        x = (O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1).requires_grad_(True)
+        y = (O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1).requires_grad_(True)
+        gy = torch.randn(b, dim, h, w, generator=torch.Generator().manual_seed(seed + 200))
+        out = mod(x, y)
+        out.backward(gy)
+        rec = {"y": out.detach().numpy(), "dx": x.grad.numpy(), "dy": y.grad.numpy()}
+        for n, q in mod.named_parameters():
+            rec["d_" + n] = q.grad.numpy()
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), **rec)
+        print(name, tuple(out.shape), len(rec))
 
 
 if __name__ == "__main__":
