@@ -9,6 +9,7 @@ identity, so nothing of the reference is imported here):
   * blocks  ``norms[0..1], mixer, ffn``          (moce_ir.EncoderBlock, moce_ir.py:805-834)
   * MDTA    ``temperature, qkv, qkv_dwconv, project_out``   (Attention, Restormer.py:99-132)
   * GDFN    ``project_in, dwconv, project_out``             (FeedForward, Restormer.py:76-93)
+  * cross-MDTA ``temperature, q, q_dwconv, kv, kv_dwconv, project_out``   (moce_ir.CrossAttention, moce_ir.py:325-368)
   * LayerNorm wrappers with a ``body`` holding ``weight`` (and ``bias``)   (Restormer.py:60-70)
   * ``Downsample`` / ``Upsample`` = Sequential(conv3x3 no-bias, PixelUnshuffle/PixelShuffle(2))  (Restormer.py:171-189)
 
@@ -69,6 +70,23 @@ def _is_gdfn(m) -> bool:
             and m.project_out.out_channels == m.project_in.in_channels)
 
 
+def _is_cross(m) -> bool:
+    """MoCE-IR CrossAttention (moce_ir.py:325-343): q / q_dwconv(3x3) from one input, kv / kv_dwconv(7x7) from another."""
+    need = ("temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out", "num_heads")
+    if not all(hasattr(m, a) for a in need):
+        return False
+    pn = {n.split(".")[0] for n, _ in m.named_parameters()}
+    if pn != {"temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out"}:
+        return False
+    c = m.q.in_channels
+    kk = m.kv_dwconv.kernel_size[0] if isinstance(m.kv_dwconv, nn.Conv2d) else 0
+    return (_conv_ok(m.q, 1, 1) and _conv_ok(m.q_dwconv, 3, c) and _conv_ok(m.kv, 1, 1) and kk in (3, 5, 7)
+            and _conv_ok(m.kv_dwconv, kk, 2 * c) and _conv_ok(m.project_out, 1, 1)
+            and m.q.out_channels == c and m.kv.in_channels == c and m.kv.out_channels == 2 * c
+            and m.project_out.in_channels == c == m.project_out.out_channels
+            and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
+
+
 def _is_resize(m):
     """Sequential(conv3x3 (no bias), PixelUnshuffle(2) | PixelShuffle(2)) wrapped as `.body` -> 'down' | 'up' | None."""
     body = getattr(m, "body", None)
@@ -104,6 +122,14 @@ def _adopt_mdta(m):
     return a
 
 
+def _adopt_cross(m):
+    a = _bare(M.CrossAttention)
+    a.num_heads = m.num_heads
+    a.temperature = m.temperature
+    a.q, a.q_dwconv, a.kv, a.kv_dwconv, a.project_out = m.q, m.q_dwconv, m.kv, m.kv_dwconv, m.project_out
+    return a
+
+
 def _adopt_gdfn(m):
     f = _bare(M.FeedForward)
     f.project_in, f.dwconv, f.project_out = m.project_in, m.dwconv, m.project_out
@@ -112,8 +138,8 @@ def _adopt_gdfn(m):
 
 def _adopt(m):
     """-> (replacement, kind) or (None, None)."""
-    if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.FeedForward, M.LayerNorm, M.Downsample,
-                      M.Upsample)):
+    if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.CrossAttention, M.FeedForward, M.LayerNorm,
+                      M.Downsample, M.Upsample)):
         return None, None
     kids = dict(m.named_children())
     if set(kids) == {"norm1", "attn", "norm2", "ffn"} and _is_ln(m.norm1) and _is_ln(m.norm2) and _is_mdta(m.attn) \
@@ -130,6 +156,8 @@ def _adopt(m):
         return b, "encoder_block"
     if _is_mdta(m):
         return _adopt_mdta(m), "attention"
+    if _is_cross(m):
+        return _adopt_cross(m), "cross_attention"
     if _is_gdfn(m):
         return _adopt_gdfn(m), "feedforward"
     if _is_ln(m):
@@ -149,6 +177,8 @@ def _in_channels(new, kind):
         return new.mixer.qkv.in_channels
     if kind == "attention":
         return new.qkv.in_channels
+    if kind == "cross_attention":
+        return new.q.in_channels
     if kind == "feedforward":
         return new.project_in.in_channels
     if kind == "layernorm":
@@ -168,8 +198,12 @@ def _agrees(old, new, kind, tol):
     tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
     torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
     try:
-        ref = old(x)
-        got = new(x)
+        if kind == "cross_attention":
+            y = (torch.rand(x.shape, generator=g) * 2 - 1).to(p.device)
+            ref, got = old(x, y), new(x, y)
+        else:
+            ref = old(x)
+            got = new(x)
     except Exception:
         return False
     finally:

@@ -71,3 +71,30 @@ def test_accelerate_swaps_in_place_and_keeps_the_contract():
     loss = (net(img.cuda()) - 0.5).abs().mean()
     loss.backward()
     assert all(p.grad is not None for p in net.parameters())
+
+
+def test_accelerate_adopts_cross_attention():
+    """A module with CrossAttention's structure (q / q_dwconv 3x3 / kv / kv_dwconv 7x7 / project_out) is swapped for
+    b200ir.CrossAttention, forward and backward keep working through the ORIGINAL parameters."""
+    import b200ir
+    from torch_models import RefDecoderMixerNet
+    torch.manual_seed(1)
+    net = RefDecoderMixerNet(32, 2)
+    net.mixer.temperature.data.add_(0.3 * torch.randn(2, 1, 1))
+    x = O.synth_image(2, 16, 24, seed=5, c=32) * 2 - 1
+    xr = x.clone().requires_grad_(True)
+    ref = net(xr)
+    ref.abs().mean().backward()
+    gref = {n: p.grad.clone() for n, p in net.named_parameters()}
+    net.zero_grad()
+    net = net.cuda()
+    net, stats = b200ir.accelerate(net, verify=True)
+    assert stats == {"cross_attention": 1}, stats
+    assert isinstance(net.mixer, b200ir.CrossAttention)
+    xg = x.cuda().requires_grad_(True)
+    got = net(xg)
+    _close(got.detach(), ref.detach(), 2e-4)
+    got.abs().mean().backward()
+    _close(xg.grad, xr.grad, 1e-3)
+    for n, p in net.named_parameters():
+        _close(p.grad, gref[n], 1e-3)

@@ -129,3 +129,33 @@ class RefMiniNet(nn.Module):
         x = x + self.dec_attn(n)
         x = x + self.dec_ffn(n)
         return self.out(x) + img
+
+
+class RefCrossAttention(nn.Module):
+    """Stand-in with the attribute names / shapes of MoCE-IR's CrossAttention (moce_ir.py:325-343); forward = the oracle."""
+
+    def __init__(self, dim, num_heads, bias, kv_kernel=7):
+        super().__init__()
+        self.num_heads = num_heads
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.q = nn.Conv2d(dim, dim, 1, bias=bias)
+        self.q_dwconv = nn.Conv2d(dim, dim, 3, 1, 1, groups=dim, bias=bias)
+        self.kv = nn.Conv2d(dim, dim * 2, 1, bias=bias)
+        self.kv_dwconv = nn.Conv2d(dim * 2, dim * 2, kv_kernel, 1, kv_kernel // 2, groups=dim * 2, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, 1, bias=bias)
+
+    def forward(self, x, y):
+        return O.cross_attention(x, y, dict(self.named_parameters()), "", self.num_heads)
+
+
+class RefDecoderMixerNet(nn.Module):
+    """Two branches mixed by a cross attention plus a residual, the way moce_ir.DecoderBlock.forward uses it (:894)."""
+
+    def __init__(self, dim=32, heads=2):
+        super().__init__()
+        self.a = nn.Conv2d(dim, dim, 1)
+        self.b = nn.Conv2d(dim, dim, 1)
+        self.mixer = RefCrossAttention(dim, heads, True)
+
+    def forward(self, x):
+        return self.mixer(self.a(x), self.b(x)) + x
