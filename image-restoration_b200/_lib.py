@@ -27,6 +27,8 @@ SIGNATURES = {
     "b200ir_dwconv_kxk_bwd_input": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_dwconv_kxk_wgrad_nparts": [_i, _i, _i],
     "b200ir_dwconv_kxk_wgrad": [_vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_sigmoid_gate_fwd": [_vp, _i64, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_sigmoid_gate_bwd": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _vp, _i64, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_dwconv3x3_bwd_input": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
     "b200ir_dwconv3x3_gelu_gate_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
     "b200ir_mdta_gram_nslab": [_i, _i, _i, _i64],

@@ -238,6 +238,26 @@ def dwconv_kxk(x, w, bias):
     return ops.dwconv_kxk(x, _p(w), _p(bias))
 
 
+class _SigmoidGate(torch.autograd.Function):
+    """y = u * sigmoid(g) with a head-wise or element-wise gate (gated MDTA variants)."""
+
+    @staticmethod
+    def forward(ctx, u, g):
+        ctx.save_for_backward(u, g)
+        return ops.sigmoid_gate(u, g)
+
+    @staticmethod
+    def backward(ctx, dy):
+        u, g = ctx.saved_tensors
+        return ops.sigmoid_gate_bwd(u, g, _cg(dy))
+
+
+def sigmoid_gate(u, g):
+    if _needs_grad(u, g):
+        return _SigmoidGate.apply(u, g)
+    return ops.sigmoid_gate(u, g)
+
+
 class _DwGate(torch.autograd.Function):
     """dwconv + chunk + gelu(x1)*x2 (Restormer.py:84,90-91); the conv output is recomputed in backward."""
 

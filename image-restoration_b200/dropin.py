@@ -9,6 +9,7 @@ identity, so nothing of the reference is imported here):
   * blocks  ``norms[0..1], mixer, ffn``          (moce_ir.EncoderBlock, moce_ir.py:805-834)
   * MDTA    ``temperature, qkv, qkv_dwconv, project_out``   (Attention, Restormer.py:99-132)
   * GDFN    ``project_in, dwconv, project_out``             (FeedForward, Restormer.py:76-93)
+  * gated MDTA ``gate_type`` + Attention's names with ``3*dim + gate`` qkv channels   (experiment GatedMDTA)
   * cross-MDTA ``temperature, q, q_dwconv, kv, kv_dwconv, project_out``   (moce_ir.CrossAttention, moce_ir.py:325-368)
   * LayerNorm wrappers with a ``body`` holding ``weight`` (and ``bias``)   (Restormer.py:60-70)
   * ``Downsample`` / ``Upsample`` = Sequential(conv3x3 no-bias, PixelUnshuffle/PixelShuffle(2))  (Restormer.py:171-189)
@@ -70,6 +71,22 @@ def _is_gdfn(m) -> bool:
             and m.project_out.out_channels == m.project_in.in_channels)
 
 
+def _is_gated_mdta(m) -> bool:
+    """GatedMDTA of the gated-attention experiment: Attention's names, `gate_type` in {headwise, elementwise} and
+    3*dim + (num_heads | dim) qkv channels laid out [q | gate | k | v]."""
+    need = ("temperature", "qkv", "qkv_dwconv", "project_out", "num_heads", "gate_type")
+    if not all(hasattr(m, a) for a in need) or m.gate_type not in ("headwise", "elementwise"):
+        return False
+    pn = {n.split(".")[0] for n, _ in m.named_parameters()}
+    if pn != {"temperature", "qkv", "qkv_dwconv", "project_out"}:
+        return False
+    c = m.qkv.in_channels
+    ct = 3 * c + (m.num_heads if m.gate_type == "headwise" else c)
+    return (_conv_ok(m.qkv, 1, 1) and _conv_ok(m.qkv_dwconv, 3, ct) and _conv_ok(m.project_out, 1, 1)
+            and m.qkv.out_channels == ct and m.project_out.in_channels == c == m.project_out.out_channels
+            and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
+
+
 def _is_cross(m) -> bool:
     """MoCE-IR CrossAttention (moce_ir.py:325-343): q / q_dwconv(3x3) from one input, kv / kv_dwconv(7x7) from another."""
     need = ("temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out", "num_heads")
@@ -122,6 +139,15 @@ def _adopt_mdta(m):
     return a
 
 
+def _adopt_gated(m):
+    a = _bare(M.GatedMDTA)
+    a.num_heads, a.gate_type, a.dim, a.bias = m.num_heads, m.gate_type, m.qkv.in_channels, m.qkv.bias is not None
+    a.qkv_out_channels = m.qkv.out_channels
+    a.temperature = m.temperature
+    a.qkv, a.qkv_dwconv, a.project_out = m.qkv, m.qkv_dwconv, m.project_out
+    return a
+
+
 def _adopt_cross(m):
     a = _bare(M.CrossAttention)
     a.num_heads = m.num_heads
@@ -138,8 +164,8 @@ def _adopt_gdfn(m):
 
 def _adopt(m):
     """-> (replacement, kind) or (None, None)."""
-    if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.CrossAttention, M.FeedForward, M.LayerNorm,
-                      M.Downsample, M.Upsample)):
+    if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.CrossAttention, M.GatedMDTA,
+                      M.GatedTransformerBlock, M.FeedForward, M.LayerNorm, M.Downsample, M.Upsample)):
         return None, None
     kids = dict(m.named_children())
     if set(kids) == {"norm1", "attn", "norm2", "ffn"} and _is_ln(m.norm1) and _is_ln(m.norm2) and _is_mdta(m.attn) \
@@ -158,6 +184,8 @@ def _adopt(m):
         return _adopt_mdta(m), "attention"
     if _is_cross(m):
         return _adopt_cross(m), "cross_attention"
+    if _is_gated_mdta(m):
+        return _adopt_gated(m), "gated_attention"
     if _is_gdfn(m):
         return _adopt_gdfn(m), "feedforward"
     if _is_ln(m):
@@ -175,7 +203,7 @@ def _in_channels(new, kind):
         return new.attn.qkv.in_channels
     if kind == "encoder_block":
         return new.mixer.qkv.in_channels
-    if kind == "attention":
+    if kind in ("attention", "gated_attention"):
         return new.qkv.in_channels
     if kind == "cross_attention":
         return new.q.in_channels

@@ -129,6 +129,78 @@ class Attention(nn.Module):
 
 
 ##########################################################################
+## Gated MDTA of the reference's gated-attention experiment (experiment/baseline_restormer_new_train/
+## 20251116_use_headwise_gate_model/MoCE-IR-main/src/net/moce_ir.py:84-171)
+class GatedMDTA(nn.Module):
+    """MDTA whose qkv projection carries gate channels after q (``[q | gate | k | v]``; ``num_heads`` channels for
+    gate_type='headwise', ``dim`` for 'elementwise', none for None) and whose attention output is multiplied by
+    sigmoid(gate) BEFORE project_out.  The gate sits between attn.v and project_out, so project_out cannot be folded
+    into the attention matrix: attn.v comes from the same Gram / softmax+fold / per-sample GEMM kernels with an
+    identity fold, then the sigmoid-gate kernel (csrc/gate.cu), then project_out (+ bias + residual) as one more GEMM."""
+
+    def __init__(self, dim, num_heads, bias, gate_type=None):
+        super().__init__()
+        if gate_type not in (None, "headwise", "elementwise"):
+            raise ValueError(f"Unsupported gate_type: {gate_type}, choose from None, 'headwise', 'elementwise'")
+        self.num_heads, self.gate_type, self.dim, self.bias = num_heads, gate_type, dim, bias
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.qkv_out_channels = dim * 3 + {None: 0, "headwise": num_heads, "elementwise": dim}[gate_type]
+        self.qkv = nn.Conv2d(dim, self.qkv_out_channels, kernel_size=1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(self.qkv_out_channels, self.qkv_out_channels, kernel_size=3, stride=1, padding=1,
+                                    groups=self.qkv_out_channels, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
+
+    def _eye(self, device):
+        e = self.__dict__.get("_b200ir_eye")
+        if e is None or e.device != device:
+            e = torch.eye(self.dim, device=device, dtype=torch.float32).view(self.dim, self.dim, 1, 1)
+            self.__dict__["_b200ir_eye"] = e
+        return e
+
+    def _run(self, x, norm=None, res=None, out=None):
+        ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        C, G = self.dim, self.qkv_out_channels - 3 * self.dim
+        t = A.ln_conv1x1(x, self.qkv.weight, self.qkv.bias, ln_type, lw, lb, None, cache=cache, key=("qkv", id(norm)))
+        wd, bd = self.qkv_dwconv.weight, self.qkv_dwconv.bias
+        if G == 0:
+            qkv = A.dwconv3x3(t, wd, bd)
+            del t
+            return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
+                               res, out=out, cache=cache)
+        sl = lambda a, b: (t[:, a:b], wd[a:b], bd[a:b] if bd is not None else None)
+        q = A.dwconv3x3(*sl(0, C))
+        gate = A.dwconv3x3(*sl(C, C + G))
+        kv = A.dwconv3x3(*sl(C + G, 3 * C + G))
+        del t
+        u = A.mdta_core(torch.cat([q, kv], dim=1), self.temperature, self._eye(x.device), None, self.num_heads, None,
+                        cache=cache)                      # attn . v (identity fold)
+        del q, kv
+        ug = A.sigmoid_gate(u, gate)                      # * sigmoid(gate), head-wise or element-wise
+        del u, gate
+        return A.ln_conv1x1(ug, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
+                            cache=cache, key="out")
+
+    def forward(self, x):
+        return self._run(x)
+
+
+class GatedTransformerBlock(nn.Module):
+    """x = x + attn(norm1(x)); x = x + ffn(norm2(x)) with the gated attention (same file, :180-193)."""
+
+    def __init__(self, dim, num_heads, ffn_expansion_factor, bias, LayerNorm_type, gate_type=None):
+        super().__init__()
+        self.norm1 = LayerNorm(dim, LayerNorm_type)
+        self.attn = GatedMDTA(dim, num_heads, bias, gate_type=gate_type)
+        self.norm2 = LayerNorm(dim, LayerNorm_type)
+        self.ffn = FeedForward(dim, ffn_expansion_factor, bias)
+
+    def forward(self, x, out=None):
+        x = self.attn._run(x, norm=self.norm1, res=x)
+        return self.ffn._run(x, norm=self.norm2, res=x, out=out)
+
+
+##########################################################################
 ## MoCE-IR decoder mixer (moce_ir.py:325-368; SURVEY.md §8 f1): MDTA with q from one tensor and k, v from another.
 class CrossAttention(nn.Module):
     """q = q_dwconv(q(x)) (1x1 + depthwise 3x3), k, v = kv_dwconv(kv(y)).chunk(2) (1x1 + depthwise 7x7); the two

@@ -170,6 +170,42 @@ def dwconv_kxk_bwd(dy, x, w, want_bias=False, want_input=True):
     return dx, dw, (d[:, K * K].contiguous() if want_bias else None)
 
 
+def sigmoid_gate(u, g, out=None):
+    """y = u * sigmoid(g); g has G channels, each gating C/G consecutive channels of u (G = C or G = heads)."""
+    B, C, H, W_ = u.shape
+    G = g.shape[1]
+    up, ubs, udt = _act(u, "u")
+    gp, gbs, gdt = _act(g, "g")
+    if gdt != udt or g.shape[0] != B or tuple(g.shape[2:]) != (H, W_):
+        raise ValueError("sigmoid_gate: u / g mismatch")
+    if out is None:
+        out = torch.empty((B, C, H, W_), device=u.device, dtype=u.dtype)
+    yp, ybs, _ = _act(out, "out")
+    with _timed("sigmoid_gate", B, C, G, H * W_, udt):
+        rc = lib.b200ir_sigmoid_gate_fwd(up, ubs, gp, gbs, udt, yp, ybs, B, C, G, H * W_, _stream())
+    L.check(rc, "b200ir_sigmoid_gate_fwd")
+    return out
+
+
+def sigmoid_gate_bwd(u, g, dy):
+    """-> (du, dg)."""
+    B, C, H, W_ = u.shape
+    G = g.shape[1]
+    up, ubs, udt = _act(u, "u")
+    gp, gbs, _ = _act(g, "g")
+    dp, dbs, ddt = _act(dy, "dy")
+    if ddt != udt:
+        raise ValueError("sigmoid_gate_bwd: dtype mismatch")
+    du = torch.empty((B, C, H, W_), device=u.device, dtype=u.dtype)
+    dg = torch.empty((B, G, H, W_), device=u.device, dtype=u.dtype)
+    dup, dubs, _ = _act(du, "du")
+    dgp, dgbs, _ = _act(dg, "dg")
+    with _timed("sigmoid_gate_bwd", B, C, G, H * W_, udt):
+        rc = lib.b200ir_sigmoid_gate_bwd(up, ubs, gp, gbs, dp, dbs, udt, dup, dubs, dgp, dgbs, B, C, G, H * W_, _stream())
+    L.check(rc, "b200ir_sigmoid_gate_bwd")
+    return du, dg
+
+
 def dwconv3x3_bwd_input(dy, w):
     """Input gradient of the depthwise 3x3 conv: depthwise conv of dy with w's taps in reverse order."""
     B, C, H, W_ = dy.shape

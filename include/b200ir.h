@@ -107,6 +107,16 @@ int b200ir_dwconv_kxk_wgrad_nparts(int B, int H, int W);
 int b200ir_dwconv_kxk_wgrad(const void* dy, int64_t dy_bstride, const void* x, int64_t x_bstride, int dtype,
                             float* parts, int nparts, int B, int C, int H, int W, int K, b200ir_stream_t stream);
 
+/* Multiplicative sigmoid gate of the gated MDTA variants (GatedMDTA.forward of experiment/
+ * baseline_restormer_new_train/20251116_use_headwise_gate_model/.../moce_ir.py:155-166): y[b,c,p] = u[b,c,p] *
+ * sigmoid(g[b, c / (C/G), p]).  G = C: element-wise gate, G = heads: head-wise gate.  u, g, y (and dy, du, dg) share
+ * `dtype`.  Backward: du = dy * sigmoid(g), dg = sigmoid'(g) * sum over the gated channels of dy * u. */
+int b200ir_sigmoid_gate_fwd(const void* u, int64_t u_bstride, const void* g, int64_t g_bstride, int dtype, void* y,
+                            int64_t y_bstride, int B, int C, int G, int64_t HW, b200ir_stream_t stream);
+int b200ir_sigmoid_gate_bwd(const void* u, int64_t u_bstride, const void* g, int64_t g_bstride, const void* dy,
+                            int64_t dy_bstride, int dtype, void* du, int64_t du_bstride, void* dg, int64_t dg_bstride,
+                            int B, int C, int G, int64_t HW, b200ir_stream_t stream);
+
 /* ---- tcgen05 / TMEM / TMA path (bf16 activations) -------------------------------------------------
  * Same math as b200ir_ln_conv1x1_fwd, as a persistent tensor-core GEMM (csrc/gemm_tc.cu).  Weights are
  * first packed once per parameter update:

@@ -43,6 +43,14 @@ CROSS_CASES = [
 ]
 
 
+# GatedMDTA of the gated-attention experiment: name, dim, heads, bias, gate_type, batch, H, W, seed
+GATED_CASES = [
+    ("gated_mdta_headwise_c32_h2", 32, 2, True, "headwise", 2, 12, 16, 71),
+    ("gated_mdta_elementwise_c48_h1", 48, 1, False, "elementwise", 1, 8, 8, 72),
+    ("gated_mdta_none_c32_h4", 32, 4, True, None, 1, 8, 16, 73),
+]
+
+
 def moce_block_params(dim, heads, f, bias, ln, nblk, seed):
     """Seeded synthetic state_dict of an EncoderResidualGroup: Restormer block parameters renamed to the MoCE-IR
     attribute names (norm1 -> norms.0, norm2 -> norms.1, attn -> mixer; moce_ir.py:817-823) under ``layers.{i}.``."""

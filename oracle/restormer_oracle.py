@@ -96,6 +96,46 @@ def cross_attention(x: Tensor, y: Tensor, p: Dict[str, Tensor], prefix: str, num
     return F.conv2d(out, g("project_out.weight"), g("project_out.bias"))                      # :367
 
 
+def gated_attention(x: Tensor, p: Dict[str, Tensor], prefix: str, num_heads: int, gate_type: Optional[str]) -> Tensor:
+    """``GatedMDTA.forward`` of the reference's gated-attention experiment (experiment/baseline_restormer_new_train/
+    20251116_use_headwise_gate_model/MoCE-IR-main/src/net/moce_ir.py:117-171): MDTA whose qkv projection carries extra
+    gate channels after q -- ``[q | gate | k | v]`` with ``num_heads`` ('headwise') or ``dim`` ('elementwise') gate
+    channels -- and whose attention output is multiplied by ``sigmoid(gate)`` before ``project_out``."""
+    b, c, h, w = x.shape
+    g = lambda k: p.get(prefix + k)
+    t = F.conv2d(x, g("qkv.weight"), g("qkv.bias"))                                             # :122 1x1
+    t = F.conv2d(t, g("qkv_dwconv.weight"), g("qkv_dwconv.bias"), padding=1, groups=t.shape[1])   # :122 dw3x3
+    ng = {None: 0, "headwise": num_heads, "elementwise": c}[gate_type]
+    q, gate, k, v = t.split([c, ng, c, c], dim=1)                                                # :125-140
+    d = c // num_heads
+    q = F.normalize(q.reshape(b, num_heads, d, h * w), dim=-1)                                   # :144,149
+    k = F.normalize(k.reshape(b, num_heads, d, h * w), dim=-1)                                   # :145,150
+    v = v.reshape(b, num_heads, d, h * w)                                                        # :146
+    attn = ((q @ k.transpose(-2, -1)) * g("temperature")).softmax(dim=-1)                        # :151-152
+    out = attn @ v                                                                               # :155
+    if gate_type == "headwise":
+        out = out * torch.sigmoid(gate.reshape(b, num_heads, 1, h * w))                          # :160-166
+    elif gate_type == "elementwise":
+        out = out * torch.sigmoid(gate.reshape(b, num_heads, d, h * w))                          # :162-166
+    return F.conv2d(out.reshape(b, c, h, w), g("project_out.weight"), g("project_out.bias"))     # :169-170
+
+
+def synth_gated_attention_params(dim: int, heads: int, bias: bool, gate_type: Optional[str], seed: int) -> Dict[str, Tensor]:
+    """Seeded synthetic state_dict of a GatedMDTA module (same names as Attention; qkv has 3*dim + gate channels)."""
+    gen = torch.Generator().manual_seed(seed)
+    ng = {None: 0, "headwise": heads, "elementwise": dim}[gate_type]
+    ct = 3 * dim + ng
+    sd = {"temperature": 0.5 + torch.rand(heads, 1, 1, generator=gen)}
+    sd["qkv.weight"] = (torch.rand(ct, dim, 1, 1, generator=gen) - 0.5) * (2.0 / dim ** 0.5)
+    sd["qkv_dwconv.weight"] = (torch.rand(ct, 1, 3, 3, generator=gen) - 0.5) * (2.0 / 3.0)
+    sd["project_out.weight"] = (torch.rand(dim, dim, 1, 1, generator=gen) - 0.5) * (2.0 / dim ** 0.5)
+    if bias:
+        sd["qkv.bias"] = (torch.rand(ct, generator=gen) - 0.5) * 0.2
+        sd["qkv_dwconv.bias"] = (torch.rand(ct, generator=gen) - 0.5) * 0.2
+        sd["project_out.bias"] = (torch.rand(dim, generator=gen) - 0.5) * 0.2
+    return sd
+
+
 def synth_cross_attention_params(dim: int, heads: int, bias: bool, seed: int, kv_kernel: int = 7) -> Dict[str, Tensor]:
     """Seeded synthetic state_dict of a CrossAttention module (names of moce_ir.py:334-343)."""
     gen = torch.Generator().manual_seed(seed)

@@ -98,3 +98,19 @@ def test_accelerate_adopts_cross_attention():
     _close(xg.grad, xr.grad, 1e-3)
     for n, p in net.named_parameters():
         _close(p.grad, gref[n], 1e-3)
+
+
+def test_accelerate_adopts_gated_mdta():
+    import b200ir
+    from torch_models import RefGatedMDTA
+    torch.manual_seed(2)
+    net = torch.nn.Sequential(RefGatedMDTA(32, 2, True, "headwise"), RefGatedMDTA(32, 4, False, "elementwise"))
+    x = O.synth_image(2, 16, 24, seed=6, c=32) * 2 - 1
+    with torch.no_grad():
+        ref = net(x)
+    net = net.cuda()
+    net, stats = b200ir.accelerate(net, verify=True)
+    assert stats == {"gated_attention": 2}, stats
+    assert isinstance(net[0], b200ir.GatedMDTA) and net[1].gate_type == "elementwise"
+    with torch.no_grad():
+        _close(net(x.cuda()), ref, 2e-4)

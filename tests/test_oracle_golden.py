@@ -120,3 +120,19 @@ def test_cross_attention_oracle_vs_reference_golden():
         out = O.cross_attention(x, y, p, "", heads)
         gold = np.load(os.path.join(GOLDEN, name + ".npz"))["y"]
         assert np.abs(out.numpy() - gold).max() <= 1e-6
+
+
+def test_gated_attention_oracle_vs_reference_golden():
+    """oracle.gated_attention (restated from the gated-attention experiment's GatedMDTA.forward) against the stored
+    outputs of the reference module (oracle/gen_golden_gated.py)."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from oracle import restormer_oracle as O
+    from oracle.gen_golden_cases import GATED_CASES
+    for name, dim, heads, bias, gate_type, b, h, w, seed in GATED_CASES:
+        p = O.synth_gated_attention_params(dim, heads, bias, gate_type, seed)
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        out = O.gated_attention(x, p, "", heads, gate_type)
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))["y"]
+        assert np.abs(out.numpy() - gold).max() <= 1e-6

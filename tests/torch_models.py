@@ -159,3 +159,19 @@ class RefDecoderMixerNet(nn.Module):
 
     def forward(self, x):
         return self.mixer(self.a(x), self.b(x)) + x
+
+
+class RefGatedMDTA(nn.Module):
+    """Stand-in with the structure of the gated-attention experiment's GatedMDTA; forward = the oracle."""
+
+    def __init__(self, dim, num_heads, bias, gate_type):
+        super().__init__()
+        self.num_heads, self.gate_type = num_heads, gate_type
+        ct = dim * 3 + {None: 0, "headwise": num_heads, "elementwise": dim}[gate_type]
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.qkv = nn.Conv2d(dim, ct, 1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(ct, ct, 3, 1, 1, groups=ct, bias=bias)
+        self.project_out = nn.Conv2d(dim, dim, 1, bias=bias)
+
+    def forward(self, x):
+        return O.gated_attention(x, dict(self.named_parameters()), "", self.num_heads, self.gate_type)
