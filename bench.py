@@ -143,6 +143,8 @@ def main():
         return run_reference(args)
     args.warmup = max(args.warmup, 3)
 
+    # NCCL's own log lines (e.g. 'NCCL version ...' when the box sets NCCL_DEBUG) go to stderr: stdout carries the JSON line only
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     import torch.distributed as dist
     import b200ir
     from b200ir import ops
