@@ -198,3 +198,42 @@ class GraphedTrainStep:
         ops.LAUNCHES += self.launches_per_step
         A.bump_param_epoch()   # parameters changed under the packed-weight caches
         return self.loss
+
+
+class GraphedForward:
+    """Inference counterpart of GraphedTrainStep: the forward of ``net`` for one fixed input shape captured in a CUDA
+    graph (the ~320 launches of a Restormer forward become one graph launch; measured 30.1 -> 29.6 ms at 16 x 256x256).
+    ``out = fwd(x)`` copies x into the static input buffer, replays, and returns the static output tensor (overwritten
+    by the next call).  Parameters are read in place; after changing them call ``refresh()`` (packed bf16 weight caches
+    were baked into the graph)."""
+
+    def __init__(self, net: nn.Module, example: torch.Tensor, warmup: int = 2):
+        self.net = net
+        self.x = example.detach().clone()
+        self._capture(warmup)
+
+    def _capture(self, warmup):
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), torch.no_grad():
+            for _ in range(warmup):
+                self.net(self.x)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        launches0 = ops.LAUNCHES
+        with torch.no_grad(), torch.cuda.graph(self.graph):
+            self.y = self.net(self.x)
+        self.launches_per_call = ops.LAUNCHES - launches0
+
+    def refresh(self):
+        self._capture(1)
+
+    def __call__(self, x: torch.Tensor) -> torch.Tensor:
+        if x.shape != self.x.shape:
+            raise ValueError(f"GraphedForward was captured for {tuple(self.x.shape)}, got {tuple(x.shape)}")
+        self.x.copy_(x, non_blocking=True)
+        self.graph.replay()
+        ops.LAUNCHES += self.launches_per_call
+        return self.y
+

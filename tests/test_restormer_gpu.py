@@ -81,3 +81,17 @@ def test_cfg5_hires_1024_bf16_vs_fp32_path():
     assert torch.isfinite(y16).all()
     assert torch.equal(y16, y16b)
     assert O.psnr(y16.cpu(), y32.cpu()) >= 50.0, O.psnr(y16.cpu(), y32.cpu())
+
+
+def test_graphed_forward_equals_eager():
+    """b200ir.GraphedForward (CUDA-graph replay of the forward) is bitwise the eager forward, for several inputs."""
+    import b200ir
+    net, full = _net({}, 0)
+    net.set_compute_dtype(torch.bfloat16)
+    xs = [O.synth_image(2, 64, 64, seed=s).cuda() for s in (1, 2, 3)]
+    fwd = b200ir.GraphedForward(net, xs[0])
+    with torch.no_grad():
+        for x in xs:
+            assert torch.equal(fwd(x), net(x))
+    with pytest.raises(ValueError):
+        fwd(xs[0][:1])
