@@ -39,6 +39,7 @@ SIGNATURES = {
     "b200ir_gemm_tc_geometry": [_i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "b200ir_pack_conv1x1": [_vp, _i64, _i, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _vp],
     "b200ir_pack_conv1x1_t": [_vp, _i, _i, _vp, _vp, _vp],
+    "b200ir_pack_conv1x1_multi": [_vp, _i, _i, _vp],
     "b200ir_conv3x3_tc_geometry": [_i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],
     "b200ir_nchw_to_nhwc": [_vp, _i64, _vp, _i, _i, _i64, _vp],
     "b200ir_pack_conv3x3": [_vp, _vp, _i, _i, _vp, _vp, _vp],
@@ -83,3 +84,13 @@ def check(rc: int, what: str):
     if rc != 0:
         msg = lib.b200ir_last_error_string()
         raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+class PackDesc(C.Structure):
+    """ctypes mirror of b200ir_pack_desc_t (include/b200ir.h)."""
+    _fields_ = [("w", C.c_void_p), ("bias", C.c_void_p), ("ln_w", C.c_void_p), ("ln_b", C.c_void_p),
+                ("wp", C.c_void_p), ("st", C.c_void_p),
+                ("Cin", C.c_int), ("Cout", C.c_int), ("Kpad", C.c_int), ("Nrows", C.c_int),
+                ("ln_type", C.c_int), ("transposed", C.c_int), ("first_block", C.c_int),
+                ("reserved", C.c_int)]
+

@@ -54,6 +54,90 @@ def packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b):
     return ent[1]
 
 
+def packed_weights_t(cache, key, w):
+    """Operand of the input-gradient GEMM (W^T packed), from the block's cache when a Prepacker filled it this epoch."""
+    cout, cin = w.shape[0], w.shape[1]
+    if cache is not None and key is not None:
+        ent = cache.get(("T", key))
+        if ent is not None and ent[0] == _sig(w):
+            return ent[1]
+    return ops.pack_conv1x1_t(_p(w).reshape(cout, cin))
+
+
+class Prepacker:
+    """All 1x1-conv weight packs of a model's Restormer blocks in ONE kernel launch (b200ir_pack_conv1x1_multi): the
+    LayerNorm-folded forward operands of qkv / project_in / project_out and the transposed operands of their
+    input-gradient GEMMs.  A training step repacks every weight after the optimizer update; done one by one that is
+    ~260 launches of 3-5 us.  ``run()`` refreshes the (persistent) packed buffers and stamps the per-module caches with
+    the current parameter signature, so that the forward / backward code paths find them instead of packing."""
+
+    def __init__(self, model):
+        import ctypes
+        import numpy as np
+        from . import modules as M
+        self.entries = []          # (cache dict, key, (w, bias, ln_w, ln_b), ln_type, packed tuple, transposed)
+        descs, blocks = [], 0
+        keep = []
+
+        def add(cache, key, conv, norm, transposed):
+            nonlocal blocks
+            w, bias = conv.weight, (None if transposed else conv.bias)
+            cout, cin = w.shape[0], w.shape[1]
+            ln_type, lw, lb = (M._ln_args(norm) if (norm is not None and not transposed) else (L.LN_NONE, None, None))
+            geo = ops.gemm_tc_geometry(cout, cin) if transposed else ops.gemm_tc_geometry(cin, cout)
+            if geo is None or w.dtype != torch.float32 or not w.is_cuda:
+                return
+            kpad, nrows = geo
+            wp = torch.empty((1, nrows, kpad), device=w.device, dtype=torch.bfloat16)
+            st = torch.empty((2, nrows), device=w.device, dtype=torch.float32)
+            d = L.PackDesc()
+            d.w = w.data_ptr()
+            d.bias = bias.data_ptr() if bias is not None else None
+            d.ln_w = lw.data_ptr() if lw is not None else None
+            d.ln_b = lb.data_ptr() if (lb is not None and ln_type == L.LN_WITHBIAS) else None
+            d.wp, d.st = wp.data_ptr(), st.data_ptr()
+            d.Cin, d.Cout, d.Kpad, d.Nrows = cin, cout, kpad, nrows
+            d.ln_type, d.transposed, d.first_block, d.reserved = ln_type, int(transposed), blocks, 0
+            blocks += ((kpad + 31) // 32) * ((nrows + 31) // 32) if transposed else (nrows + 7) // 8
+            descs.append(d)
+            self.entries.append((cache, key, (w, bias, lw, lb), ln_type, (wp, st), transposed))
+
+        for m in model.modules():
+            if isinstance(m, (M.TransformerBlock, M.EncoderBlock)):
+                if isinstance(m, M.TransformerBlock):
+                    n1, attn, n2, ffn = m.norm1, m.attn, m.norm2, m.ffn
+                else:
+                    n1, attn, n2, ffn = m.norms[0], m.mixer, m.norms[1], m.ffn
+                ca = attn.__dict__.setdefault("_b200ir_cache", {})
+                cf = ffn.__dict__.setdefault("_b200ir_cache", {})
+                for cache, key, conv, norm in ((ca, ("qkv", id(n1)), attn.qkv, n1), (cf, ("in", id(n2)), ffn.project_in, n2),
+                                               (cf, "out", ffn.project_out, None)):
+                    add(cache, key, conv, norm, False)
+                    add(cache, key, conv, None, True)
+        self.ndesc, self.total_blocks = len(descs), blocks
+        self.descs_dev = None
+        if descs:
+            arr = (L.PackDesc * len(descs))(*descs)
+            host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
+            self.descs_dev = host.to(self.entries[0][2][0].device)
+        self.ptrs = tuple(e[2][0].data_ptr() for e in self.entries)
+
+    def valid(self):
+        """Parameters still live where the table says (no .to()/.cuda()/re-flattening since construction)."""
+        return self.descs_dev is not None and self.ptrs == tuple(e[2][0].data_ptr() for e in self.entries)
+
+    def run(self):
+        if not self.valid():
+            return False
+        ops.pack_conv1x1_multi(self.descs_dev, self.ndesc, self.total_blocks)
+        for cache, key, (w, bias, lw, lb), ln_type, packed, transposed in self.entries:
+            if transposed:
+                cache[("T", key)] = (_sig(w), packed)
+            else:
+                cache[key] = (_sig(w, bias, lw, lb) + (ln_type,), packed)
+        return True
+
+
 USE_TC = True  # bf16 activations -> tcgen05 GEMMs (set False to force the CUDA-core kernels, e.g. for A/B tests)
 
 
@@ -180,8 +264,7 @@ class _LnConv1x1(torch.autograd.Function):
         xn = x if ctx.ln_type == L.LN_NONE else None
         if need[0] or ctx.ln_type != L.LN_NONE:
             if USE_TC and ops.gemm_tc_usable(dy, cin) and x.dtype == torch.bfloat16:
-                dn = ops.gemm_tc(dy, ops.pack_conv1x1_t(_p(w).reshape(cout, cin)), cin, L.LN_NONE, None,
-                                 out_dtype=x.dtype)
+                dn = ops.gemm_tc(dy, packed_weights_t(ctx.cache, ctx.key, w), cin, L.LN_NONE, None, out_dtype=x.dtype)
             else:
                 wt = _p(w).reshape(cout, cin).t().contiguous()
                 dn = ops.ln_conv1x1(dy, wt, None, L.LN_NONE, None, None, None, out_dtype=x.dtype)

@@ -242,6 +242,69 @@ pack_conv1x1_t_kernel(const float* __restrict__ w, int Cin, int Cout, int Kpad, 
   }
 }
 
+// Every pack of a model in one launch: CTA -> descriptor by binary search over first_block, then the same per-row /
+// per-tile work as pack_conv1x1_kernel / pack_conv1x1_t_kernel (bitwise the same results).
+__global__ void __launch_bounds__(256)
+pack_multi_kernel(const b200ir_pack_desc_t* __restrict__ descs, int ndesc) {
+  __shared__ float tile[32][33];
+  int lo = 0, hi = ndesc - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (descs[mid].first_block <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const b200ir_pack_desc_t d = descs[lo];
+  const int blk = (int)blockIdx.x - d.first_block;
+  bf16* wp = (bf16*)d.wp;
+  if (d.transposed) {
+    const int tiles_k = (d.Kpad + 31) / 32;
+    const int k0 = (blk % tiles_k) * 32, r0 = (blk / tiles_k) * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int o = k0 + ty + 8 * i, c = r0 + tx;
+      tile[ty + 8 * i][tx] = (o < d.Cout && c < d.Cin) ? d.w[(size_t)o * d.Cin + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int r = r0 + ty + 8 * i, k = k0 + tx;
+      if (r < d.Nrows && k < d.Kpad) wp[(size_t)r * d.Kpad + k] = __float2bfloat16_rn(tile[tx][ty + 8 * i]);
+    }
+    if (k0 == 0 && threadIdx.x < 32 && r0 + threadIdx.x < d.Nrows) {
+      d.st[r0 + threadIdx.x] = 0.f;
+      d.st[d.Nrows + r0 + threadIdx.x] = 0.f;
+    }
+    return;
+  }
+  const int lane = threadIdx.x & 31;
+  const int row = blk * 8 + (threadIdx.x >> 5);
+  if (row >= d.Nrows) return;
+  bf16* dst = wp + (size_t)row * d.Kpad;
+  float s = 0.f, t = 0.f;
+  if (row < d.Cout) {
+    const float* src = d.w + (size_t)row * d.Cin;
+    for (int c = lane; c < d.Kpad; c += 32) {
+      float v = 0.f;
+      if (c < d.Cin) {
+        const float wv = src[c];
+        v = d.ln_type != B200IR_LN_NONE ? wv * d.ln_w[c] : wv;
+        if (d.ln_type == B200IR_LN_WITHBIAS) t = fmaf(wv, d.ln_b[c], t);
+      }
+      const bf16 q = __float2bfloat16_rn(v);
+      s += __bfloat162float(q);
+      dst[c] = q;
+    }
+  } else {
+    for (int c = lane; c < d.Kpad; c += 32) dst[c] = __float2bfloat16_rn(0.f);
+  }
+  s = warp_sum(s);
+  t = warp_sum(t);
+  if (lane == 0) {
+    d.st[row] = s;
+    d.st[d.Nrows + row] = (row < d.Cout) ? t + (d.bias ? d.bias[row] : 0.f) : 0.f;
+  }
+}
+
 }  // namespace b200ir
 
 namespace b200ir {
@@ -869,6 +932,13 @@ extern "C" int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, co
   pack_conv1x1_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(w, w_bstride, bias, ln_type, ln_w, ln_b, Cin, Cout,
                                                               g.Kpad, g.Nrows, (bf16*)wp, st);
   return check_launch("pack_conv1x1");
+}
+
+extern "C" int b200ir_pack_conv1x1_multi(const b200ir_pack_desc_t* descs, int ndesc, int total_blocks,
+                                         b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(descs && ndesc > 0 && total_blocks > 0, "pack_conv1x1_multi: bad args");
+  pack_multi_kernel<<<(unsigned)total_blocks, 256, 0, (cudaStream_t)stream>>>(descs, ndesc);
+  return check_launch("pack_conv1x1_multi");
 }
 
 extern "C" int b200ir_pack_conv1x1_t(const float* w, int Cin, int Cout, void* wp, float* st, b200ir_stream_t stream) {

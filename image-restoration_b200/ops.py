@@ -362,6 +362,13 @@ def pack_conv1x1(w, bias=None, ln_type=L.LN_NONE, ln_w=None, ln_b=None, per_samp
     return wp, st
 
 
+def pack_conv1x1_multi(descs_dev, ndesc, total_blocks):
+    """One launch for a whole table of packs (descs_dev: device uint8 tensor holding b200ir_pack_desc_t[ndesc])."""
+    with _timed("pack_conv1x1_multi", ndesc, total_blocks):
+        rc = lib.b200ir_pack_conv1x1_multi(descs_dev.data_ptr(), ndesc, total_blocks, _stream())
+    L.check(rc, "b200ir_pack_conv1x1_multi")
+
+
 def pack_conv1x1_t(w):
     """Operand of the input-gradient GEMM dx = W^T.dy: same result as pack_conv1x1(w.t()), packed from w [Cout,Cin]."""
     Cout, Cin = w.shape

@@ -126,6 +126,11 @@ def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.
     restored = net(degrad); loss = L1(restored, clean); backward; (all-reduce); AdamW.  Returns the loss (device scalar)."""
     loss_fn = loss_fn or L1Loss()
     opt.zero_grad()
+    if degraded.is_cuda and getattr(net, "compute_dtype", None) == torch.bfloat16:
+        pre = net.__dict__.get("_b200ir_prepacker")
+        if pre is None or not pre.valid():
+            pre = net.__dict__["_b200ir_prepacker"] = A.Prepacker(net)
+        pre.run()     # every 1x1 weight pack of the step in one launch (the forward / backward find them cached)
     restored = net(degraded)
     loss = loss_fn(restored, clean)
     loss.backward()
@@ -170,7 +175,10 @@ class GraphedTrainStep:
         self.g1 = torch.cuda.CUDAGraph()
         self.g2 = None
         launches0 = ops.LAUNCHES
+        pre = net.__dict__.get("_b200ir_prepacker")   # built by the warm-up steps (bf16 compute only)
         with torch.cuda.graph(self.g1):
+            if pre is not None and pre.valid():
+                pre.run()
             restored = net(self.degraded)
             loss = self.loss_fn(restored, self.clean)
             loss.backward()

@@ -135,6 +135,21 @@ int b200ir_pack_conv1x1(const float* w, int64_t w_bstride, int Bw, const float* 
  * b200ir_pack_conv1x1(w^T, ln NONE, no bias) for a GEMM with Cin' = Cout, Cout' = Cin; sizes from
  * b200ir_gemm_tc_geometry(Cout, Cin). */
 int b200ir_pack_conv1x1_t(const float* w, int Cin, int Cout, void* wp, float* st, b200ir_stream_t stream);
+/* All weight packs of a model in ONE launch (a training step repacks every 1x1 weight after the optimizer update: ~260
+ * tiny launches otherwise).  descs: DEVICE array of ndesc descriptors; desc i owns CTAs [first_block, next first_block)
+ * of the launch (total_blocks CTAs of 256 threads): transposed = 0 -> ceil(Nrows/8) CTAs, same result as
+ * b200ir_pack_conv1x1 (Bw = 1); transposed = 1 -> ceil(Kpad/32)*ceil(Nrows/32) CTAs, same result as
+ * b200ir_pack_conv1x1_t.  Kpad / Nrows from b200ir_gemm_tc_geometry of the GEMM the pack feeds. */
+typedef struct {
+  const float* w;      /* [Cout][Cin] */
+  const float* bias;   /* [Cout] or NULL (transposed: ignored) */
+  const float* ln_w;   /* [Cin] or NULL */
+  const float* ln_b;   /* [Cin] or NULL */
+  void* wp;            /* bf16 [Nrows][Kpad] */
+  float* st;           /* fp32 [2][Nrows] */
+  int Cin, Cout, Kpad, Nrows, ln_type, transposed, first_block, reserved;
+} b200ir_pack_desc_t;
+int b200ir_pack_conv1x1_multi(const b200ir_pack_desc_t* descs, int ndesc, int total_blocks, b200ir_stream_t stream);
 int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st, int ln_type,
                        const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
                        int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);

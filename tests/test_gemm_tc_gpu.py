@@ -173,3 +173,39 @@ def test_pack_conv1x1_t_equals_pack_of_transpose(Cout, Cin):
     assert wp0.shape == wp1.shape
     assert torch.equal(wp0.view(torch.int16), wp1.view(torch.int16))
     assert torch.equal(st0[1], st1[1])   # t = 0 (no bias); s (row sums) is only read by the LayerNorm epilogue
+
+
+def test_prepacker_fills_caches_with_identical_packs():
+    """Prepacker.run(): one launch packs the forward (LayerNorm-folded) and transposed operands of every block conv;
+    results are bitwise what pack_conv1x1 / pack_conv1x1_t give, and the forward / backward then find them cached."""
+    import b200ir
+    from b200ir import ops, autograd_ops as A, modules as M
+    L = b200ir._lib
+    torch.manual_seed(0)
+    blk = b200ir.TransformerBlock(48, 2, 2.66, True, "WithBias").cuda()
+    enc = b200ir.EncoderBlock(32, 1, 2.0, False, "BiasFree").cuda()
+    net = torch.nn.Sequential(blk)
+    for p in list(blk.parameters()) + list(enc.parameters()):
+        p.data.add_(0.1 * torch.randn_like(p))
+    for model, (n1, attn, n2, ffn) in ((net, (blk.norm1, blk.attn, blk.norm2, blk.ffn)),
+                                       (enc, (enc.norms[0], enc.mixer, enc.norms[1], enc.ffn))):
+        pre = A.Prepacker(model)
+        assert pre.ndesc == 6 and pre.run()
+        for cache, key, conv, norm in ((attn._b200ir_cache, ("qkv", id(n1)), attn.qkv, n1),
+                                       (ffn._b200ir_cache, ("in", id(n2)), ffn.project_in, n2),
+                                       (ffn._b200ir_cache, "out", ffn.project_out, None)):
+            cout, cin = conv.weight.shape[:2]
+            ln_type, lw, lb = M._ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
+            wp0, st0 = ops.pack_conv1x1(conv.weight.detach().reshape(cout, cin), conv.bias.detach() if conv.bias is not None else None,
+                                        ln_type, lw.detach() if lw is not None else None, lb.detach() if lb is not None else None)
+            wp1, st1 = cache[key][1]
+            assert torch.equal(wp0.view(torch.int16), wp1.view(torch.int16)) and torch.equal(st0, st1), key
+            wt0, _ = ops.pack_conv1x1_t(conv.weight.detach().reshape(cout, cin))
+            assert torch.equal(wt0.view(torch.int16), cache[("T", key)][1][0].view(torch.int16)), key
+        # a forward + backward after run() packs nothing itself
+        x = (torch.rand(2, attn.qkv.in_channels, 16, 16, device="cuda") - 0.5).bfloat16().requires_grad_(True)
+        ops.timing_start(only=["pack_conv1x1"])
+        model(x).float().sum().backward()
+        torch.cuda.synchronize()
+        left = [k for k in ops.timing_stop() if k[1] == 1]     # (name, Bw, Cin, Cout): per-sample MDTA packs (Bw > 1) stay
+        assert not left, ("blocks still packed shared weights one by one", left)
