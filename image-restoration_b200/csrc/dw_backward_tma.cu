@@ -63,36 +63,69 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
   }
   __syncthreads();
 
+  // A CTA owns a CONTIGUOUS range of work items (tile fastest, then channel group, then sample), as in the forward
+  // kernel (dwconv_tma.cu): the position advances without divisions, the taps are re-read only when the channel changes,
+  // and the weight-gradient sums keep accumulating in registers over the consecutive tiles of one plane -- the CTA-wide
+  // reduction runs once per plane segment (the other tiles' partial slots are written as zeros).
   const int tiles = P.tiles_x * P.tiles_y;
   const uint32_t cgroups = (uint32_t)((P.Cout + P.ncg - 1) / P.ncg);
-  auto issue = [&](uint32_t item, int stage) {   // thread 0
+  struct Pos {
+    int tx, ty, cg, b;
+  };
+  auto decode = [&](uint32_t item) {
     const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int c = (int)(pc % cgroups) * P.ncg, b = (int)(pc / cgroups);
-    const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
+    Pos q;
+    q.tx = (int)(t % (uint32_t)P.tiles_x); q.ty = (int)(t / (uint32_t)P.tiles_x);
+    q.cg = (int)(pc % cgroups); q.b = (int)(pc / cgroups);
+    return q;
+  };
+  auto advance = [&](Pos& q) {
+    if (++q.tx == P.tiles_x) {
+      q.tx = 0;
+      if (++q.ty == P.tiles_y) {
+        q.ty = 0;
+        if (++q.cg == (int)cgroups) { q.cg = 0; ++q.b; }
+      }
+    }
+  };
+  auto issue = [&](const Pos& q, int stage) {   // thread 0
     mbar_arrive_expect_tx(&bar_full[stage], cplane * (uint32_t)P.ncg * NIN);
 #pragma unroll
     for (int k = 0; k < NIN; ++k)
-      tma_load_4d(smem + (size_t)stage * stage_bytes + (size_t)k * plane_bytes, &tmX, &bar_full[stage], x0 - DW_XP,
-                  y0 - 1, c + k * P.Cout, b);
+      tma_load_4d(smem + (size_t)stage * stage_bytes + (size_t)k * plane_bytes, &tmX, &bar_full[stage],
+                  q.tx * P.TW - DW_XP, q.ty * P.TH - 1, q.cg * P.ncg + k * P.Cout, q.b);
   };
 
-  const uint32_t first = blockIdx.x, step = gridDim.x;
+  const uint32_t per = (uint32_t)P.nitems / gridDim.x, rem = (uint32_t)P.nitems % gridDim.x;
+  const uint32_t begin = blockIdx.x * per + (blockIdx.x < rem ? blockIdx.x : rem);
+  const uint32_t count = per + (blockIdx.x < rem ? 1u : 0u);
+  Pos cur = decode(begin), nxt = cur;     // nxt: the next item to stage (thread 0 runs P.S items ahead)
+  uint32_t staged = 0;
   if (tid == 0)
-    for (int s = 0; s < P.S; ++s)
-      if (first + s * step < (uint32_t)P.nitems) issue(first + s * step, s);
+    for (; staged < (uint32_t)P.S && staged < count; ++staged) {
+      issue(nxt, (int)staged);
+      advance(nxt);
+    }
 
   const int cs = tid / tpc, rr = tid - cs * tpc;      // channel of the group, thread within the channel plane
   const int xg = rr % P.nxg, strip = rr / P.nxg;
   const int64_t HWp = (int64_t)P.H * P.W;
-  uint32_t it = 0;
-  for (uint32_t item = first; item < (uint32_t)P.nitems; item += step, ++it) {
-    const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
-    const uint32_t t = item % (uint32_t)tiles, pc = item / (uint32_t)tiles;
-    const int cb = (int)(pc % cgroups) * P.ncg, c = cb + cs, b = (int)(pc / cgroups);
-    const int x0 = (t % P.tiles_x) * P.TW, y0 = (t / P.tiles_x) * P.TH;
-    float acc[NV];
+  const uint32_t thr_base = smem_u32(smem) + (uint32_t)cs * cplane + (uint32_t)(strip * BW_RS) * pitch +
+                            (uint32_t)(DW_XP + xg * 8) * 2u;
+  int wc = -1;                            // channel whose taps are in registers (GATE)
+  float2 wk[9], bs = make_float2(0.f, 0.f);
+  float acc[NV];                          // weight / bias gradient sums of the current plane segment
 #pragma unroll
-    for (int i = 0; i < NV; ++i) acc[i] = 0.f;
+  for (int i = 0; i < NV; ++i) acc[i] = 0.f;
+  constexpr uint32_t NS = GATE ? 2 : 3;   // ring depth (= P.S; compile-time so that stage / phase are bit ops of `it`)
+  for (uint32_t it = 0; it < count; ++it) {
+    const uint32_t stage = it % NS, ph = (it / NS) & 1;
+    const int cb = cur.cg * P.ncg, c = cb + cs, b = cur.b;
+    const int x0 = cur.tx * P.TW, y0 = cur.ty * P.TH;
+    const int t = cur.ty * P.tiles_x + cur.tx;
+    Pos after = cur;
+    advance(after);
+    const bool flush = it + 1 == count || after.cg != cur.cg || after.b != cur.b;   // last tile of the plane segment
 
     if (tid < nthreads && c < P.Cout) {
       const int gx = x0 + xg * 8;
@@ -100,15 +133,16 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
       const bf16* grow = P.g + (int64_t)b * P.g_bs + (int64_t)c * HWp + poff;
       const bool xok = gx < P.W;
       const int yrem = P.H - (y0 + strip * BW_RS);
-      const uint32_t base = smem_u32(smem) + stage * stage_bytes + (uint32_t)cs * cplane +
-                            (uint32_t)(strip * BW_RS) * pitch + (uint32_t)(DW_XP + xg * 8) * 2u;
+      const uint32_t base = thr_base + stage * stage_bytes;
       if (GATE) {
         bf16* a1row = P.da + (int64_t)b * P.da_bs + (int64_t)c * HWp + poff;
         bf16* a2row = a1row + (int64_t)P.Cout * HWp;
-        float2 wk[9];
+        if (c != wc) {
+          wc = c;
 #pragma unroll
-        for (int i = 0; i < 9; ++i) wk[i] = make_float2(__ldg(P.w + c * 9 + i), __ldg(P.w + (c + P.Cout) * 9 + i));
-        const float2 bs = P.bias ? make_float2(__ldg(P.bias + c), __ldg(P.bias + c + P.Cout)) : make_float2(0.f, 0.f);
+          for (int i = 0; i < 9; ++i) wk[i] = make_float2(__ldg(P.w + c * 9 + i), __ldg(P.w + (c + P.Cout) * 9 + i));
+          if (P.bias) bs = make_float2(__ldg(P.bias + c), __ldg(P.bias + c + P.Cout));
+        }
         float2 ac2[10];
 #pragma unroll
         for (int i = 0; i < 10; ++i) ac2[i] = make_float2(0.f, 0.f);
@@ -165,8 +199,8 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
         }
 #pragma unroll
         for (int i = 0; i < 10; ++i) {
-          acc[i] = ac2[i].x;
-          acc[(NV - 10) + i] = ac2[i].y;
+          acc[i] += ac2[i].x;
+          acc[(NV - 10) + i] += ac2[i].y;
         }
       } else {
         mbar_wait(&bar_full[stage], ph);
@@ -192,52 +226,56 @@ dw_bwd_tma_kernel(const __grid_constant__ CUtensorMap tmX, const DwBwdParams P) 
     } else {
       mbar_wait(&bar_full[stage], ph);   // keep every thread's view of the barrier phase in step
     }
+    const size_t slot = ((size_t)b * tiles + t) * P.Ctot;
     if (P.ncg > 1) {
       // small planes: the tpc (power of two <= 32) threads of a channel are consecutive lanes of one warp: butterfly
       // within that lane group (fixed order), its first lane writes the channel's sums
+      const bool writer = tid < nthreads && c < P.Cout && rr == 0;
+      if (flush) {
 #pragma unroll
-      for (int i = 0; i < NV; ++i) {
-        float v = acc[i];
-        for (int o = tpc >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        acc[i] = v;
+        for (int i = 0; i < NV; ++i) {
+          float v = acc[i];
+          for (int o = tpc >> 1; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+          acc[i] = v;
+        }
       }
-      if (tid < nthreads && c < P.Cout && rr == 0) {
+      if (writer) {
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
           const int plane = (GATE && i >= 10) ? c + P.Cout : c;
-          P.parts[(((size_t)b * tiles + t) * P.Ctot + plane) * 10 + (i % 10)] = acc[i];
+          P.parts[(slot + plane) * 10 + (i % 10)] = flush ? acc[i] : 0.f;
         }
+      }
+      if (flush) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) acc[i] = 0.f;
       }
       __syncthreads();   // every thread is done reading this stage
-      if (tid == 0) {
-        const uint32_t nxt = item + (uint32_t)P.S * step;
-        if (nxt < (uint32_t)P.nitems) {
-          fence_proxy_async();
-          issue(nxt, stage);
+    } else {
+      // fixed-order CTA reduction of the plane segment's sums
+      float (*rb)[NV] = red[it & 1];
+      if (flush) {
+#pragma unroll
+        for (int i = 0; i < NV; ++i) {
+          const float v = warp_sum(acc[i]);
+          if (lane == 0) rb[warp][i] = v;
+          acc[i] = 0.f;
         }
       }
-      continue;
-    }
-    // fixed-order CTA reduction of the per-item sums
-    float (*rb)[NV] = red[it & 1];
-#pragma unroll
-    for (int i = 0; i < NV; ++i) {
-      const float v = warp_sum(acc[i]);
-      if (lane == 0) rb[warp][i] = v;
-    }
-    __syncthreads();   // every thread is done reading this stage; rb complete
-    if (tid < NV) {
-      const float s = rb[0][tid] + rb[1][tid] + rb[2][tid] + rb[3][tid];
-      const int plane = (GATE && tid >= 10) ? cb + P.Cout : cb;   // ncg == 1 here
-      P.parts[(((size_t)b * tiles + t) * P.Ctot + plane) * 10 + (tid % 10)] = s;
-    }
-    if (tid == 0) {
-      const uint32_t nxt = item + (uint32_t)P.S * step;
-      if (nxt < (uint32_t)P.nitems) {
-        fence_proxy_async();
-        issue(nxt, stage);
+      __syncthreads();   // every thread is done reading this stage; rb complete
+      if (tid < NV) {
+        const float s = flush ? rb[0][tid] + rb[1][tid] + rb[2][tid] + rb[3][tid] : 0.f;
+        const int plane = (GATE && tid >= 10) ? cb + P.Cout : cb;   // ncg == 1 here
+        P.parts[(slot + plane) * 10 + (tid % 10)] = s;
       }
     }
+    if (tid == 0 && staged < count) {
+      fence_proxy_async();
+      issue(nxt, (int)stage);
+      advance(nxt);
+      ++staged;
+    }
+    cur = after;
   }
 }
 
@@ -305,7 +343,7 @@ int dw_bwd_tma_launch(const void* x, int64_t x_bs, const void* g, int64_t g_bs, 
   std::call_once(once, [] {
     cudaFuncSetAttribute(dw_bwd_tma_kernel<GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   });
-  int ctas_per_sm = (int)((220 * 1024) / (smem + 2048));
+  int ctas_per_sm = resident_ctas(dw_bwd_tma_kernel<GATE>, 128, smem);   // exactly the resident CTAs (static contiguous ranges; registers are the limit here)
   if (ctas_per_sm > 8) ctas_per_sm = 8;
   if (ctas_per_sm < 1) ctas_per_sm = 1;
   int64_t grid = 148ll * ctas_per_sm;

@@ -1,9 +1,29 @@
 // dwconv_tma.cuh — shared pieces of the TMA-staged depthwise 3x3 kernels (forward: dwconv_tma.cu, backward:
 // dw_backward_tma.cu): work-item geometry, packed fp32x2 FMA, bf16 window loads from the staged halo tile.
 #pragma once
+#include <map>
+#include <mutex>
+
 #include "tc_common.cuh"
 
 namespace b200ir {
+
+// CTAs of `kernel` resident per SM at this dynamic shared-memory size (cached: the occupancy query is a host call)
+template <typename K>
+inline int resident_ctas(K kernel, int threads, size_t smem) {
+  static std::mutex mu;
+  static std::map<size_t, int> cache;
+  std::lock_guard<std::mutex> lk(mu);
+  auto it = cache.find(smem);
+  if (it != cache.end()) return it->second;
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem) != cudaSuccess || n < 1) {
+    cudaGetLastError();
+    n = 1;
+  }
+  cache[smem] = n;
+  return n;
+}
 
 struct DwTmaParams {
   bf16* y;
@@ -43,6 +63,16 @@ __device__ __forceinline__ float gelu_fast(float x) {
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
   return x * r;
 #endif
+}
+
+// 2 * gelu(x) = x + x * tanh(x * q(x^2)/2) (same fit as gelu_fast; the caller folds the 0.5 into the other factor)
+__device__ __forceinline__ float gelu2_fast(float x) {
+  const float x2 = fminf(x * x, 64.f);
+  float t = fmaf(-3.5151753375e-4f, x2, 3.7005650955e-2f);
+  t = fmaf(t, x2, 0.79750787845f);
+  float th;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(th) : "f"(t * x));
+  return fmaf(x, th, x);
 }
 
 // packed fp32x2 FMA (sm_100): d = a * b + c on both halves, one issue slot
