@@ -132,26 +132,20 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
     // LayerNorm statistics of the 128 pixels of each item, from the staged activation tiles (shifted sums)
     if (has_ln) {
       const int m = (warp - kGsWarpStats0) * 32 + lane;
-      const uint32_t mblk = m >> 6, pi = m & 63;
+      const uint32_t ring_addr = smem_u32(ring);
       uint32_t it = 0, icount = 0;
       for (int item = blockIdx.x; item < P.total_items; item += gridDim.x, ++icount) {
-        float x0 = 0.f, sum = 0.f, sq = 0.f;
+        LnStatAcc acc;
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_full[stage], ph);
           const int rows = min(64, P.Cin - kc * 64);
-          const uint8_t* base = ring + (size_t)stage * stage_bytes + mblk * 8192 + (pi & 7) * 2;
-          if (kc == 0) x0 = __bfloat162float(*(const bf16*)(base + ((pi >> 3) << 4)));
-#pragma unroll 8
-          for (int r = 0; r < rows; ++r) {
-            const float v = __bfloat162float(*(const bf16*)(base + r * 128 + (((pi >> 3) ^ (r & 7)) << 4)));
-            const float d = v - x0;
-            sum += d;
-            sq = fmaf(d, d, sq);
-          }
+          ln_stat_chunk(ring_addr + stage * stage_bytes, 8192u, m, rows, kc == 0, acc);
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_empty[stage]);
         }
+        float x0, sum, sq;
+        ln_stat_finish(acc, m, x0, sum, sq);
         const float md = sum * P.inv_cin;
         const float var = fmaxf(sq * P.inv_cin - md * md, 0.f);
         const uint32_t sp = icount & 1, sph = (icount >> 1) & 1;

@@ -547,26 +547,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     // ================= LayerNorm statistics =================
     if (has_ln) {
       const int m = (warp - kWarpStats0) * 32 + lane;
-      const uint32_t mblk = m >> 6, pi = m & 63;
+      const uint32_t ring_addr = smem_u32(ring);
       uint32_t it = 0, tcount = 0;
       for (int tile = t_begin; tile < t_end; ++tile, ++tcount) {
-        float x0 = 0.f, sum = 0.f, sq = 0.f;
+        LnStatAcc acc;
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_full[stage], ph);
           const int rows = min(P.BK, P.Cin - kc * P.BK);
-          const uint8_t* base = ring + (size_t)stage * kStageBytes + mblk * P.BK * 128 + (pi & 7) * 2;
-          if (kc == 0) x0 = __bfloat162float(*(const bf16*)(base + ((pi >> 3) << 4)));
-#pragma unroll 8
-          for (int r = 0; r < rows; ++r) {
-            const float v = __bfloat162float(*(const bf16*)(base + r * 128 + (((pi >> 3) ^ (r & 7)) << 4)));
-            const float d = v - x0;
-            sum += d;
-            sq = fmaf(d, d, sq);
-          }
+          ln_stat_chunk(ring_addr + stage * kStageBytes, (uint32_t)P.BK * 128u, m, rows, kc == 0, acc);
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_empty[stage]);
         }
+        float x0, sum, sq;
+        ln_stat_finish(acc, m, x0, sum, sq);
         const float md = sum * P.inv_cin;
         const float var = fmaxf(sq * P.inv_cin - md * md, 0.f);
         const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;

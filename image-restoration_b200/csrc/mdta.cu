@@ -6,6 +6,8 @@
 //   :124      (q @ k^T) * temperature[h]
 //   :125      softmax over the last dim (rows of length d = C/heads)
 //   :127-131  attn @ v, then project_out  -> folded into m[b] = W_out . blockdiag(attn[b,h])
+#include <mutex>
+
 #include "common.cuh"
 
 namespace b200ir {
@@ -151,29 +153,65 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
 // ---- stage 2b: fold project_out into the attention matrix: m[b][o][h*d+j] = sum_i w_out[o][h*d+i] attn[b,h][i][j]
 // grid (ceil(C/kFoldRows), heads, B), 256 threads; kFoldRows = 32 or 8 (launcher).  Writes fp32 m [B,C,C] and/or the bf16 operand of the tcgen05 GEMM
 // mp [B][nrows][kpad] (zero padded) so that no separate packing launch is needed.
+// Register-tiled: the 256 threads form a 16 x 16 grid, thread (ty, tx) owns output rows ty*RT .. ty*RT+RT-1 and columns
+// tx + 16 k (k < KC, KC = ceil(d/16)): per reduction step RT + KC shared loads feed RT*KC FMAs (the one-output-per-thread
+// form issued 2 LDS per FMA and was LDS-bound: 40 us at C=384).  The i-sum runs in increasing i in every variant, so
+// the result does not depend on RT / the row-block size.
+template <int RT, int KC>
 __global__ void __launch_bounds__(256)
 mdta_fold_kernel(const float* __restrict__ attn, const float* __restrict__ w_out, float* __restrict__ m,
-                 bf16* __restrict__ mp, int kpad, int nrows, int C, int d, int kFoldRows) {
+                 bf16* __restrict__ mp, int kpad, int nrows, int C, int d) {
+  constexpr int kFoldRows = 16 * RT;
   extern __shared__ float sm[];
-  float* at = sm;                    // [d][d+1]
-  float* ws = sm + (size_t)d * (d + 1);  // [kFoldRows][d+1]
-  const int tid = threadIdx.x;
+  float* at = sm;                    // [d][d]      (column reads are consecutive over tx: conflict-free unpadded)
+  float* ws = sm + (size_t)d * d;    // [kFoldRows][d+1]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tx = tid & 15, ty = tid >> 4;
   const int h = blockIdx.y, b = blockIdx.z, heads = gridDim.y;
   const int o0 = blockIdx.x * kFoldRows;
   const float* a = attn + ((size_t)b * heads + h) * d * d;
-  for (int e = tid; e < d * d; e += 256) at[(e / d) * (d + 1) + (e % d)] = a[e];
-  for (int e = tid; e < kFoldRows * d; e += 256) {
-    const int o = o0 + e / d, i = e % d;
-    ws[(e / d) * (d + 1) + i] = o < C ? w_out[(size_t)o * C + h * d + i] : 0.f;
+  if ((d & 3) == 0) {
+    const float4* a4 = reinterpret_cast<const float4*>(a);
+    float4* at4 = reinterpret_cast<float4*>(at);
+    for (int e = tid; e < (d * d) >> 2; e += 256) at4[e] = a4[e];
+  } else {
+    for (int e = tid; e < d * d; e += 256) at[e] = a[e];
+  }
+  for (int r = warp; r < kFoldRows; r += 8) {
+    const int o = o0 + r;
+    const float* src = w_out + (size_t)o * C + h * d;
+    for (int i = lane; i < d; i += 32) ws[r * (d + 1) + i] = o < C ? src[i] : 0.f;
   }
   __syncthreads();
-  for (int e = tid; e < kFoldRows * d; e += 256) {
-    const int ol = e / d, j = e % d, o = o0 + ol;
+  float acc[RT][KC];
+#pragma unroll
+  for (int r = 0; r < RT; ++r)
+#pragma unroll
+    for (int k = 0; k < KC; ++k) acc[r][k] = 0.f;
+  const float* wrow = ws + (size_t)(ty * RT) * (d + 1);
+#pragma unroll 4
+  for (int i = 0; i < d; ++i) {
+    float av[KC], wv[RT];
+#pragma unroll
+    for (int k = 0; k < KC; ++k) av[k] = (tx + 16 * k < d) ? at[i * d + tx + 16 * k] : 0.f;
+#pragma unroll
+    for (int r = 0; r < RT; ++r) wv[r] = wrow[r * (d + 1) + i];
+#pragma unroll
+    for (int r = 0; r < RT; ++r)
+#pragma unroll
+      for (int k = 0; k < KC; ++k) acc[r][k] = fmaf(wv[r], av[k], acc[r][k]);
+  }
+#pragma unroll
+  for (int r = 0; r < RT; ++r) {
+    const int o = o0 + ty * RT + r;
     if (o >= C) continue;
-    float s = 0.f;
-    for (int i = 0; i < d; ++i) s = fmaf(ws[ol * (d + 1) + i], at[i * (d + 1) + j], s);
-    if (m) m[((size_t)b * C + o) * C + h * d + j] = s;
-    if (mp) mp[((size_t)b * nrows + o) * kpad + h * d + j] = __float2bfloat16_rn(s);
+#pragma unroll
+    for (int k = 0; k < KC; ++k) {
+      const int j = tx + 16 * k;
+      if (j >= d) continue;
+      if (m) m[((size_t)b * C + o) * C + h * d + j] = acc[r][k];
+      if (mp) mp[((size_t)b * nrows + o) * kpad + h * d + j] = __float2bfloat16_rn(acc[r][k]);
+    }
   }
   if (mp) {  // zero padding: columns [C,kpad) of valid rows (head 0 blocks) and whole rows [C,nrows) (last row block)
     if (h == 0)
@@ -262,15 +300,36 @@ extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, co
                         st>>>(partials, nslab, temperature, attn, d);
   int rc = check_launch("mdta_softmax");
   if (rc) return rc;
-  // output rows per block: 32 when that already fills the GPU, else 8 (few heads / small batch)
-  const int kFoldRows = (int64_t)((C + 31) / 32) * heads * B >= 2 * 148 ? 32 : 8;
-  const size_t smem = ((size_t)d * (d + 1) + kFoldRows * (size_t)(d + 1)) * sizeof(float);
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(mdta_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    attr_set = true;
-  }
-  mdta_fold_kernel<<<dim3((unsigned)((C + kFoldRows - 1) / kFoldRows), (unsigned)heads, (unsigned)B), 256, smem, st>>>(
-      attn, w_out, m, (bf16*)mp, kpad, nrows, C, d, kFoldRows);
+  // output rows per block (16 per register row RT): the largest of 64 / 32 / 16 that still gives every SM a block
+  int RT = 1;
+  for (int rt = 4; rt >= 1; rt >>= 1)
+    if ((int64_t)((C + 16 * rt - 1) / (16 * rt)) * heads * B >= 148) {
+      RT = rt;
+      break;
+    }
+  const int kFoldRows = 16 * RT;
+  const int KC = (d + 15) / 16;   // 1..8
+  const size_t smem = ((size_t)d * d + kFoldRows * (size_t)(d + 1)) * sizeof(float);
+  const dim3 grid((unsigned)((C + kFoldRows - 1) / kFoldRows), (unsigned)heads, (unsigned)B);
+#define FOLD_LAUNCH(RT_, KC_)                                                                                       \
+  do {                                                                                                              \
+    static std::once_flag once;                                                                                     \
+    std::call_once(once, [] {                                                                                       \
+      cudaFuncSetAttribute(mdta_fold_kernel<RT_, KC_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);    \
+    });                                                                                                             \
+    mdta_fold_kernel<RT_, KC_><<<grid, 256, smem, st>>>(attn, w_out, m, (bf16*)mp, kpad, nrows, C, d);              \
+  } while (0)
+#define FOLD_KC(RT_)                                                                                                \
+  do {                                                                                                              \
+    if (KC <= 2) FOLD_LAUNCH(RT_, 2);                                                                               \
+    else if (KC <= 3) FOLD_LAUNCH(RT_, 3);                                                                          \
+    else if (KC <= 6) FOLD_LAUNCH(RT_, 6);                                                                          \
+    else FOLD_LAUNCH(RT_, 8);                                                                                       \
+  } while (0)
+  if (RT == 4) FOLD_KC(4);
+  else if (RT == 2) FOLD_KC(2);
+  else FOLD_KC(1);
+#undef FOLD_KC
+#undef FOLD_LAUNCH
   return check_launch("mdta_fold");
 }

@@ -151,6 +151,65 @@ __device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t* r) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---------------- LayerNorm statistics from a staged activation tile ----------------
+// The 128 statistics threads of a GEMM CTA read the MN-major SWIZZLE_128B activation tile ([2 halves of 64 px][rows =
+// channels][128 B]) that TMA staged for the MMA.  Thread m (0..127) = 8-pixel group G = m>>3 (half G>>3, 16-byte chunk
+// G&7) x row subset sub = m&7 (rows r with r&7 == sub): one LDS.128 brings 8 pixels of one channel, so a thread issues
+// rows/8 vector loads per chunk and carries 8 independent (sum, sum of squares) chains.  (The first form read one bf16
+// per load through a generic pointer, one pixel per thread: 192 dependent-latency loads per tile at C=192 made the
+// statistics warps the critical path of the level-3/4 GEMMs -- ncu source page, profiles/r1m.)  The 8 lanes of a group
+// sit in one quarter-warp phase and hit 8 different chunk positions (c ^ sub): conflict-free.
+struct LnStatAcc {
+  float x0[8], sum[8], sq[8];
+};
+__device__ __forceinline__ void ln_stat_unpack(uint32_t saddr, float* v) {
+  uint32_t a, b, c, d;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(saddr));
+  v[0] = __uint_as_float(a << 16); v[1] = __uint_as_float(a & 0xffff0000u);
+  v[2] = __uint_as_float(b << 16); v[3] = __uint_as_float(b & 0xffff0000u);
+  v[4] = __uint_as_float(c << 16); v[5] = __uint_as_float(c & 0xffff0000u);
+  v[6] = __uint_as_float(d << 16); v[7] = __uint_as_float(d & 0xffff0000u);
+}
+// tile_addr: shared address of the stage's activation tile; half_bytes = rows-per-half * 128; first: kc == 0
+__device__ __forceinline__ void ln_stat_chunk(uint32_t tile_addr, uint32_t half_bytes, int m, int rows, bool first,
+                                              LnStatAcc& a) {
+  const uint32_t G = (uint32_t)m >> 3, sub = (uint32_t)m & 7u, c = G & 7u;
+  const uint32_t half = tile_addr + (G >> 3) * half_bytes;
+  if (first) {
+    ln_stat_unpack(half + (c << 4), a.x0);   // row 0: the shift of the one-trip variance
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a.sum[j] = a.sq[j] = 0.f;
+  }
+  uint32_t addr = half + sub * 128u + ((c ^ sub) << 4);
+#pragma unroll 2
+  for (int r = (int)sub; r < rows; r += 8, addr += 1024u) {
+    float v[8];
+    ln_stat_unpack(addr, v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const float d = v[j] - a.x0[j];
+      a.sum[j] += d;
+      a.sq[j] = fmaf(d, d, a.sq[j]);
+    }
+  }
+}
+// fold the 8 row subsets (lanes differing in bits 0..2) and return this thread's pixel m: (x0, sum, sq)
+__device__ __forceinline__ void ln_stat_finish(LnStatAcc& a, int m, float& x0, float& sum, float& sq) {
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+      a.sum[j] += __shfl_xor_sync(0xffffffffu, a.sum[j], o);
+      a.sq[j] += __shfl_xor_sync(0xffffffffu, a.sq[j], o);
+    }
+  }
+  const int sub = m & 7;
+  x0 = a.x0[0]; sum = a.sum[0]; sq = a.sq[0];
+#pragma unroll
+  for (int j = 1; j < 8; ++j)
+    if (sub == j) { x0 = a.x0[j]; sum = a.sum[j]; sq = a.sq[j]; }
+}
+
 // ---------------- descriptors ----------------
 // Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor, mma_sm100_desc.hpp): start>>4 [0,14),
 // LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout_type [61,64) (2 = SWIZZLE_128B).
