@@ -4,16 +4,19 @@ set -e
 cd "$(dirname "$0")"
 NVCC=${NVCC:-/usr/local/cuda/bin/nvcc}
 FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC --use_fast_math=false"
-FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xptxas -v"
-mkdir -p build
+FLAGS="-gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -std=c++17 -Xcompiler -fPIC -Xptxas -v $EXTRA_FLAGS"
+# A/B builds: EXTRA_FLAGS="-D..." BUILD=build_x OUT=../../tools/ab/libx.so bash build.sh ; run with B200IR_LIB=tools/ab/libx.so
+BUILD=${BUILD:-build}
+OUT=${OUT:-../libb200ir.so}
+mkdir -p $BUILD "$(dirname $OUT)"
 OBJS=""
 for f in *.cu; do
-  o=build/${f%.cu}.o
+  o=$BUILD/${f%.cu}.o
   if [ ! -f "$o" ] || [ "$f" -nt "$o" ] || [ common.cuh -nt "$o" ] || [ ../../include/b200ir.h -nt "$o" ] || [ tc_common.cuh -nt "$o" ] || [ dwconv_tma.cuh -nt "$o" ]; then
     echo "nvcc $f"
-    $NVCC $FLAGS -c "$f" -o "$o" 2> build/${f%.cu}.ptxas.log || { cat build/${f%.cu}.ptxas.log; exit 1; }
+    $NVCC $FLAGS -c "$f" -o "$o" 2> $BUILD/${f%.cu}.ptxas.log || { cat $BUILD/${f%.cu}.ptxas.log; exit 1; }
   fi
   OBJS="$OBJS $o"
 done
-$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o ../libb200ir.so $OBJS
-echo "built $(cd ..; pwd)/libb200ir.so"
+$NVCC -gencode arch=compute_100a,code=sm_100a -shared -o $OUT $OBJS
+echo "built $OUT"

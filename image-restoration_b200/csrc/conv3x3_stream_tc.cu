@@ -81,7 +81,7 @@ conv3x3_stream_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
+    {   // whole warp, convergent; the issuing lane is elected per instruction (tc_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, P.Ntile, 0, 0);
       const uint32_t ring_addr = smem_u32(ring);
       for (int kc = 0; kc < P.kchunks; ++kc) {
@@ -93,11 +93,11 @@ conv3x3_stream_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_c
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t da = make_smem_desc_sw128(aa + ks * 32, 16u, 1024u);
           const uint64_t dw = make_smem_desc_sw128(wa + ks * 32, 16u, 1024u);
-          umma_bf16(tmem_base, da, dw, idesc, (kc | ks) != 0 ? 1u : 0u);
+          umma_bf16_elect(tmem_base, da, dw, idesc, (kc | ks) != 0 ? 1u : 0u);
         }
-        umma_commit(&bar_empty[stage]);
+        umma_commit_elect(&bar_empty[stage]);
       }
-      umma_commit(bar_acc);
+      umma_commit_elect(bar_acc);
     }
   } else {
     // epilogue: thread <-> TMEM lane = pixel of the patch

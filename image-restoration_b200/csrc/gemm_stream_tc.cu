@@ -103,7 +103,7 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
       }
     }
   } else if (warp == kGsWarpMma) {
-    if (lane == 0) {
+    {   // whole warp, convergent; the issuing lane is elected per instruction (tc_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, P.Ntile, 1, 0);
       const uint32_t ring_addr = smem_u32(ring);
       uint32_t it = 0, acc_it = 0;
@@ -121,11 +121,11 @@ gemm_stream_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_cons
           for (int ks = 0; ks < 4; ++ks) {
             const uint64_t da = make_smem_desc_sw128(aa + ks * 2048, 8192u, 1024u);
             const uint64_t dw = make_smem_desc_sw128(wa + ks * 32, 16u, 1024u);
-            umma_bf16(d_tmem, da, dw, idesc, (kc | ks) != 0 ? 1u : 0u);
+            umma_bf16_elect(d_tmem, da, dw, idesc, (kc | ks) != 0 ? 1u : 0u);
           }
-          umma_commit(&bar_empty[stage]);
+          umma_commit_elect(&bar_empty[stage]);
         }
-        umma_commit(&bar_accfull[as]);
+        umma_commit_elect(&bar_accfull[as]);
       }
     }
   } else if (warp >= kGsWarpStats0) {

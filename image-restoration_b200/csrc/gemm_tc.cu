@@ -324,7 +324,25 @@ struct GemmTcParams {
   int gpw, epi_warp_bytes; // TMA epilogue: 16-col groups per warp, bytes of staging per warp
   int kpt;                 // channel chunks per tap (== kchunks for 1x1)
   int H, W, TW, TWs, TH, tiles_x, tiles_y;   // conv tile = TW x TH pixels (TW*TH = 128, TW = 1<<TWs)
+  int dbg;                 // B200IR_GEMM_DBG (timing experiments only, wrong results): 1 no TMA stores, 2 no statistics, 4 no epilogue math
 };
+
+#ifdef B200IR_TIMELINE
+// debug builds only (tools/ab): per-role clock64 timeline of CTA (0,0); one private region per role (plain stores)
+__device__ unsigned long long g_tl[4 * 4096 * 2];
+#define TL_DECL int tl_cnt = 0; const int tl_slot = (blockIdx.x | blockIdx.y) ? -1 : (warp == kWarpProducer ? 0 : warp == kWarpMma ? 1 : warp == kWarpStats0 ? 2 : warp == 0 ? 3 : -1);
+#define TL(tag, id)                                                                                    \
+  do {                                                                                                 \
+    if (tl_slot >= 0 && tl_cnt < 4096) {                                                               \
+      g_tl[(tl_slot * 4096 + tl_cnt) * 2] = ((unsigned long long)(tag) << 32) | (unsigned)(id);        \
+      g_tl[(tl_slot * 4096 + tl_cnt) * 2 + 1] = (unsigned long long)clock64();                         \
+      ++tl_cnt;                                                                                        \
+    }                                                                                                  \
+  } while (0)
+#else
+#define TL_DECL
+#define TL(tag, id)
+#endif
 
 constexpr int kStageBytes = 16384;  // 128 px x 64 ch x 2 B
 constexpr int kEpiWarps = 16;       // 4 per TMEM lane quadrant
@@ -367,6 +385,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   __shared__ uint64_t bar_full[8], bar_empty[8], bar_wfull[1], bar_wempty[1], bar_accfull[4], bar_accempty[4],
       bar_stfull[2], bar_stempty[2], bar_res[2 * kEpiWarps];
   __shared__ uint32_t tmem_slot[1];
+  __shared__ __align__(16) uint32_t s_bdesc[256];            // low words of the weight descriptors, (ch, kc, ks)
   __shared__ __align__(16) float s_mu[256], s_rstd[256];   // [2][128]: (-rstd*mu, rstd) per pixel, double buffered
   __shared__ __align__(16) float2 s_st[512];               // (s, t) of this CTA's out-channel slice
 
@@ -407,6 +426,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  TL_DECL
 
   // contiguous tile range of this CTA
   const int gx = gridDim.x;
@@ -442,11 +462,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_empty[stage], ph ^ 1);
+          TL(1, tile * 8 + kc);
+          if (P.dbg & 16) { mbar_arrive(&bar_full[stage]); continue; }
           mbar_arrive_expect_tx(&bar_full[stage], ONE ? 2u * P.BK * 128u : (uint32_t)kStageBytes);
           uint8_t* dst = ring + (size_t)stage * kStageBytes;
           if (ONE) {
             tma_load_3d(dst, &tmX, &bar_full[stage], p0, kc * P.BK, b);
             tma_load_3d(dst + P.BK * 128, &tmX, &bar_full[stage], p0 + 64, kc * P.BK, b);
+            TL(2, tile * 8 + kc);
           } else {
             const int tap = kc / P.kpt, cc = kc - tap * P.kpt;
             const int dy = tap / 3 - 1, dx = tap - (tap / 3) * 3 - 1;
@@ -457,7 +480,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
     }
   } else if (warp == kWarpMma) {
     // ================= MMA issuer =================
-    if (lane == 0) {
+    {   // whole warp, convergent: the issuing lane is elected per instruction (tc_common.cuh)
       uint32_t it = 0, acc_it = 0, wload = 0;
       int cur = -1;
       const uint32_t ring_addr = smem_u32(ring), w_addr = smem_u32(Wsm);
@@ -492,55 +515,83 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
                     w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)mt * 16384u + (kglob & 63) * 2u, 16u, 1024u);
                 const uint64_t bdesc = make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048,
                                                             (uint32_t)P.BK * 128u, 1024u);
-                umma_bf16(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
+                umma_bf16_elect(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
               }
-              if (mt == mtiles - 1) umma_commit(&bar_empty[stage]);
+              if (mt == mtiles - 1) umma_commit_elect(&bar_empty[stage]);
             }
-            umma_commit(&bar_accfull[as]);
+            umma_commit_elect(&bar_accfull[as]);
           }
           it += P.kchunks;
-          if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit(bar_wempty);
+          if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit_elect(bar_wempty);
         }
       } else
-      for (int tile = t_begin; tile < t_end; ++tile) {
-        const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
-        if (cur < 0 || (P.per_sample_w && b != cur)) {
-          mbar_wait(bar_wfull, wload & 1);
-          ++wload;
-          cur = b;
+      {
+        // Weight descriptors do not depend on the tile: their low words are tabulated once ((ch, kc, ks) -> s_bdesc) and
+        // the activation descriptor of a stage advances by a constant per K step, so that one MMA issue is a table
+        // load, two adds and the instruction (the issue loop was ~59 instructions per MMA = ~450 cycles of one warp's
+        // dependent issue, tools/gemm_timeline.py, against 72..128 cycles of tensor-pipe time per MMA).
+        const int nent = P.nchunks * P.kchunks * 4;
+        for (int e = lane; e < nent; e += 32) {
+          const int ks = e & 3, kc = (e >> 2) % P.kchunks, ch = (e >> 2) / P.kchunks;
+          const int kglob = kc * P.BK + ks * 16;
+          const uint32_t baddr =
+              w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)(ch * P.NC) * 128u + (kglob & 63) * 2u;
+          s_bdesc[e] = (uint32_t)make_smem_desc_sw128(baddr, 16u, 1024u);
         }
-        for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
-          const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
-          mbar_wait(&bar_accempty[as], aph ^ 1);
-          tc_fence_after();
-          const uint32_t d_tmem = tmem_base + as * 256;
-          const int ncols = min(P.NC, P.Nslice - ch * P.NC);
-          const uint32_t idesc = make_idesc_bf16(128, ncols, MODE == 0 ? 1 : 0, 0);
-          for (int kc = 0; kc < P.kchunks; ++kc) {
-            const uint32_t cit = it + kc, stage = cit % P.S, ph = (cit / P.S) & 1;
-            if (ch == 0) {
-              mbar_wait(&bar_full[stage], ph);
-              tc_fence_after();
-            }
-            const int rows = min(P.BK, P.Cin - (MODE == 0 ? kc : kc % P.kpt) * P.BK);
-            const int ksteps = (rows + 15) >> 4;
-            for (int ks = 0; ks < ksteps; ++ks) {
-              const int kglob = kc * P.BK + ks * 16;
-              const uint64_t adesc =
-                  MODE == 0 ? make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048, (uint32_t)P.BK * 128u, 1024u)
-                            : make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 32, 16u, 1024u);
-              const uint32_t baddr =
-                  w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)(ch * P.NC) * 128u + (kglob & 63) * 2u;
-              const uint64_t bdesc = make_smem_desc_sw128(baddr, 16u, 1024u);
-              umma_bf16(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
-            }
-            if (ch == P.nchunks - 1) umma_commit(&bar_empty[stage]);
+        __syncwarp();
+        const uint32_t desc_hi = (uint32_t)(make_smem_desc_sw128(0u, 16u, 1024u) >> 32);   // SBO, version, swizzle
+        const uint32_t a_lbo = MODE == 0 ? (((uint32_t)P.BK * 128u) >> 4) << 16 : 1u << 16;
+        const uint32_t a_step = MODE == 0 ? 2048u >> 4 : 32u >> 4;
+        uint32_t st0 = 0, ph0 = 0;   // ring position of the tile's first K chunk
+        for (int tile = t_begin; tile < t_end; ++tile) {
+          const int b = MODE == 0 ? tile / P.tiles_per_sample : 0;
+          if (cur < 0 || (P.per_sample_w && b != cur)) {
+            mbar_wait(bar_wfull, wload & 1);
+            ++wload;
+            cur = b;
           }
-          umma_commit(&bar_accfull[as]);
+          uint32_t stage = st0, ph = ph0;
+          for (int ch = 0; ch < P.nchunks; ++ch, ++acc_it) {
+            const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
+            mbar_wait(&bar_accempty[as], aph ^ 1);
+            TL(10, tile * 8 + ch);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem_base + as * 256;
+            const int ncols = min(P.NC, P.Nslice - ch * P.NC);
+            const uint32_t idesc = make_idesc_bf16(128, ncols, MODE == 0 ? 1 : 0, 0);
+            const uint32_t* btab = s_bdesc + ch * P.kchunks * 4;
+            stage = st0; ph = ph0;
+            int kcc = 0;   // channel chunk within the tap (MODE > 0), == kc for 1x1
+            for (int kc = 0; kc < P.kchunks; ++kc) {
+              if (ch == 0) {
+                mbar_wait(&bar_full[stage], ph);
+                TL(11, tile * 8 + kc);
+                tc_fence_after();
+              }
+              const int rows = min(P.BK, P.Cin - kcc * P.BK);
+              const int ksteps = (rows + 15) >> 4;
+              const uint4 bl = *reinterpret_cast<const uint4*>(btab + kc * 4);
+              const uint32_t blo[4] = {bl.x, bl.y, bl.z, bl.w};
+              uint32_t alo = (((ring_addr + stage * kStageBytes) >> 4) & 0x3fffu) | a_lbo;
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks) {
+                if (ks < ksteps && !(P.dbg & 8))
+                  umma_bf16_elect(d_tmem, ((uint64_t)desc_hi << 32) | alo, ((uint64_t)desc_hi << 32) | blo[ks], idesc,
+                                  (kc | ks) != 0 ? 1u : 0u);
+                alo += a_step;
+              }
+              if (ch == P.nchunks - 1) umma_commit_elect(&bar_empty[stage]);
+              if (++stage == (uint32_t)P.S) { stage = 0; ph ^= 1u; }
+              if (MODE != 0 && ++kcc == P.kpt) kcc = 0;
+              if (MODE == 0) ++kcc;
+            }
+            umma_commit_elect(&bar_accfull[as]);
+            TL(12, tile * 8 + ch);
+          }
+          st0 = stage; ph0 = ph;
+          if (MODE == 0 && P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b)
+            umma_commit_elect(bar_wempty);
         }
-        it += P.kchunks;
-        if (MODE == 0 && P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b)
-          umma_commit(bar_wempty);
       }
     }
   } else if (warp >= kWarpStats0) {
@@ -554,8 +605,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         for (int kc = 0; kc < P.kchunks; ++kc, ++it) {
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_full[stage], ph);
+          if (warp == kWarpStats0 && lane == 0) TL(20, tile * 8 + kc);
           const int rows = min(P.BK, P.Cin - kc * P.BK);
-          ln_stat_chunk(ring_addr + stage * kStageBytes, (uint32_t)P.BK * 128u, m, rows, kc == 0, acc);
+          if (!(P.dbg & 2) || kc == 0) ln_stat_chunk(ring_addr + stage * kStageBytes, (uint32_t)P.BK * 128u, m, (P.dbg & 2) ? 0 : rows, kc == 0, acc);
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_empty[stage]);
         }
@@ -564,7 +616,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const float md = sum * P.inv_cin;
         const float var = fmaxf(sq * P.inv_cin - md * md, 0.f);
         const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+        if (warp == kWarpStats0 && lane == 0) TL(21, tile * 8);
         mbar_wait(&bar_stempty[sp], sph ^ 1);
+        if (warp == kWarpStats0 && lane == 0) TL(22, tile * 8);
         const float rstd = 1.0f / sqrtf(var + 1e-5f);
         // epilogue form: y = acc*rstd + (-rstd*mu)*s[o] + t[o]
         s_mu[sp * 128 + m] = (P.ln_type == B200IR_LN_WITHBIAS) ? -rstd * (x0 + md) : 0.f;
@@ -725,7 +779,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         if (ch == 0 && has_ln) {
           const uint32_t sp = tcount & 1, sph = (tcount >> 1) & 1;
+          if (warp == 0 && lane == 0) TL(29, tile * 8 + ch);
           mbar_wait(&bar_stfull[sp], sph);
+          if (warp == 0 && lane == 0) TL(30, tile * 8 + ch);
           nmr = s_mu[sp * 128 + m];
           rstd = s_rstd[sp * 128 + m];
           __syncwarp();
@@ -733,14 +789,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         }
         const uint32_t as = acc_it & 1, aph = (acc_it >> 1) & 1;
         mbar_wait(&bar_accfull[as], aph);
+        if (warp == 0 && lane == 0) TL(31, tile * 8 + ch);
         tc_fence_after();
         if (lane == 0) bulk_wait_read<0>();   // the stores of the previous item have drained the staging buffer
         __syncwarp();
+        if (warp == 0 && lane == 0) TL(32, tile * 8 + ch);
         if (HAS_RES && g_hi > g_lo) mbar_wait(&rbar[acc_it & 1], (acc_it >> 1) & 1);
         const uint32_t tbase = tmem_base + as * 256 + ((uint32_t)(quad * 32) << 16);
         const uint32_t rsrc = smem_u32(resb) + (uint32_t)(acc_it & 1) * P.gpw * 1024u + lane * 2u;
         const uint32_t sdst = smem_u32(stg) + lane * 2u;
-        for (int g = g_lo; g < g_hi; ++g) {
+        for (int g = g_lo; g < g_hi && !(P.dbg & 4); ++g) {
           uint32_t r[16];
           tmem_ld_32x16(tbase + g * 16, r);
           const float4* stp = reinterpret_cast<const float4*>(&s_st[nbase + g * 16]);  // (s,t) pairs of 2 columns
@@ -763,14 +821,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             st_shared_bf16(d0 + j * 64u, v);
           }
         }
+        if (warp == 0 && lane == 0) TL(34, tile * 8 + ch);
         tc_fence_before();
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&bar_accempty[as]);
-          for (int g = g_lo; g < g_hi; ++g)
-            tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
+          if (warp == 0) TL(35, tile * 8 + ch);
+          if (!(P.dbg & 1))
+            for (int g = g_lo; g < g_hi; ++g)
+              tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
           bulk_commit();
+          if (warp == 0) TL(36, tile * 8 + ch);
         }
       }
     }
@@ -944,6 +1006,18 @@ extern "C" int b200ir_pack_conv1x1_t(const float* w, int Cin, int Cout, void* wp
   return check_launch("pack_conv1x1_t");
 }
 
+#ifdef B200IR_TIMELINE
+extern "C" int b200ir_debug_timeline(unsigned long long* out, int max_pairs) {
+  cudaDeviceSynchronize();
+  const int n = 4 * 4096;
+  if (out && max_pairs >= n) cudaMemcpyFromSymbol(out, b200ir::g_tl, (size_t)n * 16);
+  void* p = nullptr;
+  cudaGetSymbolAddress(&p, b200ir::g_tl);
+  cudaMemset(p, 0, (size_t)n * 16);
+  return n;
+}
+#endif
+
 namespace b200ir {
 int gemm_stream_launch(const void* x, int64_t x_bs, const void* wp, int Bw, const float* st, int ln_type,
                        const void* res, int64_t res_bs, int res_dt, void* y, int64_t y_bs, int y_dt, int B, int Cin,
@@ -1037,7 +1111,9 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   P.kc64 = g.Kpad / 64; P.S = g.S;
   P.per_sample_w = (Bw > 1) ? 1 : 0;
   P.inv_cin = 1.0f / (float)Cin;
+  B200IR_UNSUPPORTED(mode4 || g.nchunks * g.kchunks * 4 <= 256, "gemm_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
   P.kpt = g.kchunks; P.H = P.W = P.TW = P.TWs = P.TH = P.tiles_x = P.tiles_y = 0;
+  { const char* de = getenv("B200IR_GEMM_DBG"); P.dbg = de ? atoi(de) : 0; }
 
   int sms = 148;
   int gx = sms / g.nslices;
@@ -1168,8 +1244,9 @@ extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const voi
   P.total_tiles = B * P.tiles_x * P.tiles_y;
   P.BK = g.BK; P.kchunks = g.kchunks; P.kpt = g.kpt; P.Nslice = g.Nslice; P.NC = g.NC; P.nchunks = g.nchunks;
   P.nbox = g.nbox; P.kc64 = g.Kpad / 64; P.S = g.S;
+  B200IR_UNSUPPORTED(g.nchunks * g.kchunks * 4 <= 256, "conv3x3_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
   P.per_sample_w = 0;
-  P.inv_cin = 0.f;
+  P.inv_cin = 0.f; P.dbg = 0;
   int gx = 148 / g.nslices;
   if (gx < 1) gx = 1;
   if (gx > P.total_tiles) gx = P.total_tiles;

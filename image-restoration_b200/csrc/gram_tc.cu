@@ -82,7 +82,7 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const GramTcParams P) {
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
+    {   // whole warp, convergent; the issuing lane is elected per instruction (tc_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, d, 0, 0);
       const uint32_t ring_addr = smem_u32(ring);
       for (int i = 0; i < nchunks; ++i) {
@@ -95,13 +95,13 @@ gram_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const GramTcParams P) {
           const uint64_t dq = make_smem_desc_sw128(qa + ks * 32, 16u, 1024u);
           const uint64_t dk = make_smem_desc_sw128(ka + ks * 32, 16u, 1024u);
           const uint32_t acc = (i | ks) != 0 ? 1u : 0u;
-          umma_bf16(tmem_base + colD1, dq, dk, idesc, acc);
-          umma_bf16(tmem_base + colD2, dq, dq, idesc, acc);
-          if (P.three) umma_bf16(tmem_base + colD3, dk, dk, idesc, acc);
+          umma_bf16_elect(tmem_base + colD1, dq, dk, idesc, acc);
+          umma_bf16_elect(tmem_base + colD2, dq, dq, idesc, acc);
+          if (P.three) umma_bf16_elect(tmem_base + colD3, dk, dk, idesc, acc);
         }
-        umma_commit(&bar_empty[stage]);
+        umma_commit_elect(&bar_empty[stage]);
       }
-      umma_commit(bar_acc);
+      umma_commit_elect(bar_acc);
     }
   } else {
     // epilogue: thread <-> TMEM lane (row of D)

@@ -35,8 +35,12 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                "r"(bytes)
                : "memory");
 }
+#ifndef B200IR_MBAR_MODE
+#define B200IR_MBAR_MODE 0
+#endif
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
+#if B200IR_MBAR_MODE == 0
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
       "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
@@ -44,6 +48,24 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "=r"(ok)
       : "r"(smem_u32(bar)), "r"(parity), "r"(0x989680u)   // suspend-time hint: sleep in hardware, do not spin
       : "memory");
+#elif B200IR_MBAR_MODE == 1
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+#else
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  if (!ok) __nanosleep(B200IR_MBAR_MODE);
+#endif
   return ok != 0;
 }
 // Bounded wait: a protocol bug traps (launch error) instead of hanging the GPU box.
@@ -125,6 +147,19 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
+}
+
+// Whole-warp forms: every lane runs the (warp-uniform) issue loop and ONE elected lane executes the instruction.  With the
+// loop under `if (lane == 0)` the compiler cannot prove uniformity: it builds the descriptors in vector registers, moves
+// them with 7 R2UR per MMA and wraps each UTCHMMA in an elect/branch waterfall -- ~370 cycles per MMA issue measured
+// (tools/gemm_timeline.py), 3-5x the tensor-pipe time of a 128 x N x 16 MMA, which made the issuer thread the critical
+// path of every GEMM here.
+__device__ __forceinline__ void umma_bf16_elect(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                uint32_t accumulate) {
+  if (elect_one()) umma_bf16(tmem_d, desc_a, desc_b, idesc, accumulate);
+}
+__device__ __forceinline__ void umma_commit_elect(uint64_t* bar) {
+  if (elect_one()) umma_commit(bar);
 }
 
 // 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread l <-> lane base+l)

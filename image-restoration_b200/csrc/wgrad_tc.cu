@@ -81,7 +81,7 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
+    {   // whole warp, convergent; the issuing lane is elected per instruction (tc_common.cuh)
       const uint32_t idesc = make_idesc_bf16(128, P.Ntile, 0, 0);
       const uint32_t ring_addr = smem_u32(ring);
       for (int i = 0; i < nchunks; ++i) {
@@ -93,11 +93,11 @@ wgrad_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         for (int ks = 0; ks < 4; ++ks) {
           const uint64_t da = make_smem_desc_sw128(aa + ks * 32, 16u, 1024u);
           const uint64_t dx = make_smem_desc_sw128(xa + ks * 32, 16u, 1024u);
-          umma_bf16(tmem_base, da, dx, idesc, (i | ks) != 0 ? 1u : 0u);
+          umma_bf16_elect(tmem_base, da, dx, idesc, (i | ks) != 0 ? 1u : 0u);
         }
-        umma_commit(&bar_empty[stage]);
+        umma_commit_elect(&bar_empty[stage]);
       }
-      umma_commit(bar_acc);
+      umma_commit_elect(bar_acc);
     }
   } else {
     // epilogue: thread <-> TMEM lane = row of the dy slab
