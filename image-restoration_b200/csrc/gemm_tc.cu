@@ -1053,12 +1053,12 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
 
   // Deep levels (Cin >= 384: level 4 and the level-3/4 project_out): the weight matrix needs 3..15 resident slices, every
   // slice re-reads the activations and issues narrow MMAs -> stream both operands instead (gemm_stream_tc.cu; measured
-  // 384->2042 103 -> 62 us, 1021->384 84 -> 39 us).  With short K the streamed weights cost more L2 traffic than the
+  // 384->2042 103 -> 62 us, 1021->384 84 -> 39 us; three resident slices still win: 510->192 at 64x64 57 vs 82 us).  With short K the streamed weights cost more L2 traffic than the
   // output is worth, so everything else stays on the resident-weight kernel.  B200IR_GEMM_STREAM=0 / 1 forces never /
   // always (tests, A/B runs).
   {
     const char* se = getenv("B200IR_GEMM_STREAM");
-    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && (g.nslices >= 3 || (!res && g.nslices >= 2)));
+    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && (g.nslices >= 4 || (!res && g.nslices >= 2)));
     if (!mode4 && want && Cin >= 64)
       return gemm_stream_launch(x, x_bstride, wp, Bw, st, ln_type, res, res_bstride, res_dtype, y, y_bstride, y_dtype,
                                 B, Cin, Cout, HW, g.Kpad, g.Nrows, (cudaStream_t)stream);
