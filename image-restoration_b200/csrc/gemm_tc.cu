@@ -121,6 +121,10 @@ bool gemm_tc_geometry(int Cin, int Cout, GemmGeom* g, int taps = 1, bool has_res
     g->Nslice = ceil_to((Npad + g->nslices - 1) / g->nslices, 16);
     g->nchunks = (g->Nslice + 255) / 256;
     g->NC = ceil_to((g->Nslice + g->nchunks - 1) / g->nchunks, 16);
+    // the 16-column groups of a chunk are dealt to 4 epilogue warps per TMEM quadrant: prefer chunks whose group count
+    // is a multiple of 4 (288 = 192 + 96 -> busiest warp handles 5 groups per tile instead of 6 with 144 + 144)
+    if (g->nchunks > 1 && ceil_to(g->NC, 64) <= 256 && ceil_to(g->NC, 64) * (g->nchunks - 1) < g->Nslice)
+      g->NC = ceil_to(g->NC, 64);
     g->nbox = 16;
     for (int nb = 256; nb >= 16; nb -= 16)
       if (g->Nslice % nb == 0) {
@@ -791,7 +795,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         mbar_wait(&bar_accfull[as], aph);
         if (warp == 0 && lane == 0) TL(31, tile * 8 + ch);
         tc_fence_after();
-        if (lane == 0) bulk_wait_read<0>();   // the stores of the previous item have drained the staging buffer
+        if (elect_one()) bulk_wait_read<0>();   // the stores of the previous item have drained the staging buffer
         __syncwarp();
         if (warp == 0 && lane == 0) TL(32, tile * 8 + ch);
         if (HAS_RES && g_hi > g_lo) mbar_wait(&rbar[acc_it & 1], (acc_it >> 1) & 1);
@@ -825,18 +829,18 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         tc_fence_before();
         fence_proxy_async();
         __syncwarp();
-        if (lane == 0) {
-          mbar_arrive(&bar_accempty[as]);
-          if (warp == 0) TL(35, tile * 8 + ch);
-          if (!(P.dbg & 1))
-            for (int g = g_lo; g < g_hi; ++g)
-              tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
-          bulk_commit();
-          if (warp == 0) TL(36, tile * 8 + ch);
-        }
+        // convergent issue, one elected lane per instruction (the same lane every time: bulk groups are per thread);
+        // under `if (lane == 0)` every UTMASTG sat in an R2UR / branch waterfall (~200 cycles per store)
+        if (elect_one()) mbar_arrive(&bar_accempty[as]);
+        if (warp == 0) TL(35, tile * 8 + ch);
+        if (!(P.dbg & 1))
+          for (int g = g_lo; g < g_hi; ++g)
+            if (elect_one()) tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
+        if (elect_one()) bulk_commit();
+        if (warp == 0) TL(36, tile * 8 + ch);
       }
     }
-    if (lane == 0) bulk_wait<0>();
+    if (elect_one()) bulk_wait<0>();
   } else {
     // ===== epilogue: warp w <-> TMEM lane quadrant w%4, 16-column groups g = w/4, w/4+4, ... =====
     const int quad = warp & 3, wq = warp >> 2;

@@ -127,6 +127,39 @@ def test_mdta_core(b200ir, dtype, C, heads, H, W):
         assert rel_err(y, ref) < 6e-3
 
 
+@pytest.mark.parametrize("B,C,heads,nslab", [(16, 384, 8, 2), (16, 192, 4, 4), (16, 96, 1, 9), (3, 80, 2, 3),
+                                            (2, 24, 1, 1), (5, 112, 1, 2), (16, 48, 1, 18)])
+@pytest.mark.parametrize("packed", [False, True])
+def test_mdta_softmax_fold_shapes(b200ir, B, C, heads, nslab, packed):
+    """Slab reduce + normalise + temperature softmax + W_out fold (Restormer.py:121-131) over every row-block variant of
+    the register-tiled fold kernel (64 / 32 / 16 rows per CTA) and head dims that are not multiples of 16."""
+    from b200ir import ops
+    d = C // heads
+    g = torch.Generator().manual_seed(C + heads)
+    parts = torch.rand(B, heads, nslab, d * d + 2 * d, generator=g) - 0.3
+    parts[..., d * d:] = parts[..., d * d:].abs() + 0.05          # squared norms are positive
+    temp = 0.5 + torch.rand(heads, generator=g)
+    wout = (torch.rand(C, C, generator=g) - 0.5) / C ** 0.5
+    tot = parts.double().sum(2)
+    G = tot[..., :d * d].reshape(B, heads, d, d)
+    nq = tot[..., d * d:d * d + d].sqrt().clamp_min(1e-12)
+    nk = tot[..., d * d + d:].sqrt().clamp_min(1e-12)
+    attn = (G / (nq[..., :, None] * nk[..., None, :]) * temp.double()[None, :, None, None]).softmax(-1)
+    m = torch.zeros(B, C, C, dtype=torch.float64)
+    for h in range(heads):
+        m[:, :, h * d:(h + 1) * d] = wout.double()[None, :, h * d:(h + 1) * d] @ attn[:, h]
+    with torch.no_grad():
+        out, a = ops.mdta_softmax_fold(dev(parts), dev(temp), dev(wout), want_attn=True, packed=packed)
+    assert (a.cpu().double() - attn).abs().max() <= 2e-6
+    if packed:
+        o = out.float().cpu()
+        assert (o[:, :C, :C].double() - m).abs().max() <= 4e-3 * m.abs().max()     # bf16 operand
+        assert o[:, C:, :].abs().max() == 0 if o.shape[1] > C else True            # zero padding rows / columns
+        assert o[:, :, C:].abs().max() == 0 if o.shape[2] > C else True
+    else:
+        assert (out.cpu().double() - m).abs().max() <= 2e-6
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("mode,Cin,Cout,H,W", [("none", 3, 48, 16, 24), ("unshuffle", 48, 24, 16, 16),
                                                ("shuffle", 96, 192, 8, 12), ("none", 96, 3, 20, 18),
