@@ -804,7 +804,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const uint32_t sdst = smem_u32(stg) + lane * 2u;
         for (int g = g_lo; g < g_hi && !(P.dbg & 4); ++g) {
           uint32_t r[16];
+#ifdef B200IR_EPI_NO_TMEMLD   // A/B timing builds only (wrong results): which part of the epilogue slows the tensor pipe
+#pragma unroll
+          for (int j = 0; j < 16; ++j) r[j] = (uint32_t)(g + j);
+#else
           tmem_ld_32x16(tbase + g * 16, r);
+#endif
           const float4* stp = reinterpret_cast<const float4*>(&s_st[nbase + g * 16]);  // (s,t) pairs of 2 columns
           float4 st4[8];
 #pragma unroll
@@ -822,7 +827,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             const float ty = (j & 1) ? st4[j >> 1].w : st4[j >> 1].y;
             float v = has_ln ? fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, sx, ty)) : __uint_as_float(r[j]) + ty;
             if (HAS_RES) v += rr[j];
+#ifdef B200IR_EPI_NO_STS
+            if (v == 1.2345e30f) st_shared_bf16(d0 + j * 64u, v);
+#else
             st_shared_bf16(d0 + j * 64u, v);
+#endif
           }
         }
         if (warp == 0 && lane == 0) TL(34, tile * 8 + ch);
