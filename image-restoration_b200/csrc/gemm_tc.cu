@@ -821,18 +821,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           }
           tmem_ld_wait();
           const uint32_t d0 = sdst + (uint32_t)(g - g_lo) * 1024u;
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float sx = (j & 1) ? st4[j >> 1].z : st4[j >> 1].x;
-            const float ty = (j & 1) ? st4[j >> 1].w : st4[j >> 1].y;
-            float v = has_ln ? fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, sx, ty)) : __uint_as_float(r[j]) + ty;
-            if (HAS_RES) v += rr[j];
+          // two copies of the loop instead of a per-element select: with the select the compiler issued BOTH arithmetic
+          // forms under opposite predicates, and these kernels are issue-bound (ncu r1n: 74-79 % issue slots busy)
+#define B200IR_EPI_ELEMS(EXPR)                                                       \
+  _Pragma("unroll") for (int j = 0; j < 16; ++j) {                                   \
+    const float sx = (j & 1) ? st4[j >> 1].z : st4[j >> 1].x;                         \
+    const float ty = (j & 1) ? st4[j >> 1].w : st4[j >> 1].y;                         \
+    float v = (EXPR);                                                                 \
+    (void)sx;                                                                         \
+    if (HAS_RES) v += rr[j];                                                          \
+    B200IR_EPI_STORE(d0 + j * 64u, v);                                                \
+  }
 #ifdef B200IR_EPI_NO_STS
-            if (v == 1.2345e30f) st_shared_bf16(d0 + j * 64u, v);
+#define B200IR_EPI_STORE(a, v) if ((v) == 1.2345e30f) st_shared_bf16((a), (v))
 #else
-            st_shared_bf16(d0 + j * 64u, v);
+#define B200IR_EPI_STORE(a, v) st_shared_bf16((a), (v))
 #endif
+          if (HAS_RES) {   // residual variants: the split costs registers (spills at 704 threads), keep the select
+            B200IR_EPI_ELEMS(has_ln ? fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, sx, ty)) : __uint_as_float(r[j]) + ty)
+          } else if (has_ln) {
+            B200IR_EPI_ELEMS(fmaf(__uint_as_float(r[j]), rstd, fmaf(nmr, sx, ty)))
+          } else {
+            B200IR_EPI_ELEMS(__uint_as_float(r[j]) + ty)
           }
+#undef B200IR_EPI_ELEMS
+#undef B200IR_EPI_STORE
         }
         if (warp == 0 && lane == 0) TL(34, tile * 8 + ch);
         tc_fence_before();
