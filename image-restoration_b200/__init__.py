@@ -4,7 +4,8 @@ from .modules import (Attention, BiasFree_LayerNorm, CrossAttention, GatedMDTA, 
                       Restormer, TransformerBlock, Upsample, WithBias_LayerNorm)
 
 from .dropin import accelerate  # noqa: F401
+from .autograd_ops import invalidate_caches  # noqa: F401
 from .training import AdamW, GraphedForward, GraphedTrainStep, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
 
-__all__ = ["accelerate", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+__all__ = ["accelerate", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
            "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -13,6 +13,7 @@ F32, BF16 = 0, 1
 LN_NONE, LN_WITHBIAS, LN_BIASFREE = 0, 1, 2
 SHUFFLE_NONE, UNSHUFFLE2, SHUFFLE2 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+GEMM_AUTO, GEMM_RESIDENT, GEMM_STREAM, GEMM_RESIDENT_CH = 0, 1, 2, 3
 
 _vp, _i64, _i, _sz, _f = C.c_void_p, C.c_int64, C.c_int, C.c_size_t, C.c_float
 
@@ -45,6 +46,7 @@ SIGNATURES = {
     "b200ir_pack_conv3x3": [_vp, _vp, _i, _i, _vp, _vp, _vp],
     "b200ir_conv3x3_tc_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_gemm_tc_fwd": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _vp],
+    "b200ir_gemm_tc_fwd_ex": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _i, _vp],
     "b200ir_ln_fwd": [_vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_ln_bwd_nparts": [_i, _i64],
     "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i64, _vp, _i, _i, _i,
@@ -61,6 +63,7 @@ SIGNATURES = {
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
     "b200ir_l1_loss_bwd": [_vp, _i, _vp, _i, _i64, _vp, _vp, _i, _vp],
     "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],
+    "b200ir_adamw_step_ex": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _i, _vp, _f, _vp],
 }
 
 

@@ -37,6 +37,14 @@ def bump_param_epoch():
     PARAM_EPOCH += 1
 
 
+def invalidate_caches():
+    """Drop every packed bf16 weight cache (exported as ``b200ir.invalidate_caches``).  The caches key on
+    ``(data_ptr, tensor._version)``; in-place writes through ``p.data`` (EMA ``p.data.mul_().add_()``, re-initialisation
+    ``w.data.normal_()``, hand-written optimizers) change neither, so call this after such an update.  Optimizers that
+    update ``p`` itself (torch.optim.*, including the fused / foreach AdamW) bump ``_version`` and need nothing."""
+    bump_param_epoch()
+
+
 def _sig(*ts):
     return (PARAM_EPOCH,) + tuple((t.data_ptr(), t._version) if t is not None else None for t in ts)
 
@@ -120,11 +128,15 @@ class Prepacker:
             arr = (L.PackDesc * len(descs))(*descs)
             host = torch.frombuffer(bytearray(bytes(arr)), dtype=torch.uint8)
             self.descs_dev = host.to(self.entries[0][2][0].device)
-        self.ptrs = tuple(e[2][0].data_ptr() for e in self.entries)
+        self.ptrs = self._pointers()
+
+    def _pointers(self):
+        return tuple(t.data_ptr() if t is not None else 0 for e in self.entries for t in e[2])
 
     def valid(self):
-        """Parameters still live where the table says (no .to()/.cuda()/re-flattening since construction)."""
-        return self.descs_dev is not None and self.ptrs == tuple(e[2][0].data_ptr() for e in self.entries)
+        """EVERY parameter the table captured (weights, biases, LayerNorm weight / bias) still lives where the
+        descriptors say (no .to()/.cuda()/re-flattening since construction)."""
+        return self.descs_dev is not None and self.ptrs == self._pointers()
 
     def run(self):
         if not self.valid():
@@ -279,6 +291,30 @@ class _LnConv1x1(torch.autograd.Function):
         del xn
         dres = dy if ctx.has_res else None
         return (dx, dw.view(w.shape).to(w.dtype), db, dlw, dlb, dres, None, None, None, None)
+
+
+class _LayerNorm(torch.autograd.Function):
+    """Stand-alone channel LayerNorm (Restormer.py:60-70 called outside a TransformerBlock, e.g. the 18 norms
+    dropin.accelerate() adopts inside MoCE-IR's decoder)."""
+
+    @staticmethod
+    def forward(ctx, x, ln_w, ln_b, ln_type):
+        ctx.save_for_backward(x, ln_w, ln_b)
+        ctx.ln_type = ln_type
+        return ops.ln_fwd(x, ln_type, _p(ln_w), _p(ln_b))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, ln_w, ln_b = ctx.saved_tensors
+        dx, dlw, dlb = ops.ln_bwd(x, _cg(dy).to(x.dtype), ctx.ln_type, _p(ln_w), None, _p(ln_b))
+        return dx, dlw.to(ln_w.dtype), (dlb.to(ln_b.dtype) if ln_b is not None else None), None
+
+
+def layernorm(x, ln_type, ln_w, ln_b):
+    x = _cg(x)
+    if _needs_grad(x, ln_w, ln_b):
+        return _LayerNorm.apply(x, ln_w, ln_b, ln_type)
+    return ops.ln_fwd(x, ln_type, _p(ln_w), _p(ln_b))
 
 
 class _DwConv(torch.autograd.Function):

@@ -648,7 +648,12 @@ __global__ void l1_loss_bwd_kernel(const void* __restrict__ pred, int p_dt, cons
 // =====================================================================================================
 __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                              float* __restrict__ v, int64_t n, float lr, float beta1, float beta2, float eps, float wd,
-                             float bc1, float bc2_sqrt, float gscale, const int* __restrict__ step_dev) {
+                             float bc1, float bc2_sqrt, float gscale, const int* __restrict__ step_dev,
+                             const float* __restrict__ hyper_dev) {
+  if (hyper_dev) {  // learning rate / weight decay live on the device: a scheduler can change them under a captured graph
+    lr = hyper_dev[0];
+    wd = hyper_dev[1];
+  }
   if (step_dev) {  // CUDA-graph replay: the step count lives on the device (b200ir_adamw_step, step_dev != NULL)
     const double st = (double)step_dev[0];
     bc1 = (float)(1.0 - pow((double)beta1, st));
@@ -691,7 +696,7 @@ extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int 
   const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
 #define B200IR_LN_FWD(DT)                                                                                        \
-  ln_fwd_kernel<DT><<<grid_1d(ntiles, 1, 148 * 16), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w, \
+  ln_fwd_kernel<DT><<<grid_1d(ntiles, 1, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, ln_type, ln_w, \
                                                                                    ln_b, y, y_bstride, y_dtype, C, HW,  \
                                                                                    tps, ntiles)
   if (x_dtype == y_dtype && x_dtype == B200IR_BF16) B200IR_LN_FWD(B200IR_BF16);
@@ -704,7 +709,7 @@ extern "C" int b200ir_ln_fwd(const void* x, int64_t x_bstride, int x_dtype, int 
 extern "C" int b200ir_ln_bwd_nparts(int B, int64_t HW) {
   if (B <= 0 || HW <= 0) return B200IR_E_BADARG;
   const int64_t ntiles = (int64_t)B * ((HW + LN_PX - 1) / LN_PX);
-  return grid_1d(ntiles, 1, 148 * 4);
+  return grid_1d(ntiles, 1, num_sms() * 4);
 }
 
 extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, int64_t g_bstride,
@@ -729,7 +734,7 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   const bool same = x_dtype == g_dtype && x_dtype == dx_dtype && (!res || res_dtype == x_dtype);
   auto even = [](const void* q, int64_t bs) { return !q || (((uintptr_t)q & 3) == 0 && (bs & 1) == 0); };
   // (tiny planes keep the 32-pixel tiles: twice as many CTAs to spread the channel loop over)
-  if (same && x_dtype == B200IR_BF16 && (HW & 1) == 0 && (int64_t)B * ((HW + 63) / 64) >= 2 * 148 && even(x, x_bstride) && even(g, g_bstride) &&
+  if (same && x_dtype == B200IR_BF16 && (HW & 1) == 0 && (int64_t)B * ((HW + 63) / 64) >= 2 * num_sms() && even(x, x_bstride) && even(g, g_bstride) &&
       even(res, res_bstride) && even(dx, dx_bstride) && even(xn, xn_bstride)) {
     const int tps2 = (int)((HW + 63) / 64);
     ln_bwd_bf16x2_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
@@ -747,7 +752,7 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
 extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride,
                                       b200ir_stream_t stream) {
   B200IR_CHECK_ARG(in && out && n > 0 && K > 0 && stride >= K, "reduce_partials: bad args");
-  reduce_partials_kernel<<<grid_1d(K, 32, 148 * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
+  reduce_partials_kernel<<<grid_1d(K, 32, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
   return check_launch("reduce_partials");
 }
 
@@ -768,7 +773,7 @@ static void wgrad_split(int B, int M, int N, int64_t HW, int per_sample, int* ns
   int mt, nt, ntile;
   wgrad_tc_tiles(M, N, &mt, &nt, &ntile);
   const int64_t tiles = (int64_t)mt * nt * (per_sample ? B : 1);
-  int64_t want = (2 * 148 + tiles - 1) / tiles;
+  int64_t want = (2 * num_sms() + tiles - 1) / tiles;
   if (want > 64) want = 64;
   if (want > total) want = total;
   if (want < 1) want = 1;
@@ -854,7 +859,7 @@ extern "C" int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, i
   B200IR_CHECK_ARG(mode != B200IR_SHUFFLE2 || C % 4 == 0, "pixel_shuffle: PixelShuffle(2) needs C%%4==0");
   B200IR_CHECK_ARG(mode != B200IR_UNSHUFFLE2 || (H % 2 == 0 && W % 2 == 0), "pixel_shuffle: needs even H,W");
   const int64_t n = (int64_t)C * H * W;
-  pixel_shuffle_kernel<<<dim3((unsigned)grid_1d(n, 256, 148 * 8), (unsigned)B), 256, 0, (cudaStream_t)stream>>>(
+  pixel_shuffle_kernel<<<dim3((unsigned)grid_1d(n, 256, num_sms() * 8), (unsigned)B), 256, 0, (cudaStream_t)stream>>>(
       x, x_bstride, y, y_bstride, dtype, C, H, W, mode);
   return check_launch("pixel_shuffle");
 }
@@ -874,7 +879,7 @@ extern "C" int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* 
                                   const float* gscale, void* grad, int grad_dtype, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(pred && target && gscale && grad && n > 0, "l1_loss_bwd: bad args");
   B200IR_CHECK_ARG(dtype_ok(pred_dtype) && dtype_ok(target_dtype) && dtype_ok(grad_dtype), "l1_loss_bwd: bad dtype");
-  l1_loss_bwd_kernel<<<grid_1d(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, target_dtype,
+  l1_loss_bwd_kernel<<<grid_1d(n, 256, num_sms() * 8), 256, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, target_dtype,
                                                                                 n, gscale, 1.0f / (float)n, grad,
                                                                                 grad_dtype);
   return check_launch("l1_loss_bwd");
@@ -883,17 +888,26 @@ extern "C" int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* 
 extern "C" int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
                                  float beta2, float eps, float weight_decay, int step, int* step_dev, float grad_scale,
                                  b200ir_stream_t stream) {
+  return b200ir_adamw_step_ex(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, step, step_dev, 1, nullptr, grad_scale,
+                              stream);
+}
+
+extern "C" int b200ir_adamw_step_ex(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1,
+                                    float beta2, float eps, float weight_decay, int step, int* step_dev, int tick,
+                                    const float* hyper_dev, float grad_scale, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(p && g && m && v && n > 0 && (step >= 1 || step_dev), "adamw_step: bad args");
   double bc1 = 1.0, bc2 = 1.0;
   if (step_dev) {  // ++*step_dev on the stream, then the update reads it: replayable inside a CUDA graph
-    counter_inc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(step_dev);
-    int rc = check_launch("adamw_tick");
-    if (rc) return rc;
+    if (tick) {
+      counter_inc_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(step_dev);
+      int rc = check_launch("adamw_tick");
+      if (rc) return rc;
+    }
   } else {
     bc1 = 1.0 - pow((double)beta1, (double)step);
     bc2 = 1.0 - pow((double)beta2, (double)step);
   }
-  adamw_kernel<<<grid_1d(n, 256, 148 * 8), 256, 0, (cudaStream_t)stream>>>(
-      p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale, step_dev);
+  adamw_kernel<<<grid_1d(n, 256, num_sms() * 8), 256, 0, (cudaStream_t)stream>>>(
+      p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, (float)bc1, (float)sqrt(bc2), grad_scale, step_dev, hyper_dev);
   return check_launch("adamw_step");
 }

@@ -71,6 +71,12 @@ __device__ __forceinline__ float warp_max(float v) {
   return v;
 }
 
+// SM count of the CURRENT device (one cudaDeviceGetAttribute per device, cached): grids are sized in multiples of it
+int num_sms();
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (function, device): the attribute is per device, a
+// process-wide std::call_once would leave a second GPU of the same process at the 48 KB default
+void ensure_dyn_smem(const void* func, int bytes);
+
 inline int dtype_size(int dt) { return dt == B200IR_BF16 ? 2 : 4; }
 inline bool dtype_ok(int dt) { return dt == B200IR_F32 || dt == B200IR_BF16; }
 

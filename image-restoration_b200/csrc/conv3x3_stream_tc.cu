@@ -177,10 +177,7 @@ int conv3x3_stream_launch(const void* x, int64_t x_bs, const void* wp, const flo
     set_error("conv3x3_stream: too many pixel tiles (%lld)", (long long)tiles);
     return B200IR_E_UNSUPPORTED;
   }
-  static std::once_flag once;
-  std::call_once(once, [] {
-    cudaFuncSetAttribute(conv3x3_stream_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  });
+  ensure_dyn_smem((const void*)conv3x3_stream_tc_kernel, 227 * 1024);
   conv3x3_stream_tc_kernel<<<dim3((unsigned)nt, (unsigned)tiles), kCsThreads, smem, stream>>>(tmX, tmW, P);
   return check_launch("conv3x3_stream_tc");
 }

@@ -184,7 +184,7 @@ gelu_gate_bwd_tile_kernel(const void* __restrict__ t, int64_t t_bs, const float*
 
 static int dw_nsplit(int B, int C, int H, int W) {
   const DwTile T = dw_tile(H, W);
-  int64_t want = (8 * 148 + (int64_t)B * C - 1) / ((int64_t)B * C);
+  int64_t want = (8 * num_sms() + (int64_t)B * C - 1) / ((int64_t)B * C);
   if (want > T.ntiles) want = T.ntiles;
   if (want > 256) want = 256;
   if (want < 1) want = 1;

@@ -304,7 +304,11 @@ void dw_bwd_tma_tiles(int H, int W, int* TW, int* TH, int* nxg, int* nstrips, in
 }
 
 bool dw_bwd_tma_shape_ok(int H, int W) {
+#ifdef B200IR_AB
   static const bool small_ok = !(getenv("B200IR_DW_SMALL") && getenv("B200IR_DW_SMALL")[0] == '0');   // A/B switch
+#else
+  const bool small_ok = true;
+#endif
   return (((W == 16 || W == 32) && small_ok) || (W % 8 == 0 && W >= 64)) && H >= 8;
 }
 
@@ -339,14 +343,11 @@ int dw_bwd_tma_launch(const void* x, int64_t x_bs, const void* g, int64_t g_bs, 
   const size_t stage = plane * (GATE ? 2 : 1);
   P.S = GATE ? 2 : 3;
   const size_t smem = stage * P.S + 256;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    cudaFuncSetAttribute(dw_bwd_tma_kernel<GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  });
+  ensure_dyn_smem((const void*)dw_bwd_tma_kernel<GATE>, 200 * 1024);
   int ctas_per_sm = resident_ctas(dw_bwd_tma_kernel<GATE>, 128, smem);   // exactly the resident CTAs (static contiguous ranges; registers are the limit here)
   if (ctas_per_sm > 8) ctas_per_sm = 8;
   if (ctas_per_sm < 1) ctas_per_sm = 1;
-  int64_t grid = 148ll * ctas_per_sm;
+  int64_t grid = (int64_t)num_sms() * ctas_per_sm;
   if (grid > P.nitems) grid = P.nitems;
   dw_bwd_tma_kernel<GATE><<<(unsigned)grid, 128, smem, st>>>(tm, P);
   return check_launch(GATE ? "gelu_gate_bwd_tma" : "dwconv3x3_wgrad_tma");

@@ -277,16 +277,13 @@ int dwconv_tma_launch(const void* x, int64_t x_bs, const float* w, const float* 
   const size_t stage = plane * (GATE ? 2 : 1);
   P.S = GATE ? B200IR_DW_GATE_STAGES : 3;
   const size_t smem = stage * P.S + 256;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    cudaFuncSetAttribute(dwconv_tma_kernel<GATE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-  });
+  ensure_dyn_smem((const void*)dwconv_tma_kernel<GATE>, 200 * 1024);
   // static contiguous ranges: the grid must be exactly what is resident at once (registers limit the gated kernel to
   // 4 CTAs per SM although 5 would fit in shared memory -- a fifth "wave" of 148 CTAs ran alone at quarter occupancy)
   int ctas_per_sm = resident_ctas(dwconv_tma_kernel<GATE>, FW_THREADS, smem);
   if (ctas_per_sm > 8) ctas_per_sm = 8;
   if (ctas_per_sm < 1) ctas_per_sm = 1;
-  int64_t grid = 148ll * ctas_per_sm;
+  int64_t grid = (int64_t)num_sms() * ctas_per_sm;
   if (grid > P.nitems) grid = P.nitems;
   dwconv_tma_kernel<GATE><<<(unsigned)grid, FW_THREADS, smem, st>>>(tm, P);
   return check_launch(GATE ? "dwconv3x3_gelu_gate_tma" : "dwconv3x3_tma");

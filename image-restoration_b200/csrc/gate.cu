@@ -49,7 +49,7 @@ sigmoid_gate_bwd_kernel(const void* __restrict__ u, int64_t u_bs, const void* __
 
 static inline int gate_grid(int64_t n) {
   int64_t b = (n + 255) / 256;
-  return (int)(b < 148 * 16 ? (b < 1 ? 1 : b) : 148 * 16);
+  return (int)(b < num_sms() * 16 ? (b < 1 ? 1 : b) : num_sms() * 16);
 }
 
 }  // namespace b200ir

@@ -159,7 +159,7 @@ extern "C" int b200ir_copy_cast(const void* x, int64_t x_bstride, int x_dtype, v
   B200IR_CHECK_ARG(x && y && B > 0 && CHW > 0 && B <= 65535, "copy_cast: bad args");
   B200IR_CHECK_ARG(dtype_ok(x_dtype) && dtype_ok(y_dtype), "copy_cast: bad dtype");
   int64_t blocks = (CHW + 255) / 256;
-  if (blocks > 148 * 16) blocks = 148 * 16;
+  if (blocks > num_sms() * 16) blocks = num_sms() * 16;
   copy_cast_kernel<<<dim3((unsigned)blocks, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(x, x_bstride, x_dtype, y,
                                                                                           y_bstride, y_dtype, CHW);
   return check_launch("copy_cast");

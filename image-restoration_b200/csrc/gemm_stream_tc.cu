@@ -299,15 +299,11 @@ int gemm_stream_launch(const void* x, int64_t x_bs, const void* wp, int Bw, cons
   if (S > 8) S = 8;
   P.S = S;
   const size_t smem = (size_t)S * stage + kGsEpiWarps * 4096 + 1024;
-  int grid = 148;
+  int grid = num_sms();
   if (grid > P.total_items) grid = P.total_items;
 #define B200IR_LAUNCH_GS(TRES, TOUT)                                                                             \
   do {                                                                                                          \
-    static std::once_flag once;                                                                                 \
-    std::call_once(once, [] {                                                                                   \
-      cudaFuncSetAttribute(gemm_stream_tc_kernel<TRES, TOUT>, cudaFuncAttributeMaxDynamicSharedMemorySize,      \
-                           216 * 1024);                                                                         \
-    });                                                                                                         \
+    ensure_dyn_smem((const void*)gemm_stream_tc_kernel<TRES, TOUT>, 216 * 1024);                                                                                                         \
     gemm_stream_tc_kernel<TRES, TOUT><<<grid, kGsThreads, smem, stream>>>(tmX, tmW, tmY, P);                         \
   } while (0)
   const bool ob = y_dt == B200IR_BF16;

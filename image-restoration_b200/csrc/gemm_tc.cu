@@ -348,6 +348,13 @@ __device__ unsigned long long g_tl[4 * 4096 * 2];
 #define TL(tag, id)
 #endif
 
+// timing experiments (tools/ab builds with -DB200IR_AB only; results with a bit set are WRONG by design): 1 no TMA stores,
+// 2 no statistics, 4 no epilogue math, 8 no MMAs, 16 no activation loads.  The default library compiles them out.
+#ifdef B200IR_AB
+#define B200IR_DBG(bit) (P.dbg & (bit))
+#else
+#define B200IR_DBG(bit) false
+#endif
 constexpr int kStageBytes = 16384;  // 128 px x 64 ch x 2 B
 constexpr int kEpiWarps = 16;       // 4 per TMEM lane quadrant
 constexpr int kWarpProducer = 16, kWarpMma = 17, kWarpStats0 = 18;
@@ -467,7 +474,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           const uint32_t stage = it % P.S, ph = (it / P.S) & 1;
           mbar_wait(&bar_empty[stage], ph ^ 1);
           TL(1, tile * 8 + kc);
-          if (P.dbg & 16) { mbar_arrive(&bar_full[stage]); continue; }
+          if (B200IR_DBG(16)) { mbar_arrive(&bar_full[stage]); continue; }
           mbar_arrive_expect_tx(&bar_full[stage], ONE ? 2u * P.BK * 128u : (uint32_t)kStageBytes);
           uint8_t* dst = ring + (size_t)stage * kStageBytes;
           if (ONE) {
@@ -579,7 +586,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
               uint32_t alo = (((ring_addr + stage * kStageBytes) >> 4) & 0x3fffu) | a_lbo;
 #pragma unroll
               for (int ks = 0; ks < 4; ++ks) {
-                if (ks < ksteps && !(P.dbg & 8))
+                if (ks < ksteps && !B200IR_DBG(8))
                   umma_bf16_elect(d_tmem, ((uint64_t)desc_hi << 32) | alo, ((uint64_t)desc_hi << 32) | blo[ks], idesc,
                                   (kc | ks) != 0 ? 1u : 0u);
                 alo += a_step;
@@ -611,7 +618,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
           mbar_wait(&bar_full[stage], ph);
           if (warp == kWarpStats0 && lane == 0) TL(20, tile * 8 + kc);
           const int rows = min(P.BK, P.Cin - kc * P.BK);
-          if (!(P.dbg & 2) || kc == 0) ln_stat_chunk(ring_addr + stage * kStageBytes, (uint32_t)P.BK * 128u, m, (P.dbg & 2) ? 0 : rows, kc == 0, acc);
+          if (!B200IR_DBG(2) || kc == 0) ln_stat_chunk(ring_addr + stage * kStageBytes, (uint32_t)P.BK * 128u, m, B200IR_DBG(2) ? 0 : rows, kc == 0, acc);
           __syncwarp();
           if (lane == 0) mbar_arrive(&bar_empty[stage]);
         }
@@ -802,7 +809,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         const uint32_t tbase = tmem_base + as * 256 + ((uint32_t)(quad * 32) << 16);
         const uint32_t rsrc = smem_u32(resb) + (uint32_t)(acc_it & 1) * P.gpw * 1024u + lane * 2u;
         const uint32_t sdst = smem_u32(stg) + lane * 2u;
-        for (int g = g_lo; g < g_hi && !(P.dbg & 4); ++g) {
+        for (int g = g_lo; g < g_hi && !B200IR_DBG(4); ++g) {
           uint32_t r[16];
 #ifdef B200IR_EPI_NO_TMEMLD   // A/B timing builds only (wrong results): which part of the epilogue slows the tensor pipe
 #pragma unroll
@@ -855,7 +862,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         // under `if (lane == 0)` every UTMASTG sat in an R2UR / branch waterfall (~200 cycles per store)
         if (elect_one()) mbar_arrive(&bar_accempty[as]);
         if (warp == 0) TL(35, tile * 8 + ch);
-        if (!(P.dbg & 1))
+        if (!B200IR_DBG(1))
           for (int g = g_lo; g < g_hi; ++g)
             if (elect_one()) tma_store_3d(&tmY, stg + (size_t)(g - g_lo) * 1024, p0, n_lo + nbase + g * 16, b);
         if (elect_one()) bulk_commit();
@@ -1054,6 +1061,15 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
                                   int ln_type, const void* res, int64_t res_bstride, int res_dtype, void* y,
                                   int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int64_t HW,
                                   b200ir_stream_t stream) {
+  return b200ir_gemm_tc_fwd_ex(x, x_bstride, wp, Bw, st, ln_type, res, res_bstride, res_dtype, y, y_bstride, y_dtype, B,
+                               Cin, Cout, HW, B200IR_GEMM_AUTO, stream);
+}
+
+extern "C" int b200ir_gemm_tc_fwd_ex(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st,
+                                     int ln_type, const void* res, int64_t res_bstride, int res_dtype, void* y,
+                                     int64_t y_bstride, int y_dtype, int B, int Cin, int Cout, int64_t HW, int variant,
+                                     b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(variant >= B200IR_GEMM_AUTO && variant <= B200IR_GEMM_RESIDENT_CH, "gemm_tc: bad variant");
   B200IR_CHECK_ARG(x && wp && st && y && B > 0 && HW > 0, "gemm_tc: bad args");
   B200IR_CHECK_ARG(Bw == 1 || Bw == B, "gemm_tc: Bw must be 1 or B");
   B200IR_CHECK_ARG(dtype_ok(y_dtype) && (!res || dtype_ok(res_dtype)), "gemm_tc: bad dtype");
@@ -1062,12 +1078,11 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
                        ((uintptr_t)y % 16) == 0 && (!res || (res_bstride % 8 == 0 && ((uintptr_t)res % 16) == 0));
   B200IR_UNSUPPORTED(tma_epi || y_dtype == B200IR_F32,
                      "gemm_tc: bf16 output / residual must be 16B-aligned with batch strides %% 8 == 0");
-  // Two epilogues.  Default: pixels on the TMEM lanes (MODE 0).  B200IR_GEMM_EPI=ch selects the channels-on-lanes
+  // Two epilogues.  Default: pixels on the TMEM lanes (MODE 0).  variant = B200IR_GEMM_RESIDENT_CH selects the channels-on-lanes
   // variant (MODE 4: D = W.X, a thread owns 32 pixels of one channel, 2.4x fewer instructions).  Measured on B200 it is
   // not faster (K4 352 vs 334 us, K6 191 vs 193 us): these GEMMs sit at the HBM WRITE roof (3.95 TB/s write-only vs
   // 6.6 TB/s copy, tools/bw_probe.py), not at the issue limit, so MODE 0 stays the default.
-  const char* epi_env = getenv("B200IR_GEMM_EPI");
-  const bool force_px = !(epi_env && epi_env[0] == 'c');
+  const bool force_px = variant != B200IR_GEMM_RESIDENT_CH;
   const bool al16 = ((uintptr_t)y % 16) == 0 && y_bstride % 8 == 0 &&
                     (!res || (((uintptr_t)res % 16) == 0 && res_bstride % 8 == 0));
   bool mode4 = !force_px && al16 && gemm_tc_geometry_t(Cin, Cout, y_dtype == B200IR_BF16, &g);
@@ -1080,11 +1095,11 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   // Deep levels (Cin >= 384: level 4 and the level-3/4 project_out): the weight matrix needs 3..15 resident slices, every
   // slice re-reads the activations and issues narrow MMAs -> stream both operands instead (gemm_stream_tc.cu; measured
   // 384->2042 103 -> 62 us, 1021->384 84 -> 39 us; three resident slices still win: 510->192 at 64x64 57 vs 82 us).  With short K the streamed weights cost more L2 traffic than the
-  // output is worth, so everything else stays on the resident-weight kernel.  B200IR_GEMM_STREAM=0 / 1 forces never /
-  // always (tests, A/B runs).
+  // output is worth, so everything else stays on the resident-weight kernel.  variant = B200IR_GEMM_RESIDENT / B200IR_GEMM_STREAM (b200ir_gemm_tc_fwd_ex) forces never / always
+  // (tests, A/B runs); no environment variable is read.
   {
-    const char* se = getenv("B200IR_GEMM_STREAM");
-    const bool want = se ? (se[0] == '1') : (g.Kpad >= 384 && Bw == 1 && (g.nslices >= 4 || (!res && g.nslices >= 2)));
+    bool want = g.Kpad >= 384 && Bw == 1 && (g.nslices >= 4 || (!res && g.nslices >= 2));
+    if (variant != B200IR_GEMM_AUTO) want = variant == B200IR_GEMM_STREAM;
     if (!mode4 && want && Cin >= 64)
       return gemm_stream_launch(x, x_bstride, wp, Bw, st, ln_type, res, res_bstride, res_dtype, y, y_bstride, y_dtype,
                                 B, Cin, Cout, HW, g.Kpad, g.Nrows, (cudaStream_t)stream);
@@ -1139,9 +1154,12 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   P.inv_cin = 1.0f / (float)Cin;
   B200IR_UNSUPPORTED(mode4 || g.nchunks * g.kchunks * 4 <= 256, "gemm_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
   P.kpt = g.kchunks; P.H = P.W = P.TW = P.TWs = P.TH = P.tiles_x = P.tiles_y = 0;
-  { const char* de = getenv("B200IR_GEMM_DBG"); P.dbg = de ? atoi(de) : 0; }
+  P.dbg = 0;
+#ifdef B200IR_AB
+  if (const char* de = getenv("B200IR_GEMM_DBG")) P.dbg = atoi(de);
+#endif
 
-  int sms = 148;
+  int sms = num_sms();
   int gx = sms / g.nslices;
   if (gx < 1) gx = 1;
   if (gx > P.total_tiles) gx = P.total_tiles;
@@ -1149,14 +1167,8 @@ extern "C" int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* 
   cudaStream_t st_ = (cudaStream_t)stream;
 #define B200IR_LAUNCH_GEMM(TRES, TOUT)                                                                          \
   do {                                                                                                          \
-    static std::once_flag once;                                                                                 \
-    std::call_once(once, [] {                                                                                   \
-      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
-    });                                                                                                         \
-    static std::once_flag once4;                                                                                \
-    std::call_once(once4, [] {                                                                                  \
-      cudaFuncSetAttribute(gemm_tc_kernel<TRES, TOUT, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
-    });                                                                                                         \
+    ensure_dyn_smem((const void*)gemm_tc_kernel<TRES, TOUT, 0>, 219 * 1024);                                                                                                         \
+    ensure_dyn_smem((const void*)gemm_tc_kernel<TRES, TOUT, 4>, 219 * 1024);                                                                                                         \
     if (mode4) gemm_tc_kernel<TRES, TOUT, 4><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);           \
     else gemm_tc_kernel<TRES, TOUT, 0><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmY, tmR, P);                 \
   } while (0)
@@ -1273,17 +1285,14 @@ extern "C" int b200ir_conv3x3_tc_fwd(const void* x, int64_t x_bstride, const voi
   B200IR_UNSUPPORTED(g.nchunks * g.kchunks * 4 <= 256, "conv3x3_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
   P.per_sample_w = 0;
   P.inv_cin = 0.f; P.dbg = 0;
-  int gx = 148 / g.nslices;
+  int gx = num_sms() / g.nslices;
   if (gx < 1) gx = 1;
   if (gx > P.total_tiles) gx = P.total_tiles;
   const dim3 grid((unsigned)gx, (unsigned)g.nslices);
   cudaStream_t st_ = (cudaStream_t)stream;
 #define B200IR_LAUNCH_CONV(TOUT, MODE)                                                                           \
   do {                                                                                                           \
-    static std::once_flag once;                                                                                  \
-    std::call_once(once, [] {                                                                                    \
-      cudaFuncSetAttribute(gemm_tc_kernel<void, TOUT, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 219 * 1024); \
-    });                                                                                                          \
+    ensure_dyn_smem((const void*)gemm_tc_kernel<void, TOUT, MODE>, 219 * 1024);                                                                                                          \
     gemm_tc_kernel<void, TOUT, MODE><<<grid, kThreads, g.smem, st_>>>(tmX, tmW, tmX, tmX, P);                    \
   } while (0)
   const int mode = shuffle_mode + 1;

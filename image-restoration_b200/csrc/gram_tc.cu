@@ -184,10 +184,7 @@ int gram_tc_launch(const void* qkv, int64_t bstride, int B, int C, int heads, in
   if (S < 2) S = 2;
   P.S = S;
   const size_t smem = (size_t)S * stage + 16384 + 1024 + 1024;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    cudaFuncSetAttribute(gram_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  });
+  ensure_dyn_smem((const void*)gram_tc_kernel, 227 * 1024);
   gram_tc_kernel<<<dim3((unsigned)nslab, (unsigned)heads, (unsigned)B), kGramThreads, smem, st>>>(tm, P);
   return check_launch("mdta_gram_tc");
 }

@@ -229,7 +229,7 @@ int gram_slab_len(int B, int d, int heads, int64_t HW, int* nslab_out) {
   // (b, head, slab) work items = CTAs: as many as run CONCURRENTLY on 148 SMs and no more, so that there is no
   // nearly-empty last wave (19 slabs x 16 samples = 304 CTAs on 148 resident slots ran as 2.05 -> 3 waves).  Head dims
   // <= 64 fit two CTAs per SM (TMEM columns and shared memory), larger ones one.  Slabs are multiples of 256 pixels.
-  const int64_t cap = d <= 64 ? 2 * 148 : 148;
+  const int64_t cap = d <= 64 ? 2 * num_sms() : num_sms();
   int64_t want = cap / ((int64_t)B * heads);
   int64_t maxslab = (HW + 255) / 256;
   if (want > maxslab) want = maxslab;
@@ -303,7 +303,7 @@ extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, co
   // output rows per block (16 per register row RT): the largest of 64 / 32 / 16 that still gives every SM a block
   int RT = 1;
   for (int rt = 4; rt >= 1; rt >>= 1)
-    if ((int64_t)((C + 16 * rt - 1) / (16 * rt)) * heads * B >= 148) {
+    if ((int64_t)((C + 16 * rt - 1) / (16 * rt)) * heads * B >= num_sms()) {
       RT = rt;
       break;
     }
@@ -313,10 +313,7 @@ extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, co
   const dim3 grid((unsigned)((C + kFoldRows - 1) / kFoldRows), (unsigned)heads, (unsigned)B);
 #define FOLD_LAUNCH(RT_, KC_)                                                                                       \
   do {                                                                                                              \
-    static std::once_flag once;                                                                                     \
-    std::call_once(once, [] {                                                                                       \
-      cudaFuncSetAttribute(mdta_fold_kernel<RT_, KC_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);    \
-    });                                                                                                             \
+    ensure_dyn_smem((const void*)mdta_fold_kernel<RT_, KC_>, 100 * 1024);                                                                                                             \
     mdta_fold_kernel<RT_, KC_><<<grid, 256, smem, st>>>(attn, w_out, m, (bf16*)mp, kpad, nrows, C, d);              \
   } while (0)
 #define FOLD_KC(RT_)                                                                                                \

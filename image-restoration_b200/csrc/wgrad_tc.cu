@@ -206,10 +206,7 @@ int wgrad_tc_launch(const void* dy, int64_t dy_bs, int dy_dt, const void* x, int
   if (S < 2) S = 2;
   P.S = S;
   const size_t smem = (size_t)S * stage + 1024 + 256;
-  static std::once_flag once;
-  std::call_once(once, [] {
-    cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-  });
+  ensure_dyn_smem((const void*)wgrad_tc_kernel, 227 * 1024);
   dim3 grid((unsigned)ntiles, (unsigned)mtiles, (unsigned)(P.G * nsplit));
   wgrad_tc_kernel<<<grid, kWgThreads, smem, st>>>(tmA, tmX, P);
   int rc = check_launch("conv_wgrad_tc");

@@ -87,11 +87,23 @@ def _is_gated_mdta(m) -> bool:
             and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
 
 
+def _heads_of(m):
+    """Head count of an attention module: ``num_heads`` (Restormer, MoCE-IR) or ``num_head`` (AdaIR)."""
+    for a in ("num_heads", "num_head"):
+        v = getattr(m, a, None)
+        if isinstance(v, int) and v > 0:
+            return v
+    return None
+
+
 def _is_cross(m) -> bool:
-    """MoCE-IR CrossAttention (moce_ir.py:325-343): q / q_dwconv(3x3) from one input, kv / kv_dwconv(7x7) from another."""
-    need = ("temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out", "num_heads")
-    if not all(hasattr(m, a) for a in need):
+    """MoCE-IR CrossAttention (moce_ir.py:325-343): q / q_dwconv(3x3) from one input, kv / kv_dwconv(7x7) from another;
+    AdaIR Chanel_Cross_Attention (AdaIR-main/net/model.py:177-216) is the same module with a 3x3 kv_dwconv and the head
+    count spelled ``num_head``."""
+    need = ("temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out")
+    if not all(hasattr(m, a) for a in need) or _heads_of(m) is None:
         return False
+    heads = _heads_of(m)
     pn = {n.split(".")[0] for n, _ in m.named_parameters()}
     if pn != {"temperature", "q", "q_dwconv", "kv", "kv_dwconv", "project_out"}:
         return False
@@ -101,7 +113,7 @@ def _is_cross(m) -> bool:
             and _conv_ok(m.kv_dwconv, kk, 2 * c) and _conv_ok(m.project_out, 1, 1)
             and m.q.out_channels == c and m.kv.in_channels == c and m.kv.out_channels == 2 * c
             and m.project_out.in_channels == c == m.project_out.out_channels
-            and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
+            and tuple(m.temperature.shape) == (heads, 1, 1) and c % heads == 0)
 
 
 def _is_resize(m):
@@ -127,7 +139,6 @@ def _bare(cls):
 def _adopt_ln(m):
     ln = _bare(M.LayerNorm)
     ln.body = m.body
-    ln._eye = None
     return ln
 
 
@@ -150,7 +161,7 @@ def _adopt_gated(m):
 
 def _adopt_cross(m):
     a = _bare(M.CrossAttention)
-    a.num_heads = m.num_heads
+    a.num_heads = _heads_of(m)
     a.temperature = m.temperature
     a.q, a.q_dwconv, a.kv, a.kv_dwconv, a.project_out = m.q, m.q_dwconv, m.kv, m.kv_dwconv, m.project_out
     return a

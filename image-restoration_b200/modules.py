@@ -23,10 +23,6 @@ from . import ops
 from . import autograd_ops as A
 
 
-def _w2d(conv: nn.Conv2d) -> torch.Tensor:
-    return conv.weight
-
-
 def _ln_args(norm: "LayerNorm"):
     body = norm.body  # ours, or a reference LayerNorm body adopted by dropin.accelerate(): told apart by its parameters
     if getattr(body, "bias", None) is not None:
@@ -61,7 +57,8 @@ class WithBias_LayerNorm(nn.Module):
 
 class LayerNorm(nn.Module):
     """Channel LayerNorm over an NCHW tensor (Restormer.py:60-70).  Inside TransformerBlock it is
-    fused into the following 1x1 conv; called on its own it runs the same kernel with W = I."""
+    fused into the following 1x1 conv; called on its own it is one pass of the stand-alone LayerNorm kernel
+    (b200ir_ln_fwd; backward b200ir_ln_bwd)."""
 
     def __init__(self, dim, LayerNorm_type):
         super().__init__()
@@ -69,14 +66,10 @@ class LayerNorm(nn.Module):
             self.body = BiasFree_LayerNorm(dim)
         else:
             self.body = WithBias_LayerNorm(dim)
-        self._eye = None
 
     def forward(self, x):
         ln_type, w, b = _ln_args(self)
-        c = x.shape[1]
-        if self._eye is None or self._eye.device != x.device:
-            self._eye = torch.eye(c, device=x.device, dtype=torch.float32)
-        return A.ln_conv1x1(x, self._eye, None, ln_type, w, b, None)
+        return A.layernorm(x, ln_type, w, b)
 
 
 ##########################################################################
@@ -336,9 +329,8 @@ class Restormer(nn.Module):
                  heads=[1, 2, 4, 8],
                  ffn_expansion_factor=2.66,
                  bias=False,
-                 LayerNorm_type='WithBias',  ## Other option 'BiasFree'
-                 dual_pixel_task=False  ## True for dual-pixel defocus deblurring only. Also set inp_channels=6
-                 ):
+                 LayerNorm_type='WithBias',
+                 dual_pixel_task=False):
         super().__init__()
 
         def stack(d, h, n):

@@ -384,8 +384,9 @@ def pack_conv1x1_t(w):
     return wp, st
 
 
-def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=None):
-    """y = res + W.LN(x) + bias on tcgen05 tensor cores; `packed` = pack_conv1x1(...)."""
+def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=None, variant=L.GEMM_AUTO):
+    """y = res + W.LN(x) + bias on tcgen05 tensor cores; `packed` = pack_conv1x1(...).  `variant` forces a kernel
+    (L.GEMM_RESIDENT / GEMM_STREAM / GEMM_RESIDENT_CH) instead of the shape-based choice (tests, A/B timing)."""
     wp, st = packed
     B, Cin, H, W_ = x.shape
     xp, xbs, xdt = _act(x, "x")
@@ -401,8 +402,8 @@ def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=No
         rp, rbs, rdt = _act(res, "res")
     Bw = wp.shape[0]
     with _timed("gemm_tc", B, Cin, Cout, H * W_, ln_type, int(res is not None), int(Bw > 1), xdt, ydt):
-        rc = lib.b200ir_gemm_tc_fwd(xp, xbs, wp.data_ptr(), Bw, st.data_ptr(), ln_type, rp, rbs, rdt, yp, ybs, ydt,
-                                    B, Cin, Cout, H * W_, _stream())
+        rc = lib.b200ir_gemm_tc_fwd_ex(xp, xbs, wp.data_ptr(), Bw, st.data_ptr(), ln_type, rp, rbs, rdt, yp, ybs, ydt,
+                                       B, Cin, Cout, H * W_, variant, _stream())
     L.check(rc, "b200ir_gemm_tc_fwd")
     return out
 
@@ -663,18 +664,23 @@ def l1_loss_bwd(pred, target, gscale):
     return grad
 
 
-def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, step_dev=None):
-    """One AdamW update of a flat buffer.  `step_dev` (int32 CUDA tensor [1]) replaces the host `step`: the call
-    increments it on the stream and the kernel derives the bias corrections from it (CUDA-graph replayable)."""
+def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale=1.0, step_dev=None, tick=True,
+               hyper_dev=None):
+    """One AdamW update of a flat buffer (or of a sub-range: pass views).  `step_dev` (int32 CUDA tensor [1]) replaces
+    the host `step`: with `tick` the call increments it on the stream and the kernel derives the bias corrections from
+    it (CUDA-graph replayable).  `hyper_dev` (float32 CUDA tensor [2] = lr, weight_decay) overrides the host scalars."""
     for t in (p, g, m, v):
         if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda or t.numel() != p.numel():
             raise ValueError("adamw_step: flat contiguous float32 CUDA buffers of equal size expected")
     if step_dev is not None and (step_dev.dtype != torch.int32 or not step_dev.is_cuda):
         raise ValueError("adamw_step: step_dev must be an int32 CUDA tensor")
+    if hyper_dev is not None and (hyper_dev.dtype != torch.float32 or not hyper_dev.is_cuda or hyper_dev.numel() < 2):
+        raise ValueError("adamw_step: hyper_dev must be a float32 CUDA tensor [2]")
     global LAUNCHES
-    LAUNCHES += 1 if step_dev is not None else 0
+    LAUNCHES += 1 if (step_dev is not None and tick) else 0
     with _timed("adamw_step", p.numel()):
-        rc = lib.b200ir_adamw_step(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr, beta1, beta2,
-                                   eps, weight_decay, step, step_dev.data_ptr() if step_dev is not None else None,
-                                   grad_scale, _stream())
+        rc = lib.b200ir_adamw_step_ex(p.data_ptr(), g.data_ptr(), m.data_ptr(), v.data_ptr(), p.numel(), lr, beta1, beta2,
+                                      eps, weight_decay, step, step_dev.data_ptr() if step_dev is not None else None,
+                                      int(bool(tick)), hyper_dev.data_ptr() if hyper_dev is not None else None,
+                                      grad_scale, _stream())
     L.check(rc, "b200ir_adamw_step")

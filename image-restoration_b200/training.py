@@ -31,23 +31,31 @@ class L1Loss(nn.Module):
         return A.l1_loss(pred, target)
 
 
-class AdamW:
+class AdamW(torch.optim.Optimizer):
     """``torch.optim.AdamW`` semantics (decoupled weight decay, bias correction, eps outside the sqrt) on flat buffers.
 
-    Constructor signature follows ``torch.optim.AdamW(params, lr, betas, eps, weight_decay)``.  Parameters must be
-    fp32 CUDA tensors; after construction each ``p.data`` is a view into ``self.flat_p``.
+    A ``torch.optim.Optimizer`` subclass with ONE parameter group, so that the reference recipe
+    (``optim.AdamW(self.parameters(), lr=2e-4)`` + ``LinearWarmupCosineAnnealingLR``, MoCE-IR-main/src/train.py:83-86)
+    attaches unchanged: schedulers write ``param_groups[0]['lr']``; ``step()`` mirrors lr / weight decay into a
+    two-float device buffer that the update kernel reads, so they also change under a captured CUDA graph
+    (``GraphedTrainStep``).  Parameters must be fp32 CUDA tensors; after construction each ``p.data`` is a view into
+    ``self.flat_p``.  Parameters whose ``.grad`` is None at ``step()`` are skipped (no decay, no moment update), like
+    torch.  Difference from torch: the bias-correction step count is one counter for all parameters (torch counts per
+    parameter, which only differs for a parameter that receives gradients in some steps and not in others).
     """
 
     def __init__(self, params: Iterable[nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-2):
-        self.params = [p for p in params if p.requires_grad]
+        super().__init__(params, dict(lr=lr, betas=tuple(betas), eps=eps, weight_decay=weight_decay))
+        if len(self.param_groups) != 1:
+            raise ValueError("b200ir.AdamW supports a single parameter group (one flat buffer)")
+        self.params = [p for p in self.param_groups[0]["params"] if p.requires_grad]
         if not self.params:
             raise ValueError("AdamW: no trainable parameters")
         dev = self.params[0].device
         for p in self.params:
             if not p.is_cuda or p.dtype != torch.float32 or p.device != dev:
                 raise ValueError("AdamW: parameters must be float32 CUDA tensors on one device (no CPU fallback)")
-        self.lr, self.betas, self.eps, self.weight_decay = lr, tuple(betas), eps, weight_decay
         self.offsets, n = [], 0
         for p in self.params:
             self.offsets.append(n)
@@ -66,34 +74,76 @@ class AdamW:
                 self.grad_views.append(self.flat_g[o:o + p.numel()].view(p.shape))
         self.step_count = 0
         # the step count also lives on the device: the update kernel increments and reads it there, so that a captured
-        # CUDA graph of the whole training step replays with the right bias corrections
+        # CUDA graph of the whole training step replays with the right bias corrections; lr / weight decay likewise
         self.step_dev = torch.zeros(1, device=dev, dtype=torch.int32)
+        self.hyper = torch.tensor([lr, weight_decay], device=dev, dtype=torch.float32)
+        self._hyper_last = (float(lr), float(weight_decay))
+        self._present = None
+        self._runs = [(0, n)]
+        A.bump_param_epoch()
+
+    # scalar hyper-parameters live in param_groups[0] (what torch schedulers edit)
+    lr = property(lambda self: self.param_groups[0]["lr"], lambda self, v: self.param_groups[0].__setitem__("lr", v))
+    betas = property(lambda self: self.param_groups[0]["betas"],
+                     lambda self, v: self.param_groups[0].__setitem__("betas", tuple(v)))
+    eps = property(lambda self: self.param_groups[0]["eps"], lambda self, v: self.param_groups[0].__setitem__("eps", v))
+    weight_decay = property(lambda self: self.param_groups[0]["weight_decay"],
+                            lambda self, v: self.param_groups[0].__setitem__("weight_decay", v))
 
     def zero_grad(self, set_to_none: bool = True):
         for p in self.params:
             p.grad = None
 
+    def sync_hyper(self):
+        """Mirror (lr, weight_decay) of param_groups[0] into the device buffer the kernel reads (8-byte copy, only when
+        they changed; never inside a stream capture: GraphedTrainStep calls this before each replay)."""
+        cur = (float(self.lr), float(self.weight_decay))
+        if cur != self._hyper_last and not torch.cuda.is_current_stream_capturing():
+            self.hyper.copy_(torch.tensor(cur, dtype=torch.float32))
+            self._hyper_last = cur
+
     def gather_grads(self):
-        """Collect ``p.grad`` into the flat gradient buffer (no-op for gradients that already live there)."""
-        src, dst = [], []
+        """Collect ``p.grad`` into the flat gradient buffer (no-op for gradients that already live there) and note which
+        parameters have one: the update runs over the contiguous runs of those."""
+        src, dst, present = [], [], []
         for p, gv in zip(self.params, self.grad_views):
-            if p.grad is None:
-                gv.zero_()
-            elif p.grad.data_ptr() != gv.data_ptr():
+            present.append(p.grad is not None)
+            if p.grad is not None and p.grad.data_ptr() != gv.data_ptr():
                 src.append(p.grad)
                 dst.append(gv)
         if src:
             torch._foreach_copy_(dst, src)
+        if present != self._present:
+            self._present, self._runs, start = present, [], None
+            for i, ok in enumerate(present):
+                if ok and start is None:
+                    start = self.offsets[i]
+                if not ok and start is not None:
+                    self._runs.append((start, self.offsets[i]))
+                    start = None
+            if start is not None:
+                self._runs.append((start, self.numel))
         return self.flat_g
 
     @torch.no_grad()
-    def step(self, grad_scale: float = 1.0, gathered: bool = False):
+    def step(self, closure=None, grad_scale: float = 1.0, gathered: bool = False):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
         if not gathered:
             self.gather_grads()
+        self.sync_hyper()
+        if not self._runs:
+            return loss
         self.step_count += 1
-        ops.adamw_step(self.flat_p, self.flat_g, self.exp_avg, self.exp_avg_sq, self.lr, self.betas[0], self.betas[1],
-                       self.eps, self.weight_decay, self.step_count, grad_scale, step_dev=self.step_dev)
+        b1, b2 = self.betas
+        for i, (a, b) in enumerate(self._runs):
+            ops.adamw_step(self.flat_p[a:b], self.flat_g[a:b], self.exp_avg[a:b], self.exp_avg_sq[a:b], float(self.lr),
+                           b1, b2, self.eps, float(self.weight_decay), self.step_count, grad_scale,
+                           step_dev=self.step_dev, tick=(i == 0), hyper_dev=self.hyper)
         A.bump_param_epoch()   # packed bf16 weight caches key on this (the kernel does not bump tensor versions)
+        return loss
 
     def state_dict(self):
         return {"step": self.step_count, "exp_avg": self.exp_avg, "exp_avg_sq": self.exp_avg_sq, "lr": self.lr,
@@ -105,6 +155,7 @@ class AdamW:
         self.exp_avg.copy_(sd["exp_avg"])
         self.exp_avg_sq.copy_(sd["exp_avg_sq"])
         self.lr, self.betas, self.eps, self.weight_decay = sd["lr"], tuple(sd["betas"]), sd["eps"], sd["weight_decay"]
+        self.sync_hyper()
 
 
 def allreduce_flat_grads(flat_g: torch.Tensor, group=None) -> float:
@@ -197,6 +248,7 @@ class GraphedTrainStep:
     def __call__(self, degraded: torch.Tensor, clean: torch.Tensor) -> torch.Tensor:
         self.degraded.copy_(degraded, non_blocking=True)
         self.clean.copy_(clean, non_blocking=True)
+        self.opt.sync_hyper()   # lr / weight decay changed by a scheduler since the last replay -> device scalars
         self.g1.replay()
         if self.g2 is not None:
             import torch.distributed as dist

@@ -153,6 +153,14 @@ int b200ir_pack_conv1x1_multi(const b200ir_pack_desc_t* descs, int ndesc, int to
 int b200ir_gemm_tc_fwd(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st, int ln_type,
                        const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
                        int B, int Cin, int Cout, int64_t HW, b200ir_stream_t stream);
+/* Same call with the kernel variant chosen by the caller instead of by shape (tests, A/B timing): AUTO = what
+ * b200ir_gemm_tc_fwd picks; RESIDENT = weights resident in shared memory (gemm_tc.cu); STREAM = both operands streamed
+ * (gemm_stream_tc.cu, Cin >= 64); RESIDENT_CH = resident weights with the channels-on-TMEM-lanes epilogue.  The
+ * library reads no environment variable: every switch is an argument. */
+enum { B200IR_GEMM_AUTO = 0, B200IR_GEMM_RESIDENT = 1, B200IR_GEMM_STREAM = 2, B200IR_GEMM_RESIDENT_CH = 3 };
+int b200ir_gemm_tc_fwd_ex(const void* x, int64_t x_bstride, const void* wp, int Bw, const float* st, int ln_type,
+                          const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
+                          int B, int Cin, int Cout, int64_t HW, int variant, b200ir_stream_t stream);
 
 /* Dense 3x3 conv (pad 1, +bias) on the same tcgen05 kernel: 9 tap-shifted GEMMs accumulated in TMEM, zero padding
  * from TMA out-of-bounds fill, PixelUnshuffle(2)/PixelShuffle(2) folded into the store (Downsample / Upsample,
@@ -235,6 +243,14 @@ int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int
 int b200ir_adamw_step(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
                       float eps, float weight_decay, int step, int* step_dev, float grad_scale,
                       b200ir_stream_t stream);
+/* Same update over a sub-range of the flat buffers.  tick = 0 leaves step_dev as it is (several ranges share one
+ * optimizer step: parameters whose gradient is None are skipped the way torch.optim.AdamW skips them, so the buffer is
+ * updated as a few contiguous runs).  hyper_dev (optional, device float[2] = {lr, weight_decay}) overrides the host
+ * scalars: an LR scheduler (LinearWarmupCosineAnnealingLR in MoCE-IR-main/src/train.py:84-86) changes the learning rate
+ * between replays of a captured CUDA graph by writing that buffer. */
+int b200ir_adamw_step_ex(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+                         float eps, float weight_decay, int step, int* step_dev, int tick, const float* hyper_dev,
+                         float grad_scale, b200ir_stream_t stream);
 
 #ifdef __cplusplus
 }

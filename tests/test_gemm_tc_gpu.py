@@ -93,10 +93,8 @@ def test_gemm_tc_large_tail_and_multi_cta():
 
 
 def test_gemm_tc_channels_on_lanes_epilogue_matches_default():
-    """The opt-in channels-on-lanes epilogue (B200IR_GEMM_EPI=ch, gemm_tc_kernel MODE 4) gives the same bf16 results as
+    """The opt-in channels-on-lanes epilogue (variant GEMM_RESIDENT_CH, gemm_tc_kernel MODE 4) gives the same bf16 results as
     the default pixels-on-lanes epilogue (identical fp32 accumulators, identical rounding point)."""
-    import os
-    import torch
     import b200ir
     from b200ir import ops
     L = b200ir._lib
@@ -109,24 +107,18 @@ def test_gemm_tc_channels_on_lanes_epilogue_matches_default():
         lw, lb = (torch.rand(Cin, generator=g) + 0.5).cuda(), (torch.rand(Cin, generator=g) - 0.5).cuda()
         r = (torch.rand(B, Cout, H, W, generator=g) - 0.5).bfloat16().cuda() if res else None
         packed = ops.pack_conv1x1(w, bias, ln, lw if ln else None, lb if ln == L.LN_WITHBIAS else None)
-        os.environ.pop("B200IR_GEMM_EPI", None)
-        y0 = ops.gemm_tc(x, packed, Cout, ln, r)
-        os.environ["B200IR_GEMM_EPI"] = "ch"
-        try:
-            y1 = ops.gemm_tc(x, packed, Cout, ln, r)
-            y1f = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
-        finally:
-            os.environ.pop("B200IR_GEMM_EPI", None)
+        y0 = ops.gemm_tc(x, packed, Cout, ln, r, variant=L.GEMM_RESIDENT)
+        y1 = ops.gemm_tc(x, packed, Cout, ln, r, variant=L.GEMM_RESIDENT_CH)
+        y1f = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32, variant=L.GEMM_RESIDENT_CH)
         torch.cuda.synchronize()
         assert (y0.float() - y1.float()).abs().max() <= 2e-2 * y0.float().abs().max()
         assert ((y1f - y0.float()).norm() / y0.float().norm()) < 4e-3
 
 
 def test_gemm_stream_matches_resident_weights_kernel():
-    """Deep-level shapes go to the streamed-operand kernel (gemm_stream_tc.cu); B200IR_GEMM_STREAM=0 forces the
+    """Deep-level shapes go to the streamed-operand kernel (gemm_stream_tc.cu); variant GEMM_RESIDENT forces the
     resident-weight kernel.  Same packed operands, same fp32 accumulation -> results agree to bf16 rounding; ragged pixel
     tiles, several items per CTA, per-sample weights, all LayerNorm kinds, residual, both output dtypes."""
-    import os
     import b200ir
     from b200ir import ops
     L = b200ir._lib
@@ -143,17 +135,9 @@ def test_gemm_stream_matches_resident_weights_kernel():
         r = (torch.rand(B, Cout, H, W, generator=g) - 0.5).bfloat16().cuda() if res else None
         packed = ops.pack_conv1x1(w, bias, ln, lw if ln else None, lb if ln == L.LN_WITHBIAS else None,
                                   per_sample=per_sample)
-        os.environ["B200IR_GEMM_STREAM"] = "0"
-        try:
-            y0 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
-        finally:
-            os.environ.pop("B200IR_GEMM_STREAM", None)
-        os.environ["B200IR_GEMM_STREAM"] = "1"
-        try:
-            y1 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32)
-            y1b = ops.gemm_tc(x, packed, Cout, ln, r)
-        finally:
-            os.environ.pop("B200IR_GEMM_STREAM", None)
+        y0 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32, variant=L.GEMM_RESIDENT)
+        y1 = ops.gemm_tc(x, packed, Cout, ln, r, out_dtype=torch.float32, variant=L.GEMM_STREAM)
+        y1b = ops.gemm_tc(x, packed, Cout, ln, r, variant=L.GEMM_STREAM)
         torch.cuda.synchronize()
         scale = y0.abs().max()
         assert (y0 - y1).abs().max() <= 1e-4 * scale, (Cin, Cout, float((y0 - y1).abs().max()), float(scale))
