@@ -93,21 +93,63 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
-def cpu_reference_run(steps, warmup, sample_hw=256):
+def refuse_debug_env():
+    """A number measured with an A/B library or a stage-dropping debug switch is not a bench number."""
+    bad = sorted(k for k in os.environ if k.startswith("B200IR_") and k != "B200IR_COMPUTE_DTYPE")
+    if bad:
+        raise SystemExit(f"bench.py refuses to run with debug variables set: {bad}")
+
+
+def cpu_reference_run(steps, warmup, sample_hw=256, x=None, keep_out=False):
     """The reference's CPU path (oracle port: identical ATen CPU ops) on all host cores; B=1 sample per step."""
     from oracle import restormer_oracle as O
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
     sd = O.synth_state_dict({}, seed=0)
-    x = O.synth_image(1, sample_hw, sample_hw, seed=1234)
+    if x is None:
+        x = O.synth_image(1, sample_hw, sample_hw, seed=1234)
+    y = None
     with torch.no_grad():
         for _ in range(warmup):
-            O.restormer_forward(sd, x)
+            y = O.restormer_forward(sd, x)
         t0 = time.perf_counter()
         for _ in range(steps):
-            O.restormer_forward(sd, x)
+            y = O.restormer_forward(sd, x)
         dt = (time.perf_counter() - t0) / max(steps, 1)
-    return (sample_hw * sample_hw / 1e6) / dt, dt, cores, f"1 of the 16 images ({sample_hw}x{sample_hw}, fp32) per step"
+    r = ((sample_hw * sample_hw / 1e6) / dt, dt, cores, f"1 of the 16 images ({sample_hw}x{sample_hw}, fp32) per step")
+    return r + (y,) if keep_out else r
+
+
+def incumbent_gpu(O, sd, xs, steps):
+    """Informational: what stock eager PyTorch gives on the SAME GPU for the same forward (the oracle's functional
+    restatement of Restormer.py on CUDA tensors = the ATen/cuDNN/cuBLAS kernels the reference would launch): fp32 with
+    TF32 off (the reference's precision) and under bf16 autocast.  Never the target, never in `value`."""
+    out = {}
+    sdd = {k: v.to(xs[0].device) for k, v in sd.items()}
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    try:
+        for name, auto in (("fp32_tf32_off", False), ("bf16_autocast", True)):
+            torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+            try:
+                with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16, enabled=auto):
+                    O.restormer_forward(sdd, xs[0])
+                    torch.cuda.synchronize()
+                    e0.record()
+                    for i in range(steps):
+                        O.restormer_forward(sdd, xs[i % len(xs)])
+                    e1.record()
+                    torch.cuda.synchronize()
+                ms = e0.elapsed_time(e1) / steps
+                b, _, h, w = xs[0].shape
+                out[name] = {"value": b * h * w / 1e6 / (ms * 1e-3), "unit": "MP/s", "ms_per_step": ms}
+            except Exception as e:  # e.g. out of memory on a shared box: the leg is informational
+                out[name] = {"error": str(e)[:200]}
+                torch.cuda.empty_cache()
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+    out["what"] = "eager PyTorch (oracle restatement of Restormer.py on CUDA tensors), same batch, 1 GPU; informational"
+    return out
 
 
 def run_reference(args):
@@ -138,9 +180,11 @@ def main():
     ap.add_argument("--no-train", action="store_true", help="skip the cfg4 training-step leg")
     ap.add_argument("--no-hires", action="store_true", help="skip the cfg5 1024x1024 leg")
     ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
+    ap.add_argument("--no-incumbent", action="store_true", help="skip the eager-PyTorch-on-GPU informational leg")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
+    refuse_debug_env()
     args.warmup = max(args.warmup, 3)
 
     # NCCL's own log lines (e.g. 'NCCL version ...' when the box sets NCCL_DEBUG) go to stderr: stdout carries the JSON line only
@@ -217,6 +261,17 @@ def main():
         barrier()
         ms_e2e = max_over_ranks(e0.elapsed_time(e1) / args.steps)
         del fwd
+        # ---- parity samples (checked against the CPU oracle below, outside every timed region) ----
+        par_bf16 = net(dev_in[0])[0:1].float().cpu() if rank == 0 else None
+        par_x128 = O.synth_image(1, 128, 128, seed=1234)
+        par_fp32 = None
+        if rank == 0:
+            net.set_compute_dtype(torch.float32)
+            par_fp32 = net(par_x128.to(dev)).cpu()      # BASELINE configs[0]: B1 128x128 fp32
+            net.set_compute_dtype(cd)
+        incumbent = None
+        if rank == 0 and not args.no_incumbent:
+            incumbent = incumbent_gpu(O, O.synth_state_dict({}, seed=0), dev_in[:3], 3)
         # ---- optional per-kernel table (separate pass, not part of any reported number) ----
         table = None
         if args.kernel_table and rank == 0:
@@ -306,10 +361,20 @@ def main():
         out["train_step"] = train
     if hires is not None:
         out["hires"] = hires
+    if incumbent is not None:
+        out["incumbent_gpu"] = incumbent
     if not args.no_cpu_baseline:
-        v, dt, cores, sample = cpu_reference_run(2, 1)
+        # the timed CPU sample IS image 0 of input batch 0: its output doubles as the parity reference for the GPU output
+        v, dt, cores, sample, ref256 = cpu_reference_run(2, 1, x=host[0][0:1].clone(), keep_out=True)
         out["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample,
                                "s_per_step": dt}
+        with torch.no_grad():
+            ref128 = O.restormer_forward(O.synth_state_dict({}, seed=0), par_x128)
+        out["parity"] = {
+            "bf16_psnr_db": O.psnr(par_bf16, ref256), "bf16_config": f"cfg2 sample 0 of {B}, {H}x{W}, {args.dtype} GPU vs fp32 CPU oracle",
+            "fp32_max_abs": float((par_fp32 - ref128).abs().max()), "fp32_config": "cfg1 B1 128x128, fp32 GPU path vs fp32 CPU oracle",
+            "tolerance": {"bf16_psnr_db_min": 50.0, "fp32_max_abs_max": 1e-4}}
+        out["parity"]["ok"] = bool(out["parity"]["bf16_psnr_db"] >= 50.0 and out["parity"]["fp32_max_abs"] <= 1e-4)
     if table is not None:
         rows = sorted(([list(k), n, m, n * m] for k, (n, m) in table.items()), key=lambda r: -r[3])
         json.dump({"total_ms": sum(r[3] for r in rows), "rows": rows}, open(args.kernel_table, "w"), indent=0)

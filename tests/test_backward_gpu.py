@@ -283,11 +283,23 @@ def test_restormer_train_steps(b200ir, dtype):
     else:
         for a, b in zip(got, losses):
             assert abs(a - b) <= 2e-2 * abs(b), (got, losses)
-        # bf16 activations, third step (two AdamW sign-like updates amplify rounding differences): the 4x4-pixel latent
-        # level sits at 8-11 % whichever depthwise kernel runs (tools/train_grad_probe.py); >= 95 % of the 120 gradient
-        # tensors within 15 %, the per-kernel tests above hold each backward op to 1e-2 / 2e-3
-        bad = [n for n, gref in grads.items() if rel(params[n].grad, gref) > 0.15]
-        assert len(bad) <= len(grads) // 20, bad
+        # bf16 activations: EVERY gradient tensor is held to a per-tensor bound, on the FIRST step (identical weights on
+        # both sides; after AdamW's sign-like updates the two trajectories are different networks and a comparison of
+        # their gradients no longer measures the kernels).  Real-size check: test_parity_fullsize_gpu.py (cfg4).
+        _, grads1, _ = O.train_step_reference(sd, NET_CFG, degraded, clean, steps=1)
+        net1 = b200ir.Restormer(**cfg).cuda()
+        net1.load_state_dict(sd, strict=True)
+        net1.set_compute_dtype(dtype)
+        b200ir.train_step(net1, b200ir.AdamW(net1.parameters(), lr=2e-4), degraded.cuda(), clean.cuda())
+        p1 = dict(net1.named_parameters())
+        rows = []
+        for n, gref in grads1.items():
+            a, r = p1[n].grad.detach().double().cpu().flatten(), gref.double().flatten()
+            rows.append((n, float(torch.dot(a, r) / (a.norm() * r.norm()).clamp_min(1e-300)), rel(p1[n].grad, gref)))
+        rows.sort(key=lambda t: -t[2])
+        print("worst bf16 gradient tensors (name, cosine, rel L2):", rows[:6])
+        bad = [t for t in rows if t[1] < 0.999 or t[2] > 3e-2]
+        assert not bad, bad
     # loss must go down on a repeated batch
     assert got[-1] < got[0]
 
@@ -419,7 +431,7 @@ def test_train_steps_match_reference_golden(b200ir):
     assert np.allclose(losses, gold["losses"], rtol=0, atol=1e-5), (losses, gold["losses"])
     for n, q in net.named_parameters():
         close32(q.grad, torch.from_numpy(gold["g_" + n]), 1e-3)
-        assert (q.detach().cpu() - torch.from_numpy(gold["p_" + n])).abs().max() <= 2 * 2e-4 + 1e-6, n
+        assert (q.detach().cpu() - torch.from_numpy(gold["p_" + n])).abs().max() <= 2e-5, n
 
 
 def test_block_grads_match_reference_golden(b200ir):
