@@ -47,6 +47,10 @@ SIGNATURES = {
     "b200ir_conv3x3_tc_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_gemm_tc_fwd": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _vp],
     "b200ir_gemm_tc_fwd_ex": [_vp, _i64, _vp, _i, _vp, _i, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i64, _i, _vp],
+    "b200ir_fused_proj_dw_geometry": [_i, _i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],
+    "b200ir_pack_fused_proj_dw": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp, _vp],
+    "b200ir_ln_proj_dw_supported": [_i, _i, _i, _i, _i],
+    "b200ir_ln_proj_dw_fwd": [_vp, _i64, _vp, _vp, _vp, _i, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_ln_fwd": [_vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_ln_bwd_nparts": [_i, _i64],
     "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i64, _vp, _i, _i, _i,

@@ -37,11 +37,26 @@ def bump_param_epoch():
     PARAM_EPOCH += 1
 
 
+def _optimizer_step_hook(optimizer, args, kwargs):
+    """Global torch.optim post-step hook: ANY optimizer step invalidates the packed bf16 weight caches.  Needed because
+    a tensor's ``_version`` is not a reliable change signal for every optimizer implementation (measured on B200 with
+    torch 2.11: after ``torch.optim.AdamW(fused=True).step()`` the caches keyed on ``(data_ptr, _version)`` served stale
+    weights, tests/test_parity_fullsize_gpu.py::test_ddp_wrap_and_stock_adamw)."""
+    bump_param_epoch()
+
+
+try:   # torch >= 2.0
+    from torch.optim.optimizer import register_optimizer_step_post_hook as _reg_hook
+    _reg_hook(_optimizer_step_hook)
+except Exception:   # pragma: no cover  (older torch: rely on _version; invalidate_caches() stays available)
+    pass
+
+
 def invalidate_caches():
     """Drop every packed bf16 weight cache (exported as ``b200ir.invalidate_caches``).  The caches key on
     ``(data_ptr, tensor._version)``; in-place writes through ``p.data`` (EMA ``p.data.mul_().add_()``, re-initialisation
-    ``w.data.normal_()``, hand-written optimizers) change neither, so call this after such an update.  Optimizers that
-    update ``p`` itself (torch.optim.*, including the fused / foreach AdamW) bump ``_version`` and need nothing."""
+    ``w.data.normal_()``, hand-written optimizers) change neither, so call this after such an update.  Every torch.optim
+    optimizer step invalidates the caches by itself (global post-step hook above)."""
     bump_param_epoch()
 
 

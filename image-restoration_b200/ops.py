@@ -408,6 +408,63 @@ def gemm_tc(x, packed, Cout, ln_type=L.LN_NONE, res=None, out=None, out_dtype=No
     return out
 
 
+_GEOMF = {}
+
+
+def fused_proj_dw_geometry(C, Cout, gate):
+    """(kf, nrows) of the packed weight of the fused LN + 1x1 + depthwise kernel, or None if (C, Cout) is unsupported."""
+    key = (C, Cout, bool(gate))
+    if key not in _GEOMF:
+        kf, nr = _C.c_int(0), _C.c_int(0)
+        rc = lib.b200ir_fused_proj_dw_geometry(C, Cout, int(bool(gate)), _C.byref(kf), _C.byref(nr))
+        _GEOMF[key] = (kf.value, nr.value) if rc == 0 else None
+    return _GEOMF[key]
+
+
+def ln_proj_dw_usable(x, Cout, gate):
+    B, C, H, W_ = x.shape
+    return (x.dtype == torch.bfloat16 and x.data_ptr() % 16 == 0 and (B == 1 or x.stride(0) % 8 == 0)
+            and lib.b200ir_ln_proj_dw_supported(C, Cout, H, W_, int(bool(gate))) == 1)
+
+
+def pack_fused_proj_dw(w, bias, ln_type, ln_w, ln_b, Cout, gate):
+    """Pack the fp32 1x1 weight [Ctot, C] (Ctot = 2*Cout with the gate, Cout without) for ln_proj_dw: bf16 [nrows, kf]."""
+    Ctot, Cin = w.shape[0], w.shape[1]
+    if Ctot != (2 * Cout if gate else Cout):
+        raise ValueError("pack_fused_proj_dw: weight rows do not match Cout / gate")
+    geo = fused_proj_dw_geometry(Cin, Cout, gate)
+    if geo is None:
+        raise ValueError(f"pack_fused_proj_dw: ({Cin},{Cout}) unsupported")
+    kf, nrows = geo
+    wf = torch.empty((nrows, kf), device=w.device, dtype=torch.bfloat16)
+    with _timed("pack_fused_proj_dw", Cin, Cout, int(bool(gate))):
+        rc = lib.b200ir_pack_fused_proj_dw(_par(w, "w", Ctot * Cin), _par(bias, "bias", Ctot), ln_type,
+                                           _par(ln_w, "ln_w", Cin if ln_type else None),
+                                           _par(ln_b, "ln_b", Cin if ln_type == L.LN_WITHBIAS else None), Cin, Cout,
+                                           int(bool(gate)), wf.data_ptr(), _stream())
+    L.check(rc, "b200ir_pack_fused_proj_dw")
+    return wf
+
+
+def ln_proj_dw(x, wf, dw_w, dw_b, ln_type, Cout, gate, out=None):
+    """out = [gelu-gate of] dwconv3x3(conv1x1(LN(x))) in ONE kernel; `wf` = pack_fused_proj_dw(...)."""
+    B, Cin, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if xdt != L.BF16:
+        raise ValueError("ln_proj_dw: activations must be bfloat16")
+    if out is None:
+        out = torch.empty((B, Cout, H, W_), device=x.device, dtype=torch.bfloat16)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != L.BF16 or tuple(out.shape) != (B, Cout, H, W_):
+        raise ValueError("ln_proj_dw: out must be bfloat16 [B, Cout, H, W]")
+    Ctot = 2 * Cout if gate else Cout
+    with _timed("ln_proj_dw", B, Cin, Cout, H, W_, int(bool(gate))):
+        rc = lib.b200ir_ln_proj_dw_fwd(xp, xbs, wf.data_ptr(), _par(dw_w, "dw_w", Ctot * 9), _par(dw_b, "dw_b", Ctot),
+                                       ln_type, yp, ybs, B, Cin, Cout, H, W_, int(bool(gate)), _stream())
+    L.check(rc, "b200ir_ln_proj_dw_fwd")
+    return out
+
+
 _GEOM3 = {}
 
 

@@ -162,6 +162,20 @@ int b200ir_gemm_tc_fwd_ex(const void* x, int64_t x_bstride, const void* wp, int 
                           const void* res, int64_t res_bstride, int res_dtype, void* y, int64_t y_bstride, int y_dtype,
                           int B, int Cin, int Cout, int64_t HW, int variant, b200ir_stream_t stream);
 
+/* LayerNorm + 1x1 conv + depthwise 3x3 (+ GELU gate) as ONE kernel (fused_ln_proj_dw.cu): the widest tensor of the
+ * block never reaches HBM.  gate = 1: GDFN, out[c] = gelu(dw(t)[c]) * dw(t)[c+Cout] with t = project_in(norm2(x)), Cout =
+ * hidden_features, conv weights w [2*Cout][C], dw_w [2*Cout][9] (Restormer.py:88-91).  gate = 0: MDTA front end,
+ * out = qkv_dwconv(qkv(norm1(x))), Cout = 3*C (Restormer.py:114).  x, y bf16 NCHW.  wf = b200ir_pack_fused_proj_dw(...)
+ * (bf16 [nrows][kf], sizes from b200ir_fused_proj_dw_geometry): LayerNorm gamma folded into the weights, bias + W.beta
+ * carried by two constant-one K rows.  b200ir_ln_proj_dw_supported: 1 if the shape fits (C <= 240, shared memory). */
+int b200ir_fused_proj_dw_geometry(int C, int Cout, int gate, int* kf, int* nrows);
+int b200ir_pack_fused_proj_dw(const float* w, const float* bias, int ln_type, const float* ln_w, const float* ln_b,
+                              int C, int Cout, int gate, void* wf, b200ir_stream_t stream);
+int b200ir_ln_proj_dw_supported(int C, int Cout, int H, int W, int gate);
+int b200ir_ln_proj_dw_fwd(const void* x, int64_t x_bstride, const void* wf, const float* dw_w, const float* dw_b,
+                          int ln_type, void* y, int64_t y_bstride, int B, int C, int Cout, int H, int W, int gate,
+                          b200ir_stream_t stream);
+
 /* Dense 3x3 conv (pad 1, +bias) on the same tcgen05 kernel: 9 tap-shifted GEMMs accumulated in TMEM, zero padding
  * from TMA out-of-bounds fill, PixelUnshuffle(2)/PixelShuffle(2) folded into the store (Downsample / Upsample,
  * Restormer.py:171-189).  x bf16 NHWC with Cin%8==0; wp/st from b200ir_pack_conv3x3 (w fp32 [Cout,Cin,3,3]). */
