@@ -30,6 +30,8 @@ def main():
     which = sys.argv[1] if len(sys.argv) > 1 else "all"
     B = 16
     levels = [(96, 255, 256), (48, 127, 256), (96, 255, 128), (192, 510, 64)]
+    if os.environ.get("FUSED_LEVELS"):
+        levels = levels[:int(os.environ["FUSED_LEVELS"])]
     g = torch.Generator().manual_seed(0)
     rows = []
     for C, Hd, HW in levels:
