@@ -182,6 +182,27 @@ def _ln_conv1x1_fwd(x, w, bias, ln_type, ln_w, ln_b, res, out=None, out_dtype=No
     return ops.ln_conv1x1(x, _p(w), _p(bias), ln_type, _p(ln_w), _p(ln_b), res, out=out, out_dtype=out_dtype)
 
 
+USE_FUSED = True  # inference: LN + 1x1 + depthwise 3x3 (+gate) as one kernel where the shape is supported (fused_ln_proj_dw.cu)
+
+
+def fused_ln_proj_dw(x, conv_w, conv_b, dw_w, dw_b, ln_type, ln_w, ln_b, cout, gate, cache=None, key=None):
+    """out = [gate of] dwconv3x3(conv1x1(LN(x))) in ONE kernel, or None when the fused kernel does not apply (autograd
+    needed, fp32 activations, unsupported shape): the caller then runs the two-kernel path.  Reference:
+    Restormer.py:88-91 (gate = True) / :114 (gate = False)."""
+    if not USE_FUSED or ln_type == L.LN_NONE or _needs_grad(x, conv_w, conv_b, dw_w, dw_b, ln_w, ln_b):
+        return None
+    if not ops.ln_proj_dw_usable(x, cout, gate):
+        return None
+    sig = _sig(conv_w, conv_b, ln_w, ln_b) + (ln_type, "fused")
+    ent = cache.get(key) if cache is not None else None
+    if ent is None or ent[0] != sig:
+        ctot, cin = conv_w.shape[0], conv_w.shape[1]
+        ent = (sig, ops.pack_fused_proj_dw(_p(conv_w).reshape(ctot, cin), _p(conv_b), ln_type, _p(ln_w), _p(ln_b), cout, gate))
+        if cache is not None:
+            cache[key] = ent
+    return ops.ln_proj_dw(x, ent[1], _p(dw_w), _p(dw_b), ln_type, cout, gate)
+
+
 def dwconv3x3(x, w, bias):
     if _needs_grad(x, w, bias):
         return _DwConv.apply(x, w, bias)

@@ -86,10 +86,14 @@ class FeedForward(nn.Module):
     def _run(self, x, norm=None, res=None, out=None):
         ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
         cache = self.__dict__.setdefault("_b200ir_cache", {})
-        t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None,
-                         cache=cache, key=("in", id(norm)))
-        g = A.dwconv3x3_gelu_gate(t, self.dwconv.weight, self.dwconv.bias)
-        del t
+        hd = self.project_out.in_channels
+        g = A.fused_ln_proj_dw(x, self.project_in.weight, self.project_in.bias, self.dwconv.weight, self.dwconv.bias,
+                               ln_type, lw, lb, hd, True, cache=cache, key=("fin", id(norm)))
+        if g is None:   # training / fp32 / shapes the fused kernel does not take: two kernels, 2*hd channels through HBM
+            t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None,
+                             cache=cache, key=("in", id(norm)))
+            g = A.dwconv3x3_gelu_gate(t, self.dwconv.weight, self.dwconv.bias)
+            del t
         return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
                             cache=cache, key="out")
 
