@@ -20,7 +20,7 @@ GATE_CASES = [
     (96, 255, 9, 72, 1, False),      # ragged: 2 strips, H not a multiple of the band height
     (48, 127, 24, 256, 1, True),     # 5 strips
     (64, 128, 16, 24, 3, True),      # MoCE-IR ffn factor 2 (Hd = 2C), plane narrower than one strip
-    (192, 510, 16, 64, 1, False),    # 4 channel blocks, 256-column weight tiles
+    (128, 340, 16, 64, 1, False),    # 3 channel blocks, 3 K blocks of weights
     (96, 255, 70, 56, 1, False),     # several bands per strip
     (32, 85, 8, 16, 2, True),
 ]
@@ -74,7 +74,7 @@ PLAIN_CASES = [
     (48, 144, 16, 64, 1, False),
     (96, 288, 24, 128, 2, True),
     (96, 288, 9, 72, 1, False),
-    (192, 576, 16, 64, 1, True),
+    (128, 384, 16, 64, 1, True),
     (32, 96, 8, 16, 2, False),
 ]
 
@@ -116,3 +116,13 @@ def test_fused_full_size_properties():
     torch.cuda.synchronize()
     assert torch.equal(y[3:4], y1)
     assert rel_err(y.float(), y3.float()) < 8e-3
+
+
+def test_fused_unsupported_shapes_fall_back():
+    """C = 192 (weights 128 KB + three 26 KB activation stages + output staging > 227 KB of shared memory) and C = 384 are
+    not taken by the fused kernel: `ln_proj_dw_usable` says so and FeedForward keeps the two-kernel path there."""
+    from b200ir import ops
+    for C, Hd in ((192, 510), (384, 1021), (40, 106)):
+        x = torch.zeros(1, C, 16, 64, device="cuda", dtype=torch.bfloat16)
+        assert not ops.ln_proj_dw_usable(x, Hd, True)
+    assert not ops.ln_proj_dw_usable(torch.zeros(1, 96, 16, 64, device="cuda"), 255, True)   # fp32 activations
