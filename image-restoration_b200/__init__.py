@@ -4,8 +4,10 @@ from .modules import (Attention, BiasFree_LayerNorm, CrossAttention, GatedMDTA, 
                       Restormer, TransformerBlock, Upsample, WithBias_LayerNorm)
 
 from .dropin import accelerate  # noqa: F401
+from .moce import (AdapterLayer, DecoderBlock, DecoderResidualGroup, FFTAttention, FrequencyEmbedding, HighPassConv2d,  # noqa: F401
+                   ModExpert, MoCEIR, RoutingFunction)
 from .autograd_ops import invalidate_caches  # noqa: F401
 from .training import AdamW, GraphedForward, GraphedTrainStep, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
 
-__all__ = ["accelerate", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+__all__ = ["accelerate", "MoCEIR", "DecoderBlock", "DecoderResidualGroup", "AdapterLayer", "ModExpert", "FFTAttention", "RoutingFunction", "FrequencyEmbedding", "HighPassConv2d", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
            "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -66,6 +66,10 @@ SIGNATURES = {
     "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
     "b200ir_l1_loss_bwd": [_vp, _i, _vp, _i, _i64, _vp, _vp, _i, _vp],
+    "b200ir_circconv_patch": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_ew": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i64, _i, _vp],
+    "b200ir_scale_rows": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i64, _i, _vp],
+    "b200ir_spatial_mean": [_vp, _i64, _i, _vp, _i, _i, _i64, _i, _vp],
     "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],
     "b200ir_adamw_step_ex": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _i, _vp, _f, _vp],
 }

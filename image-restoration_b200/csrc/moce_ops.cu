@@ -1,0 +1,181 @@
+// moce_ops.cu — the MoCE-IR decoder pieces that are not a Restormer block: the FFT expert's per-patch
+// spectral product, the small elementwise gates around it, and the global average pools of the router / frequency
+// embedding.  Reference: /root/reference/moce_ir.py FFTAttention :373-422, ModExpert.process :548-560,
+// RoutingFunction.gate (AdaptiveAvgPool2d) :703-707, FrequencyEmbedding.forward :1068-1075.
+//
+// FFTAttention computes, per p x p patch and channel, irfft2(rfft2(q) * rfft2(k)): by the convolution theorem that is
+// the CIRCULAR CONVOLUTION of the two real patches,
+//     out[i, j] = sum_{a, b} q[a, b] * k[(i - a) mod p, (j - b) mod p],
+// evaluated here directly from shared memory in fp32 (p in {4, 8, 16, 32}: at most 1024 x 1024 MACs per patch, no FFT
+// library, no complex arithmetic, exact zero padding of ragged planes like F.pad at :391).  The two gradients are
+// circular cross-correlations and run on the same kernel (mode 1): dq = corr(dout, k), dk = corr(dout, q).
+#include "common.cuh"
+
+namespace b200ir {
+
+// mode 0: y = a (*) b (circular convolution);  mode 1: y[s] = sum_i a[i] * b[(i - s) mod p]  (correlation of a with b)
+template <typename T>
+__global__ void __launch_bounds__(256)
+circconv_patch_kernel(const T* __restrict__ a, int64_t a_bs, const T* __restrict__ b, int64_t b_bs, T* __restrict__ y,
+                      int64_t y_bs, int C, int H, int W, int p, int npx, int mode) {
+  extern __shared__ float sm[];
+  float* sa = sm;
+  float* sb = sm + p * p;
+  const int patch = blockIdx.x, c = blockIdx.y, n = blockIdx.z;
+  const int py = patch / npx, px = patch - py * npx;
+  const int y0 = py * p, x0 = px * p, pp = p * p, msk = p - 1;
+  const int lg = 31 - __clz(p);
+  const int64_t plane = (int64_t)c * H * W;
+  for (int i = threadIdx.x; i < pp; i += blockDim.x) {
+    const int r = i >> lg, q = i & msk;
+    const bool in = (y0 + r) < H && (x0 + q) < W;
+    const int64_t off = plane + (int64_t)(y0 + r) * W + (x0 + q);
+    sa[i] = in ? to_f<T>(a[(int64_t)n * a_bs + off]) : 0.f;
+    sb[i] = in ? to_f<T>(b[(int64_t)n * b_bs + off]) : 0.f;
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < pp; o += blockDim.x) {
+    const int oi = o >> lg, oj = o & msk;
+    if (y0 + oi >= H || x0 + oj >= W) continue;
+    float acc = 0.f;
+    if (mode == 0) {
+      for (int r = 0; r < p; ++r) {
+        const float* ar = sa + r * p;
+        const float* br = sb + ((oi - r) & msk) * p;
+#pragma unroll 4
+        for (int q = 0; q < p; ++q) acc = fmaf(ar[q], br[(oj - q) & msk], acc);
+      }
+    } else {
+      for (int r = 0; r < p; ++r) {
+        const float* ar = sa + r * p;
+        const float* br = sb + ((r - oi) & msk) * p;
+#pragma unroll 4
+        for (int q = 0; q < p; ++q) acc = fmaf(ar[q], br[(q - oj) & msk], acc);
+      }
+    }
+    y[(int64_t)n * y_bs + plane + (int64_t)(y0 + oi) * W + (x0 + oj)] = from_f<T>(acc);
+  }
+}
+
+// elementwise over NCHW views (batch stride free): op 0 y = a*b, 1 y = a*silu(b), 2 y = a+b, 3 y = gelu_erf(a),
+// 4 y = a * (1 - ...) unused; 5: y = b * (sigmoid(a) * (1 + a * (1 - sigmoid(a))))  (d silu(a)/da times b)
+template <typename T>
+__global__ void ew_kernel(const T* __restrict__ a, int64_t a_bs, const T* __restrict__ b, int64_t b_bs, T* __restrict__ y,
+                          int64_t y_bs, int64_t per, int op) {
+  const int n = blockIdx.y;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (int64_t)gridDim.x * blockDim.x) {
+    const float av = to_f<T>(a[(int64_t)n * a_bs + i]);
+    const float bv = b ? to_f<T>(b[(int64_t)n * b_bs + i]) : 0.f;
+    float r;
+    if (op == 0) r = av * bv;
+    else if (op == 1) r = av * (bv / (1.f + __expf(-bv)));
+    else if (op == 2) r = av + bv;
+    else if (op == 3) r = gelu_erf(av);
+    else {
+      const float s = 1.f / (1.f + __expf(-av));
+      r = bv * (s * (1.f + av * (1.f - s)));
+    }
+    y[(int64_t)n * y_bs + i] = from_f<T>(r);
+  }
+}
+
+// y[b] = (accumulate ? y[b] : 0) + g[b] * x[b]   (per-sample gate of an expert output, AdapterLayer.forward :672-676)
+template <typename T>
+__global__ void scale_rows_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restrict__ g, T* __restrict__ y,
+                                  int64_t y_bs, int64_t per, int accumulate) {
+  const int n = blockIdx.y;
+  const float gv = g[n];
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (int64_t)gridDim.x * blockDim.x) {
+    float r = gv * to_f<T>(x[(int64_t)n * x_bs + i]);
+    if (accumulate) r += to_f<T>(y[(int64_t)n * y_bs + i]);
+    y[(int64_t)n * y_bs + i] = from_f<T>(r);
+  }
+}
+
+// out[b, c] = mean over HW of x[b, c, :]  (fp32 accumulation, one warp per plane, fixed order)
+template <typename T>
+__global__ void spatial_mean_kernel(const T* __restrict__ x, int64_t x_bs, float* __restrict__ out, int B, int C,
+                                    int64_t HW, int gelu) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  const int c = warp % C, n = warp / C;
+  if (n >= B) return;
+  const T* p = x + (int64_t)n * x_bs + (int64_t)c * HW;
+  float s = 0.f;
+  for (int64_t i = lane; i < HW; i += 32) {
+    const float v = to_f<T>(p[i]);
+    s += gelu ? gelu_erf(v) : v;
+  }
+  s = warp_sum(s);
+  if (lane == 0) out[(int64_t)n * C + c] = s / (float)HW;
+}
+
+}  // namespace b200ir
+
+using namespace b200ir;
+
+extern "C" int b200ir_circconv_patch(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, void* y,
+                                     int64_t y_bstride, int dtype, int B, int C, int H, int W, int patch, int mode,
+                                     b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(a && b && y && B > 0 && C > 0 && H > 0 && W > 0, "circconv_patch: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype) && (mode == 0 || mode == 1), "circconv_patch: bad dtype / mode");
+  B200IR_UNSUPPORTED(patch >= 2 && patch <= 32 && (patch & (patch - 1)) == 0, "circconv_patch: patch %d unsupported (2..32, power of 2)", patch);
+  B200IR_UNSUPPORTED(B <= 65535 && C <= 65535, "circconv_patch: B, C <= 65535");
+  const int npx = (W + patch - 1) / patch, npy = (H + patch - 1) / patch;
+  const dim3 grid((unsigned)(npx * npy), (unsigned)C, (unsigned)B);
+  const size_t smem = (size_t)2 * patch * patch * sizeof(float);
+  const int threads = patch * patch >= 256 ? 256 : (patch * patch < 32 ? 32 : patch * patch);
+  if (dtype == B200IR_BF16)
+    circconv_patch_kernel<bf16><<<grid, threads, smem, (cudaStream_t)stream>>>((const bf16*)a, a_bstride, (const bf16*)b,
+                                                                              b_bstride, (bf16*)y, y_bstride, C, H, W,
+                                                                              patch, npx, mode);
+  else
+    circconv_patch_kernel<float><<<grid, threads, smem, (cudaStream_t)stream>>>((const float*)a, a_bstride,
+                                                                               (const float*)b, b_bstride, (float*)y,
+                                                                               y_bstride, C, H, W, patch, npx, mode);
+  return check_launch("circconv_patch");
+}
+
+extern "C" int b200ir_ew(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, void* y, int64_t y_bstride,
+                         int dtype, int B, int64_t per_sample, int op, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(a && y && B > 0 && B <= 65535 && per_sample > 0 && op >= 0 && op <= 5, "ew: bad args");
+  B200IR_CHECK_ARG(b || op == 3, "ew: second operand missing");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "ew: bad dtype");
+  int64_t gx = (per_sample + 255) / 256;
+  if (gx > num_sms() * 8) gx = num_sms() * 8;
+  const dim3 grid((unsigned)gx, (unsigned)B);
+  if (dtype == B200IR_BF16)
+    ew_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)a, a_bstride, (const bf16*)b, b_bstride, (bf16*)y,
+                                                            y_bstride, per_sample, op);
+  else
+    ew_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)a, a_bstride, (const float*)b, b_bstride,
+                                                             (float*)y, y_bstride, per_sample, op);
+  return check_launch("ew");
+}
+
+extern "C" int b200ir_scale_rows(const void* x, int64_t x_bstride, const float* g, void* y, int64_t y_bstride, int dtype,
+                                 int B, int64_t per_sample, int accumulate, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && g && y && B > 0 && B <= 65535 && per_sample > 0, "scale_rows: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "scale_rows: bad dtype");
+  int64_t gx = (per_sample + 255) / 256;
+  if (gx > num_sms() * 8) gx = num_sms() * 8;
+  const dim3 grid((unsigned)gx, (unsigned)B);
+  if (dtype == B200IR_BF16)
+    scale_rows_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_bstride, g, (bf16*)y, y_bstride,
+                                                                    per_sample, accumulate);
+  else
+    scale_rows_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, x_bstride, g, (float*)y, y_bstride,
+                                                                     per_sample, accumulate);
+  return check_launch("scale_rows");
+}
+
+extern "C" int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, float* out, int B, int C, int64_t HW,
+                                   int gelu, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && out && B > 0 && B <= 65535 && C > 0 && HW > 0, "spatial_mean: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "spatial_mean: bad dtype");
+  const unsigned grid = (unsigned)(((int64_t)B * C + 7) / 8);   // one warp per (sample, channel) plane, 8 warps per CTA
+  if (dtype == B200IR_BF16)
+    spatial_mean_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_bstride, out, B, C, HW, gelu);
+  else
+    spatial_mean_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, x_bstride, out, B, C, HW, gelu);
+  return check_launch("spatial_mean");
+}

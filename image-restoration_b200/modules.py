@@ -215,7 +215,9 @@ class CrossAttention(nn.Module):
         self.kv_dwconv = nn.Conv2d(dim * 2, dim * 2, kernel_size=7, stride=1, padding=7 // 2, groups=dim * 2, bias=bias)
         self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
 
-    def forward(self, x, y):
+    def forward(self, x, y, res=None):
+        """`res` (optional, not in the reference signature): added to the output inside the last GEMM's epilogue
+        (DecoderBlock's `mixer(x_a, x_s) + shortcut`, moce_ir.py:892)."""
         B, C, H, W = x.shape
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         tq = A.ln_conv1x1(x, self.q.weight, self.q.bias, L.LN_NONE, None, None, None, cache=cache, key="q")
@@ -229,7 +231,7 @@ class CrossAttention(nn.Module):
             ops.dwconv_kxk(tkv, A._p(self.kv_dwconv.weight), A._p(self.kv_dwconv.bias), out=qkv[:, C:])
         del tq, tkv
         return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
-                           None, cache=cache)
+                           res, cache=cache)
 
 
 ##########################################################################

@@ -741,3 +741,78 @@ def adamw_step(p, g, m, v, lr, beta1, beta2, eps, weight_decay, step, grad_scale
                                       int(bool(tick)), hyper_dev.data_ptr() if hyper_dev is not None else None,
                                       grad_scale, _stream())
     L.check(rc, "b200ir_adamw_step")
+
+
+# ---------------------------------------------------------------------------------------------------
+# MoCE-IR decoder pieces (csrc/moce_ops.cu)
+# ---------------------------------------------------------------------------------------------------
+EW_MUL, EW_SILU_MUL, EW_ADD, EW_GELU, EW_DSILU_MUL = 0, 1, 2, 3, 5
+
+
+def circconv_patch(a, b, patch, mode=0, out=None):
+    """Per (patch x patch) tile and channel: mode 0 circular convolution (= irfft2(rfft2(a) * rfft2(b)), FFTAttention,
+    moce_ir.py:406-412), mode 1 circular correlation sum_i a[i] b[i - s] (its gradients)."""
+    B, C, H, W_ = a.shape
+    if tuple(b.shape) != tuple(a.shape) or b.dtype != a.dtype:
+        raise ValueError("circconv_patch: operands must have the same shape and dtype")
+    ap, abs_, adt = _act(a, "a")
+    bp, bbs, _ = _act(b, "b")
+    if out is None:
+        out = torch.empty((B, C, H, W_), device=a.device, dtype=a.dtype)
+    yp, ybs, _ = _act(out, "out")
+    with _timed("circconv_patch", B, C, H, W_, patch, mode, adt):
+        rc = lib.b200ir_circconv_patch(ap, abs_, bp, bbs, yp, ybs, adt, B, C, H, W_, patch, mode, _stream())
+    L.check(rc, "b200ir_circconv_patch")
+    return out
+
+
+def ew(a, b, op, out=None):
+    """Elementwise on NCHW (or [B, N]) views: EW_MUL a*b, EW_SILU_MUL a*silu(b), EW_ADD a+b, EW_GELU gelu(a) (b None),
+    EW_DSILU_MUL b * d silu(a)/da."""
+    if a.dim() == 2:
+        a4 = a.view(a.shape[0], a.shape[1], 1, 1)
+        b4 = b.view(b.shape[0], b.shape[1], 1, 1) if b is not None else None
+        o4 = out.view(a4.shape) if out is not None else None
+        return ew(a4, b4, op, o4).view(a.shape)
+    B, C, H, W_ = a.shape
+    ap, abs_, adt = _act(a, "a")
+    bp, bbs = None, 0
+    if b is not None:
+        if tuple(b.shape) != tuple(a.shape) or b.dtype != a.dtype:
+            raise ValueError("ew: operands must have the same shape and dtype")
+        bp, bbs, _ = _act(b, "b")
+    if out is None:
+        out = torch.empty((B, C, H, W_), device=a.device, dtype=a.dtype)
+    yp, ybs, _ = _act(out, "out")
+    with _timed("ew", B, C * H * W_, op, adt):
+        rc = lib.b200ir_ew(ap, abs_, bp, bbs, yp, ybs, adt, B, C * H * W_, op, _stream())
+    L.check(rc, "b200ir_ew")
+    return out
+
+
+def scale_rows(x, g, out=None, accumulate=False):
+    """out[b] (+)= g[b] * x[b]; g fp32 [B]."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        if accumulate:
+            raise ValueError("scale_rows: accumulate needs an out tensor")
+        out = torch.empty((B, C, H, W_), device=x.device, dtype=x.dtype)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != xdt:
+        raise ValueError("scale_rows: dtype mismatch")
+    with _timed("scale_rows", B, C * H * W_, xdt):
+        rc = lib.b200ir_scale_rows(xp, xbs, _par(g, "g", B), yp, ybs, xdt, B, C * H * W_, int(accumulate), _stream())
+    L.check(rc, "b200ir_scale_rows")
+    return out
+
+
+def spatial_mean(x, gelu=False):
+    """fp32 [B, C] = mean over H, W of x (of gelu(x) with gelu=True)."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    out = torch.empty((B, C), device=x.device, dtype=torch.float32)
+    with _timed("spatial_mean", B, C, H * W_, xdt):
+        rc = lib.b200ir_spatial_mean(xp, xbs, xdt, out.data_ptr(), B, C, H * W_, int(gelu), _stream())
+    L.check(rc, "b200ir_spatial_mean")
+    return out

@@ -266,6 +266,24 @@ int b200ir_adamw_step_ex(float* p, const float* g, float* m, float* v, int64_t n
                          float eps, float weight_decay, int step, int* step_dev, int tick, const float* hyper_dev,
                          float grad_scale, b200ir_stream_t stream);
 
+/* ---- MoCE-IR decoder pieces (moce_ops.cu) ----
+ * Per p x p patch and channel: mode 0 y = circular convolution of a and b = irfft2(rfft2(a) * rfft2(b)) of FFTAttention
+ * (moce_ir.py:406-412; planes are zero-padded to a multiple of p like F.pad at :391 and cropped back); mode 1
+ * y[s] = sum_i a[i] b[(i - s) mod p] (the two gradients: dq = corr(dout, k), dk = corr(dout, q)).  p in {2,4,8,16,32}. */
+int b200ir_circconv_patch(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, void* y, int64_t y_bstride,
+                          int dtype, int B, int C, int H, int W, int patch, int mode, b200ir_stream_t stream);
+/* Elementwise over [B][per_sample] views: op 0 a*b, 1 a*silu(b) (ModExpert.process, moce_ir.py:556), 2 a+b, 3 gelu(a)
+ * (b NULL), 5 b * dsilu(a). */
+int b200ir_ew(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, void* y, int64_t y_bstride, int dtype,
+              int B, int64_t per_sample, int op, b200ir_stream_t stream);
+/* y[b] (+)= g[b] * x[b]: per-sample gate of an expert output (AdapterLayer.forward, moce_ir.py:672-676). */
+int b200ir_scale_rows(const void* x, int64_t x_bstride, const float* g, void* y, int64_t y_bstride, int dtype, int B,
+                      int64_t per_sample, int accumulate, b200ir_stream_t stream);
+/* out[b][c] = mean_hw x[b,c,:] (gelu = 1: mean of gelu(x)): AdaptiveAvgPool2d(1) of the router (moce_ir.py:703-707) and
+ * x.mean(dim=(-2,-1)) of FrequencyEmbedding (:1072).  out fp32 [B][C]. */
+int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, float* out, int B, int C, int64_t HW, int gelu,
+                        b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

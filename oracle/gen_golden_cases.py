@@ -62,3 +62,42 @@ def moce_block_params(dim, heads, f, bias, ln, nblk, seed):
             k = k.replace("norm1.", "norms.0.").replace("norm2.", "norms.1.").replace("attn.", "mixer.")
             sd[f"layers.{i}.{k}"] = v
     return sd
+
+
+# Whole MoCE-IR model (moce_ir.py:1080-1231; SURVEY.md §8 f1, BASELINE configs[2]): name, constructor kwargs, batch, H, W,
+# weight seed, input seed, torch.manual_seed set right before the forward (routing noise, moce_ir.py:741)
+MOCEIR_SMALL = dict(dim=16, levels=4, heads=[1, 2, 2, 4], num_blocks=[1, 1, 1, 2], num_dec_blocks=[1, 1, 2],
+                    ffn_expansion_factor=2, num_refinement_blocks=1, LayerNorm_type="WithBias", bias=False, rank=2,
+                    num_experts=4, depth_type="constant", stage_depth=[1, 1, 1], rank_type="spread", topk=1,
+                    with_complexity=False, complexity_scale="max")
+MOCEIR_CASES = [
+    ("moceir_small_b1_64", MOCEIR_SMALL, 1, 64, 64, 71, 72, 73),
+    ("moceir_small_b2_64x96", MOCEIR_SMALL, 2, 64, 96, 74, 75, 76),    # batch > 1: the eval-mode expert-sum quirk
+    ("moceir_small_bias_b1_32", dict(MOCEIR_SMALL, bias=True, LayerNorm_type="BiasFree", topk=2), 1, 32, 32, 77, 78, 79),
+]
+
+
+def synth_like(template_sd, seed):
+    """Seeded synthetic state_dict with the keys / shapes of `template_sd` (a freshly constructed model's state_dict):
+    LayerNorm weights near 1, biases small, temperatures near 1, conv / linear weights ~ U(-1, 1) / sqrt(fan_in); buffers
+    computed by the constructor (`complexity`) and the fixed high-pass kernel keep the constructor's value."""
+    import torch
+    g = torch.Generator().manual_seed(seed)
+    out = {}
+    for k in sorted(template_sd):
+        t = template_sd[k]
+        if k.endswith("complexity") or k.endswith("high_conv.0.conv.weight"):
+            out[k] = t.detach().clone()
+        elif k.endswith("temperature"):
+            out[k] = 1.0 + 0.3 * (torch.rand(t.shape, generator=g) - 0.5)
+        elif t.dim() == 1:
+            if k.endswith("body.weight"):
+                out[k] = 1.0 + 0.2 * (torch.rand(t.shape, generator=g) - 0.5)
+            else:
+                out[k] = 0.2 * (torch.rand(t.shape, generator=g) - 0.5)
+        else:
+            fan_in = 1
+            for d in t.shape[1:]:
+                fan_in *= d
+            out[k] = (torch.rand(t.shape, generator=g) - 0.5) * 2.0 / fan_in ** 0.5
+    return out
