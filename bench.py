@@ -179,6 +179,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-train", action="store_true", help="skip the cfg4 training-step leg")
     ap.add_argument("--no-hires", action="store_true", help="skip the cfg5 1024x1024 leg")
+    ap.add_argument("--no-moce", action="store_true", help="skip the cfg3 MoCE-IR leg")
     ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
     ap.add_argument("--no-incumbent", action="store_true", help="skip the eager-PyTorch-on-GPU informational leg")
     args = ap.parse_args()
@@ -299,6 +300,34 @@ def main():
                  "value": world * HR * HR / 1e6 / (ms_hr * 1e-3), "unit": "MP/s", "ms_per_step": ms_hr}
         del hin
 
+    # ---- MoCE-IR leg (BASELINE configs[2]): whole all-in-one model, 256x256 degraded inputs, batch 8, random-init experts --
+    moce = None
+    if not args.no_moce:
+        from oracle.gen_golden_cases import MOCEIR_CFG3, synth_like
+        MB = 8
+        mnet = b200ir.MoCEIR(**MOCEIR_CFG3)
+        mnet.load_state_dict(synth_like(mnet.state_dict(), 81), strict=True)
+        mnet = mnet.to(dev).eval().set_compute_dtype(cd)
+        min_ = [O.synth_image(MB, H, W, seed=555 + 10 * rank + i).to(dev) for i in range(4)]
+        with torch.no_grad():
+            for i in range(args.warmup):
+                mnet(min_[i % 4])
+            barrier()
+            ml0 = ops.LAUNCHES
+            e0.record()
+            for i in range(args.steps):
+                mnet(min_[i % 4])
+            e1.record()
+            barrier()
+        ms_mo = max_over_ranks(e0.elapsed_time(e1) / args.steps)
+        moce = {"workload": f"MoCEIR(dim=48,[4,6,6,8],dec[2,4,4],4 experts, top-1) forward, {H}x{W}, batch {MB}/GPU, {args.dtype}, "
+                            f"eval; BASELINE configs[2]; the router's softmax/top-k on [B,4] logits and one host sync per "
+                            f"decoder block are plain torch, everything tensor-sized is libb200ir",
+                "value": world * MB * H * W / 1e6 / (ms_mo * 1e-3), "unit": "MP/s", "ms_per_step": ms_mo,
+                "gpu_launches_per_step": (ops.LAUNCHES - ml0) // max(args.steps, 1)}
+        del mnet, min_
+        torch.cuda.empty_cache()
+
     # ---- training-step leg (BASELINE configs[3]): L1 + AdamW, 128x128 patches, batch 8 per GPU, DDP all-reduce --------
     train = None
     if not args.no_train:
@@ -361,6 +390,8 @@ def main():
         out["train_step"] = train
     if hires is not None:
         out["hires"] = hires
+    if moce is not None:
+        out["moce_ir"] = moce
     if incumbent is not None:
         out["incumbent_gpu"] = incumbent
     if not args.no_cpu_baseline:

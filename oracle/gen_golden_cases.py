@@ -70,7 +70,12 @@ MOCEIR_SMALL = dict(dim=16, levels=4, heads=[1, 2, 2, 4], num_blocks=[1, 1, 1, 2
                     ffn_expansion_factor=2, num_refinement_blocks=1, LayerNorm_type="WithBias", bias=False, rank=2,
                     num_experts=4, depth_type="constant", stage_depth=[1, 1, 1], rank_type="spread", topk=1,
                     with_complexity=False, complexity_scale="max")
+# BASELINE configs[2] / SURVEY.md 8d: the MoCE_IR model of MoCE-IR-main/src/options.py:54-84
+MOCEIR_CFG3 = dict(dim=48, num_blocks=[4, 6, 6, 8], num_dec_blocks=[2, 4, 4], levels=4, heads=[1, 2, 4, 8],
+                   num_refinement_blocks=4, topk=1, num_experts=4, rank=2, depth_type="constant", stage_depth=[1, 1, 1],
+                   rank_type="spread", complexity_scale="max")
 MOCEIR_CASES = [
+    ("moceir_cfg3_b1_64", MOCEIR_CFG3, 1, 64, 64, 81, 82, 83),         # the real cfg3 network at a CPU-affordable size
     ("moceir_small_b1_64", MOCEIR_SMALL, 1, 64, 64, 71, 72, 73),
     ("moceir_small_b2_64x96", MOCEIR_SMALL, 2, 64, 96, 74, 75, 76),    # batch > 1: the eval-mode expert-sum quirk
     ("moceir_small_bias_b1_32", dict(MOCEIR_SMALL, bias=True, LayerNorm_type="BiasFree", topk=2), 1, 32, 32, 77, 78, 79),
