@@ -1,6 +1,6 @@
 """b200ir — B200-native (sm_100a) Restormer-family transformer block behind the reference's nn.Module API."""
 from . import _lib, ops  # noqa: F401  (fails loudly if libb200ir.so is missing)
-from .modules import (Attention, BiasFree_LayerNorm, CrossAttention, GatedMDTA, GatedTransformerBlock, Downsample, EncoderBlock, EncoderResidualGroup, FeedForward, LayerNorm, OverlapPatchEmbed,  # noqa: F401
+from .modules import (Attention, ElementwiseGatedAttention, GatedSpatialFFN, BiasFree_LayerNorm, CrossAttention, GatedMDTA, GatedTransformerBlock, Downsample, EncoderBlock, EncoderResidualGroup, FeedForward, LayerNorm, OverlapPatchEmbed,  # noqa: F401
                       Restormer, TransformerBlock, Upsample, WithBias_LayerNorm)
 
 from .dropin import accelerate  # noqa: F401
@@ -9,5 +9,5 @@ from .moce import (AdapterLayer, DecoderBlock, DecoderResidualGroup, FFTAttentio
 from .autograd_ops import invalidate_caches  # noqa: F401
 from .training import AdamW, GraphedForward, GraphedTrainStep, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
 
-__all__ = ["accelerate", "MoCEIR", "DecoderBlock", "DecoderResidualGroup", "AdapterLayer", "ModExpert", "FFTAttention", "RoutingFunction", "FrequencyEmbedding", "HighPassConv2d", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+__all__ = ["accelerate", "ElementwiseGatedAttention", "GatedSpatialFFN", "MoCEIR", "DecoderBlock", "DecoderResidualGroup", "AdapterLayer", "ModExpert", "FFTAttention", "RoutingFunction", "FrequencyEmbedding", "HighPassConv2d", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
            "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -35,6 +35,8 @@ SIGNATURES = {
     "b200ir_mdta_gram_nslab": [_i, _i, _i, _i64],
     "b200ir_mdta_gram_fwd": [_vp, _i64, _i, _i, _i, _i, _i64, _vp, _i, _i, _vp],
     "b200ir_mdta_softmax_fold_fwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "b200ir_mdta_softmax_fold_fwd_ex": [_vp, _i, _vp, _i, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_gelu_sigmoid_gate_fwd": [_vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i, _i, _vp],
     "b200ir_conv3x3_fwd": [_vp, _i64, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_copy_cast": [_vp, _i64, _i, _vp, _i64, _i, _i, _i64, _vp],
     "b200ir_gemm_tc_geometry": [_i, _i, C.POINTER(C.c_int), C.POINTER(C.c_int)],

@@ -215,8 +215,15 @@ def dwconv3x3_gelu_gate(x, w, bias):
     return ops.dwconv3x3_gelu_gate(x, _p(w), _p(bias))
 
 
-def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None, cache=None):
-    """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147)."""
+def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None, cache=None, dynamic_temp=None):
+    """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147).
+    `dynamic_temp` ([B] or [B,1,1,1], inference only): per-sample factor on the temperature
+    (experiment/RectiFormer.py:309-311)."""
+    if dynamic_temp is not None:
+        if _needs_grad(qkv, temperature, w_out, b_out, res, dynamic_temp):
+            raise RuntimeError("mdta_core: the dynamic-temperature variant is an inference path (no backward kernel)")
+        temperature = (_p(temperature).reshape(1, -1) * dynamic_temp.detach().float().reshape(-1, 1)).contiguous()
+        return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out, cache)[0]
     if _needs_grad(qkv, temperature, w_out, b_out, res):
         return _MdtaCore.apply(qkv, temperature, w_out, b_out, res, heads, cache)
     return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out, cache)[0]
@@ -237,13 +244,18 @@ def _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out=None, cache=N
     partials = ops.mdta_gram(qkv, heads)
     v = qkv[:, 2 * C:]
     if USE_TC and ops.gemm_tc_usable(v, C):
-        mp, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), packed=True,
-                                         want_attn=True)
+        mp, attn = ops.mdta_softmax_fold(partials, _temp(temperature), _p(w_out).reshape(C, C), packed=True, want_attn=True)
         y = ops.gemm_tc(v, (mp, _bias_st(b_out, C, mp.shape[1], qkv.device, cache)), C, L.LN_NONE, res, out=out)
     else:
-        m, attn = ops.mdta_softmax_fold(partials, _p(temperature).reshape(-1), _p(w_out).reshape(C, C), want_attn=True)
+        m, attn = ops.mdta_softmax_fold(partials, _temp(temperature), _p(w_out).reshape(C, C), want_attn=True)
         y = ops.ln_conv1x1(v, m, _p(b_out), L.LN_NONE, None, None, res, out=out, per_sample_w=True)
     return y, partials, attn
+
+
+def _temp(temperature):
+    """[heads] parameter view, or the [B, heads] per-sample (dynamic) temperature as it is."""
+    t = _p(temperature)
+    return t if t.dim() == 2 else t.reshape(-1)
 
 
 def _bias_st(bias, C, nrows, device, cache=None):

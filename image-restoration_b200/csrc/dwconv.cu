@@ -56,7 +56,7 @@ __device__ __forceinline__ void load_row(const T* __restrict__ plane, int r, int
   out[N + 1] = (x0 + N < W) ? to_f<T>(__ldg(row + N)) : 0.f;
 }
 
-template <typename T, bool GATE>
+template <typename T, int GATE>
 __global__ void __launch_bounds__(256)
 dwconv3x3_vec_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restrict__ w,
                      const float* __restrict__ bias, T* __restrict__ y, int64_t y_bs, int Cout, int H, int W,
@@ -115,13 +115,15 @@ dwconv3x3_vec_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restr
     }
     float outv[N];
 #pragma unroll
-    for (int i = 0; i < N; ++i) outv[i] = GATE ? gelu_erf(o[0][i]) * o[NIN - 1][i] : o[0][i];
+    for (int i = 0; i < N; ++i)
+      outv[i] = GATE == 2 ? gelu_erf(o[0][i]) / (1.f + __expf(-o[NIN - 1][i]))
+                          : (GATE ? gelu_erf(o[0][i]) * o[NIN - 1][i] : o[0][i]);
     *reinterpret_cast<typename Vec<T>::raw*>(oplane + (int64_t)yy * W + x0) = Vec<T>::pack(outv);
   }
 }
 
 // generic fallback: any W / alignment, one output pixel per thread
-template <typename T, bool GATE>
+template <typename T, int GATE>
 __global__ void __launch_bounds__(256)
 dwconv3x3_scalar_kernel(const T* __restrict__ x, int64_t x_bs, const float* __restrict__ w,
                         const float* __restrict__ bias, T* __restrict__ y, int64_t y_bs, int Cout, int H, int W,
@@ -152,10 +154,11 @@ dwconv3x3_scalar_kernel(const T* __restrict__ x, int64_t x_bs, const float* __re
       }
     o[k] = a;
   }
-  y[(int64_t)b * y_bs + (int64_t)c * HWp + (int64_t)yy * W + xx] = from_f<T>(GATE ? gelu_erf(o[0]) * o[1] : o[0]);
+  y[(int64_t)b * y_bs + (int64_t)c * HWp + (int64_t)yy * W + xx] =
+      from_f<T>(GATE == 2 ? gelu_erf(o[0]) / (1.f + __expf(-o[1])) : (GATE ? gelu_erf(o[0]) * o[1] : o[0]));
 }
 
-template <typename T, bool GATE>
+template <typename T, int GATE>
 static int launch_dwconv(const void* x, int64_t x_bs, const float* w, const float* bias, void* y, int64_t y_bs,
                          int B, int Cout, int H, int W, cudaStream_t st, int flip = 0) {
   constexpr int N = Vec<T>::N;
@@ -194,8 +197,8 @@ extern "C" int b200ir_dwconv3x3_fwd(const void* x, int64_t x_bstride, const floa
   if (dwconv_tma_supported(dtype, H, W, x_bstride, y_bstride, x, y))
     return dwconv_tma_launch<false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
   if (dtype == B200IR_BF16)
-    return launch_dwconv<bf16, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
-  return launch_dwconv<float, false>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
+    return launch_dwconv<bf16, 0>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
+  return launch_dwconv<float, 0>(x, x_bstride, w, bias, y, y_bstride, B, C, H, W, (cudaStream_t)stream);
 }
 
 extern "C" int b200ir_dwconv3x3_bwd_input(const void* dy, int64_t dy_bstride, const float* w, void* dx,
@@ -206,8 +209,8 @@ extern "C" int b200ir_dwconv3x3_bwd_input(const void* dy, int64_t dy_bstride, co
   if (dwconv_tma_supported(dtype, H, W, dy_bstride, dx_bstride, dy, dx))
     return dwconv_tma_launch<false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
   if (dtype == B200IR_BF16)
-    return launch_dwconv<bf16, false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
-  return launch_dwconv<float, false>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
+    return launch_dwconv<bf16, 0>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
+  return launch_dwconv<float, 0>(dy, dy_bstride, w, nullptr, dx, dx_bstride, B, C, H, W, (cudaStream_t)stream, 1);
 }
 
 extern "C" int b200ir_dwconv3x3_gelu_gate_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias,
@@ -218,6 +221,18 @@ extern "C" int b200ir_dwconv3x3_gelu_gate_fwd(const void* x, int64_t x_bstride, 
   if (dwconv_tma_supported(dtype, H, W, x_bstride, y_bstride, x, y))
     return dwconv_tma_launch<true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
   if (dtype == B200IR_BF16)
-    return launch_dwconv<bf16, true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
-  return launch_dwconv<float, true>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
+    return launch_dwconv<bf16, 1>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
+  return launch_dwconv<float, 1>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
+}
+
+// Split-gate FFN of the reference's RectiFormer experiment (experiment/RectiFormer.py:231-266):
+// out[c] = gelu(dw_content(t)[c]) * sigmoid(dw_gate(t)[c + Hd]); same kernel, gate function 2 (CUDA-core path).
+extern "C" int b200ir_dwconv3x3_gelu_sigmoid_gate_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias,
+                                                      void* y, int64_t y_bstride, int dtype, int B, int Hd, int H, int W,
+                                                      b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && w && y && B > 0 && Hd > 0 && H > 0 && W > 0, "dwconv3x3_gelu_sigmoid_gate: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "dwconv3x3_gelu_sigmoid_gate: bad dtype %d", dtype);
+  if (dtype == B200IR_BF16)
+    return launch_dwconv<bf16, 2>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
+  return launch_dwconv<float, 2>(x, x_bstride, w, bias, y, y_bstride, B, Hd, H, W, (cudaStream_t)stream);
 }

@@ -106,7 +106,7 @@ __device__ __forceinline__ float ordered_sum(const float* __restrict__ p, size_t
 // ---- stage 2a: slab reduce + normalise + temperature + row softmax.  grid (ceil(d/8), heads, B), 256 threads:
 // one warp per attention row (8 rows per block), so B*heads*d/8 blocks share the slab reduction.
 __global__ void __launch_bounds__(256)
-mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ temperature,
+mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ temperature, int temp_bs,
                     float* __restrict__ attn, int d) {
   extern __shared__ float sm[];
   float* nk = sm;             // [d]  max(||k_j||, eps)
@@ -128,7 +128,7 @@ mdta_softmax_kernel(const float* __restrict__ partials, int nslab, const float* 
     nq = fmaxf(sqrtf(s), 1e-12f);                                                             // (:121)
   }
   nq = __shfl_sync(0xffffffffu, nq, 0);
-  const float temp = temperature[h];
+  const float temp = temperature[(size_t)b * temp_bs + h];   // temp_bs = heads: per-sample (dynamic) temperature
   float* row = rowbuf + warp * d;
   float mx = -INFINITY;
   for (int j = lane; j < d; j += 32) {
@@ -289,6 +289,13 @@ extern "C" int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype,
 extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
                                             const float* w_out, float* m, float* attn, void* mp, int kpad, int nrows,
                                             int B, int C, int heads, b200ir_stream_t stream) {
+  return b200ir_mdta_softmax_fold_fwd_ex(partials, nslab, temperature, 0, w_out, m, attn, mp, kpad, nrows, B, C, heads,
+                                         stream);
+}
+
+extern "C" int b200ir_mdta_softmax_fold_fwd_ex(const float* partials, int nslab, const float* temperature,
+                                               int temp_per_sample, const float* w_out, float* m, float* attn, void* mp,
+                                               int kpad, int nrows, int B, int C, int heads, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(partials && temperature && w_out && attn && (m || mp) && nslab > 0 && B > 0 && C > 0 && heads > 0,
                    "mdta_softmax_fold: bad args");
   B200IR_CHECK_ARG(C % heads == 0 && B <= 65535 && heads <= 65535, "mdta_softmax_fold: bad C/heads/B");
@@ -297,7 +304,7 @@ extern "C" int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, co
   B200IR_UNSUPPORTED(d <= 128, "mdta_softmax_fold: head dim %d > 128 unsupported", d);
   cudaStream_t st = (cudaStream_t)stream;
   mdta_softmax_kernel<<<dim3((unsigned)((d + 7) / 8), (unsigned)heads, (unsigned)B), 256, (size_t)9 * d * sizeof(float),
-                        st>>>(partials, nslab, temperature, attn, d);
+                        st>>>(partials, nslab, temperature, temp_per_sample ? heads : 0, attn, d);
   int rc = check_launch("mdta_softmax");
   if (rc) return rc;
   // output rows per block (16 per register row RT): the largest of 64 / 32 / 16 that still gives every SM a block

@@ -182,6 +182,89 @@ class GatedMDTA(nn.Module):
         return self._run(x)
 
 
+##########################################################################
+## RectiFormer experiment variants (experiment/RectiFormer.py:231-325)
+class GatedSpatialFFN(nn.Module):
+    """Split-gate FFN: project_in -> chunk -> gelu(dwconv_content(content)) * sigmoid(dwconv_gate(gate)) -> project_out.
+    The two half-width depthwise convs are one launch (their weights form the [content | gate] weight of the same
+    kernel that runs GDFN, with the gate function gelu(a) * sigmoid(b))."""
+
+    def __init__(self, dim, ffn_expansion_factor, bias):
+        super().__init__()
+        hidden_features = int(dim * ffn_expansion_factor)
+        self.project_in = nn.Conv2d(dim, hidden_features * 2, kernel_size=1, bias=bias)
+        self.dwconv_gate = nn.Conv2d(hidden_features, hidden_features, kernel_size=3, stride=1, padding=1,
+                                     groups=hidden_features, bias=bias)
+        self.dwconv_content = nn.Conv2d(hidden_features, hidden_features, kernel_size=3, stride=1, padding=1,
+                                        groups=hidden_features, bias=bias)
+        self.project_out = nn.Conv2d(hidden_features, dim, kernel_size=1, bias=bias)
+
+    def _dw_pair(self):
+        ps = (self.dwconv_content.weight, self.dwconv_gate.weight, self.dwconv_content.bias, self.dwconv_gate.bias)
+        sig = A._sig(*ps)
+        ent = self.__dict__.get("_b200ir_dw")
+        if ent is None or ent[0] != sig:
+            w = torch.cat([ps[0].detach(), ps[1].detach()], 0).float().contiguous()
+            b = torch.cat([ps[2].detach(), ps[3].detach()], 0).float().contiguous() if ps[2] is not None else None
+            ent = (sig, w, b)
+            self.__dict__["_b200ir_dw"] = ent
+        return ent[1], ent[2]
+
+    def _run(self, x, norm=None, res=None, out=None):
+        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and x.requires_grad:
+            raise RuntimeError("GatedSpatialFFN is an inference path (no backward kernel for the sigmoid gate variant)")
+        ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None, cache=cache,
+                         key=("in", id(norm)))
+        w, b = self._dw_pair()
+        g = ops.dwconv3x3_gelu_sigmoid_gate(t, w, b)
+        del t
+        return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
+                            cache=cache, key="out")
+
+    def forward(self, x):
+        return self._run(x)
+
+
+class ElementwiseGatedAttention(nn.Module):
+    """MDTA with an element-wise sigmoid gate from its own branch (depthwise 3x3 -> 1x1 on x) between attn.v and
+    project_out, and an optional per-sample dynamic temperature (experiment/RectiFormer.py:270-325)."""
+
+    def __init__(self, dim, num_heads, bias):
+        super().__init__()
+        self.num_heads = num_heads
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.dim = dim
+        self.qkv = nn.Conv2d(dim, dim * 3, kernel_size=1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(dim * 3, dim * 3, kernel_size=3, stride=1, padding=1, groups=dim * 3, bias=bias)
+        self.gate_generator = nn.Sequential(
+            nn.Conv2d(dim, dim, kernel_size=3, stride=1, padding=1, groups=dim, bias=bias),
+            nn.Conv2d(dim, dim, kernel_size=1, bias=bias))
+        self.project_out = nn.Conv2d(dim, dim, kernel_size=1, bias=bias)
+
+    def _eye(self, device):
+        e = self.__dict__.get("_b200ir_eye")
+        if e is None or e.device != device:
+            e = torch.eye(self.dim, device=device, dtype=torch.float32).view(self.dim, self.dim, 1, 1)
+            self.__dict__["_b200ir_eye"] = e
+        return e
+
+    def forward(self, x, dynamic_temp=None, res=None):
+        cache = self.__dict__.setdefault("_b200ir_cache", {})
+        t = A.ln_conv1x1(x, self.qkv.weight, self.qkv.bias, L.LN_NONE, None, None, None, cache=cache, key="qkv")
+        qkv = A.dwconv3x3(t, self.qkv_dwconv.weight, self.qkv_dwconv.bias)
+        del t
+        gd = A.dwconv3x3(x, self.gate_generator[0].weight, self.gate_generator[0].bias)
+        gate = A.ln_conv1x1(gd, self.gate_generator[1].weight, self.gate_generator[1].bias, L.LN_NONE, None, None, None,
+                            cache=cache, key="gate")
+        u = A.mdta_core(qkv, self.temperature, self._eye(x.device), None, self.num_heads, None, cache=cache,
+                        dynamic_temp=dynamic_temp)                     # attn . v (identity fold)
+        ug = A.sigmoid_gate(u, gate)
+        return A.ln_conv1x1(ug, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res,
+                            cache=cache, key="out")
+
+
 class GatedTransformerBlock(nn.Module):
     """x = x + attn(norm1(x)); x = x + ffn(norm2(x)) with the gated attention (same file, :180-193)."""
 

@@ -236,6 +236,23 @@ def dwconv3x3_gelu_gate(x, w, bias=None, out=None):
     return out
 
 
+def dwconv3x3_gelu_sigmoid_gate(x, w, bias=None, out=None):
+    """out[c] = gelu(dw(x)[c]) * sigmoid(dw(x)[c + Hd]) (split-gate FFN, experiment/RectiFormer.py:231-266)."""
+    B, C2, H, W_ = x.shape
+    Hd = C2 // 2
+    xp, xbs, xdt = _act(x, "x")
+    if out is None:
+        out = torch.empty((B, Hd, H, W_), device=x.device, dtype=x.dtype)
+    yp, ybs, ydt = _act(out, "out")
+    if ydt != xdt or C2 % 2:
+        raise ValueError("dwconv3x3_gelu_sigmoid_gate: dtype / channel mismatch")
+    with _timed("dwconv3x3_gelu_sigmoid_gate", B, Hd, H, W_, xdt):
+        rc = lib.b200ir_dwconv3x3_gelu_sigmoid_gate_fwd(xp, xbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), yp, ybs,
+                                                        xdt, B, Hd, H, W_, _stream())
+    L.check(rc, "b200ir_dwconv3x3_gelu_sigmoid_gate_fwd")
+    return out
+
+
 def mdta_gram(qkv, heads, impl=L.IMPL_AUTO):
     """Partial Grams / norms per (b, head, HW-slab): fp32 [B, heads, nslab, d*d+2d]."""
     B, C3, H, W_ = qkv.shape
@@ -267,11 +284,14 @@ def mdta_softmax_fold(partials, temperature, w_out, want_attn=False, packed=Fals
         m = torch.empty((B, C, C), device=partials.device, dtype=torch.float32)
     global LAUNCHES
     LAUNCHES += 1  # two kernels (softmax, fold)
+    per_sample = temperature.numel() == B * heads and temperature.dim() == 2     # [B, heads]: dynamic temperature
     with _timed("mdta_softmax_fold", B, C, heads, nslab):
-        rc = lib.b200ir_mdta_softmax_fold_fwd(partials.data_ptr(), nslab, _par(temperature, "temperature", heads),
-                                              _par(w_out, "w_out", C * C), m.data_ptr() if m is not None else None,
-                                              attn.data_ptr(), mp.data_ptr() if mp is not None else None, kpad, nrows,
-                                              B, C, heads, _stream())
+        rc = lib.b200ir_mdta_softmax_fold_fwd_ex(partials.data_ptr(), nslab,
+                                                 _par(temperature, "temperature", B * heads if per_sample else heads),
+                                                 int(per_sample), _par(w_out, "w_out", C * C),
+                                                 m.data_ptr() if m is not None else None, attn.data_ptr(),
+                                                 mp.data_ptr() if mp is not None else None, kpad, nrows, B, C, heads,
+                                                 _stream())
     L.check(rc, "b200ir_mdta_softmax_fold_fwd")
     out = mp if packed else m
     return (out, attn) if want_attn else out

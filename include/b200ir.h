@@ -79,6 +79,16 @@ int b200ir_mdta_gram_fwd(const void* qkv, int64_t bstride, int dtype, int B, int
 int b200ir_mdta_softmax_fold_fwd(const float* partials, int nslab, const float* temperature,
                                  const float* w_out, float* m, float* attn, void* mp, int kpad, int nrows,
                                  int B, int C, int heads, b200ir_stream_t stream);
+/* Same with a per-sample temperature [B][heads] when temp_per_sample != 0: the dynamic temperature of the reference's
+ * RectiFormer experiment (temp = temperature * dynamic_temp[B,1,1,1], experiment/RectiFormer.py:309-311). */
+int b200ir_mdta_softmax_fold_fwd_ex(const float* partials, int nslab, const float* temperature, int temp_per_sample,
+                                    const float* w_out, float* m, float* attn, void* mp, int kpad, int nrows,
+                                    int B, int C, int heads, b200ir_stream_t stream);
+/* Split-gate FFN (experiment/RectiFormer.py:231-266): out[c] = gelu(dw(t)[c]) * sigmoid(dw(t)[c + Hd]); w [2*Hd][9] =
+ * dwconv_content | dwconv_gate. */
+int b200ir_dwconv3x3_gelu_sigmoid_gate_fwd(const void* x, int64_t x_bstride, const float* w, const float* bias, void* y,
+                                           int64_t y_bstride, int dtype, int B, int Hd, int H, int W,
+                                           b200ir_stream_t stream);
 
 /* Dense 3x3 conv, pad 1 (+bias) (+res) with PixelUnshuffle(2)/PixelShuffle(2) folded into the
  * store: OverlapPatchEmbed (Restormer.py:162-165), Downsample (:171-179), Upsample (:181-189),

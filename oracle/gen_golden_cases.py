@@ -106,3 +106,17 @@ def synth_like(template_sd, seed):
                 fan_in *= d
             out[k] = (torch.rand(t.shape, generator=g) - 0.5) * 2.0 / fan_in ** 0.5
     return out
+
+
+# RectiFormer experiment variants (experiment/RectiFormer.py:231-325): name, kind, dim, heads, ffn factor, bias, B, H, W, seed
+RECTI_CASES = [
+    ("recti_ffn_c32", "ffn", 32, 0, 2.66, True, 2, 16, 24, 91),
+    ("recti_ffn_c48_nobias", "ffn", 48, 0, 2.0, False, 1, 8, 40, 92),
+    ("recti_attn_c32_h2", "attn", 32, 2, 0, True, 2, 16, 24, 93),
+    ("recti_attn_dyn_c48_h1", "attn_dyn", 48, 1, 0, False, 3, 8, 16, 94),
+]
+# AdaIR Chanel_Cross_Attention (AdaIR-main/net/model.py:177-216): name, dim, heads, bias, B, H, W, seed
+ADAIR_CCA_CASES = [
+    ("adair_cca_c32_h2", 32, 2, True, 2, 12, 20, 95),
+    ("adair_cca_c48_h1_nobias", 48, 1, False, 1, 8, 8, 96),
+]

@@ -1,0 +1,57 @@
+"""Generate tests/golden/recti_*.npz and adair_cca_*.npz from the UNMODIFIED reference modules (build container only):
+``experiment/RectiFormer.py`` GatedSpatialFFN (:231-266) and ElementwiseGatedAttention (:270-325, with and without the
+per-sample dynamic temperature) and ``AdaIR-main/net/model.py`` Chanel_Cross_Attention (:177-216).  SURVEY.md §8 f2 / f3."""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+from oracle import restormer_oracle as O  # noqa: E402
+from oracle.gen_golden_cases import RECTI_CASES, ADAIR_CCA_CASES, synth_like  # noqa: E402
+
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def load(path, name):
+    spec = importlib.util.spec_from_file_location(name, path)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+def main():
+    RF = load("/root/reference/experiment/RectiFormer.py", "ref_rectiformer")
+    for name, kind, dim, heads, f, bias, b, h, w, seed in RECTI_CASES:
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        if kind == "ffn":
+            mod = RF.GatedSpatialFFN(dim, f, bias).eval()
+        else:
+            mod = RF.ElementwiseGatedAttention(dim, heads, bias).eval()
+        mod.load_state_dict(synth_like(mod.state_dict(), seed), strict=True)
+        with torch.no_grad():
+            if kind == "attn_dyn":
+                dt = (torch.rand(b, generator=torch.Generator().manual_seed(seed + 7)) * 2).view(b, 1, 1, 1)
+                y = mod(x, dt)
+            else:
+                y = mod(x)
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=y.numpy(), keys=np.array(sorted(mod.state_dict())))
+        print(name, tuple(y.shape))
+    AD = load("/root/reference/AdaIR-main/net/model.py", "ref_adair_model")
+    for name, dim, heads, bias, b, h, w, seed in ADAIR_CCA_CASES:
+        mod = AD.Chanel_Cross_Attention(dim, heads, bias).eval()
+        mod.load_state_dict(synth_like(mod.state_dict(), seed), strict=True)
+        x = O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1
+        y2 = O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1
+        with torch.no_grad():
+            y = mod(x, y2)
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=y.numpy(), keys=np.array(sorted(mod.state_dict())))
+        print(name, tuple(y.shape))
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,80 @@
+"""SURVEY.md §8 f2 / f3 variants against outputs of the UNMODIFIED reference modules (oracle/gen_golden_recti.py):
+RectiFormer's split-gate FFN and element-wise gated attention with per-sample dynamic temperature
+(experiment/RectiFormer.py:231-325) and AdaIR's Chanel_Cross_Attention (AdaIR-main/net/model.py:177-216)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import restormer_oracle as O
+from oracle.gen_golden_cases import ADAIR_CCA_CASES, RECTI_CASES, synth_like
+
+pytestmark = pytest.mark.gpu
+
+
+def _rel(a, b):
+    return ((a.double() - b.double()).norm() / b.double().norm().clamp_min(1e-30)).item()
+
+
+@pytest.mark.parametrize("case", RECTI_CASES, ids=[c[0] for c in RECTI_CASES])
+def test_rectiformer_variants_vs_reference_golden(case):
+    import b200ir
+    name, kind, dim, heads, f, bias, b, h, w, seed = case
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    mod = b200ir.GatedSpatialFFN(dim, f, bias) if kind == "ffn" else b200ir.ElementwiseGatedAttention(dim, heads, bias)
+    assert sorted(mod.state_dict()) == [str(k) for k in gold["keys"]]
+    mod.load_state_dict(synth_like(mod.state_dict(), seed), strict=True)
+    mod = mod.cuda().eval()
+    x = (O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1).cuda()
+    ref = torch.from_numpy(gold["y"])
+    with torch.no_grad():
+        if kind == "attn_dyn":
+            dt = (torch.rand(b, generator=torch.Generator().manual_seed(seed + 7)) * 2).view(b, 1, 1, 1).cuda()
+            y32 = mod(x, dt).cpu()
+            y16 = mod(x.bfloat16(), dt).float().cpu()
+        else:
+            y32 = mod(x).cpu()
+            y16 = mod(x.bfloat16()).float().cpu()
+    assert (y32 - ref).abs().max() <= 1e-4 * max(1.0, ref.abs().max().item()), float((y32 - ref).abs().max())
+    assert _rel(y16, ref) < 2e-2, _rel(y16, ref)
+
+
+@pytest.mark.parametrize("case", ADAIR_CCA_CASES, ids=[c[0] for c in ADAIR_CCA_CASES])
+def test_adair_chanel_cross_attention_vs_reference_golden(case):
+    """b200ir.CrossAttention with a 3x3 kv depthwise conv == AdaIR's Chanel_Cross_Attention (same state_dict keys)."""
+    import b200ir
+    name, dim, heads, bias, b, h, w, seed = case
+    gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+    mod = b200ir.CrossAttention(dim, heads, bias)
+    mod.kv_dwconv = torch.nn.Conv2d(dim * 2, dim * 2, kernel_size=3, stride=1, padding=1, groups=dim * 2, bias=bias)
+    assert sorted(mod.state_dict()) == [str(k) for k in gold["keys"]]
+    mod.load_state_dict(synth_like(mod.state_dict(), seed), strict=True)
+    mod = mod.cuda().eval()
+    x = (O.synth_image(b, h, w, seed=seed + 100, c=dim) * 2 - 1).cuda()
+    y2 = (O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1).cuda()
+    ref = torch.from_numpy(gold["y"])
+    with torch.no_grad():
+        y32 = mod(x, y2).cpu()
+        y16 = mod(x.bfloat16(), y2.bfloat16()).float().cpu()
+    assert (y32 - ref).abs().max() <= 1e-4 * max(1.0, ref.abs().max().item())
+    assert _rel(y16, ref) < 2e-2
+
+
+def test_accelerate_adopts_adair_num_head_cross_attention():
+    """dropin.accelerate() takes a module with Chanel_Cross_Attention's structure (`num_head`, 3x3 kv dwconv)."""
+    import b200ir
+    from torch_models import RefAdaIRFusion
+    torch.manual_seed(2)
+    net = RefAdaIRFusion(32, 2)
+    x = O.synth_image(2, 16, 24, seed=6, c=32) * 2 - 1
+    with torch.no_grad():
+        ref = net(x)
+    net = net.cuda()
+    net, stats = b200ir.accelerate(net, verify=True)
+    assert stats == {"cross_attention": 1}, stats
+    assert isinstance(net.cca, b200ir.CrossAttention) and net.cca.num_heads == 2
+    with torch.no_grad():
+        got = net(x.cuda()).cpu()
+    assert (got - ref).abs().max() <= 2e-4 * max(1.0, ref.abs().max().item())

@@ -175,3 +175,29 @@ class RefGatedMDTA(nn.Module):
 
     def forward(self, x):
         return O.gated_attention(x, dict(self.named_parameters()), "", self.num_heads, self.gate_type)
+
+
+class RefChanelCrossAttention(RefCrossAttention):
+    """Stand-in with the structure of AdaIR's Chanel_Cross_Attention (AdaIR-main/net/model.py:177-216): CrossAttention
+    with a 3x3 kv depthwise conv and the head count spelled ``num_head``."""
+
+    def __init__(self, dim, num_head, bias):
+        super().__init__(dim, num_head, bias, kv_kernel=3)
+        del self.num_heads
+        self.num_head = num_head
+
+    def forward(self, x, y):
+        return O.cross_attention(x, y, dict(self.named_parameters()), "", self.num_head)
+
+
+class RefAdaIRFusion(nn.Module):
+    """x -> cross attention between two projections of x, the way AdaIR's FreRefine-style fusion calls it."""
+
+    def __init__(self, dim=32, heads=2):
+        super().__init__()
+        self.a = nn.Conv2d(dim, dim, 1)
+        self.b = nn.Conv2d(dim, dim, 1)
+        self.cca = RefChanelCrossAttention(dim, heads, True)
+
+    def forward(self, x):
+        return self.cca(self.a(x), self.b(x)) + x
