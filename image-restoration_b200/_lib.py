@@ -72,6 +72,12 @@ SIGNATURES = {
     "b200ir_ew": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i64, _i, _vp],
     "b200ir_scale_rows": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i64, _i, _vp],
     "b200ir_spatial_mean": [_vp, _i64, _i, _vp, _i, _i, _i64, _i, _vp],
+    "b200ir_lowfreq_split": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_bilinear_resize": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_spatial_gate": [_vp, _i64, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
+    "b200ir_spatial_max": [_vp, _i64, _i, _vp, _i, _i, _i64, _vp],
+    "b200ir_fre_combine": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_affine2": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],
     "b200ir_adamw_step_ex": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _i, _vp, _f, _vp],
 }

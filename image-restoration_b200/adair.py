@@ -1,0 +1,112 @@
+"""AdaIR extras: mirrors of ``Chanel_Cross_Attention``, ``SpatialGate``, ``ChannelGate``, ``FreRefine`` and
+``FreModule`` of ``/root/reference/AdaIR-main/net/model.py:177-372`` with the reference's parameter names, running on
+libb200ir kernels (``csrc/adair_ops.cu`` + the two-source MDTA).  Inference path (AdaIR's TransformerBlocks themselves are
+plain Restormer blocks and are taken by ``modules.TransformerBlock`` / ``dropin.accelerate``).
+
+FreModule.fft keeps only the spectrum bins inside a centred rectangle of half-size (h_, w_) = int(H // 128 * t) as the
+"low" band; it is synthesised here from those few bins directly instead of fft2 -> mask -> ifft2 (see adair_ops.cu).
+The tiny tensors of the threshold / channel-gate MLPs ([B, dim] and smaller) go through the 1x1-conv kernel; their
+ReLU / sigmoid / int() on a few dozen numbers are torch ops.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import _lib as L
+from . import autograd_ops as A
+from . import ops
+from .modules import CrossAttention
+
+
+def _mm(x2d, conv):
+    """[B, Cin] fp32 through a bias-free 1x1 nn.Conv2d's weight -> [B, Cout]."""
+    w = A._p(conv.weight).reshape(conv.out_channels, conv.in_channels)
+    y = ops.ln_conv1x1(x2d.float().contiguous().view(x2d.shape[0], x2d.shape[1], 1, 1), w, A._p(conv.bias))
+    return y.view(x2d.shape[0], -1)
+
+
+class Chanel_Cross_Attention(CrossAttention):
+    """model.py:177-216: CrossAttention whose k, v depthwise conv is 3x3 and whose head count is spelled ``num_head``."""
+
+    def __init__(self, dim, num_head, bias):
+        super().__init__(dim, num_head, bias)
+        self.num_head = num_head
+        self.kv_dwconv = nn.Conv2d(dim * 2, dim * 2, kernel_size=3, stride=1, padding=1, groups=dim * 2, bias=bias)
+
+    def forward(self, x, y, res=None):
+        assert x.shape == y.shape, 'The shape of feature maps from image and features are not equal!'
+        return super().forward(x, y, res=res)
+
+
+class SpatialGate(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.spatial = nn.Conv2d(2, 1, kernel_size=7, padding=3, bias=False)
+
+    def forward(self, x):
+        return ops.spatial_gate(x, A._p(self.spatial.weight))          # fp32 [B, H*W]
+
+
+class ChannelGate(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.avg = nn.AdaptiveAvgPool2d((1, 1))
+        self.max = nn.AdaptiveMaxPool2d((1, 1))
+        self.mlp = nn.Sequential(nn.Conv2d(dim, dim // 16, 1, bias=False), nn.ReLU(), nn.Conv2d(dim // 16, dim, 1, bias=False))
+
+    def _mlp(self, v):
+        return _mm(torch.relu(_mm(v, self.mlp[0])), self.mlp[2])
+
+    def forward(self, x):
+        return torch.sigmoid(self._mlp(ops.spatial_mean(x)) + self._mlp(ops.spatial_max(x))).contiguous()   # fp32 [B, C]
+
+
+class FreRefine(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.SpatialGate = SpatialGate()
+        self.ChannelGate = ChannelGate(dim)
+        self.proj = nn.Conv2d(dim, dim, kernel_size=1)
+
+    def forward(self, low, high):
+        out = ops.fre_combine(low, high, self.SpatialGate(high), self.ChannelGate(low))
+        return A.ln_conv1x1(out, self.proj.weight, self.proj.bias, L.LN_NONE, None, None, None,
+                            cache=self.__dict__.setdefault("_b200ir_cache", {}), key="proj")
+
+
+class FreModule(nn.Module):
+    """Adaptive Frequency Learning Block (model.py:295-365)."""
+
+    def __init__(self, dim, num_heads, bias, in_dim=3):
+        super().__init__()
+        self.conv = nn.Conv2d(in_dim, dim, kernel_size=3, stride=1, padding=1, bias=False)     # unused by forward (as in the reference)
+        self.conv1 = nn.Conv2d(in_dim, dim, kernel_size=3, stride=1, padding=1, bias=False)
+        self.score_gen = nn.Conv2d(2, 2, 7, padding=3)                                          # unused by forward
+        self.para1 = nn.Parameter(torch.zeros(dim, 1, 1))
+        self.para2 = nn.Parameter(torch.ones(dim, 1, 1))
+        self.channel_cross_l = Chanel_Cross_Attention(dim, num_head=num_heads, bias=bias)
+        self.channel_cross_h = Chanel_Cross_Attention(dim, num_head=num_heads, bias=bias)
+        self.channel_cross_agg = Chanel_Cross_Attention(dim, num_head=num_heads, bias=bias)
+        self.frequency_refine = FreRefine(dim)
+        self.rate_conv = nn.Sequential(nn.Conv2d(dim, dim // 8, 1, bias=False), nn.GELU(), nn.Conv2d(dim // 8, 2, 1, bias=False))
+
+    def fft(self, x, n=128, out_dtype=None):
+        x = A.conv3x3(x, self.conv1.weight, None, None, L.SHUFFLE_NONE, out_dtype=out_dtype)
+        B, C, h, w = x.shape
+        t = _mm(ops.ew(_mm(ops.spatial_mean(x), self.rate_conv[0]).contiguous(), None, ops.EW_GELU), self.rate_conv[2])
+        thr = torch.sigmoid(t)                                                                   # [B, 2]
+        counts = torch.stack([(h // n * thr[:, 0]).int(), (w // n * thr[:, 1]).int()], 1).contiguous()
+        return ops.lowfreq_split(x, counts, 4 * (h // n) * (w // n))
+
+    def forward(self, x, y):
+        if torch.is_grad_enabled() and (y.requires_grad or x.requires_grad):
+            raise RuntimeError("b200ir.FreModule is an inference path")
+        _, _, H, W = y.size()
+        x = ops.bilinear_resize(x.contiguous(), H, W)
+        high_feature, low_feature = self.fft(x, out_dtype=y.dtype)
+        high_feature = self.channel_cross_l(high_feature, y)
+        low_feature = self.channel_cross_h(low_feature, y)
+        agg = self.frequency_refine(low_feature, high_feature)
+        out = self.channel_cross_agg(y, agg)
+        return ops.affine2(out, y, A._p(self.para1).reshape(-1), A._p(self.para2).reshape(-1))

@@ -836,3 +836,92 @@ def spatial_mean(x, gelu=False):
         rc = lib.b200ir_spatial_mean(xp, xbs, xdt, out.data_ptr(), B, C, H * W_, int(gelu), _stream())
     L.check(rc, "b200ir_spatial_mean")
     return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# AdaIR frequency mining / modulation pieces (csrc/adair_ops.cu)
+# ---------------------------------------------------------------------------------------------------
+def lowfreq_split(x, hw_counts, max_modes):
+    """FreModule.fft's mask -> ifft2 -> abs (AdaIR-main/net/model.py:335-365): (high, low).  hw_counts int32 [B, 2]."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    if hw_counts.dtype != torch.int32 or not hw_counts.is_cuda or tuple(hw_counts.shape) != (B, 2):
+        raise ValueError("lowfreq_split: hw_counts must be an int32 CUDA tensor [B, 2]")
+    hw_counts = hw_counts.contiguous()
+    high, low = torch.empty_like(x, memory_format=torch.contiguous_format), torch.empty_like(x, memory_format=torch.contiguous_format)
+    hp, hbs, _ = _act(high, "high")
+    lp, lbs, _ = _act(low, "low")
+    ws = torch.empty((B, C, 64, 2), device=x.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("lowfreq_split", B, C, H, W_, xdt):
+        rc = lib.b200ir_lowfreq_split(xp, xbs, hw_counts.data_ptr(), ws.data_ptr(), hp, hbs, lp, lbs, xdt, B, C, H, W_,
+                                      max_modes, _stream())
+    L.check(rc, "b200ir_lowfreq_split")
+    return high, low
+
+
+def bilinear_resize(x, H, W_):
+    B, C, Hi, Wi = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    y = torch.empty((B, C, H, W_), device=x.device, dtype=x.dtype)
+    yp, ybs, _ = _act(y, "y")
+    with _timed("bilinear_resize", B, C, Hi, Wi, H, W_, xdt):
+        rc = lib.b200ir_bilinear_resize(xp, xbs, yp, ybs, xdt, B, C, Hi, Wi, H, W_, _stream())
+    L.check(rc, "b200ir_bilinear_resize")
+    return y
+
+
+def spatial_gate(x, w7):
+    """fp32 [B, H*W] = sigmoid(conv7x7([max_c x, mean_c x])) (SpatialGate); w7 fp32 [1, 2, 7, 7]."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    ws = torch.empty((B, 2, H * W_), device=x.device, dtype=torch.float32)
+    gate = torch.empty((B, H * W_), device=x.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("spatial_gate", B, C, H, W_, xdt):
+        rc = lib.b200ir_spatial_gate(xp, xbs, xdt, _par(w7, "w7", 98), ws.data_ptr(), gate.data_ptr(), B, C, H, W_, _stream())
+    L.check(rc, "b200ir_spatial_gate")
+    return gate
+
+
+def spatial_max(x):
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    out = torch.empty((B, C), device=x.device, dtype=torch.float32)
+    with _timed("spatial_max", B, C, H * W_, xdt):
+        rc = lib.b200ir_spatial_max(xp, xbs, xdt, out.data_ptr(), B, C, H * W_, _stream())
+    L.check(rc, "b200ir_spatial_max")
+    return out
+
+
+def fre_combine(low, high, sw, cw):
+    """low * sw[b, p] + high * cw[b, c]; sw fp32 [B, H*W], cw fp32 [B, C]."""
+    B, C, H, W_ = low.shape
+    lp, lbs, ldt = _act(low, "low")
+    hp, hbs, hdt = _act(high, "high")
+    if hdt != ldt or tuple(high.shape) != tuple(low.shape):
+        raise ValueError("fre_combine: low / high mismatch")
+    y = torch.empty((B, C, H, W_), device=low.device, dtype=low.dtype)
+    yp, ybs, _ = _act(y, "y")
+    with _timed("fre_combine", B, C, H * W_, ldt):
+        rc = lib.b200ir_fre_combine(lp, lbs, hp, hbs, _par(sw, "sw", B * H * W_), _par(cw, "cw", B * C), yp, ybs, ldt, B, C,
+                                    H * W_, _stream())
+    L.check(rc, "b200ir_fre_combine")
+    return y
+
+
+def affine2(a, b, p1, p2):
+    """a * p1[c] + b * p2[c]."""
+    B, C, H, W_ = a.shape
+    ap, abs_, adt = _act(a, "a")
+    bp, bbs, bdt = _act(b, "b")
+    if bdt != adt or tuple(b.shape) != tuple(a.shape):
+        raise ValueError("affine2: operand mismatch")
+    y = torch.empty((B, C, H, W_), device=a.device, dtype=a.dtype)
+    yp, ybs, _ = _act(y, "y")
+    with _timed("affine2", B, C, H * W_, adt):
+        rc = lib.b200ir_affine2(ap, abs_, bp, bbs, _par(p1, "p1", C), _par(p2, "p2", C), yp, ybs, adt, B, C, H * W_, _stream())
+    L.check(rc, "b200ir_affine2")
+    return y

@@ -294,6 +294,30 @@ int b200ir_scale_rows(const void* x, int64_t x_bstride, const float* g, void* y,
 int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, float* out, int B, int C, int64_t HW, int gelu,
                         b200ir_stream_t stream);
 
+/* ---- AdaIR frequency mining / modulation pieces (adair_ops.cu; AdaIR-main/net/model.py:234-372) ----
+ * lowfreq_split: FreModule.fft.  hw_counts int32 [B][2] = (h_, w_) of the centred spectrum mask per sample; low =
+ * |ifft2(fft * mask)|, high = |ifft2(fft * (1 - mask))|, the <= max_modes kept bins synthesised directly (no FFT).
+ * coef_ws: fp32 scratch [B][C][64][2]. */
+int b200ir_lowfreq_split(const void* x, int64_t x_bstride, const int* hw_counts, float* coef_ws, void* high,
+                         int64_t h_bstride, void* low, int64_t l_bstride, int dtype, int B, int C, int H, int W,
+                         int max_modes, b200ir_stream_t stream);
+/* F.interpolate(mode='bilinear', align_corners=False) (model.py:313). */
+int b200ir_bilinear_resize(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B, int C, int Hin,
+                           int Win, int Hout, int Wout, b200ir_stream_t stream);
+/* SpatialGate (model.py:234-246): gate fp32 [B][H*W] = sigmoid(conv7x7([max_c x, mean_c x])); mm_ws fp32 [B][2][H*W]. */
+int b200ir_spatial_gate(const void* x, int64_t x_bstride, int dtype, const float* w7, float* mm_ws, float* gate, int B,
+                        int C, int H, int W, b200ir_stream_t stream);
+/* AdaptiveMaxPool2d(1) (ChannelGate, model.py:253): out fp32 [B][C]. */
+int b200ir_spatial_max(const void* x, int64_t x_bstride, int dtype, float* out, int B, int C, int64_t HW,
+                       b200ir_stream_t stream);
+/* FreRefine gating (model.py:279-284): y = low * sw[b][p] + high * cw[b][c]. */
+int b200ir_fre_combine(const void* low, int64_t l_bstride, const void* high, int64_t h_bstride, const float* sw,
+                       const float* cw, void* y, int64_t y_bstride, int dtype, int B, int C, int64_t HW,
+                       b200ir_stream_t stream);
+/* y = a * p1[c] + b * p2[c] (model.py:324). */
+int b200ir_affine2(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, const float* p1, const float* p2,
+                   void* y, int64_t y_bstride, int dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

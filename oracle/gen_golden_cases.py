@@ -120,3 +120,19 @@ ADAIR_CCA_CASES = [
     ("adair_cca_c32_h2", 32, 2, True, 2, 12, 20, 95),
     ("adair_cca_c48_h1_nobias", 48, 1, False, 1, 8, 8, 96),
 ]
+
+# AdaIR FreModule (AdaIR-main/net/model.py:295-365): name, dim, heads, bias, B, image (Hi, Wi), feature (H, W), seed.
+# H, W >= 128 so that the spectrum mask is not always empty (h // 128 > 0)
+FREMODULE_CASES = [
+    ("adair_fre_c16_h1_512", 16, 1, False, 1, (512, 512), (512, 512), 97),   # h // 128 = 4: a non-empty spectrum mask
+    ("adair_fre_c16_h1_resize", 16, 1, True, 2, (96, 160), (128, 256), 98),
+    ("adair_fre_c32_h2_small", 32, 2, False, 1, (64, 64), (64, 64), 99),     # h // 128 == 0: low = 0, high = |x|
+]
+
+
+def fre_sample(t):
+    """What the FreModule goldens keep of a [B, C, H, W] tensor (the full 512x512 tensors would be 16 MB): a strided
+    sample and two global checksums."""
+    import numpy as np
+    a = t.detach().cpu().float().numpy()
+    return a[:, ::3, ::7, ::5].copy(), np.array([a.mean(dtype=np.float64), np.abs(a).mean(dtype=np.float64)])

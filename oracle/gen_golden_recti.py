@@ -12,7 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 sys.path.insert(0, ROOT)
 from oracle import restormer_oracle as O  # noqa: E402
-from oracle.gen_golden_cases import RECTI_CASES, ADAIR_CCA_CASES, synth_like  # noqa: E402
+from oracle.gen_golden_cases import RECTI_CASES, ADAIR_CCA_CASES, FREMODULE_CASES, fre_sample, synth_like  # noqa: E402
 
 GOLD = os.path.join(ROOT, "tests", "golden")
 
@@ -51,6 +51,22 @@ def main():
             y = mod(x, y2)
         np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=y.numpy(), keys=np.array(sorted(mod.state_dict())))
         print(name, tuple(y.shape))
+    for name, dim, heads, bias, b, (hi, wi), (h, w), seed in FREMODULE_CASES:
+        mod = AD.FreModule(dim, heads, bias).eval()
+        sd = synth_like(mod.state_dict(), seed)
+        sd["para1"] = 0.5 + torch.rand(dim, 1, 1, generator=torch.Generator().manual_seed(seed + 1))   # (init is zeros)
+        mod.load_state_dict(sd, strict=True)
+        img = O.synth_image(b, hi, wi, seed=seed + 100)
+        y2 = O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1
+        with torch.no_grad():
+            y = mod(img, y2)
+            hf, lf = mod.fft(torch.nn.functional.interpolate(img, (h, w), mode="bilinear"))
+        ys, yc = fre_sample(y)
+        hs, hc = fre_sample(hf)
+        ls, lc = fre_sample(lf)
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=ys, y_sum=yc, high=hs, high_sum=hc, low=ls, low_sum=lc,
+                            keys=np.array(sorted(mod.state_dict())))
+        print(name, tuple(y.shape), "low band max", lf.abs().max().item())
 
 
 if __name__ == "__main__":

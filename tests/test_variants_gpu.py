@@ -78,3 +78,32 @@ def test_accelerate_adopts_adair_num_head_cross_attention():
     with torch.no_grad():
         got = net(x.cuda()).cpu()
     assert (got - ref).abs().max() <= 2e-4 * max(1.0, ref.abs().max().item())
+
+
+def test_adair_fremodule_vs_reference_golden():
+    """b200ir.FreModule (bilinear resize, conv3x3, few-bin low-pass instead of fft2/mask/ifft2, three channel cross
+    attentions, spatial / channel gates, per-channel affine) against AdaIR-main/net/model.py FreModule outputs."""
+    import b200ir
+    from oracle.gen_golden_cases import FREMODULE_CASES, fre_sample
+    for name, dim, heads, bias, b, (hi, wi), (h, w), seed in FREMODULE_CASES:
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+        mod = b200ir.FreModule(dim, heads, bias)
+        assert sorted(mod.state_dict()) == [str(k) for k in gold["keys"]]
+        sd = synth_like(mod.state_dict(), seed)
+        sd["para1"] = 0.5 + torch.rand(dim, 1, 1, generator=torch.Generator().manual_seed(seed + 1))
+        mod.load_state_dict(sd, strict=True)
+        mod = mod.cuda().eval()
+        img = O.synth_image(b, hi, wi, seed=seed + 100).cuda()
+        y2 = (O.synth_image(b, h, w, seed=seed + 300, c=dim) * 2 - 1).cuda()
+        with torch.no_grad():
+            y = mod(img, y2)
+            hf, lf = mod.fft(b200ir.ops.bilinear_resize(img, h, w))
+            y16 = mod(img, y2.bfloat16()).float()
+        for got, key, tol in ((hf, "high", 2e-4), (lf, "low", 2e-4), (y, "y", 5e-4)):
+            s, c = fre_sample(got)
+            ref = gold[key]
+            scale = max(1.0, float(np.abs(ref).max()))
+            assert np.abs(s - ref).max() <= tol * scale, (name, key, float(np.abs(s - ref).max()))
+            assert np.allclose(c, gold[key + "_sum"], rtol=1e-3, atol=1e-5), (name, key, c, gold[key + "_sum"])
+        s16, _ = fre_sample(y16)
+        assert np.linalg.norm(s16 - gold["y"]) <= 3e-2 * np.linalg.norm(gold["y"]), name
