@@ -78,6 +78,9 @@ SIGNATURES = {
     "b200ir_spatial_max": [_vp, _i64, _i, _vp, _i, _i, _i64, _vp],
     "b200ir_fre_combine": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_affine2": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_crop_augment_degrade": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
+    "b200ir_psnr_ssim_nblocks": [_i, _i],
+    "b200ir_psnr_ssim": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],
     "b200ir_adamw_step_ex": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _i, _vp, _f, _vp],
 }

@@ -318,6 +318,22 @@ int b200ir_fre_combine(const void* low, int64_t l_bstride, const void* high, int
 int b200ir_affine2(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, const float* p1, const float* p2,
                    void* y, int64_t y_bstride, int dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
 
+/* ---- input pipeline and evaluation metrics on the device (pipeline_ops.cu) ----
+ * Random-crop + flip/rot90 augmentation (mode 0..7 of MoCE-IR-main/src/utils/image_utils.py:136-166) + Gaussian-noise
+ * synthesis clip(clean + noise*sigma, 0, 255).astype(uint8) (degradation_utils.py:21-24) + ToTensor.  src uint8
+ * [B][Hs][Ws][3]; offsets int32 [B][2] (row, column of the crop); modes int32 [B]; sigma fp32 [B] (on the 0..255 scale,
+ * NULL / 0 = no noise); noise fp32 [B][P][P][3] standard-normal samples (caller's generator); clean / degraded fp32
+ * [B][3][P][P] in [0,1] (degraded may be NULL). */
+int b200ir_crop_augment_degrade(const uint8_t* src, int Hs, int Ws, const int* offsets, const int* modes,
+                                const float* sigma, const float* noise, float* clean, float* degraded, int B, int P,
+                                b200ir_stream_t stream);
+/* out fp32 [B][2] = (PSNR, SSIM) of clamp(restored,0,1) vs clean, fp32 NCHW, skimage semantics (test.py:46-52):
+ * data_range 1, SSIM with an 11x11 Gaussian window (sigma 1.5), sample covariance, mean without a 5-pixel border, then
+ * over channels.  ws: fp32 scratch [B * (1 + C) * b200ir_psnr_ssim_nblocks(H, W)]. */
+int b200ir_psnr_ssim_nblocks(int H, int W);
+int b200ir_psnr_ssim(const float* restored, const float* clean, float* ws, float* out, int B, int C, int H, int W,
+                     b200ir_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
