@@ -67,6 +67,7 @@ SIGNATURES = {
     "b200ir_mdta_bwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
+    "b200ir_l1_loss_fwd_noalloc": [_vp, _i, _vp, _i, _i64, _vp, _vp],
     "b200ir_l1_loss_bwd": [_vp, _i, _vp, _i, _i64, _vp, _vp, _i, _vp],
     "b200ir_circconv_patch": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_ew": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i64, _i, _vp],

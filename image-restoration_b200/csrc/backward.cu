@@ -7,6 +7,7 @@
 // GELU-gate input gradients, and the small per-(sample, head) softmax / normalisation backward of MDTA.
 // Every reduction is split into fixed-order partials + b200ir_reduce_partials: bitwise deterministic.
 #include <math.h>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -873,6 +874,59 @@ extern "C" int b200ir_l1_loss_fwd(const void* pred, int pred_dtype, const void* 
   if (rc) return rc;
   l1_loss_finish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(parts, nparts, 1.0f / (float)n, loss);
   return check_launch("l1_loss_finish");
+}
+
+// ---- allocation-free L1 loss (no counterpart in the reference) ----------
+// The per-block partial sums live in a file-scope device array instead of a caller-provided buffer, so the call needs no
+// cudaMalloc (callers under CUDA graph capture, tight serving loops).  16 KB per GPU that loads the library, held until
+// exit.  In host code `g_l1_noalloc_parts` is only a stand-in for the symbol: its device address is looked up once per
+// device (with that device current) and passed to the kernels.  Every call on a device shares the array: calls that
+// overlap on the GPU (two streams) race.  Nothing has to start at zero: the first kernel writes parts[0, nparts) before
+// the finishing kernel (same stream) reads exactly that range.
+static __device__ __align__(256) float g_l1_noalloc_parts[B200IR_L1_NOALLOC_MAX_PARTS];
+
+static int l1_noalloc_scratch(float** out) {
+  constexpr int kMaxDev = 64;
+  static std::mutex mu;
+  static float* addr[kMaxDev] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDev) {
+    set_error("l1_loss_fwd_noalloc: cudaGetDevice: %s", e != cudaSuccess ? cudaGetErrorString(e) : "device index >= 64");
+    return B200IR_E_DRIVER;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_l1_noalloc_parts);   // the current device's copy of the array
+    if (e != cudaSuccess || !p) {
+      set_error("l1_loss_fwd_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return B200IR_E_DRIVER;
+    }
+    addr[dev] = p;
+  }
+  *out = addr[dev];
+  return 0;
+}
+
+extern "C" int b200ir_l1_loss_fwd_noalloc(const void* pred, int pred_dtype, const void* target, int target_dtype,
+                                          int64_t n, float* loss, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(pred && target && loss && n > 0, "l1_loss_fwd_noalloc: bad args");
+  B200IR_CHECK_ARG(dtype_ok(pred_dtype) && dtype_ok(target_dtype), "l1_loss_fwd_noalloc: bad dtype");
+  if (n > (int64_t)B200IR_L1_NOALLOC_MAX_N) {
+    set_error("l1_loss_fwd_noalloc: n = %lld exceeds the built-in scratch (max %lld elements); use b200ir_l1_loss_fwd "
+              "with a caller-provided parts buffer", (long long)n, (long long)B200IR_L1_NOALLOC_MAX_N);
+    return B200IR_E_WORKSPACE;
+  }
+  float* parts = nullptr;
+  int rc = l1_noalloc_scratch(&parts);
+  if (rc) return rc;
+  const int nparts = (int)((n + B200IR_L1_NOALLOC_ELEMS_PER_PART - 1) / B200IR_L1_NOALLOC_ELEMS_PER_PART);
+  l1_loss_fwd_kernel<<<nparts, 256, 0, (cudaStream_t)stream>>>(pred, pred_dtype, target, target_dtype, n, parts);
+  rc = check_launch("l1_loss_fwd_noalloc");
+  if (rc) return rc;
+  l1_loss_finish_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(parts, nparts, 1.0f / (float)n, loss);
+  return check_launch("l1_loss_finish_noalloc");
 }
 
 extern "C" int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,

@@ -258,6 +258,19 @@ int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bs
 /* nn.L1Loss (mean) forward / backward (MoCE-IR-main/src/train.py:51,65).  parts: fp32 [nparts] scratch. */
 int b200ir_l1_loss_fwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n, float* parts,
                        int nparts, float* loss, b200ir_stream_t stream);
+/* Allocation-free variant of b200ir_l1_loss_fwd.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  The per-block partial
+ * sums go to a 16 KB file-scope __device__ array inside the library (held by every GPU that loads it, until exit) instead
+ * of a caller buffer; the call allocates nothing (no cudaMalloc / cudaFree / allocating library routine).  Limit:
+ * n <= B200IR_L1_NOALLOC_MAX_N elements (16 Mi: e.g. 16 x 3 x 512 x 512), else B200IR_E_WORKSPACE with a message in
+ * b200ir_last_error_string().  It uses nparts = ceil(n / 4096) blocks, and is bitwise equal to b200ir_l1_loss_fwd called with that
+ * nparts.  All calls on a device share the array: calls that overlap on the GPU (different streams) race; calls on one
+ * stream are safe, and nothing needs clearing between them (each call rewrites what it reads). */
+#define B200IR_L1_NOALLOC_MAX_PARTS 4096
+#define B200IR_L1_NOALLOC_ELEMS_PER_PART 4096
+#define B200IR_L1_NOALLOC_MAX_N ((int64_t)B200IR_L1_NOALLOC_MAX_PARTS * B200IR_L1_NOALLOC_ELEMS_PER_PART)
+int b200ir_l1_loss_fwd_noalloc(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
+                               float* loss, b200ir_stream_t stream);
 int b200ir_l1_loss_bwd(const void* pred, int pred_dtype, const void* target, int target_dtype, int64_t n,
                        const float* gscale, void* grad, int grad_dtype, b200ir_stream_t stream);
 /* torch.optim.AdamW step on one flat fp32 buffer (MoCE-IR-main/src/train.py:83); g is scaled by grad_scale first
