@@ -12,6 +12,9 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-fi
 python tools/bench_train.py --steps 1 > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 6000 --csv --log-file $O/${TAG}_train_launches_ncu.csv \
     python tools/bench_train.py --steps 1 > $O/ncu_train.log 2>&1
+python tools/fused_once.py > /dev/null 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:fused_ln_proj_dw_kernel -c 1 -f -o $O/${TAG}_fused \
+    python tools/fused_once.py > $O/ncu_fused.log 2>&1
 python tools/bench_ops.py gate k4 --once && {
 ncu --set full --clock-control none --import-source on -k regex:dwconv_tma_kernel -c 1 -f -o $O/${TAG}_gate \
     python tools/bench_ops.py gate --once > $O/ncu_gate.log 2>&1
