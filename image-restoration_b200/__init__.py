@@ -10,7 +10,7 @@ from .adair import Chanel_Cross_Attention, ChannelGate, FreModule, FreRefine, Sp
 from .moce import (AdapterLayer, DecoderBlock, DecoderResidualGroup, FFTAttention, FrequencyEmbedding, HighPassConv2d,  # noqa: F401
                    ModExpert, MoCEIR, RoutingFunction)
 from .autograd_ops import invalidate_caches  # noqa: F401
-from .training import AdamW, GraphedForward, GraphedTrainStep, L1Loss, allreduce_flat_grads, train_step  # noqa: F401
+from .training import AdamW, GraphedForward, GraphedTrainStep, L1Loss, PipelinedForward, allreduce_flat_grads, train_step  # noqa: F401
 
-__all__ = ["accelerate", "pipeline", "crop_augment_degrade", "psnr_ssim", "FreModule", "FreRefine", "SpatialGate", "ChannelGate", "Chanel_Cross_Attention", "ElementwiseGatedAttention", "GatedSpatialFFN", "MoCEIR", "DecoderBlock", "DecoderResidualGroup", "AdapterLayer", "ModExpert", "FFTAttention", "RoutingFunction", "FrequencyEmbedding", "HighPassConv2d", "invalidate_caches", "AdamW", "GraphedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
+__all__ = ["accelerate", "pipeline", "crop_augment_degrade", "psnr_ssim", "FreModule", "FreRefine", "SpatialGate", "ChannelGate", "Chanel_Cross_Attention", "ElementwiseGatedAttention", "GatedSpatialFFN", "MoCEIR", "DecoderBlock", "DecoderResidualGroup", "AdapterLayer", "ModExpert", "FFTAttention", "RoutingFunction", "FrequencyEmbedding", "HighPassConv2d", "invalidate_caches", "AdamW", "GraphedForward", "PipelinedForward", "GraphedTrainStep", "L1Loss", "allreduce_flat_grads", "train_step", "Attention", "BiasFree_LayerNorm", "CrossAttention", "GatedMDTA", "GatedTransformerBlock", "Downsample", "EncoderBlock", "EncoderResidualGroup", "FeedForward", "LayerNorm", "OverlapPatchEmbed",
            "Restormer", "TransformerBlock", "Upsample", "WithBias_LayerNorm", "ops"]

@@ -45,7 +45,8 @@ struct FusedParams {
 #define B200IR_FU_NCW 12
 #endif
 // timing experiments (-DB200IR_FU_DBG=<bits> A/B builds only, results WRONG): 1 read each TMEM row once (no re-read for the
-// other two tap rows), 2 no conv arithmetic, 4 no LayerNorm work, 8 no output stores, 16 no MMAs, 32 no activation loads
+// other two tap rows), 2 no conv arithmetic, 4 no LayerNorm work, 8 no output stores, 16 no MMAs, 32 no activation loads,
+// 64 one TMEM read per row but the FMAs of all three tap rows
 #ifndef B200IR_FU_DBG
 #define B200IR_FU_DBG 0
 #endif
@@ -159,7 +160,9 @@ fused_ln_proj_dw_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
   uint8_t* Ysm = Xsm + (size_t)P.S * stage_bytes;   // [NCW warps][2 buffers][32 channels][32 B] output staging
   __shared__ uint64_t bar_xfull[8], bar_xnorm[8], bar_xempty[8], bar_rowfull[4], bar_rowempty[4], bar_wfull[1], bar_wempty[1];
   __shared__ uint32_t tmem_slot[1];
-  __shared__ __align__(16) float2 s_nr[kFuLnWarps][4][8];   // (-rstd*mu, rstd) of the 8 pixels of a group, per LN warp
+  // -rstd*mu and rstd of the 8 pixels of a group, per LN warp: two separate arrays so that one LDS.128 returns pixel
+  // PAIRS in aligned register pairs (an interleaved (nm, rstd) layout cost ~110 register moves per normalise batch)
+  __shared__ __align__(16) float s_nm[kFuLnWarps][4][8], s_rs[kFuLnWarps][4][8];
   __shared__ uint32_t s_adesc[2 * 16];                       // low words of the weight descriptors, (acc, ks)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -364,17 +367,21 @@ fused_ln_proj_dw_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
         const float var = fmaxf(q1 * P.inv_c - md * md, 0.f);
         const float rstd = rsqrtf(var + 1e-5f);
         const float nmv = withbias ? -rstd * (c1 + md) : 0.f;
-        s_nr[lw][lane >> 3][sub] = make_float2(nmv, rstd);
+        s_nm[lw][lane >> 3][sub] = nmv;
+        s_rs[lw][lane >> 3][sub] = rstd;
         __syncwarp();
         if (lw == 0) FTL(1, 24, it);
         float2 nm2[4], rs2[4];
         {
-          const float4* p4 = reinterpret_cast<const float4*>(&s_nr[lw][lane >> 3][0]);
+          const float4* pn = reinterpret_cast<const float4*>(&s_nm[lw][lane >> 3][0]);
+          const float4* pr = reinterpret_cast<const float4*>(&s_rs[lw][lane >> 3][0]);
 #pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const float4 u = p4[j];
-            nm2[j] = make_float2(u.x, u.z);
-            rs2[j] = make_float2(u.y, u.w);
+          for (int j = 0; j < 2; ++j) {
+            const float4 u = pn[j], v = pr[j];
+            nm2[2 * j] = make_float2(u.x, u.y);
+            nm2[2 * j + 1] = make_float2(u.z, u.w);
+            rs2[2 * j] = make_float2(v.x, v.y);
+            rs2[2 * j + 1] = make_float2(v.z, v.w);
           }
         }
         for (int qb = 0; qb < nrow; qb += LNB) {
@@ -471,6 +478,20 @@ fused_ln_proj_dw_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
           for (int r = 0; r < ((B200IR_FU_DBG & 1) ? 1 : 3); ++r) {
             const uint32_t slot = (n + (uint32_t)i + (uint32_t)r) & 3u;
             const uint32_t ta = tlane + slot * 64u + (uint32_t)e0;
+            if ((B200IR_FU_DBG & 64) && r > 0) {   // experiment: arithmetic of all three tap rows, TMEM read of one
+#pragma unroll
+              for (int k = 0; k < 8; ++k) {
+                accA[k] = ffma2(wA[r * 3 + 0], accB[(k + 1) & 7], accA[k]);
+                accA[k] = ffma2(wA[r * 3 + 2], accB[(k + 2) & 7], accA[k]);
+                accA[k].x = fmaf(wA[r * 3 + 1].x, accB[(k + 3) & 7].x, accA[k].x);
+                accA[k].y = fmaf(wA[r * 3 + 1].x, accB[(k + 3) & 7].y, accA[k].y);
+                accB[k] = ffma2(wB[r * 3 + 0], accA[(k + 1) & 7], accB[k]);
+                accB[k] = ffma2(wB[r * 3 + 2], accA[(k + 2) & 7], accB[k]);
+                accB[k].x = fmaf(wB[r * 3 + 1].x, accA[(k + 3) & 7].x, accB[k].x);
+                accB[k].y = fmaf(wB[r * 3 + 1].x, accA[(k + 3) & 7].y, accB[k].y);
+              }
+              continue;
+            }
             {
               // 18 columns e0-1 .. e0+16: the +-1 taps read even-aligned register pairs (packed FMA); the centre tap is
               // odd-aligned -> scalar FMAs on the same registers (a second, shifted tcgen05.ld doubled the TMEM traffic,
@@ -484,9 +505,20 @@ fused_ln_proj_dw_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
               for (int k = 0; k < 8; ++k) {
                 accA[k] = ffma2(wA[r * 3 + 0], f2(O[2 * k], O[2 * k + 1]), accA[k]);
                 accA[k] = ffma2(wA[r * 3 + 2], f2(O[2 * k + 2], O[2 * k + 3]), accA[k]);
+#ifndef B200IR_FU_CENTER2
                 accA[k].x = fmaf(wA[r * 3 + 1].x, __uint_as_float(O[2 * k + 1]), accA[k].x);
                 accA[k].y = fmaf(wA[r * 3 + 1].x, __uint_as_float(O[2 * k + 2]), accA[k].y);
+#endif
               }
+#ifdef B200IR_FU_CENTER2
+              {   // A/B: centre tap packed too, from a second (even-aligned) tcgen05.ld of the same 16 columns
+                uint32_t Q[16];
+                tmem_ld_32x16(ta, Q);
+                tmem_ld_wait();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) accA[k] = ffma2(wA[r * 3 + 1], f2(Q[2 * k], Q[2 * k + 1]), accA[k]);
+              }
+#endif
             }
             if (haveB) {
               uint32_t O[18];
@@ -498,9 +530,20 @@ fused_ln_proj_dw_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_co
               for (int k = 0; k < 8; ++k) {
                 accB[k] = ffma2(wB[r * 3 + 0], f2(O[2 * k], O[2 * k + 1]), accB[k]);
                 accB[k] = ffma2(wB[r * 3 + 2], f2(O[2 * k + 2], O[2 * k + 3]), accB[k]);
+#ifndef B200IR_FU_CENTER2
                 accB[k].x = fmaf(wB[r * 3 + 1].x, __uint_as_float(O[2 * k + 1]), accB[k].x);
                 accB[k].y = fmaf(wB[r * 3 + 1].x, __uint_as_float(O[2 * k + 2]), accB[k].y);
+#endif
               }
+#ifdef B200IR_FU_CENTER2
+              {   // A/B: centre tap packed too, from a second (even-aligned) tcgen05.ld of the same 16 columns
+                uint32_t Q[16];
+                tmem_ld_32x16(ta + 256u, Q);
+                tmem_ld_wait();
+#pragma unroll
+                for (int k = 0; k < 8; ++k) accB[k] = ffma2(wB[r * 3 + 1], f2(Q[2 * k], Q[2 * k + 1]), accB[k]);
+              }
+#endif
             }
           }
           // results -> bf16 -> this warp's staging tile [32 channels][16 px] -> ONE TMA store box {16 px, 1 row, 32 ch}

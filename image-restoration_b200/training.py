@@ -297,3 +297,58 @@ class GraphedForward:
         ops.LAUNCHES += self.launches_per_call
         return self.y
 
+
+class PipelinedForward:
+    """Serving loop over HOST buffers: ``submit(host_in, host_out)`` enqueues the pinned-host -> device copy of a batch on
+    a copy stream, the forward (one CUDA-graph replay, ``GraphedForward``) on the current stream and the device -> pinned-host
+    copy of the restored batch on a second copy stream, so that the copies of batches i+1 and i-1 overlap the forward of
+    batch i.  ``depth`` input / output staging buffers on the device; results are complete after ``synchronize()`` (or
+    after waiting on the event ``submit`` returns).  The reference's serving loop is test.py's
+    ``restored = net(degrad_patch)`` over a DataLoader (MoCE-IR-main/src/test.py:95-103) with blocking ``.cuda()`` / ``.cpu()``."""
+
+    def __init__(self, net: nn.Module, example: torch.Tensor, depth: int = 2):
+        self.fwd = GraphedForward(net, example)
+        self.depth = depth
+        self.h2d, self.d2h = torch.cuda.Stream(), torch.cuda.Stream()
+        self.xin = [torch.empty_like(self.fwd.x) for _ in range(depth)]
+        self.yout = [torch.empty_like(self.fwd.y) for _ in range(depth)]
+        mk = lambda: [torch.cuda.Event() for _ in range(depth)]   # noqa: E731
+        self.ev_in, self.ev_in_free, self.ev_out, self.ev_out_free = mk(), mk(), mk(), mk()
+        self.i = 0
+
+    def submit(self, host_in: torch.Tensor, host_out: torch.Tensor):
+        if host_in.shape != self.fwd.x.shape or host_out.shape != self.fwd.y.shape:
+            raise ValueError("PipelinedForward: host buffers must have the captured input / output shapes")
+        k, first = self.i % self.depth, self.i < self.depth
+        main = torch.cuda.current_stream()
+        if not first:
+            self.h2d.wait_event(self.ev_in_free[k])          # the forward that read xin[k] has copied it out
+        with torch.cuda.stream(self.h2d):
+            self.xin[k].copy_(host_in, non_blocking=True)
+            self.ev_in[k].record(self.h2d)
+        main.wait_event(self.ev_in[k])
+        self.fwd.x.copy_(self.xin[k], non_blocking=True)
+        self.ev_in_free[k].record(main)
+        self.fwd.graph.replay()
+        ops.LAUNCHES += self.fwd.launches_per_call
+        if not first:
+            main.wait_event(self.ev_out_free[k])             # the device -> host copy that read yout[k] is done
+        self.yout[k].copy_(self.fwd.y, non_blocking=True)
+        self.ev_out[k].record(main)
+        self.d2h.wait_event(self.ev_out[k])
+        with torch.cuda.stream(self.d2h):
+            host_out.copy_(self.yout[k], non_blocking=True)
+            self.ev_out_free[k].record(self.d2h)
+        self.i += 1
+        return self.ev_out_free[k]
+
+    def join(self):
+        """make the current stream wait for every copy enqueued so far (a timing event recorded after it covers them)"""
+        main = torch.cuda.current_stream()
+        main.wait_stream(self.h2d)
+        main.wait_stream(self.d2h)
+
+    def synchronize(self):
+        self.join()
+        torch.cuda.current_stream().synchronize()
+

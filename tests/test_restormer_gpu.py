@@ -95,3 +95,22 @@ def test_graphed_forward_equals_eager():
             assert torch.equal(fwd(x), net(x))
     with pytest.raises(ValueError):
         fwd(xs[0][:1])
+
+
+def test_pipelined_forward_equals_eager():
+    """b200ir.PipelinedForward (host -> device copy stream, graph replay, device -> host copy stream, 2-deep staging): every
+    host output equals the eager forward of its own host input, bitwise, also when 7 batches are in flight back to back."""
+    import b200ir
+    net, full = _net({}, 0)
+    net.set_compute_dtype(torch.bfloat16)
+    hin = [O.synth_image(2, 64, 64, seed=10 + s).pin_memory() for s in range(7)]
+    hout = [torch.empty(2, 3, 64, 64).pin_memory() for _ in range(7)]
+    pipe = b200ir.PipelinedForward(net, hin[0].cuda())
+    for a, b in zip(hin, hout):
+        pipe.submit(a, b)
+    pipe.synchronize()
+    with torch.no_grad():
+        for a, b in zip(hin, hout):
+            assert torch.equal(b, net(a.cuda()).cpu())
+    with pytest.raises(ValueError):
+        pipe.submit(hin[0][:1], hout[0])
