@@ -64,6 +64,11 @@ def _act(t: torch.Tensor, name: str):
     """(ptr, batch_stride, dtype_code) of an NCHW activation view."""
     if not t.is_cuda:
         raise ValueError(f"{name}: expected a CUDA tensor (this package has no CPU fallback)")
+    if t.device.index != torch.cuda.current_device():
+        # every entry point enqueues on the CURRENT device's stream and sets per-device kernel attributes for it: a tensor
+        # of another GPU would be dereferenced on the wrong device
+        raise ValueError(f"{name}: tensor lives on cuda:{t.device.index} but the current device is "
+                         f"cuda:{torch.cuda.current_device()} (use torch.cuda.set_device / torch.cuda.device_of(x))")
     if t.dtype not in _DT:
         raise ValueError(f"{name}: dtype {t.dtype} unsupported (float32 / bfloat16)")
     if t.dim() != 4:
