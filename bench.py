@@ -306,16 +306,18 @@ def main():
         HR = 1024
         hin = [O.synth_image(1, HR, HR, seed=777 + 10 * rank + i).to(dev) for i in range(3)]
         with torch.no_grad():
+            hfwd = b200ir.GraphedForward(net, hin[0])
             for i in range(args.warmup):
-                net(hin[i % 3])
+                hfwd(hin[i % 3])
             barrier()
             e0.record()
             for i in range(args.steps):
-                net(hin[i % 3])
+                hfwd(hin[i % 3])
             e1.record()
             barrier()
+            del hfwd
         ms_hr = max_over_ranks(e0.elapsed_time(e1) / args.steps)
-        hires = {"workload": f"Restormer forward, one {HR}x{HR} RGB frame per GPU, {args.dtype}; BASELINE configs[4]",
+        hires = {"workload": f"Restormer forward, one {HR}x{HR} RGB frame per GPU, {args.dtype}, b200ir.GraphedForward; BASELINE configs[4]",
                  "value": world * HR * HR / 1e6 / (ms_hr * 1e-3), "unit": "MP/s", "ms_per_step": ms_hr}
         del hin
 

@@ -165,6 +165,36 @@ __global__ void spatial_mean_kernel(const T* __restrict__ x, int64_t x_bs, float
   if (lane == 0) out[(int64_t)n * C + c] = s / (float)HW;
 }
 
+// Large planes: one CTA per plane, 16-byte loads (8 bf16 / 4 fp32 per lane and step), fixed-order fold (lane sums ->
+// warp butterfly -> 8 warp sums added in order): one warp per 65 536-pixel plane ran at 0.27 TB/s (184 us at cfg3).
+template <typename T>
+__global__ void __launch_bounds__(256)
+spatial_mean_cta_kernel(const T* __restrict__ x, int64_t x_bs, float* __restrict__ out, int C, int64_t HW, int gelu) {
+  constexpr int V = 16 / (int)sizeof(T);
+  __shared__ float red[8];
+  const int c = blockIdx.x, n = blockIdx.y;
+  const T* p = x + (int64_t)n * x_bs + (int64_t)c * HW;
+  float s = 0.f;
+  for (int64_t i = (int64_t)threadIdx.x * V; i < HW; i += 256 * V) {
+    const uint4 q = __ldg(reinterpret_cast<const uint4*>(p + i));
+    const T* e = reinterpret_cast<const T*>(&q);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float v = to_f<T>(e[j]);
+      s += gelu ? gelu_erf(v) : v;
+    }
+  }
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w];
+    out[(int64_t)n * C + c] = t / (float)HW;
+  }
+}
+
 }  // namespace b200ir
 
 using namespace b200ir;
@@ -251,6 +281,15 @@ extern "C" int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, 
                                    int gelu, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(x && out && B > 0 && B <= 65535 && C > 0 && HW > 0, "spatial_mean: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype), "spatial_mean: bad dtype");
+  const int esz = dtype == B200IR_BF16 ? 2 : 4;
+  if (HW >= 4096 && C <= 65535 && (HW * esz) % 16 == 0 && (x_bstride * esz) % 16 == 0 && ((uintptr_t)x & 15) == 0) {
+    const dim3 g2((unsigned)C, (unsigned)B);
+    if (dtype == B200IR_BF16)
+      spatial_mean_cta_kernel<bf16><<<g2, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_bstride, out, C, HW, gelu);
+    else
+      spatial_mean_cta_kernel<float><<<g2, 256, 0, (cudaStream_t)stream>>>((const float*)x, x_bstride, out, C, HW, gelu);
+    return check_launch("spatial_mean");
+  }
   const unsigned grid = (unsigned)(((int64_t)B * C + 7) / 8);   // one warp per (sample, channel) plane, 8 warps per CTA
   if (dtype == B200IR_BF16)
     spatial_mean_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_bstride, out, B, C, HW, gelu);

@@ -30,6 +30,9 @@ def level(name):
             "l3": (16, 192, 4, 64, 64), "l4": (16, 384, 8, 32, 32)}[name]
 
 
+VARIANT = int(__import__('os').environ.get('BENCH_VARIANT', '0'))   # L.GEMM_AUTO / RESIDENT / STREAM / RESIDENT_CH (A/B timing)
+
+
 def make(opname, lv):
     B, C, h, H, W = level(lv)
     Hd = int(C * 2.66)
@@ -38,24 +41,34 @@ def make(opname, lv):
         x = [rnd(B, C, H, W) for _ in range(3)]
         p = ops.pack_conv1x1(rnd(3 * C, C, dtype=torch.float32), None, L.LN_WITHBIAS, torch.ones(C, device=dev), torch.zeros(C, device=dev))
         out = torch.empty(B, 3 * C, H, W, device=dev, dtype=bf)
-        return (lambda i: ops.gemm_tc(x[i % 3], p, 3 * C, L.LN_WITHBIAS, out=out)), px * (C + 3 * C) * 2
+        return (lambda i: ops.gemm_tc(x[i % 3], p, 3 * C, L.LN_WITHBIAS, out=out, variant=VARIANT)), px * (C + 3 * C) * 2
     if opname == "k4":
         x = [rnd(B, C, H, W) for _ in range(3)]
         p = ops.pack_conv1x1(rnd(2 * Hd, C, dtype=torch.float32), None, L.LN_WITHBIAS, torch.ones(C, device=dev), torch.zeros(C, device=dev))
         out = torch.empty(B, 2 * Hd, H, W, device=dev, dtype=bf)
-        return (lambda i: ops.gemm_tc(x[i % 3], p, 2 * Hd, L.LN_WITHBIAS, out=out)), px * (C + 2 * Hd) * 2
+        return (lambda i: ops.gemm_tc(x[i % 3], p, 2 * Hd, L.LN_WITHBIAS, out=out, variant=VARIANT)), px * (C + 2 * Hd) * 2
     if opname == "k6":
         x = [rnd(B, Hd, H, W) for _ in range(2)]
         r = [rnd(B, C, H, W) for _ in range(2)]
         p = ops.pack_conv1x1(rnd(C, Hd, dtype=torch.float32))
         out = torch.empty(B, C, H, W, device=dev, dtype=bf)
-        return (lambda i: ops.gemm_tc(x[i % 2], p, C, L.LN_NONE, r[i % 2], out=out)), px * (Hd + 2 * C) * 2
+        return (lambda i: ops.gemm_tc(x[i % 2], p, C, L.LN_NONE, r[i % 2], out=out, variant=VARIANT)), px * (Hd + 2 * C) * 2
     if opname == "k3b":
         qkv = [rnd(B, 3 * C, H, W) for _ in range(2)]
         r = [rnd(B, C, H, W) for _ in range(2)]
         p = ops.pack_conv1x1(rnd(B, C, C, dtype=torch.float32), None, per_sample=True)
         out = torch.empty(B, C, H, W, device=dev, dtype=bf)
-        return (lambda i: ops.gemm_tc(qkv[i % 2][:, 2 * C:], p, C, L.LN_NONE, r[i % 2], out=out)), px * 3 * C * 2
+        return (lambda i: ops.gemm_tc(qkv[i % 2][:, 2 * C:], p, C, L.LN_NONE, r[i % 2], out=out, variant=VARIANT)), px * 3 * C * 2
+    if opname == "k6n":     # K6 without the residual (A/B: what the epilogue's residual path costs)
+        x = [rnd(B, Hd, H, W) for _ in range(2)]
+        p = ops.pack_conv1x1(rnd(C, Hd, dtype=torch.float32))
+        out = torch.empty(B, C, H, W, device=dev, dtype=bf)
+        return (lambda i: ops.gemm_tc(x[i % 2], p, C, L.LN_NONE, None, out=out, variant=VARIANT)), px * (Hd + C) * 2
+    if opname == "k3bn":
+        qkv = [rnd(B, 3 * C, H, W) for _ in range(2)]
+        p = ops.pack_conv1x1(rnd(B, C, C, dtype=torch.float32), None, per_sample=True)
+        out = torch.empty(B, C, H, W, device=dev, dtype=bf)
+        return (lambda i: ops.gemm_tc(qkv[i % 2][:, 2 * C:], p, C, L.LN_NONE, None, out=out, variant=VARIANT)), px * 2 * C * 2
     if opname == "dw":
         x = [rnd(B, 3 * C, H, W) for _ in range(2)]
         w = rnd(3 * C, 1, 3, 3, dtype=torch.float32)
