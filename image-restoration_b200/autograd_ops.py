@@ -303,6 +303,106 @@ def _cg(g):
     return g if ok else g.contiguous()
 
 
+# ---- weight gradients on a side stream -------------------------------------------------------------------------------
+# Weight / bias gradients are leaves of the backward pass: nothing downstream of a layer's backward needs them before the
+# optimizer.  Inside b200ir.train_step / GraphedTrainStep (SIDE_WGRAD set there and nowhere else: a generic
+# loss.backward() under torch DDP reads gradients from hooks that know nothing about this stream) they are enqueued on a
+# second stream forked from the main one, so that the many small launches (split-K folds, deep-level weight-gradient GEMMs
+# with a handful of tiles) fill SMs the input-gradient chain leaves idle; captured in a CUDA graph this becomes a parallel
+# branch.  The arithmetic and its order are unchanged: results are bitwise those of the single-stream path.
+SIDE_WGRAD = False
+_SIDE_STREAMS = {}
+_SIDE_USED = False
+# References to the tensors the side stream reads, held until join_side(): autograd's gradient accumulation adds IN PLACE
+# into a buffered gradient nobody else references (input_buffer.cpp can_accumulate_inplace), e.g. into the dy that a
+# residual layer hands on as the gradient of its skip input -- on the main stream, while the side stream still reads it.
+_SIDE_KEEP = []
+_SIDE_GRADS = []   # (parameter, gradient computed on the side stream), assigned at join_side()
+SIDE_SITES = {"conv1x1", "dw3x3", "conv3x3", "lnfold", "gatefold"}   # which weight gradients fork (A/B, debugging)
+
+
+class _side:
+    """``with _side(site, (w, bias), in1, in2) as sd: dw = sd.give(w, f(in1, in2))`` runs f's launches on the side stream
+    after everything enqueued so far on the current stream; inputs are kept alive and marked for the allocator until
+    join_side(), which also assigns the gradients to their (leaf) parameters."""
+
+    def __init__(self, site, params, *inputs):
+        self.site, self.params, self.inputs, self.cm = site, params, inputs, None
+
+    def __enter__(self):
+        global _SIDE_USED
+        if not SIDE_WGRAD or self.site not in SIDE_SITES:
+            return self
+        if any(q is not None and not (q.is_leaf and q.requires_grad) for q in self.params):
+            return self      # a computed (non-leaf) weight: its gradient has to flow on through autograd
+        self.main = torch.cuda.current_stream()
+        dev = self.main.device.index
+        self.side = _SIDE_STREAMS.get(dev)
+        if self.side is None:
+            self.side = _SIDE_STREAMS[dev] = torch.cuda.Stream(device=dev)
+        self.side.wait_stream(self.main)
+        for t in self.inputs:
+            if t is not None:
+                t.record_stream(self.side)
+                _SIDE_KEEP.append(t)
+        self.cm = torch.cuda.stream(self.side)
+        self.cm.__enter__()
+        _SIDE_USED = True
+        return self
+
+    @property
+    def active(self):
+        return self.cm is not None
+
+    def give(self, param, grad):
+        """hand a gradient computed on the side stream to its parameter at join_side() instead of returning it to
+        autograd (AccumulateGrad may clone or add it on the MAIN stream as soon as backward() returns); -> None"""
+        if grad is None or param is None:
+            return None
+        if self.cm is None:
+            return grad
+        grad.record_stream(self.main)
+        _SIDE_GRADS.append((param, grad))
+        return None
+
+    def __exit__(self, *exc):
+        if self.cm is not None:
+            self.cm.__exit__(*exc)
+        return False
+
+
+def _side_fold(site, params):
+    """`fold` argument for ops.ln_bwd / ops.dwconv3x3_gelu_gate_bwd: run the fold of the parameter-gradient partial sums on
+    the side stream.  -> (callable, holder); holder.sd is the _side context the gradients are given through."""
+    class _H:
+        sd = None
+    h = _H()
+
+    def fold(fn, parts):
+        h.sd = _side(site, params, parts)
+        with h.sd:
+            return fn()
+    return fold, h
+
+
+def join_side():
+    """make the current stream wait for the side-stream work enqueued since the last join"""
+    global _SIDE_USED
+    if _SIDE_USED:
+        main = torch.cuda.current_stream()
+        side = _SIDE_STREAMS.get(main.device.index)
+        if side is not None:
+            main.wait_stream(side)
+        _SIDE_USED = False
+    _SIDE_KEEP.clear()
+    for prm, g in _SIDE_GRADS:
+        g = g.view(prm.shape) if g.shape != prm.shape else g
+        if g.dtype != prm.dtype:
+            g = g.to(prm.dtype)
+        prm.grad = g if prm.grad is None else prm.grad + g
+    _SIDE_GRADS.clear()
+
+
 class _LnConv1x1(torch.autograd.Function):
     """y = res + bias + W.LN(x)  (Restormer.py:37-39,54-57 + the 1x1 nn.Conv2d + :147-148)."""
 
@@ -312,6 +412,7 @@ class _LnConv1x1(torch.autograd.Function):
         ctx.save_for_backward(x, w, ln_w, ln_b)
         ctx.ln_type, ctx.has_bias, ctx.has_res = ln_type, bias is not None, res is not None
         ctx.cache, ctx.key = cache, key
+        ctx.params, ctx.lnparams = (w, bias), (ln_w, ln_b)
         return y
 
     @staticmethod
@@ -330,15 +431,19 @@ class _LnConv1x1(torch.autograd.Function):
                 dn = ops.ln_conv1x1(dy, wt, None, L.LN_NONE, None, None, None, out_dtype=x.dtype)
             if ctx.ln_type != L.LN_NONE:
                 # one pass over (x, dn): dx, dgamma/dbeta and LN(x) itself (operand of the weight gradient below)
-                dx, dlw, dlb, xn = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w), None, _p(ln_b), want_xn=True)
+                fold, h = _side_fold("lnfold", ctx.lnparams)
+                dx, dlw, dlb, xn = ops.ln_bwd(x, dn, ctx.ln_type, _p(ln_w), None, _p(ln_b), want_xn=True, fold=fold)
                 if ctx.ln_type != L.LN_WITHBIAS:
                     dlb = None
+                dlw, dlb = h.sd.give(ctx.lnparams[0], dlw), h.sd.give(ctx.lnparams[1], dlb)
             else:
                 dx = dn
-        dw, db = ops.conv_wgrad(dy, xn, 1, want_bias=ctx.has_bias)
+        with _side("conv1x1", ctx.params, dy, xn) as sd:
+            dw, db = ops.conv_wgrad(dy, xn, 1, want_bias=ctx.has_bias)
+            dw, db = sd.give(ctx.params[0], dw.view(w.shape).to(w.dtype)), sd.give(ctx.params[1], db)
         del xn
         dres = dy if ctx.has_res else None
-        return (dx, dw.view(w.shape).to(w.dtype), db, dlw, dlb, dres, None, None, None, None)
+        return (dx, dw, db, dlw, dlb, dres, None, None, None, None)
 
 
 class _LayerNorm(torch.autograd.Function):
@@ -372,15 +477,18 @@ class _DwConv(torch.autograd.Function):
     def forward(ctx, x, w, bias):
         ctx.save_for_backward(x, w)
         ctx.has_bias = bias is not None
+        ctx.params = (w, bias)
         return ops.dwconv3x3(x, _p(w), _p(bias))
 
     @staticmethod
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
         dy = _cg(dy)
+        with _side("dw3x3", ctx.params, dy, x) as sd:
+            dw, db = ops.dwconv3x3_wgrad(dy, x, want_bias=ctx.has_bias)
+            dw, db = sd.give(ctx.params[0], dw.to(w.dtype)), sd.give(ctx.params[1], db)
         dx = ops.dwconv3x3_bwd_input(dy, _p(w)) if ctx.needs_input_grad[0] else None
-        dw, db = ops.dwconv3x3_wgrad(dy, x, want_bias=ctx.has_bias)
-        return dx, dw.to(w.dtype), db
+        return dx, dw, db
 
 
 class _DwConvKxK(torch.autograd.Function):
@@ -431,15 +539,18 @@ class _DwGate(torch.autograd.Function):
     @staticmethod
     def forward(ctx, t, w, bias):
         ctx.save_for_backward(t, w, bias)
+        ctx.params = (w, bias)
         return ops.dwconv3x3_gelu_gate(t, _p(w), _p(bias))
 
     @staticmethod
     def backward(ctx, dg):
         t, w, bias = ctx.saved_tensors
         dg = _cg(dg)
-        da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None)
+        fold, h = _side_fold("gatefold", ctx.params)
+        da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None, fold=fold)
+        dw, db = h.sd.give(ctx.params[0], dw.to(w.dtype)), h.sd.give(ctx.params[1], db)
         dt = ops.dwconv3x3_bwd_input(da, _p(w)) if ctx.needs_input_grad[0] else None
-        return dt, dw.to(w.dtype), db
+        return dt, dw, db
 
 
 class _MdtaCore(torch.autograd.Function):
@@ -476,6 +587,7 @@ class _Conv3x3(torch.autograd.Function):
     def forward(ctx, x, w, bias, res, shuffle, out_dtype, cache, key):
         y = _conv3x3_fwd(x, w, bias, res, shuffle, None, out_dtype, cache, key)
         ctx.save_for_backward(x, w)
+        ctx.params = (w, bias)
         ctx.has_bias, ctx.has_res, ctx.shuffle = bias is not None, res is not None, shuffle
         return y
 
@@ -490,7 +602,9 @@ class _Conv3x3(torch.autograd.Function):
             dc = ops.pixel_shuffle(dy, L.UNSHUFFLE2)
         else:
             dc = dy
-        dw, db = ops.conv_wgrad(dc, x, 9, want_bias=ctx.has_bias)
+        with _side("conv3x3", ctx.params, dc, x) as sd:
+            dw, db = ops.conv_wgrad(dc, x, 9, want_bias=ctx.has_bias)
+            dw, db = sd.give(ctx.params[0], dw.view(w.shape).to(w.dtype)), sd.give(ctx.params[1], db)
         dx = None
         if need[0]:
             cin = w.shape[1]
@@ -500,7 +614,7 @@ class _Conv3x3(torch.autograd.Function):
             else:
                 dx = ops.conv3x3(dc, wt, None, None, L.SHUFFLE_NONE, out_dtype=x.dtype)
         dres = dy if (ctx.has_res and need[3]) else None
-        return dx, dw.view(w.shape).to(w.dtype), db, dres, None, None, None, None
+        return dx, dw, db, dres, None, None, None, None
 
 
 class _L1Loss(torch.autograd.Function):

@@ -588,7 +588,7 @@ def ln_fwd(x, ln_type, ln_w, ln_b, out_dtype=None):
     return y
 
 
-def ln_bwd(x, g, ln_type, ln_w, res=None, ln_b=None, want_xn=False):
+def ln_bwd(x, g, ln_type, ln_w, res=None, ln_b=None, want_xn=False, fold=None):
     """-> (dx, dweight[C], dbias[C]) or, with want_xn, (dx, dweight, dbias, LN(x)): the normalised tensor is a by-product
     of the same pass (operand of the following weight-gradient GEMM)."""
     B, C, H, W_ = x.shape
@@ -610,7 +610,9 @@ def ln_bwd(x, g, ln_type, ln_w, res=None, ln_b=None, want_xn=False):
                                _par(ln_b, "ln_b", C) if ln_type == L.LN_WITHBIAS and ln_b is not None else None,
                                rp, rbs, rdt, dp, dbs, ddt, np_, nbs, parts.data_ptr(), nparts, B, C, H * W_, _stream())
     L.check(rc, "b200ir_ln_bwd")
-    d = reduce_partials(parts, nparts, 2 * C)
+    # `fold`: a callable that runs the fold of the (dweight | dbias) partial sums wherever the caller wants it (the
+    # training step puts it on its side stream); default = here, on the current stream
+    d = fold(lambda: reduce_partials(parts, nparts, 2 * C), parts) if fold is not None else reduce_partials(parts, nparts, 2 * C)
     if want_xn:
         return dx, d[:C], d[C:], xn
     return dx, d[:C], d[C:]
@@ -668,7 +670,7 @@ def dwconv3x3_wgrad(dy, x, want_bias=False):
     return d[:, :9].reshape(C, 1, 3, 3), (d[:, 9] if want_bias else None)
 
 
-def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False):
+def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None):
     """Backward of the fused dwconv+GELU gate: (da [B,2Hd,H,W] = gradient w.r.t. the depthwise-conv output,
     dw [2Hd,1,3,3], db [2Hd] or None)."""
     B, C2, H, W_ = t.shape
@@ -685,8 +687,11 @@ def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False):
         rc = lib.b200ir_dwconv3x3_gelu_gate_bwd(tp, tbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), gp, gbs, ap, abs_,
                                                 tdt, parts.data_ptr(), nparts, B, Hd, H, W_, _stream())
     L.check(rc, "b200ir_dwconv3x3_gelu_gate_bwd")
-    d = parts.view(C2, 10) if nparts == 1 else reduce_partials(parts, nparts, C2 * 10).view(C2, 10)
-    return da, d[:, :9].reshape(C2, 1, 3, 3), (d[:, 9] if want_bias else None)
+    def finish():
+        d = parts.view(C2, 10) if nparts == 1 else reduce_partials(parts, nparts, C2 * 10).view(C2, 10)
+        return d[:, :9].reshape(C2, 1, 3, 3), (d[:, 9] if want_bias else None)
+    dw, db = fold(finish, parts) if fold is not None else finish()   # see ln_bwd
+    return da, dw, db
 
 
 def mdta_bwd(partials, attn, temperature, w_out, dM):

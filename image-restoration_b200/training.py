@@ -171,6 +171,19 @@ def allreduce_flat_grads(flat_g: torch.Tensor, group=None) -> float:
     return 1.0 / world
 
 
+def _backward_side(loss: torch.Tensor):
+    """loss.backward() with the weight gradients on the side stream (autograd_ops._side), joined before returning"""
+    A.SIDE_WGRAD = SIDE_WGRAD
+    try:
+        loss.backward()
+    finally:
+        A.SIDE_WGRAD = False
+        A.join_side()
+
+
+SIDE_WGRAD = True   # b200ir.training.SIDE_WGRAD = False restores the single-stream backward (A/B, debugging)
+
+
 def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.Tensor, loss_fn: Optional[nn.Module] = None,
                group=None) -> torch.Tensor:
     """``training_step`` of the reference driver (MoCE-IR-main/src/train.py:59-72) + optimizer step:
@@ -184,7 +197,7 @@ def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.
         pre.run()     # every 1x1 weight pack of the step in one launch (the forward / backward find them cached)
     restored = net(degraded)
     loss = loss_fn(restored, clean)
-    loss.backward()
+    _backward_side(loss)
     flat_g = opt.gather_grads()
     scale = allreduce_flat_grads(flat_g, group)
     opt.step(grad_scale=scale, gathered=True)
@@ -232,7 +245,7 @@ class GraphedTrainStep:
                 pre.run()
             restored = net(self.degraded)
             loss = self.loss_fn(restored, self.clean)
-            loss.backward()
+            _backward_side(loss)
             opt.gather_grads()
             self.loss = loss.detach()
             if self.world == 1:

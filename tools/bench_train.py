@@ -19,7 +19,10 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--breakdown", action="store_true")
     ap.add_argument("--graph", action="store_true")
+    ap.add_argument("--no-side", action="store_true", help="single-stream backward (A/B of the side-stream weight gradients)")
     a = ap.parse_args()
+    if a.no_side:
+        b200ir.training.SIDE_WGRAD = False
     torch.manual_seed(0)
     net = b200ir.Restormer().cuda()
     net.set_compute_dtype(torch.bfloat16 if a.dtype == "bf16" else torch.float32)
