@@ -438,7 +438,14 @@ def main():
         out["cpu_baseline"] = {"value": v, "unit": "MP/s", "cores": cores, "kind": "port", "sample": sample,
                                "s_per_step": dt}
         with torch.no_grad():
-            ref128 = O.restormer_forward(O.synth_state_dict({}, seed=0), par_x128)
+            sd0 = O.synth_state_dict({}, seed=0)
+            ref128 = O.restormer_forward(sd0, par_x128)       # warm-up of this shape + the parity reference
+            t0 = time.perf_counter()
+            O.restormer_forward(sd0, par_x128)
+            dt128 = time.perf_counter() - t0
+        # BASELINE configs[0] exactly (B1 128x128 fp32, the reference's own CPU-runnable case), beside the cfg2 sample above
+        out["cpu_baseline"]["cfg1"] = {"value": 128 * 128 / 1e6 / dt128, "unit": "MP/s", "s_per_step": dt128,
+                                       "sample": "BASELINE configs[0]: one 128x128 image, fp32, whole forward"}
         out["parity"] = {
             "bf16_psnr_db": O.psnr(par_bf16, ref256), "bf16_config": f"cfg2 sample 0 of {B}, {H}x{W}, {args.dtype} GPU vs fp32 CPU oracle",
             "fp32_max_abs": float((par_fp32 - ref128).abs().max()), "fp32_config": "cfg1 B1 128x128, fp32 GPU path vs fp32 CPU oracle",

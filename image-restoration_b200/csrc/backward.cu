@@ -290,6 +290,128 @@ ln_bwd_bf16x2_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __res
   for (int i = threadIdx.x; i < 2 * C; i += 256) out[i] = acc[i];
 }
 
+// Register-resident form of the kernel above for C = 8 * CPW, CPW <= 12 (C = 48 / 96: 24 of the 44 blocks of the default
+// net; CPW = 24 needs 247 registers).  Measured in a CUDA graph at B8 C48 128x128 the two-pass kernel took 32 us for 38 MB (0.2 of the HBM
+// roof): both passes load, and every channel of every tile pays two 5-step warp reductions for dgamma / dbeta.  Here a
+// warp's CPW channels of the tile stay in registers between the passes (one trip over x and g, all loads of a tile in
+// flight together), and dgamma / dbeta are accumulated PER LANE over all tiles of the CTA and folded across lanes once
+// at the end (fixed order: tile loop, then the shuffle tree) -- 2 * CPW reductions per CTA instead of per tile.
+template <int CPW>
+__global__ void __launch_bounds__(256)
+ln_bwd_bf16_reg_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __restrict__ g, int64_t g_bs, int ln_type,
+                       const float* __restrict__ lw, const float* __restrict__ lb, const bf16* __restrict__ res,
+                       int64_t res_bs, bf16* __restrict__ dx, int64_t dx_bs, bf16* __restrict__ xn, int64_t xn_bs,
+                       float* __restrict__ parts, int64_t HW, int tps, int64_t ntiles) {
+  constexpr int C = 8 * CPW;
+  __shared__ float2 red4[8][4][32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float invC = 1.0f / (float)C;
+  const int64_t cstep = 8 * HW;
+  float gam[CPW], bet[CPW], dgam[CPW], dbet[CPW];
+#pragma unroll
+  for (int j = 0; j < CPW; ++j) {
+    gam[j] = __ldg(lw + warp + 8 * j);
+    bet[j] = (xn && ln_type == B200IR_LN_WITHBIAS) ? __ldg(lb + warp + 8 * j) : 0.f;
+    dgam[j] = dbet[j] = 0.f;
+  }
+  for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+    const int b = (int)(t / tps);
+    const int64_t p = (t % tps) * 64 + 2 * lane;
+    const bool valid = p < HW;
+    const int64_t off = p + (int64_t)warp * HW;
+    uint32_t xr[CPW], gr[CPW];
+    uint32_t x0r = 0u;
+    if (valid) {
+      const bf16* xp = x + (int64_t)b * x_bs + off;
+      const bf16* gp = g + (int64_t)b * g_bs + off;
+      x0r = *reinterpret_cast<const uint32_t*>(x + (int64_t)b * x_bs + p);
+#pragma unroll
+      for (int j = 0; j < CPW; ++j) {
+        xr[j] = *reinterpret_cast<const uint32_t*>(xp + j * cstep);
+        gr[j] = *reinterpret_cast<const uint32_t*>(gp + j * cstep);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CPW; ++j) xr[j] = gr[j] = 0u;
+    }
+    const float2 x0 = make_float2(__uint_as_float(x0r << 16), __uint_as_float(x0r & 0xffff0000u));
+    float2 S1 = {0.f, 0.f}, S2 = {0.f, 0.f}, H1 = {0.f, 0.f}, H2 = {0.f, 0.f};
+#pragma unroll
+    for (int j = 0; j < CPW; ++j) {
+      const float d0 = __uint_as_float(xr[j] << 16) - x0.x, d1 = __uint_as_float(xr[j] & 0xffff0000u) - x0.y;
+      const float h0 = __uint_as_float(gr[j] << 16) * gam[j], h1 = __uint_as_float(gr[j] & 0xffff0000u) * gam[j];
+      S1.x += d0; S1.y += d1;
+      S2.x = fmaf(d0, d0, S2.x); S2.y = fmaf(d1, d1, S2.y);
+      H1.x += h0; H1.y += h1;
+      H2.x = fmaf(h0, d0, H2.x); H2.y = fmaf(h1, d1, H2.y);
+    }
+    __syncthreads();          // the previous tile's readers of red4 are done
+    red4[warp][0][lane] = S1;
+    red4[warp][1][lane] = S2;
+    red4[warp][2][lane] = H1;
+    red4[warp][3][lane] = H2;
+    __syncthreads();
+    S1 = S2 = H1 = H2 = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) {
+      const float2 a = red4[w][0][lane], bq = red4[w][1][lane], cq = red4[w][2][lane], dq = red4[w][3][lane];
+      S1.x += a.x; S1.y += a.y; S2.x += bq.x; S2.y += bq.y;
+      H1.x += cq.x; H1.y += cq.y; H2.x += dq.x; H2.y += dq.y;
+    }
+    float mu[2], rstd[2], s1[2], s2[2];
+    {
+      const float S1v[2] = {S1.x, S1.y}, S2v[2] = {S2.x, S2.y}, H1v[2] = {H1.x, H1.y}, H2v[2] = {H2.x, H2.y};
+      const float x0v[2] = {x0.x, x0.y};
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float md = S1v[k] * invC;
+        mu[k] = x0v[k] + md;
+        rstd[k] = 1.0f / sqrtf(fmaxf(S2v[k] * invC - md * md, 0.f) + 1e-5f);
+        s1[k] = H1v[k] * invC;
+        s2[k] = ln_type == B200IR_LN_WITHBIAS ? rstd[k] * (H2v[k] * invC - md * s1[k]) : (H2v[k] * invC + x0v[k] * s1[k]);
+      }
+    }
+    if (!valid) continue;     // warp-uniform per lane only in the ragged last tile; no barrier below this point in the body
+    const bf16* rp = res ? res + (int64_t)b * res_bs + off : nullptr;
+    bf16* dp = dx + (int64_t)b * dx_bs + off;
+    bf16* np = xn ? xn + (int64_t)b * xn_bs + off : nullptr;
+#pragma unroll
+    for (int j = 0; j < CPW; ++j) {
+      const float xs[2] = {__uint_as_float(xr[j] << 16), __uint_as_float(xr[j] & 0xffff0000u)};
+      const float gs[2] = {__uint_as_float(gr[j] << 16), __uint_as_float(gr[j] & 0xffff0000u)};
+      float2 rv = {0.f, 0.f};
+      if (rp) rv = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(rp + j * cstep));
+      float d[2], nv[2];
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float h = gs[k] * gam[j];
+        if (ln_type == B200IR_LN_WITHBIAS) {
+          const float xh = (xs[k] - mu[k]) * rstd[k];
+          d[k] = rstd[k] * (h - s1[k] - xh * s2[k]);
+          dgam[j] = fmaf(gs[k], xh, dgam[j]);
+          nv[k] = fmaf(xh, gam[j], bet[j]);
+        } else {
+          d[k] = rstd[k] * h - rstd[k] * rstd[k] * rstd[k] * (xs[k] - mu[k]) * s2[k];
+          dgam[j] = fmaf(gs[k] * xs[k], rstd[k], dgam[j]);
+          nv[k] = xs[k] * rstd[k] * gam[j];
+        }
+      }
+      dbet[j] += gs[0] + gs[1];
+      *reinterpret_cast<__nv_bfloat162*>(dp + j * cstep) = __floats2bfloat162_rn(d[0] + rv.x, d[1] + rv.y);
+      if (np) *reinterpret_cast<__nv_bfloat162*>(np + j * cstep) = __floats2bfloat162_rn(nv[0], nv[1]);
+    }
+  }
+  float* out = parts + (size_t)blockIdx.x * 2 * C;
+#pragma unroll
+  for (int j = 0; j < CPW; ++j) {
+    const float a = warp_sum(dgam[j]), bq = warp_sum(dbet[j]);
+    if (lane == 0) {
+      out[warp + 8 * j] = a;
+      out[C + warp + 8 * j] = bq;
+    }
+  }
+}
+
 // out[k] = sum_{i<n} in[i*stride + k].  CTA = 32 outputs x 8 slices of the partial index; each slice is summed
 // sequentially, the 8 slice sums are combined in fixed order (deterministic).
 __global__ void __launch_bounds__(256)
@@ -738,6 +860,16 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   if (same && x_dtype == B200IR_BF16 && (HW & 1) == 0 && (int64_t)B * ((HW + 63) / 64) >= 2 * num_sms() && even(x, x_bstride) && even(g, g_bstride) &&
       even(res, res_bstride) && even(dx, dx_bstride) && even(xn, xn_bstride)) {
     const int tps2 = (int)((HW + 63) / 64);
+#define B200IR_LN_BWD_REG(CPW_)                                                                                        \
+  {                                                                                                                    \
+    ln_bwd_bf16_reg_kernel<CPW_><<<nparts, 256, 0, (cudaStream_t)stream>>>(                                            \
+        (const bf16*)x, x_bstride, (const bf16*)g, g_bstride, ln_type, ln_w, ln_b, (const bf16*)res, res_bstride,      \
+        (bf16*)dx, dx_bstride, (bf16*)xn, xn_bstride, parts, HW, tps2, (int64_t)B * tps2);                             \
+    return check_launch("ln_bwd_bf16_reg");                                                                            \
+  }
+    if (C == 48) B200IR_LN_BWD_REG(6)
+    if (C == 96) B200IR_LN_BWD_REG(12)
+#undef B200IR_LN_BWD_REG
     ln_bwd_bf16x2_kernel<<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(
         (const bf16*)x, x_bstride, (const bf16*)g, g_bstride, ln_type, ln_w, ln_b, (const bf16*)res, res_bstride,
         (bf16*)dx, dx_bstride, (bf16*)xn, xn_bstride, parts, C, HW, tps2, (int64_t)B * tps2);

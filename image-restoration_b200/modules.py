@@ -166,13 +166,24 @@ class GatedMDTA(nn.Module):
             return A.mdta_core(qkv, self.temperature, self.project_out.weight, self.project_out.bias, self.num_heads,
                                res, out=out, cache=cache)
         sl = lambda a, b: (t[:, a:b], wd[a:b], bd[a:b] if bd is not None else None)
-        q = A.dwconv3x3(*sl(0, C))
-        gate = A.dwconv3x3(*sl(C, C + G))
-        kv = A.dwconv3x3(*sl(C + G, 3 * C + G))
+        if A._needs_grad(t, wd, bd):
+            q = A.dwconv3x3(*sl(0, C))
+            gate = A.dwconv3x3(*sl(C, C + G))
+            kv = A.dwconv3x3(*sl(C + G, 3 * C + G))
+            qkv = torch.cat([q, kv], dim=1)
+            del q, kv
+        else:
+            # inference: the q and k|v depthwise launches write their channel slices of ONE [q|k|v] buffer (no torch.cat)
+            qkv = torch.empty((t.shape[0], 3 * C, t.shape[2], t.shape[3]), device=t.device, dtype=t.dtype)
+            for (a, b), dst in (((0, C), qkv[:, :C]), ((C + G, 3 * C + G), qkv[:, C:])):
+                xs, ws, bs = sl(a, b)
+                ops.dwconv3x3(xs, A._p(ws), A._p(bs), out=dst)
+            xs, ws, bs = sl(C, C + G)
+            gate = ops.dwconv3x3(xs, A._p(ws), A._p(bs))
         del t
-        u = A.mdta_core(torch.cat([q, kv], dim=1), self.temperature, self._eye(x.device), None, self.num_heads, None,
+        u = A.mdta_core(qkv, self.temperature, self._eye(x.device), None, self.num_heads, None,
                         cache=cache)                      # attn . v (identity fold)
-        del q, kv
+        del qkv
         ug = A.sigmoid_gate(u, gate)                      # * sigmoid(gate), head-wise or element-wise
         del u, gate
         return A.ln_conv1x1(ug, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
