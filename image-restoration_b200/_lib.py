@@ -73,6 +73,9 @@ SIGNATURES = {
     "b200ir_ew": [_vp, _i64, _vp, _i64, _vp, _i64, _i, _i, _i64, _i, _vp],
     "b200ir_scale_rows": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i64, _i, _vp],
     "b200ir_spatial_mean": [_vp, _i64, _i, _vp, _i, _i, _i64, _i, _vp],
+    "b200ir_spatial_mean_bwd": [_vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i64, _i, _vp],
+    "b200ir_rows_copy": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i, _i64, _i, _i, _vp],
+    "b200ir_rowdot": [_vp, _i64, _vp, _vp, _i64, _vp, _vp, _i, _i64, _i, _vp],
     "b200ir_lowfreq_split": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_bilinear_resize": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_spatial_gate": [_vp, _i64, _i, _vp, _vp, _vp, _i, _i, _i, _i, _vp],

@@ -636,3 +636,154 @@ def l1_loss(pred, target):
     if _needs_grad(pred):
         return _L1Loss.apply(pred, target)
     return ops.l1_loss_fwd(pred.contiguous(), target.contiguous())
+
+
+# ---- MoCE-IR adapter pieces (moce_ir.py:71-141, 373-422, 548-560, 659-667, 703-707, 1068-1075) --------------------
+class _CircConv(torch.autograd.Function):
+    """Per-patch circular convolution irfft2(rfft2(a) * rfft2(b)) (FFTAttention, moce_ir.py:406-412); the gradients are
+    the circular correlations of the output gradient with the other operand."""
+
+    @staticmethod
+    def forward(ctx, a, b, patch):
+        ctx.save_for_backward(a, b)
+        ctx.patch = patch
+        return ops.circconv_patch(a, b, patch)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        g = _cg(g).to(a.dtype)
+        da = ops.circconv_patch(g, b, ctx.patch, mode=1) if ctx.needs_input_grad[0] else None
+        db = ops.circconv_patch(g, a, ctx.patch, mode=1) if ctx.needs_input_grad[1] else None
+        return da, db, None
+
+
+def circconv_patch(a, b, patch):
+    if _needs_grad(a, b):
+        return _CircConv.apply(a, b, patch)
+    return ops.circconv_patch(a, b, patch)
+
+
+class _EwMul(torch.autograd.Function):
+    """y = a * b (FFTAttention: LayerNorm(out) * v, moce_ir.py:418)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return ops.ew(a, b, ops.EW_MUL)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        g = _cg(g).to(a.dtype)
+        return (ops.ew(g, b, ops.EW_MUL) if ctx.needs_input_grad[0] else None,
+                ops.ew(g, a, ops.EW_MUL) if ctx.needs_input_grad[1] else None)
+
+
+class _EwSiluMul(torch.autograd.Function):
+    """y = a * silu(b) (ModExpert.process, moce_ir.py:556-558)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        ctx.save_for_backward(a, b)
+        return ops.ew(a, b, ops.EW_SILU_MUL)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b = ctx.saved_tensors
+        g = _cg(g).to(a.dtype)
+        da = ops.ew(g, b, ops.EW_SILU_MUL) if ctx.needs_input_grad[0] else None
+        db = ops.ew(b, ops.ew(g, a, ops.EW_MUL), ops.EW_DSILU_MUL) if ctx.needs_input_grad[1] else None
+        return da, db
+
+
+def ew_mul(a, b):
+    return _EwMul.apply(a, b) if _needs_grad(a, b) else ops.ew(a, b, ops.EW_MUL)
+
+
+def ew_silu_mul(a, b):
+    return _EwSiluMul.apply(a, b) if _needs_grad(a, b) else ops.ew(a, b, ops.EW_SILU_MUL)
+
+
+class _SpatialMean(torch.autograd.Function):
+    """fp32 [B, C] = mean over (H, W) of x, or of gelu(x): AdaptiveAvgPool2d(1) of the router (moce_ir.py:703-707) and
+    FrequencyEmbedding's gelu(...).mean(dim=(-2, -1)) (:1068-1073)."""
+
+    @staticmethod
+    def forward(ctx, x, gelu):
+        ctx.save_for_backward(x)
+        ctx.gelu = gelu
+        return ops.spatial_mean(x, gelu=gelu)
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        return ops.spatial_mean_bwd(g, x, gelu=ctx.gelu), None
+
+
+def spatial_mean(x, gelu=False):
+    x = _cg(x)
+    return _SpatialMean.apply(x, gelu) if _needs_grad(x) else ops.spatial_mean(x, gelu=gelu)
+
+
+class _GatherRows(torch.autograd.Function):
+    """y[j] = x[idx[j]]: SparseDispatcher.dispatch, ``inp[self._batch_index]`` for one expert (moce_ir.py:94-104)."""
+
+    @staticmethod
+    def forward(ctx, x, idx):
+        ctx.save_for_backward(idx)
+        ctx.shape = x.shape
+        n = idx.numel()
+        y = torch.empty((n,) + tuple(x.shape[1:]), device=x.device, dtype=x.dtype)
+        return ops.rows_copy(x, y, n, src_idx=idx)
+
+    @staticmethod
+    def backward(ctx, g):
+        (idx,) = ctx.saved_tensors
+        g = _cg(g)
+        dx = torch.zeros(ctx.shape, device=g.device, dtype=g.dtype)
+        ops.rows_copy(g, dx, idx.numel(), dst_idx=idx)
+        return dx, None
+
+
+def gather_rows(x, idx):
+    """x [B, C, H, W] (sample-contiguous), idx int32 [n] -> [n, C, H, W]"""
+    x = x.contiguous()
+    return _GatherRows.apply(x, idx) if _needs_grad(x) else ops.rows_copy(
+        x, torch.empty((idx.numel(),) + tuple(x.shape[1:]), device=x.device, dtype=x.dtype), idx.numel(), src_idx=idx)
+
+
+class _Combine(torch.autograd.Function):
+    """out[b] = sum over experts e and their samples j with idx_e[j] == b of g_e[j] * y_e[j]: SparseDispatcher.combine,
+    ``zeros.index_add(0, batch_index, stitched * nonzero_gates)`` (moce_ir.py:106-123), experts in ascending order."""
+
+    @staticmethod
+    def forward(ctx, B, idxs, *ts):
+        ne = len(idxs)
+        ys, gs = ts[:ne], ts[ne:]
+        out = torch.zeros((B,) + tuple(ys[0].shape[1:]), device=ys[0].device, dtype=ys[0].dtype)
+        for y, g, idx in zip(ys, gs, idxs):
+            ops.rows_copy(y, out, idx.numel(), dst_idx=idx, scale=g, accumulate=True)
+        ctx.save_for_backward(*ys, *gs, *idxs)
+        ctx.ne = ne
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        ne = ctx.ne
+        sv = ctx.saved_tensors
+        ys, gs, idxs = sv[:ne], sv[ne:2 * ne], sv[2 * ne:]
+        dout = _cg(dout).to(ys[0].dtype)
+        dys, dgs = [], []
+        for y, g, idx in zip(ys, gs, idxs):
+            n = idx.numel()
+            dys.append(ops.rows_copy(dout, torch.empty_like(y), n, src_idx=idx, scale=g))
+            dgs.append(ops.rowdot(y, dout, n, b_idx=idx))
+        return (None, None) + tuple(dys) + tuple(dgs)
+
+
+def combine_rows(B, ys, gs, idxs):
+    """ys[e] [n_e, C, H, W] (contiguous), gs[e] fp32 [n_e], idxs[e] int32 [n_e] -> [B, C, H, W]"""
+    ys = [y.contiguous() for y in ys]
+    gs = [g.float().contiguous() for g in gs]
+    return _Combine.apply(B, tuple(idxs), *ys, *gs)

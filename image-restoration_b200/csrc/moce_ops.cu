@@ -297,3 +297,117 @@ extern "C" int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, 
     spatial_mean_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, x_bstride, out, B, C, HW, gelu);
   return check_launch("spatial_mean");
 }
+
+// =====================================================================================================
+// Training mode of the MoCE-IR adapter (SparseDispatcher, moce_ir.py:71-141, 659-667): samples are gathered per expert,
+// the expert outputs are scattered back weighted by their gates, and the global pools need gradients.
+// =====================================================================================================
+namespace b200ir {
+
+// y[dst(j)] (+)= (scale ? scale[j] : 1) * x[src(j)],  j < n rows of `per` elements (row = one sample of an NCHW tensor);
+// src / dst index arrays may be NULL (identity).  dispatch = gather by src, combine = scatter-accumulate by dst; the
+// indices of one call are distinct (a sample meets an expert once), so there is no write conflict.
+template <typename T>
+__global__ void rows_copy_kernel(const T* __restrict__ x, int64_t x_rs, T* __restrict__ y, int64_t y_rs,
+                                 const int* __restrict__ src, const int* __restrict__ dst, const float* __restrict__ scale,
+                                 int64_t per, int accumulate) {
+  const int j = blockIdx.y;
+  const int64_t so = (int64_t)(src ? src[j] : j) * x_rs, dof = (int64_t)(dst ? dst[j] : j) * y_rs;
+  const float g = scale ? scale[j] : 1.f;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (int64_t)gridDim.x * blockDim.x) {
+    float r = g * to_f<T>(x[so + i]);
+    if (accumulate) r += to_f<T>(y[dof + i]);
+    y[dof + i] = from_f<T>(r);
+  }
+}
+
+// out[j] = sum_i a[ia(j), i] * b[ib(j), i]  (fp32, one CTA per row, fixed order): the gate gradient of the weighted combine
+template <typename T>
+__global__ void __launch_bounds__(256)
+rowdot_kernel(const T* __restrict__ a, int64_t a_rs, const int* __restrict__ ia, const T* __restrict__ b, int64_t b_rs,
+              const int* __restrict__ ib, float* __restrict__ out, int64_t per) {
+  __shared__ float red[8];
+  const int j = blockIdx.x;
+  const T* pa = a + (int64_t)(ia ? ia[j] : j) * a_rs;
+  const T* pb = b + (int64_t)(ib ? ib[j] : j) * b_rs;
+  float s = 0.f;
+  for (int64_t i = threadIdx.x; i < per; i += 256) s = fmaf(to_f<T>(pa[i]), to_f<T>(pb[i]), s);
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w];
+    out[j] = t;
+  }
+}
+
+// backward of spatial_mean: dx[b, c, i] = g[b, c] / HW * (gelu ? gelu'(x[b, c, i]) : 1)
+template <typename T>
+__global__ void spatial_mean_bwd_kernel(const float* __restrict__ g, const T* __restrict__ x, int64_t x_bs,
+                                        T* __restrict__ dx, int64_t dx_bs, int C, int64_t HW, int gelu) {
+  const int c = blockIdx.y, n = blockIdx.z;
+  const float gv = g[(int64_t)n * C + c] / (float)HW;
+  const T* xp = x ? x + (int64_t)n * x_bs + (int64_t)c * HW : nullptr;
+  T* dp = dx + (int64_t)n * dx_bs + (int64_t)c * HW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < HW; i += (int64_t)gridDim.x * blockDim.x) {
+    float r = gv;
+    if (gelu) {
+      const float v = to_f<T>(xp[i]);
+      // d/dv [v * Phi(v)] = Phi(v) + v * phi(v)
+      r *= 0.5f * (1.f + erff(v * 0.70710678118654752f)) + v * 0.3989422804014327f * __expf(-0.5f * v * v);
+    }
+    dp[i] = from_f<T>(r);
+  }
+}
+
+}  // namespace b200ir
+
+static inline unsigned moce_grid(int64_t n, int threads, int cap) {
+  int64_t g = (n + threads - 1) / threads;
+  if (g > cap) g = cap;
+  return (unsigned)(g < 1 ? 1 : g);
+}
+
+extern "C" int b200ir_rows_copy(const void* x, int64_t x_rowstride, void* y, int64_t y_rowstride, const int* src_idx,
+                                const int* dst_idx, const float* scale, int n, int64_t per, int accumulate, int dtype,
+                                b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(x && y && n > 0 && n <= 65535 && per > 0, "rows_copy: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "rows_copy: bad dtype");
+  const dim3 grid(moce_grid(per, 256, num_sms() * 4), (unsigned)n);
+  if (dtype == B200IR_BF16)
+    rows_copy_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>((const bf16*)x, x_rowstride, (bf16*)y, y_rowstride, src_idx,
+                                                                    dst_idx, scale, per, accumulate);
+  else
+    rows_copy_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)x, x_rowstride, (float*)y, y_rowstride,
+                                                                     src_idx, dst_idx, scale, per, accumulate);
+  return check_launch("rows_copy");
+}
+
+extern "C" int b200ir_rowdot(const void* a, int64_t a_rowstride, const int* a_idx, const void* b, int64_t b_rowstride,
+                             const int* b_idx, float* out, int n, int64_t per, int dtype, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(a && b && out && n > 0 && per > 0, "rowdot: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "rowdot: bad dtype");
+  if (dtype == B200IR_BF16)
+    rowdot_kernel<bf16><<<n, 256, 0, (cudaStream_t)stream>>>((const bf16*)a, a_rowstride, a_idx, (const bf16*)b, b_rowstride,
+                                                             b_idx, out, per);
+  else
+    rowdot_kernel<float><<<n, 256, 0, (cudaStream_t)stream>>>((const float*)a, a_rowstride, a_idx, (const float*)b,
+                                                              b_rowstride, b_idx, out, per);
+  return check_launch("rowdot");
+}
+
+extern "C" int b200ir_spatial_mean_bwd(const float* g, const void* x, int64_t x_bstride, void* dx, int64_t dx_bstride,
+                                       int dtype, int B, int C, int64_t HW, int gelu, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(g && dx && (x || !gelu) && B > 0 && B <= 65535 && C > 0 && C <= 65535 && HW > 0, "spatial_mean_bwd: bad args");
+  B200IR_CHECK_ARG(dtype_ok(dtype), "spatial_mean_bwd: bad dtype");
+  const dim3 grid(moce_grid(HW, 256, 64), (unsigned)C, (unsigned)B);
+  if (dtype == B200IR_BF16)
+    spatial_mean_bwd_kernel<bf16><<<grid, 256, 0, (cudaStream_t)stream>>>(g, (const bf16*)x, x_bstride, (bf16*)dx, dx_bstride,
+                                                                           C, HW, gelu);
+  else
+    spatial_mean_bwd_kernel<float><<<grid, 256, 0, (cudaStream_t)stream>>>(g, (const float*)x, x_bstride, (float*)dx,
+                                                                            dx_bstride, C, HW, gelu);
+  return check_launch("spatial_mean_bwd");
+}

@@ -12,9 +12,11 @@ Quirks of the reference that are kept on purpose (§3.4 of SURVEY.md):
   * ``ModExpert.feat_extract`` applies ``process`` ``depth`` times to the SAME input (:566-568): one evaluation;
   * eval-mode ``AdapterLayer`` with batch > 1 and top-k = 1 runs, for every sample, the experts chosen by ALL samples on
     the whole batch and scales their SUM by the sample's own gate (:668-676, ``top_k_indices.squeeze(0)``).
-Training mode of the adapter (SparseDispatcher + auxiliary losses, :659-667) is not mirrored: ``forward`` raises in
-training mode so that nobody trains on different semantics by accident; the Restormer-family pieces inside train through
-``dropin.accelerate`` on the reference model as before.
+Training mode (round 2): ``net.train()`` switches the adapter to the reference's SparseDispatcher semantics (:71-141,
+659-667: per-expert sample gather, gate-weighted scatter-accumulate) and the router to its auxiliary importance + load
+losses (:733-800); ``net.total_loss`` is the balance loss of MoCE-IR-main/src/train.py:62.  Every tensor-sized forward
+and backward op is a libb200ir kernel behind a ``torch.autograd.Function`` (``autograd_ops.py``); pinned to outputs,
+losses and all parameter gradients of the unmodified reference (``oracle/gen_golden_moceir_train.py``).
 """
 from __future__ import annotations
 
@@ -76,6 +78,11 @@ class FrequencyEmbedding(nn.Module):
 
     def forward(self, x):
         h = self.high_conv[0](x)
+        if A._needs_grad(h, *self.mlp.parameters()):
+            # training: the pool is a kernel with a backward kernel; the MLP works on [B, dim] vectors (a few hundred
+            # numbers) and goes through torch so that autograd sees it
+            m = A.spatial_mean(h, gelu=True)
+            return self.mlp(m)
         m = ops.spatial_mean(h, gelu=True)                       # [B, dim] fp32 = gelu(h).mean((-2, -1))
         m = _linear(m, self.mlp[0])
         m = ops.ew(m.contiguous(), None, ops.EW_GELU)
@@ -101,9 +108,9 @@ class FFTAttention(nn.Module):
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         q = A.dwconv3x3(_conv1x1(x, self.q, cache=cache, key="q"), self.q_dwconv.weight, self.q_dwconv.bias)
         kv = A.dwconv_kxk(_conv1x1(x, self.kv, cache=cache, key="kv"), self.kv_dwconv.weight, self.kv_dwconv.bias)
-        out = ops.circconv_patch(q, kv[:, :c], self.patch_size)
+        out = A.circconv_patch(q, kv[:, :c], self.patch_size)
         ln_type, lw, lb = _ln_args(self.norm)
-        out = ops.ew(A.layernorm(out, ln_type, lw, lb), kv[:, c:], ops.EW_MUL)
+        out = A.ew_mul(A.layernorm(out, ln_type, lw, lb), kv[:, c:])
         return _conv1x1(out, self.proj_out, cache=cache, key="out")
 
 
@@ -123,7 +130,7 @@ class ModExpert(nn.Module):
             return x
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         t = self.body(_conv1x1(x, self.proj[0], cache=cache, key="p0"))
-        t = ops.ew(t, _conv1x1(shared, self.proj[1], cache=cache, key="p1"), ops.EW_SILU_MUL)
+        t = A.ew_silu_mul(t, _conv1x1(shared, self.proj[1], cache=cache, key="p1"))
         return _conv1x1(t, self.proj[2], res=x, cache=cache, key="p2")      # `depth` repeats give the same tensor
 
 
@@ -149,6 +156,8 @@ class RoutingFunction(nn.Module):
         self.noise_device = None
 
     def forward(self, x, freq_emb):
+        if self.training:
+            return self._forward_train(x, freq_emb)
         logits = _linear(ops.spatial_mean(x), self.gate[2]) + _linear(freq_emb, self.freq_gate)
         nd = self.noise_device or logits.device
         noise = torch.randn(logits.shape, dtype=logits.dtype, device=nd).to(logits.device) * self.noise_std
@@ -157,9 +166,42 @@ class RoutingFunction(nn.Module):
         gates = torch.zeros_like(logits).scatter_(1, top_k_indices, top_k_values)
         return gates, top_k_indices, top_k_values, 0
 
+    def _forward_train(self, x, freq_emb):
+        """Training mode (moce_ir.py:733-758): the same noisy top-k gates plus the auxiliary loss
+        0.5 * importance + 0.5 * load.  The global pool is a kernel (with a backward kernel); everything after it works on
+        the [batch, num_experts] logits and stays in torch so that autograd differentiates it like the reference's."""
+        pooled = A.spatial_mean(x)                                      # AdaptiveAvgPool2d(1), fp32 [B, dim]
+        logits = F.linear(pooled, self.gate[2].weight.float()) + F.linear(freq_emb.float(), self.freq_gate.weight.float())
+        loss_imp = self.importance_loss(logits.softmax(dim=-1))
+        nd = self.noise_device or logits.device
+        noise = torch.randn(logits.shape, dtype=logits.dtype, device=nd).to(logits.device) * self.noise_std
+        noisy_logits = logits + noise
+        gating_scores = noisy_logits.softmax(dim=-1)
+        top_k_values, top_k_indices = torch.topk(gating_scores, self.k, dim=-1)
+        loss_load = self.load_loss(logits, noisy_logits, self.noise_std)
+        aux_loss = 0.5 * loss_imp + 0.5 * loss_load
+        gates = torch.zeros_like(logits).scatter(1, top_k_indices, top_k_values)
+        return gates, top_k_indices, top_k_values, aux_loss
+
+    def importance_loss(self, gating_scores):
+        """squared coefficient of variation of the per-expert importance (moce_ir.py:760-769)"""
+        importance = gating_scores.sum(dim=0)
+        importance = importance * (self.complexity * self.tau) if self.use_complexity_bias else importance
+        return (importance.std() / (importance.mean() + 1e-8)) ** 2
+
+    def load_loss(self, logits, logits_noisy, noise_std):
+        """squared coefficient of variation of the probability that an expert is in the top-k (moce_ir.py:771-800)"""
+        thresholds = torch.topk(logits_noisy, self.k, dim=-1).indices[:, -1]
+        threshold_per_item = torch.sum(F.one_hot(thresholds, self.num_experts) * logits_noisy, dim=-1)
+        noise_required_to_win = (threshold_per_item.unsqueeze(-1) - logits) / noise_std
+        p = 1. - torch.distributions.normal.Normal(0, 1).cdf(noise_required_to_win)
+        p_mean = p.mean(dim=0)
+        return (p_mean.std() / (p_mean.mean() + 1e-8)) ** 2
+
 
 class AdapterLayer(nn.Module):
-    """Mixture of complexity experts (moce_ir.py:584-682), eval-mode semantics (see the module docstring)."""
+    """Mixture of complexity experts (moce_ir.py:584-682): eval-mode semantics in ``forward`` (see the module docstring),
+    SparseDispatcher semantics in training mode (``_forward_train``)."""
 
     def __init__(self, dim: int, rank: int, num_experts: int = 4, top_k: int = 2, expert_layer: nn.Module = FFTAttention,
                  stage_depth: int = 1, depth_type: str = "lin", rank_type: str = "constant", freq_dim: int = 128,
@@ -210,8 +252,7 @@ class AdapterLayer(nn.Module):
 
     def forward(self, x, freq_emb, shared):
         if self.training:
-            raise RuntimeError("b200ir.AdapterLayer mirrors the eval-mode path of the reference (moce_ir.py:668-676); "
-                               "call .eval(), or train the reference model with b200ir.accelerate(model)")
+            return self._forward_train(x, freq_emb, shared)
         gates, top_k_indices, _, aux = self.routing(x, freq_emb)
         self.loss = aux
         sel = top_k_indices.squeeze(0)
@@ -232,6 +273,37 @@ class AdapterLayer(nn.Module):
                 y = self.experts[e](x, shared)
                 out = ops.scale_rows(y, (g[:, 0] * float(cnt)).contiguous(), out=out, accumulate=out is not None)
         return _conv1x1(out, self.proj_out, cache=self.__dict__.setdefault("_b200ir_cache", {}), key="out")
+
+
+def _adapter_forward_train(self, x, freq_emb, shared):
+    """Training mode (moce_ir.py:659-667): SparseDispatcher semantics.  Expert e receives the samples b with
+    gates[b, e] > 0 (``dispatch``: a row gather), and the output is out[b] = sum_e gates[b, e] * expert_e(x[b], shared[b])
+    (``combine``: a gate-weighted scatter-accumulate, experts in ascending order like the reference's index_add over the
+    expert-sorted batch index).  Experts that receive no sample are not run and get no gradient, as in the reference."""
+    gates, top_k_indices, _, aux = self.routing(x, freq_emb)
+    self.loss = aux
+    B = x.shape[0]
+    sel_host = (gates.detach() > 0).cpu()                       # host sync, like the reference's `.tolist()` of part sizes
+    x, shared = x.contiguous(), shared.contiguous()
+    ys, gs, idxs = [], [], []
+    for e in range(self.num_experts):
+        rows = torch.nonzero(sel_host[:, e]).flatten()
+        n = int(rows.numel())
+        if n == 0:
+            continue
+        idx = rows.to(device=x.device, dtype=torch.int32)
+        if n == B:
+            xe, se = x, shared
+        else:
+            xe, se = A.gather_rows(x, idx), A.gather_rows(shared, idx)
+        ys.append(self.experts[e](xe, se))
+        gs.append(gates[rows.to(x.device), e])
+        idxs.append(idx)
+    out = A.combine_rows(B, ys, gs, idxs)
+    return _conv1x1(out, self.proj_out, cache=self.__dict__.setdefault("_b200ir_cache", {}), key="out")
+
+
+AdapterLayer._forward_train = _adapter_forward_train
 
 
 class DecoderBlock(nn.Module):
@@ -269,8 +341,14 @@ class DecoderBlock(nn.Module):
         dim = x.shape[1]
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         ln_type, lw, lb = _ln_args(self.norms[0])
-        w2, b2 = self._proj_pair()
-        both = A.ln_conv1x1(x, w2, b2, ln_type, lw, lb, None, cache=cache, key="pair")     # [B, 2*dim, H, W]
+        if A._needs_grad(self.proj[0].weight, self.proj[1].weight, self.proj[0].bias, self.proj[1].bias):
+            # training: the stacked weight has to stay connected to its two parameters
+            w2 = torch.cat([self.proj[0].weight, self.proj[1].weight], 0)
+            b2 = torch.cat([self.proj[0].bias, self.proj[1].bias], 0)
+            both = A.ln_conv1x1(x, w2, b2, ln_type, lw, lb, None)
+        else:
+            w2, b2 = self._proj_pair()
+            both = A.ln_conv1x1(x, w2, b2, ln_type, lw, lb, None, cache=cache, key="pair")     # [B, 2*dim, H, W]
         x_s = self.shared._run(both[:, :dim])
         x_a = self.adapter(both[:, dim:], freq_emb, x_s)
         x = self.mixer(x_a, x_s, res=x)
@@ -368,8 +446,7 @@ class MoCEIR(nn.Module):
         H, W = x.shape[-2:]
         if H % 2 ** (self.levels - 1) or W % 2 ** (self.levels - 1):
             raise ValueError(f"H and W must be multiples of {2 ** (self.levels - 1)}, got {H}x{W}")
-        if torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters())) and self.training:
-            raise RuntimeError("b200ir.MoCEIR is the inference mirror (eval mode); see the module docstring")
+        grad = torch.is_grad_enabled() and (x.requires_grad or any(p.requires_grad for p in self.parameters()))
         x = x.contiguous()
         cd = self.compute_dtype
         feats = self.patch_embed(x, out_dtype=cd)
@@ -385,9 +462,12 @@ class MoCEIR(nn.Module):
         for i, (upsample, fusion, block) in enumerate(self.dec):
             skip = enc_feats.pop()
             B, cs, h, w = skip.shape
-            buf = torch.empty((B, 2 * cs, h, w), device=x.device, dtype=cd)     # torch.cat([up, skip], 1) without a cat kernel
-            upsample(feats, out=buf[:, :cs])
-            ops.copy_cast(skip, buf[:, cs:])
+            if grad:
+                buf = torch.cat([upsample(feats), skip], 1)                     # autograd path (moce_ir.py:1219)
+            else:
+                buf = torch.empty((B, 2 * cs, h, w), device=x.device, dtype=cd)  # the same without a cat kernel
+                upsample(feats, out=buf[:, :cs])
+                ops.copy_cast(skip, buf[:, cs:])
             feats = _conv1x1(buf, fusion, cache=cache, key=("fuse", i))
             feats = block(feats, freq_emb)
             self.total_loss += block.loss

@@ -848,6 +848,71 @@ def spatial_mean(x, gelu=False):
     return out
 
 
+def spatial_mean_bwd(g, x, gelu=False):
+    """Gradient of spatial_mean w.r.t. x: g fp32 [B, C] -> dx like x."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    dx = torch.empty_like(x, memory_format=torch.contiguous_format)
+    dp, dbs, _ = _act(dx, "dx")
+    g = g.float().contiguous()
+    with _timed("spatial_mean_bwd", B, C, H * W_, xdt):
+        rc = lib.b200ir_spatial_mean_bwd(g.data_ptr(), xp, xbs, dp, dbs, xdt, B, C, H * W_, int(gelu), _stream())
+    L.check(rc, "b200ir_spatial_mean_bwd")
+    return dx
+
+
+def _rows(t, name):
+    """(ptr, row stride, elements per row, dtype code) of a tensor whose leading dimension indexes contiguous rows"""
+    if not t.is_cuda or t.dtype not in _DT:
+        raise ValueError(f"{name}: expected a float32 / bfloat16 CUDA tensor")
+    per = t[0].numel()
+    if t.shape[0] > 1 and (t.stride(0) < per or not t[0].is_contiguous()):
+        raise ValueError(f"{name}: rows must be contiguous")
+    if not t[0].is_contiguous():
+        raise ValueError(f"{name}: rows must be contiguous")
+    return t.data_ptr(), (t.stride(0) if t.shape[0] > 1 else per), per, _DT[t.dtype]
+
+
+def _idx(i, n, name):
+    if i is None:
+        return None
+    if i.dtype != torch.int32 or not i.is_cuda or i.numel() != n or not i.is_contiguous():
+        raise ValueError(f"{name}: index must be a contiguous int32 CUDA tensor of {n} elements")
+    return i.data_ptr()
+
+
+def rows_copy(x, y, n, src_idx=None, dst_idx=None, scale=None, accumulate=False):
+    """y[dst(j)] (+)= scale[j] * x[src(j)] for j < n (rows = samples); SparseDispatcher.dispatch / combine."""
+    xp, xrs, per, xdt = _rows(x, "x")
+    yp, yrs, pery, ydt = _rows(y, "y")
+    if per != pery or xdt != ydt:
+        raise ValueError("rows_copy: x / y row size or dtype mismatch")
+    sp = None
+    if scale is not None:
+        if scale.dtype != torch.float32 or scale.numel() != n or not scale.is_contiguous():
+            raise ValueError("rows_copy: scale must be contiguous float32 [n]")
+        sp = scale.data_ptr()
+    with _timed("rows_copy", n, per, xdt):
+        rc = lib.b200ir_rows_copy(xp, xrs, yp, yrs, _idx(src_idx, n, "src_idx"), _idx(dst_idx, n, "dst_idx"), sp, n, per,
+                                  int(accumulate), xdt, _stream())
+    L.check(rc, "b200ir_rows_copy")
+    return y
+
+
+def rowdot(a, b, n, a_idx=None, b_idx=None):
+    """fp32 [n]: out[j] = <a[a_idx(j)], b[b_idx(j)]>"""
+    ap, ars, per, adt = _rows(a, "a")
+    bp, brs, perb, bdt = _rows(b, "b")
+    if per != perb or adt != bdt:
+        raise ValueError("rowdot: a / b row size or dtype mismatch")
+    out = torch.empty((n,), device=a.device, dtype=torch.float32)
+    with _timed("rowdot", n, per, adt):
+        rc = lib.b200ir_rowdot(ap, ars, _idx(a_idx, n, "a_idx"), bp, brs, _idx(b_idx, n, "b_idx"), out.data_ptr(), n, per,
+                               adt, _stream())
+    L.check(rc, "b200ir_rowdot")
+    return out
+
+
 # ---------------------------------------------------------------------------------------------------
 # AdaIR frequency mining / modulation pieces (csrc/adair_ops.cu)
 # ---------------------------------------------------------------------------------------------------

@@ -185,7 +185,7 @@ SIDE_WGRAD = True   # b200ir.training.SIDE_WGRAD = False restores the single-str
 
 
 def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.Tensor, loss_fn: Optional[nn.Module] = None,
-               group=None) -> torch.Tensor:
+               group=None, balance_loss_weight: float = 0.0) -> torch.Tensor:
     """``training_step`` of the reference driver (MoCE-IR-main/src/train.py:59-72) + optimizer step:
     restored = net(degrad); loss = L1(restored, clean); backward; (all-reduce); AdamW.  Returns the loss (device scalar)."""
     loss_fn = loss_fn or L1Loss()
@@ -197,6 +197,8 @@ def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.
         pre.run()     # every 1x1 weight pack of the step in one launch (the forward / backward find them cached)
     restored = net(degraded)
     loss = loss_fn(restored, clean)
+    if balance_loss_weight:     # MoCE-IR: loss += balance_loss_weight * net.total_loss (MoCE-IR-main/src/train.py:62,71)
+        loss = loss + balance_loss_weight * net.total_loss
     _backward_side(loss)
     flat_g = opt.gather_grads()
     scale = allreduce_flat_grads(flat_g, group)

@@ -306,6 +306,21 @@ int b200ir_scale_rows(const void* x, int64_t x_bstride, const float* g, void* y,
  * x.mean(dim=(-2,-1)) of FrequencyEmbedding (:1072).  out fp32 [B][C]. */
 int b200ir_spatial_mean(const void* x, int64_t x_bstride, int dtype, float* out, int B, int C, int64_t HW, int gelu,
                         b200ir_stream_t stream);
+/* Backward of b200ir_spatial_mean: dx[b,c,:] = g[b,c] / HW (times gelu'(x) with gelu = 1).  g fp32 [B][C]. */
+int b200ir_spatial_mean_bwd(const float* g, const void* x, int64_t x_bstride, void* dx, int64_t dx_bstride, int dtype,
+                            int B, int C, int64_t HW, int gelu, b200ir_stream_t stream);
+/* Training mode of the MoCE-IR adapter, SparseDispatcher.dispatch / combine (moce_ir.py:94-123): rows = samples of
+ * `per` elements.  y[dst(j)] (+)= scale[j] * x[src(j)], j < n; src_idx / dst_idx int32 device arrays or NULL (identity),
+ * scale fp32 device array or NULL (1).  dispatch: `inp[self._batch_index]` = gather by src_idx; combine:
+ * `zeros.index_add(0, batch_index, stitched * gates)` = scatter-accumulate by dst_idx with the gates as scale.  The indices
+ * of one call must be distinct. */
+int b200ir_rows_copy(const void* x, int64_t x_rowstride, void* y, int64_t y_rowstride, const int* src_idx,
+                     const int* dst_idx, const float* scale, int n, int64_t per, int accumulate, int dtype,
+                     b200ir_stream_t stream);
+/* out[j] = sum_i a[a_idx(j), i] * b[b_idx(j), i] (fp32, fixed order): gradient of the gates of the weighted combine
+ * (autograd of `stitched.mul(self._nonzero_gates)`, moce_ir.py:117). */
+int b200ir_rowdot(const void* a, int64_t a_rowstride, const int* a_idx, const void* b, int64_t b_rowstride,
+                  const int* b_idx, float* out, int n, int64_t per, int dtype, b200ir_stream_t stream);
 
 /* ---- AdaIR frequency mining / modulation pieces (adair_ops.cu; AdaIR-main/net/model.py:234-372) ----
  * lowfreq_split: FreModule.fft.  hw_counts int32 [B][2] = (h_, w_) of the centred spectrum mask per sample; low =

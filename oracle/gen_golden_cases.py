@@ -81,6 +81,13 @@ MOCEIR_CASES = [
     ("moceir_small_bias_b1_32", dict(MOCEIR_SMALL, bias=True, LayerNorm_type="BiasFree", topk=2), 1, 32, 32, 77, 78, 79),
 ]
 
+# training mode (SparseDispatcher + auxiliary losses): batch 2 so that the two samples can go to different experts; top-1
+# and top-2 routing, with and without the complexity bias of the importance loss
+MOCEIR_TRAIN_CASES = [
+    ("moceir_train_small_b2_64", MOCEIR_SMALL, 2, 64, 64, 171, 172, 173),
+    ("moceir_train_top2_b3_32x64", dict(MOCEIR_SMALL, bias=True, topk=2, with_complexity=True), 3, 32, 64, 174, 175, 176),
+]
+
 
 def synth_like(template_sd, seed):
     """Seeded synthetic state_dict with the keys / shapes of `template_sd` (a freshly constructed model's state_dict):
