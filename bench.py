@@ -346,6 +346,29 @@ def main():
                             f"decoder block are plain torch, everything tensor-sized is libb200ir",
                 "value": world * MB * H * W / 1e6 / (ms_mo * 1e-3), "unit": "MP/s", "ms_per_step": ms_mo,
                 "gpu_launches_per_step": (ops.LAUNCHES - ml0) // max(args.steps, 1)}
+        if not args.no_train and world == 1:
+            # the reference's own training objective for this model (MoCE-IR-main/src/train.py:59-72): L1 + 0.01 * balance
+            # loss, AdamW, 128x128 patches, batch 8; eager (the dispatcher's host sync per decoder block cannot be captured)
+            mnet.train()
+            mopt = b200ir.AdamW(mnet.parameters(), lr=2e-4)
+            mc = [torch.rand(MB, 3, 128, 128, generator=torch.Generator().manual_seed(900 + i)).to(dev) for i in range(2)]
+            md = [(c + 25.0 / 255.0 * torch.randn_like(c)).clamp(0, 1) for c in mc]
+            for i in range(max(args.warmup, 2)):
+                b200ir.train_step(mnet, mopt, md[i % 2], mc[i % 2], balance_loss_weight=0.01)
+            torch.cuda.synchronize()
+            ml0 = ops.LAUNCHES
+            nst = max(args.steps // 2, 2)
+            e0.record()
+            for i in range(nst):
+                mloss = b200ir.train_step(mnet, mopt, md[i % 2], mc[i % 2], balance_loss_weight=0.01)
+            e1.record()
+            torch.cuda.synchronize()
+            ms_mt = e0.elapsed_time(e1) / nst
+            moce["train_step"] = {"workload": "MoCEIR training step (L1 + 0.01 * balance loss, AdamW), 128x128, batch 8, "
+                                              f"{args.dtype}, eager, single GPU",
+                                  "value": MB * 128 * 128 / 1e6 / (ms_mt * 1e-3), "unit": "MP/s", "ms_per_step": ms_mt,
+                                  "gpu_launches_per_step": (ops.LAUNCHES - ml0) // nst, "loss": float(mloss)}
+            del mopt, mc, md
         del mnet, min_
         torch.cuda.empty_cache()
 

@@ -56,7 +56,15 @@ class _timed:
         return False
 
 
+# torch.cuda.current_stream() / current_device() resolve the device through several Python layers (~10 us per call under
+# load: a quarter of the host time of an eager training step); the raw getters are one C call each
+_cur_device = getattr(torch._C, "_cuda_getDevice", None) or torch.cuda.current_device
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream() -> int:
+    if _raw_stream is not None:
+        return _raw_stream(_cur_device())
     return torch.cuda.current_stream().cuda_stream
 
 
@@ -64,7 +72,7 @@ def _act(t: torch.Tensor, name: str):
     """(ptr, batch_stride, dtype_code) of an NCHW activation view."""
     if not t.is_cuda:
         raise ValueError(f"{name}: expected a CUDA tensor (this package has no CPU fallback)")
-    if t.device.index != torch.cuda.current_device():
+    if t.device.index != _cur_device():
         # every entry point enqueues on the CURRENT device's stream and sets per-device kernel attributes for it: a tensor
         # of another GPU would be dereferenced on the wrong device
         raise ValueError(f"{name}: tensor lives on cuda:{t.device.index} but the current device is "
