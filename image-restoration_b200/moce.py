@@ -250,15 +250,33 @@ class AdapterLayer(nn.Module):
         self.routing = RoutingFunction(dim, freq_dim, num_experts=num_experts, k=top_k, complexity=expert_complexity,
                                        use_complexity_bias=with_complexity, complexity_scale=complexity_scale)
 
-    def forward(self, x, freq_emb, shared):
-        if self.training:
-            return self._forward_train(x, freq_emb, shared)
+    def route(self, x, freq_emb):
+        """Run the router and start the copy of its decision (top-k indices | gates > 0 per expert) to pinned host memory.
+        A caller that has other work for the GPU which does not depend on the routing (DecoderBlock: the `shared`
+        self-attention) enqueues it between route() and forward(..., routed=...): the host then waits only for this small
+        copy, not for the whole stream, and the expert kernels are launched while the GPU is still busy."""
         gates, top_k_indices, _, aux = self.routing(x, freq_emb)
         self.loss = aux
+        dec = torch.cat([top_k_indices.to(torch.int32), (gates.detach() > 0).to(torch.int32)], 1)
+        host = self.__dict__.get("_b200ir_pin")
+        if host is None or host.shape != dec.shape:
+            host = self.__dict__["_b200ir_pin"] = torch.empty(dec.shape, dtype=torch.int32).pin_memory()
+        host.copy_(dec, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        return gates, top_k_indices, host, ev
+
+    def forward(self, x, freq_emb, shared, routed=None):
+        if routed is None:
+            routed = self.route(x, freq_emb)
+        if self.training:
+            return self._forward_train(x, shared, routed)
+        gates, top_k_indices, host, ev = routed
         sel = top_k_indices.squeeze(0)
         if sel.dim() != 1 and not (sel.dim() == 2 and sel.shape[1] == 1):
             raise ValueError("eval-mode AdapterLayer supports batch 1 (any top-k) or top-k 1 (any batch), like the reference")
-        chosen: List[int] = [int(i) for i in sel.flatten().tolist()]        # host sync, as the reference's indexing does
+        ev.synchronize()                         # the routing result is on the host (the reference indexes with it too)
+        chosen: List[int] = [int(i) for i in host[:, :self.top_k].flatten().tolist()]
         g = gates.gather(1, top_k_indices).float().contiguous()              # [B, k]
         out = None
         if sel.dim() == 1:                       # batch 1: expert j scaled by its own gate
@@ -275,15 +293,15 @@ class AdapterLayer(nn.Module):
         return _conv1x1(out, self.proj_out, cache=self.__dict__.setdefault("_b200ir_cache", {}), key="out")
 
 
-def _adapter_forward_train(self, x, freq_emb, shared):
+def _adapter_forward_train(self, x, shared, routed):
     """Training mode (moce_ir.py:659-667): SparseDispatcher semantics.  Expert e receives the samples b with
     gates[b, e] > 0 (``dispatch``: a row gather), and the output is out[b] = sum_e gates[b, e] * expert_e(x[b], shared[b])
     (``combine``: a gate-weighted scatter-accumulate, experts in ascending order like the reference's index_add over the
     expert-sorted batch index).  Experts that receive no sample are not run and get no gradient, as in the reference."""
-    gates, top_k_indices, _, aux = self.routing(x, freq_emb)
-    self.loss = aux
+    gates, top_k_indices, host, ev = routed
     B = x.shape[0]
-    sel_host = (gates.detach() > 0).cpu()                       # host sync, like the reference's `.tolist()` of part sizes
+    ev.synchronize()                                            # like the reference's `.tolist()` of the part sizes
+    sel_host = host[:, self.top_k:] > 0
     x, shared = x.contiguous(), shared.contiguous()
     ys, gs, idxs = [], [], []
     for e in range(self.num_experts):
@@ -349,8 +367,9 @@ class DecoderBlock(nn.Module):
         else:
             w2, b2 = self._proj_pair()
             both = A.ln_conv1x1(x, w2, b2, ln_type, lw, lb, None, cache=cache, key="pair")     # [B, 2*dim, H, W]
-        x_s = self.shared._run(both[:, :dim])
-        x_a = self.adapter(both[:, dim:], freq_emb, x_s)
+        routed = self.adapter.route(both[:, dim:], freq_emb)     # the router does not need x_s: decide first, so that
+        x_s = self.shared._run(both[:, :dim])                      # the host has the decision while the GPU runs `shared`
+        x_a = self.adapter(both[:, dim:], freq_emb, x_s, routed=routed)
         x = self.mixer(x_a, x_s, res=x)
         x = self.ffn._run(x, norm=self.norms[1], res=x)
         return x, self.adapter.loss
