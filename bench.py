@@ -417,6 +417,8 @@ def main():
         # SURVEY.md §8d, fused K4+K5: read the C-channel residual stream once, write the Hd gated channels once (bf16)
         alg_bytes = kb * kh * kw * (kc + khd) * 2
         kname, tag = f"ln_proj_dw_gate (LN+project_in+dw3x3+GELU gate) B{kb} C{kc} Hd{khd} {kh}x{kw}", "fused"
+        # what the two kernels this one replaces had to move (K4: C + 2Hd, K5: 2Hd + Hd channels per pixel, bf16)
+        pair_bytes = kb * kh * kw * ((kc + 2 * khd) + 3 * khd) * 2
     else:
         _, kb, khd, kh, kw, kdt = key
         esz = 2 if kdt == 1 else 4
@@ -428,6 +430,10 @@ def main():
                 "traffic": ncu_traffic(tag)[0], "traffic_source": ncu_traffic(tag)[1], "launch_ms": kms,
                 "launches_timed": gate_t[key][0], "alg_bytes_per_launch": alg_bytes,
                 "share_of_step": gate_t[key][0] * kms / args.steps / ms_eager,
+                **({"unfused_pair": {"alg_bytes": pair_bytes, "frac_at_this_time": pair_bytes / (kms * 1e-3) / 1e9 / pk["hbm_gbs"],
+                                     "what": "bytes of the K4 + K5 pair this kernel replaces / this kernel's time / HBM peak: "
+                                             "the pair would need this fraction of the roof to be as fast"}}
+                   if key[0] == FUSED_KEY else {}),
                 "timed_in": "the eager loop (eager_ms_per_step): one CUDA-event pair around every launch of the kernel"}
     out = {
         "metric": METRIC, "value": mp_per_step_total / (ms * 1e-3), "unit": "MP/s", "n_gpus": world,

@@ -64,7 +64,9 @@ SIGNATURES = {
     "b200ir_dwconv3x3_bwd_nparts": [_i, _i, _i, _i],
     "b200ir_dwconv3x3_wgrad": [_vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "b200ir_dwconv3x3_gelu_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
+    "b200ir_dwconv3x3_gelu_sigmoid_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "b200ir_mdta_bwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "b200ir_mdta_bwd_ex": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
     "b200ir_l1_loss_fwd_noalloc": [_vp, _i, _vp, _i, _i64, _vp, _vp],

@@ -209,19 +209,24 @@ def dwconv3x3(x, w, bias):
     return ops.dwconv3x3(x, _p(w), _p(bias))
 
 
-def dwconv3x3_gelu_gate(x, w, bias):
+def dwconv3x3_gelu_gate(x, w, bias, sigmoid_gate=False):
     if _needs_grad(x, w, bias):
-        return _DwGate.apply(x, w, bias)
+        return _DwGate.apply(x, w, bias, sigmoid_gate)
+    if sigmoid_gate:
+        return ops.dwconv3x3_gelu_sigmoid_gate(x, _p(w), _p(bias))
     return ops.dwconv3x3_gelu_gate(x, _p(w), _p(bias))
 
 
 def mdta_core(qkv, temperature, w_out, b_out, heads, res, out=None, cache=None, dynamic_temp=None):
     """Gram+norms -> softmax+fold -> (attn.v + project_out + residual)  (Restormer.py:117-131,147).
-    `dynamic_temp` ([B] or [B,1,1,1], inference only): per-sample factor on the temperature
+    `dynamic_temp` ([B] or [B,1,1,1]): per-sample factor on the temperature
     (experiment/RectiFormer.py:309-311)."""
     if dynamic_temp is not None:
         if _needs_grad(qkv, temperature, w_out, b_out, res, dynamic_temp):
-            raise RuntimeError("mdta_core: the dynamic-temperature variant is an inference path (no backward kernel)")
+            # effective temperature [B, heads] = temperature[h] * dynamic_temp[b]: a torch op on B * heads numbers, so that
+            # autograd splits the kernel's d(effective temperature) between the parameter and the dynamic factor
+            eff = temperature.float().reshape(1, -1) * dynamic_temp.float().reshape(-1, 1)
+            return _MdtaCore.apply(qkv, eff, w_out, b_out, res, heads, cache)
         temperature = (_p(temperature).reshape(1, -1) * dynamic_temp.detach().float().reshape(-1, 1)).contiguous()
         return _mdta_core_fwd(qkv, temperature, w_out, b_out, heads, res, out, cache)[0]
     if _needs_grad(qkv, temperature, w_out, b_out, res):
@@ -537,9 +542,12 @@ class _DwGate(torch.autograd.Function):
     """dwconv + chunk + gelu(x1)*x2 (Restormer.py:84,90-91); the conv output is recomputed in backward."""
 
     @staticmethod
-    def forward(ctx, t, w, bias):
+    def forward(ctx, t, w, bias, sigmoid_gate=False):
         ctx.save_for_backward(t, w, bias)
         ctx.params = (w, bias)
+        ctx.sigmoid_gate = sigmoid_gate   # gelu(x1) * sigmoid(x2): the split-gate FFN of experiment/RectiFormer.py:231-266
+        if sigmoid_gate:
+            return ops.dwconv3x3_gelu_sigmoid_gate(t, _p(w), _p(bias))
         return ops.dwconv3x3_gelu_gate(t, _p(w), _p(bias))
 
     @staticmethod
@@ -547,10 +555,11 @@ class _DwGate(torch.autograd.Function):
         t, w, bias = ctx.saved_tensors
         dg = _cg(dg)
         fold, h = _side_fold("gatefold", ctx.params)
-        da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None, fold=fold)
+        da, dw, db = ops.dwconv3x3_gelu_gate_bwd(t, _p(w), _p(bias), dg, want_bias=bias is not None, fold=fold,
+                                                 sigmoid_gate=ctx.sigmoid_gate)
         dw, db = h.sd.give(ctx.params[0], dw.to(w.dtype)), h.sd.give(ctx.params[1], db)
         dt = ops.dwconv3x3_bwd_input(da, _p(w)) if ctx.needs_input_grad[0] else None
-        return dt, dw, db
+        return dt, dw, db, None
 
 
 class _MdtaCore(torch.autograd.Function):
@@ -571,8 +580,7 @@ class _MdtaCore(torch.autograd.Function):
         C = C3 // 3
         v = qkv[:, 2 * C:]
         dM, db = ops.conv_wgrad(dout, v, 1, per_sample=True, want_bias=ctx.has_bias)
-        mt, mqk, dw, dtemp = ops.mdta_bwd(partials, attn, _p(temperature).reshape(-1), _p(w_out).reshape(C, C),
-                                          dM.contiguous())
+        mt, mqk, dw, dtemp = ops.mdta_bwd(partials, attn, _temp(temperature), _p(w_out).reshape(C, C), dM.contiguous())
         dqkv = torch.empty_like(qkv)
         _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
         _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])

@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(MB_THREADS)
 mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
                       const float* __restrict__ temperature, const float* __restrict__ w_out,
                       const float* __restrict__ dM, float* __restrict__ mqk, float* __restrict__ dtemp_part, int C,
-                      int d) {
+                      int d, int temp_per_sample) {
   extern __shared__ float sm[];
   const int D1 = d + 1;
   float* at = sm;                        // attn  [d][d+1]
@@ -558,7 +558,7 @@ mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float
   const float* base = partials + ((size_t)b * heads + h) * nslab * per;
   const float* a_g = attn + ((size_t)b * heads + h) * d * d;
   const float* dMb = dM + (size_t)b * C * C;
-  const float temp = temperature[h];
+  const float temp = temperature[temp_per_sample ? (size_t)b * heads + h : h];   // [B][heads]: dynamic temperature
 
   for (int j = tid; j < 2 * d; j += MB_THREADS) {
     float s = 0.f;
@@ -952,6 +952,13 @@ extern "C" int b200ir_conv_wgrad(const void* dy, int64_t dy_bstride, int dy_dtyp
 extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const float* temperature,
                                const float* w_out, const float* dM, float* mt, float* mqk, float* dw_out_part,
                                float* dtemp_part, int B, int C, int heads, b200ir_stream_t stream) {
+  return b200ir_mdta_bwd_ex(partials, nslab, attn, temperature, 0, w_out, dM, mt, mqk, dw_out_part, dtemp_part, B, C, heads,
+                            stream);
+}
+
+extern "C" int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float* attn, const float* temperature,
+                                  int temp_per_sample, const float* w_out, const float* dM, float* mt, float* mqk,
+                                  float* dw_out_part, float* dtemp_part, int B, int C, int heads, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(partials && attn && temperature && w_out && dM && mt && mqk && dw_out_part && dtemp_part,
                    "mdta_bwd: null pointer");
   B200IR_CHECK_ARG(nslab > 0 && B > 0 && C > 0 && heads > 0 && C % heads == 0 && B <= 65535, "mdta_bwd: bad shape");
@@ -967,7 +974,7 @@ extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* at
     attr_set = true;
   }
   mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
-      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d);
+      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0);
   int rc = check_launch("mdta_bwd_chain");
   if (rc) return rc;
   mdta_bwd_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem2,

@@ -102,7 +102,8 @@ dwconv_wgrad_tile_kernel(const void* __restrict__ dy, int64_t dy_bs, const void*
 __global__ void __launch_bounds__(256)
 gelu_gate_bwd_tile_kernel(const void* __restrict__ t, int64_t t_bs, const float* __restrict__ w,
                           const float* __restrict__ bias, const void* __restrict__ dg, int64_t dg_bs,
-                          void* __restrict__ da, int64_t da_bs, int dt, float* __restrict__ parts, int Hd, int H, int W) {
+                          void* __restrict__ da, int64_t da_bs, int dt, float* __restrict__ parts, int Hd, int H, int W,
+                          int gate_fn) {
   __shared__ float s1[DWB_SM], s2[DWB_SM];
   const DwTile T = dw_tile(H, W);
   const int c = blockIdx.y, b = blockIdx.z, nsplit = gridDim.x;
@@ -149,8 +150,15 @@ gelu_gate_bwd_tile_kernel(const void* __restrict__ t, int64_t t_bs, const float*
           const float g = ld_any(dg, dt, go + off);
           const float cdf = 0.5f * (1.0f + erff(a1 * 0.70710678118654752440f));
           const float pdf = 0.39894228040143267794f * expf(-0.5f * a1 * a1);
-          float d1 = g * a2 * (cdf + a1 * pdf);
-          float d2 = g * a1 * cdf;
+          float d1, d2;
+          if (gate_fn == 0) {                      // y = gelu(a1) * a2               (Restormer.py:90-91)
+            d1 = g * a2 * (cdf + a1 * pdf);
+            d2 = g * a1 * cdf;
+          } else {                                 // y = gelu(a1) * sigmoid(a2)      (experiment/RectiFormer.py:258-262)
+            const float sg = 1.0f / (1.0f + expf(-a2));
+            d1 = g * sg * (cdf + a1 * pdf);
+            d2 = g * a1 * cdf * sg * (1.0f - sg);
+          }
           st_any(da, dt, a1o + off, d1);
           st_any(da, dt, a2o + off, d2);
 #pragma unroll
@@ -252,17 +260,34 @@ extern "C" int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const 
   return check_launch("dwconv3x3_wgrad");
 }
 
+static int gate_bwd_impl(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
+                         int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, float* parts, int nparts, int B,
+                         int Hd, int H, int W, int gate_fn, b200ir_stream_t stream);
+
 extern "C" int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias,
                                               const void* dg, int64_t dg_bstride, void* da, int64_t da_bstride,
                                               int dtype, float* parts, int nparts, int B, int Hd, int H, int W,
                                               b200ir_stream_t stream) {
+  return gate_bwd_impl(t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride, dtype, parts, nparts, B, Hd, H, W, 0, stream);
+}
+
+extern "C" int b200ir_dwconv3x3_gelu_sigmoid_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias,
+                                                      const void* dg, int64_t dg_bstride, void* da, int64_t da_bstride,
+                                                      int dtype, float* parts, int nparts, int B, int Hd, int H, int W,
+                                                      b200ir_stream_t stream) {
+  return gate_bwd_impl(t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride, dtype, parts, nparts, B, Hd, H, W, 1, stream);
+}
+
+static int gate_bwd_impl(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
+                         int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, float* parts, int nparts, int B,
+                         int Hd, int H, int W, int gate_fn, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(t && w && dg && da && parts && B > 0 && Hd > 0 && H > 0 && W > 0, "gelu_gate_bwd: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype) && B <= 65535 && Hd <= 65535, "gelu_gate_bwd: bad dtype / grid");
   B200IR_CHECK_ARG(nparts == b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W),
                    "gelu_gate_bwd: nparts=%d, expected %d (b200ir_dwconv3x3_bwd_nparts with C=Hd)", nparts,
                    b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W));
   cudaStream_t st = (cudaStream_t)stream;
-  if (dw_tma_ok(dtype, H, W, t, t_bstride, dg, dg_bstride, da, da_bstride)) {
+  if (gate_fn == 0 && dw_tma_ok(dtype, H, W, t, t_bstride, dg, dg_bstride, da, da_bstride)) {   // (sigmoid gate: tile kernel)
     int rc = zero_tail(parts, nparts, B * dw_bwd_tma_tiles_per_plane(H, W), (int64_t)Hd * 20, st);
     if (rc) return rc;
     return dw_bwd_tma_launch<true>(t, t_bstride, dg, dg_bstride, da, da_bstride, w, bias, parts, B, Hd, H, W, st);
@@ -271,6 +296,6 @@ extern "C" int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, 
   int rc = zero_tail(parts, nparts, B * ns, (int64_t)Hd * 20, st);
   if (rc) return rc;
   gelu_gate_bwd_tile_kernel<<<dim3((unsigned)ns, (unsigned)Hd, (unsigned)B), 256, 0, st>>>(
-      t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride, dtype, parts, Hd, H, W);
+      t, t_bstride, w, bias, dg, dg_bstride, da, da_bstride, dtype, parts, Hd, H, W, gate_fn);
   return check_launch("gelu_gate_bwd");
 }

@@ -222,14 +222,19 @@ class GatedSpatialFFN(nn.Module):
         return ent[1], ent[2]
 
     def _run(self, x, norm=None, res=None, out=None):
-        if torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()) and x.requires_grad:
-            raise RuntimeError("GatedSpatialFFN is an inference path (no backward kernel for the sigmoid gate variant)")
         ln_type, lw, lb = _ln_args(norm) if norm is not None else (L.LN_NONE, None, None)
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         t = A.ln_conv1x1(x, self.project_in.weight, self.project_in.bias, ln_type, lw, lb, None, cache=cache,
                          key=("in", id(norm)))
-        w, b = self._dw_pair()
-        g = ops.dwconv3x3_gelu_sigmoid_gate(t, w, b)
+        ps = (self.dwconv_content.weight, self.dwconv_gate.weight, self.dwconv_content.bias, self.dwconv_gate.bias)
+        if A._needs_grad(t, *ps):
+            # training: the stacked [content | gate] depthwise weight stays connected to its two parameters
+            w = torch.cat([ps[0], ps[1]], 0)
+            b = torch.cat([ps[2], ps[3]], 0) if ps[2] is not None else None
+            g = A.dwconv3x3_gelu_gate(t, w, b, sigmoid_gate=True)
+        else:
+            w, b = self._dw_pair()
+            g = ops.dwconv3x3_gelu_sigmoid_gate(t, w, b)
         del t
         return A.ln_conv1x1(g, self.project_out.weight, self.project_out.bias, L.LN_NONE, None, None, res, out=out,
                             cache=cache, key="out")

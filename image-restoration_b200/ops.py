@@ -678,7 +678,7 @@ def dwconv3x3_wgrad(dy, x, want_bias=False):
     return d[:, :9].reshape(C, 1, 3, 3), (d[:, 9] if want_bias else None)
 
 
-def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None):
+def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None, sigmoid_gate=False):
     """Backward of the fused dwconv+GELU gate: (da [B,2Hd,H,W] = gradient w.r.t. the depthwise-conv output,
     dw [2Hd,1,3,3], db [2Hd] or None)."""
     B, C2, H, W_ = t.shape
@@ -692,8 +692,9 @@ def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None):
     nparts = lib.b200ir_dwconv3x3_bwd_nparts(B, Hd, H, W_)
     parts = torch.empty((nparts, C2, 10), device=t.device, dtype=torch.float32)
     with _timed("dwconv3x3_gelu_gate_bwd", B, Hd, H, W_, tdt):
-        rc = lib.b200ir_dwconv3x3_gelu_gate_bwd(tp, tbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), gp, gbs, ap, abs_,
-                                                tdt, parts.data_ptr(), nparts, B, Hd, H, W_, _stream())
+        fn = lib.b200ir_dwconv3x3_gelu_sigmoid_gate_bwd if sigmoid_gate else lib.b200ir_dwconv3x3_gelu_gate_bwd
+        rc = fn(tp, tbs, _par(w, "w", C2 * 9), _par(bias, "bias", C2), gp, gbs, ap, abs_, tdt, parts.data_ptr(), nparts, B,
+                Hd, H, W_, _stream())
     L.check(rc, "b200ir_dwconv3x3_gelu_gate_bwd")
     def finish():
         d = parts.view(C2, 10) if nparts == 1 else reduce_partials(parts, nparts, C2 * 10).view(C2, 10)
@@ -703,7 +704,8 @@ def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None):
 
 
 def mdta_bwd(partials, attn, temperature, w_out, dM):
-    """-> (mt [B,C,C], mqk [B,2C,2C], dW_out [C,C], dtemperature [heads])."""
+    """-> (mt [B,C,C], mqk [B,2C,2C], dW_out [C,C], dtemperature [heads]); with a per-sample temperature [B, heads]
+    (dynamic temperature) the last item is its gradient [B, heads]."""
     B, heads, nslab, per = partials.shape
     C = w_out.shape[0]
     dev = partials.device
@@ -712,12 +714,14 @@ def mdta_bwd(partials, attn, temperature, w_out, dM):
     dwp = torch.empty((B, C, C), device=dev, dtype=torch.float32)
     dtp = torch.empty((B, heads), device=dev, dtype=torch.float32)
     with _timed("mdta_bwd", B, C, heads):
-        rc = lib.b200ir_mdta_bwd(partials.data_ptr(), nslab, attn.data_ptr(), _par(temperature, "temperature", heads),
-                                 _par(w_out, "w_out", C * C), _par(dM, "dM", B * C * C), mt.data_ptr(), mqk.data_ptr(),
-                                 dwp.data_ptr(), dtp.data_ptr(), B, C, heads, _stream())
-    L.check(rc, "b200ir_mdta_bwd")
+        per_sample = temperature.dim() == 2
+        rc = lib.b200ir_mdta_bwd_ex(partials.data_ptr(), nslab, attn.data_ptr(),
+                                    _par(temperature, "temperature", B * heads if per_sample else heads), int(per_sample),
+                                    _par(w_out, "w_out", C * C), _par(dM, "dM", B * C * C), mt.data_ptr(), mqk.data_ptr(),
+                                    dwp.data_ptr(), dtp.data_ptr(), B, C, heads, _stream())
+    L.check(rc, "b200ir_mdta_bwd_ex")
     dw = dwp.view(C, C) if B == 1 else reduce_partials(dwp, B, C * C).view(C, C)
-    dt = dtp.view(heads) if B == 1 else reduce_partials(dtp, B, heads)
+    dt = dtp if per_sample else (dtp.view(heads) if B == 1 else reduce_partials(dtp, B, heads))
     return mt, mqk, dw, dt
 
 

@@ -245,6 +245,11 @@ int b200ir_dwconv3x3_wgrad(const void* dy, int64_t dy_bstride, const void* x, in
 int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
                                    int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, float* parts,
                                    int nparts, int B, int Hd, int H, int W, b200ir_stream_t stream);
+/* Same for the split-gate FFN of experiment/RectiFormer.py:231-266, y = gelu(a1) * sigmoid(a2):
+ * da[c] = dg*sigmoid(a2)*gelu'(a1), da[c+Hd] = dg*gelu(a1)*sigmoid'(a2). */
+int b200ir_dwconv3x3_gelu_sigmoid_gate_bwd(const void* t, int64_t t_bstride, const float* w, const float* bias, const void* dg,
+                                   int64_t dg_bstride, void* da, int64_t da_bstride, int dtype, float* parts,
+                                   int nparts, int B, int Hd, int H, int W, b200ir_stream_t stream);
 /* MDTA backward, small per-(sample, head) part (softmax, temperature, F.normalize; Restormer.py:121-131).
  * In: Gram partials + attn of the forward, dM [B,C,C] (= conv_wgrad(dout, v, per_sample)).
  * Out: mt [B,C,C] = M_b^T (dv = mt_b.dout), mqk [B,2C,2C] (d[q;k] = mqk_b.[q;k]), dw_out_part [B,C,C] and
@@ -252,6 +257,11 @@ int b200ir_dwconv3x3_gelu_gate_bwd(const void* t, int64_t t_bstride, const float
 int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const float* temperature, const float* w_out,
                     const float* dM, float* mt, float* mqk, float* dw_out_part, float* dtemp_part, int B, int C,
                     int heads, b200ir_stream_t stream);
+/* Same with a per-sample temperature [B][heads] (temp_per_sample = 1): the dynamic temperature of
+ * experiment/RectiFormer.py:309-311; dtemp_part [B][heads] is then the gradient of that effective temperature. */
+int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float* attn, const float* temperature, int temp_per_sample,
+                       const float* w_out, const float* dM, float* mt, float* mqk, float* dw_out_part, float* dtemp_part,
+                       int B, int C, int heads, b200ir_stream_t stream);
 /* nn.PixelShuffle(2) / nn.PixelUnshuffle(2) as a copy (x [B,C,H,W]; gradients of Upsample / Downsample). */
 int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B, int C, int H,
                          int W, int mode, b200ir_stream_t stream);

@@ -39,8 +39,21 @@ def main():
                 y = mod(x, dt)
             else:
                 y = mod(x)
-        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=y.numpy(), keys=np.array(sorted(mod.state_dict())))
-        print(name, tuple(y.shape))
+        # the same module under autograd (round 2: the variants train): input, parameter and dynamic-temperature gradients
+        rec = {}
+        xg = x.clone().requires_grad_(True)
+        gy = torch.randn(y.shape, generator=torch.Generator().manual_seed(seed + 9))
+        if kind == "attn_dyn":
+            dtg = dt.clone().requires_grad_(True)
+            mod(xg, dtg).backward(gy)
+            rec["ddt"] = dtg.grad.numpy()
+        else:
+            mod(xg).backward(gy)
+        rec["dx"] = xg.grad.numpy()
+        for k, q in mod.named_parameters():
+            rec["g." + k] = q.grad.numpy()
+        np.savez_compressed(os.path.join(GOLD, name + ".npz"), y=y.numpy(), keys=np.array(sorted(mod.state_dict())), **rec)
+        print(name, tuple(y.shape), "grads", len(rec))
     AD = load("/root/reference/AdaIR-main/net/model.py", "ref_adair_model")
     for name, dim, heads, bias, b, h, w, seed in ADAIR_CCA_CASES:
         mod = AD.Chanel_Cross_Attention(dim, heads, bias).eval()
