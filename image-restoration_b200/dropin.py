@@ -116,6 +116,38 @@ def _is_cross(m) -> bool:
             and tuple(m.temperature.shape) == (heads, 1, 1) and c % heads == 0)
 
 
+def _is_split_gate_ffn(m) -> bool:
+    """RectiFormer GatedSpatialFFN (experiment/RectiFormer.py:231-266): project_in -> chunk ->
+    gelu(dwconv_content(content)) * sigmoid(dwconv_gate(gate)) -> project_out."""
+    need = ("project_in", "dwconv_gate", "dwconv_content", "project_out")
+    if not all(hasattr(m, a) for a in need):
+        return False
+    if {n.split(".")[0] for n, _ in m.named_parameters()} != set(need):
+        return False
+    hid = m.project_out.in_channels if isinstance(m.project_out, nn.Conv2d) else 0
+    return (_conv_ok(m.project_in, 1, 1) and _conv_ok(m.dwconv_gate, 3, hid) and _conv_ok(m.dwconv_content, 3, hid)
+            and _conv_ok(m.project_out, 1, 1) and m.project_in.out_channels == 2 * hid
+            and m.project_in.in_channels == m.project_out.out_channels)
+
+
+def _is_elementwise_gated(m) -> bool:
+    """RectiFormer ElementwiseGatedAttention (experiment/RectiFormer.py:270-325): MDTA + a gate branch
+    gate_generator = Sequential(dw3x3, 1x1) on the block input, optional per-sample dynamic temperature."""
+    need = ("temperature", "qkv", "qkv_dwconv", "gate_generator", "project_out")
+    if not all(hasattr(m, a) for a in need) or not isinstance(getattr(m, "num_heads", None), int):
+        return False
+    if {n.split(".")[0] for n, _ in m.named_parameters()} != set(need):
+        return False
+    gg = m.gate_generator
+    if not isinstance(gg, nn.Sequential) or len(gg) != 2:
+        return False
+    c = m.qkv.in_channels if isinstance(m.qkv, nn.Conv2d) else 0
+    return (_conv_ok(m.qkv, 1, 1) and _conv_ok(m.qkv_dwconv, 3, 3 * c) and m.qkv.out_channels == 3 * c
+            and _conv_ok(gg[0], 3, c) and _conv_ok(gg[1], 1, 1) and gg[1].in_channels == c == gg[1].out_channels
+            and _conv_ok(m.project_out, 1, 1) and m.project_out.in_channels == c == m.project_out.out_channels
+            and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
+
+
 def _is_resize(m):
     """Sequential(conv3x3 (no bias), PixelUnshuffle(2) | PixelShuffle(2)) wrapped as `.body` -> 'down' | 'up' | None."""
     body = getattr(m, "body", None)
@@ -167,6 +199,20 @@ def _adopt_cross(m):
     return a
 
 
+def _adopt_split_gate_ffn(m):
+    f = _bare(M.GatedSpatialFFN)
+    f.project_in, f.dwconv_gate, f.dwconv_content, f.project_out = m.project_in, m.dwconv_gate, m.dwconv_content, m.project_out
+    return f
+
+
+def _adopt_elementwise_gated(m):
+    a = _bare(M.ElementwiseGatedAttention)
+    a.num_heads, a.dim = m.num_heads, m.qkv.in_channels
+    a.temperature = m.temperature
+    a.qkv, a.qkv_dwconv, a.gate_generator, a.project_out = m.qkv, m.qkv_dwconv, m.gate_generator, m.project_out
+    return a
+
+
 def _adopt_gdfn(m):
     f = _bare(M.FeedForward)
     f.project_in, f.dwconv, f.project_out = m.project_in, m.dwconv, m.project_out
@@ -176,7 +222,8 @@ def _adopt_gdfn(m):
 def _adopt(m):
     """-> (replacement, kind) or (None, None)."""
     if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.CrossAttention, M.GatedMDTA,
-                      M.GatedTransformerBlock, M.FeedForward, M.LayerNorm, M.Downsample, M.Upsample)):
+                      M.GatedTransformerBlock, M.FeedForward, M.LayerNorm, M.Downsample, M.Upsample,
+                      M.GatedSpatialFFN, M.ElementwiseGatedAttention)):
         return None, None
     kids = dict(m.named_children())
     if set(kids) == {"norm1", "attn", "norm2", "ffn"} and _is_ln(m.norm1) and _is_ln(m.norm2) and _is_mdta(m.attn) \
@@ -197,6 +244,10 @@ def _adopt(m):
         return _adopt_cross(m), "cross_attention"
     if _is_gated_mdta(m):
         return _adopt_gated(m), "gated_attention"
+    if _is_elementwise_gated(m):
+        return _adopt_elementwise_gated(m), "elementwise_gated_attention"
+    if _is_split_gate_ffn(m):
+        return _adopt_split_gate_ffn(m), "split_gate_ffn"
     if _is_gdfn(m):
         return _adopt_gdfn(m), "feedforward"
     if _is_ln(m):
@@ -214,8 +265,10 @@ def _in_channels(new, kind):
         return new.attn.qkv.in_channels
     if kind == "encoder_block":
         return new.mixer.qkv.in_channels
-    if kind in ("attention", "gated_attention"):
+    if kind in ("attention", "gated_attention", "elementwise_gated_attention"):
         return new.qkv.in_channels
+    if kind == "split_gate_ffn":
+        return new.project_in.in_channels
     if kind == "cross_attention":
         return new.q.in_channels
     if kind == "feedforward":

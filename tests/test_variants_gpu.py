@@ -113,6 +113,37 @@ def test_accelerate_adopts_adair_num_head_cross_attention():
     assert (got - ref).abs().max() <= 2e-4 * max(1.0, ref.abs().max().item())
 
 
+def test_accelerate_adopts_rectiformer_variants():
+    """dropin.accelerate() swaps modules with the structure of RectiFormer's GatedSpatialFFN / ElementwiseGatedAttention
+    (the stand-ins in tests/torch_models.py are bit-identical to experiment/RectiFormer.py:231-325, checked in the build
+    container), keeps the dynamic-temperature argument, and the adopted block trains."""
+    import b200ir
+    from torch_models import RefRectiBlock
+    torch.manual_seed(4)
+    net = RefRectiBlock(32, 2, 2.0, True)
+    x = O.synth_image(2, 16, 24, seed=8, c=32) * 2 - 1
+    dt = (torch.rand(2, generator=torch.Generator().manual_seed(5)) * 2).view(2, 1, 1, 1)
+    with torch.no_grad():
+        ref, ref_dt = net(x), net(x, dt)
+    xr = x.clone().requires_grad_(True)
+    net(xr, dt).square().mean().backward()
+    gref = {k: q.grad.clone() for k, q in net.named_parameters()}
+    net.zero_grad()
+    net = net.cuda()
+    net, stats = b200ir.accelerate(net, verify=True)
+    assert stats.get("elementwise_gated_attention") == 1 and stats.get("split_gate_ffn") == 1, stats
+    assert isinstance(net.attn, b200ir.ElementwiseGatedAttention) and isinstance(net.ffn, b200ir.GatedSpatialFFN)
+    with torch.no_grad():
+        got, got_dt = net(x.cuda()).cpu(), net(x.cuda(), dt.cuda()).cpu()
+    assert (got - ref).abs().max() <= 2e-4 * max(1.0, ref.abs().max().item())
+    assert (got_dt - ref_dt).abs().max() <= 2e-4 * max(1.0, ref_dt.abs().max().item())
+    xg = x.cuda().requires_grad_(True)
+    net(xg, dt.cuda()).square().mean().backward()
+    assert _rel(xg.grad.cpu(), xr.grad) <= 1e-3
+    for k, q in net.named_parameters():
+        assert q.grad is not None and _rel(q.grad.cpu(), gref[k]) <= 2e-3, (k, _rel(q.grad.cpu(), gref[k]))
+
+
 def test_adair_fremodule_vs_reference_golden():
     """b200ir.FreModule (bilinear resize, conv3x3, few-bin low-pass instead of fft2/mask/ifft2, three channel cross
     attentions, spatial / channel gates, per-channel affine) against AdaIR-main/net/model.py FreModule outputs."""

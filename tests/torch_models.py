@@ -3,6 +3,7 @@ as Restormer.py:60-150 and moce_ir.py:805-834), whose forwards call the CPU orac
 in for "an existing reference model" in the tests of b200ir.accelerate(); nothing in the product imports this file."""
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from oracle import restormer_oracle as O
 
@@ -201,3 +202,59 @@ class RefAdaIRFusion(nn.Module):
 
     def forward(self, x):
         return self.cca(self.a(x), self.b(x)) + x
+
+
+class RefGatedSpatialFFN(nn.Module):
+    """Plain-torch stand-in with the structure and arithmetic of RectiFormer's GatedSpatialFFN
+    (experiment/RectiFormer.py:231-266): content, gate = project_in(x).chunk(2); gelu(dw_c(content)) * sigmoid(dw_g(gate))."""
+
+    def __init__(self, dim, ffn_expansion_factor, bias):
+        super().__init__()
+        hid = int(dim * ffn_expansion_factor)
+        self.project_in = nn.Conv2d(dim, hid * 2, 1, bias=bias)
+        self.dwconv_gate = nn.Conv2d(hid, hid, 3, 1, 1, groups=hid, bias=bias)
+        self.dwconv_content = nn.Conv2d(hid, hid, 3, 1, 1, groups=hid, bias=bias)
+        self.project_out = nn.Conv2d(hid, dim, 1, bias=bias)
+
+    def forward(self, x):
+        content, gate = self.project_in(x).chunk(2, dim=1)
+        return self.project_out(F.gelu(self.dwconv_content(content)) * torch.sigmoid(self.dwconv_gate(gate)))
+
+
+class RefElementwiseGatedAttention(nn.Module):
+    """Stand-in for RectiFormer's ElementwiseGatedAttention (experiment/RectiFormer.py:270-325): MDTA, output gated by
+    sigmoid(gate_generator(x)) before project_out, optional per-sample dynamic temperature."""
+
+    def __init__(self, dim, num_heads, bias):
+        super().__init__()
+        self.num_heads, self.dim = num_heads, dim
+        self.temperature = nn.Parameter(torch.ones(num_heads, 1, 1))
+        self.qkv = nn.Conv2d(dim, dim * 3, 1, bias=bias)
+        self.qkv_dwconv = nn.Conv2d(dim * 3, dim * 3, 3, 1, 1, groups=dim * 3, bias=bias)
+        self.gate_generator = nn.Sequential(nn.Conv2d(dim, dim, 3, 1, 1, groups=dim, bias=bias), nn.Conv2d(dim, dim, 1, bias=bias))
+        self.project_out = nn.Conv2d(dim, dim, 1, bias=bias)
+
+    def forward(self, x, dynamic_temp=None):
+        b, c, h, w = x.shape
+        q, k, v = self.qkv_dwconv(self.qkv(x)).chunk(3, dim=1)
+        gate = self.gate_generator(x)
+        sh = lambda t: t.reshape(b, self.num_heads, c // self.num_heads, h * w)
+        q, k, v = F.normalize(sh(q), dim=-1), F.normalize(sh(k), dim=-1), sh(v)
+        temp = self.temperature if dynamic_temp is None else self.temperature.unsqueeze(0) * dynamic_temp
+        attn = ((q @ k.transpose(-2, -1)) * temp).softmax(dim=-1)
+        out = (attn @ v).reshape(b, c, h, w) * torch.sigmoid(gate)
+        return self.project_out(out)
+
+
+class RefRectiBlock(nn.Module):
+    """x + attn(norm1(x), dynamic_temp); x + ffn(norm2(x)) with the two RectiFormer variants (the way its block calls them)."""
+
+    def __init__(self, dim=32, heads=2, f=2.0, bias=True):
+        super().__init__()
+        self.norm1, self.norm2 = RefLayerNorm(dim, "WithBias"), RefLayerNorm(dim, "WithBias")
+        self.attn = RefElementwiseGatedAttention(dim, heads, bias)
+        self.ffn = RefGatedSpatialFFN(dim, f, bias)
+
+    def forward(self, x, dynamic_temp=None):
+        x = x + self.attn(self.norm1(x), dynamic_temp)
+        return x + self.ffn(self.norm2(x))
