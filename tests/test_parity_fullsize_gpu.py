@@ -210,3 +210,24 @@ def test_adamw_skips_parameters_without_grad():
         ropt.step()
     for p, r in zip(ps, rs):
         assert (p.detach() - r.detach()).abs().max() <= 1e-6
+
+
+@pytest.mark.parametrize("kind", ["zeros", "ones", "checker"])
+def test_degenerate_frames_vs_oracle(kind):
+    """Constant and extreme-contrast frames.  A black frame makes the first LayerNorm see zero variance (rstd = 1/sqrt(eps),
+    which the fused LN + 1x1 + depthwise kernel applies in place) and leaves a network driven by its biases alone: with the
+    random synthetic weights that is ill-conditioned (the fp32 path's error grows from 6e-7 to 7e-5, measured), so bf16
+    activations are held to 30 dB there (35 dB fused, 38 dB two-kernel path: the same regime) and to 45 dB otherwise."""
+    x = torch.zeros(1, 3, 128, 128)
+    if kind == "ones":
+        x += 1.0
+    elif kind == "checker":
+        x[:, :, ::2, ::2] = 1.0
+        x[:, :, 1::2, 1::2] = 1.0
+    with torch.no_grad():
+        ref = O.restormer_forward(O.synth_state_dict({}, seed=0), x)
+        y32 = _default_net(torch.float32)(x.cuda()).cpu()
+        y16 = _default_net(torch.bfloat16)(x.cuda()).cpu()
+    assert torch.isfinite(y32).all() and torch.isfinite(y16).all()
+    assert (y32 - ref).abs().max() <= 5e-4, float((y32 - ref).abs().max())
+    assert O.psnr(y16, ref) >= (30.0 if kind == "zeros" else 45.0), O.psnr(y16, ref)

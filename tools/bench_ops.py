@@ -27,7 +27,9 @@ def rnd(*shape, dtype=bf):
 def level(name):
     # (B, C, heads, H, W)
     return {"l1a": (16, 48, 1, 256, 256), "l1b": (16, 96, 1, 256, 256), "l2": (16, 96, 2, 128, 128),
-            "l3": (16, 192, 4, 64, 64), "l4": (16, 384, 8, 32, 32)}[name]
+            "l3": (16, 192, 4, 64, 64), "l4": (16, 384, 8, 32, 32),
+            # training shapes of cfg4 (B8, 128x128 patches): the four U-Net levels
+            "t1": (8, 48, 1, 128, 128), "t2": (8, 96, 2, 64, 64), "t3": (8, 192, 4, 32, 32), "t4": (8, 384, 8, 16, 16)}[name]
 
 
 VARIANT = int(__import__('os').environ.get('BENCH_VARIANT', '0'))   # L.GEMM_AUTO / RESIDENT / STREAM / RESIDENT_CH (A/B timing)
