@@ -197,6 +197,10 @@ spatial_mean_cta_kernel(const T* __restrict__ x, int64_t x_bs, float* __restrict
 
 }  // namespace b200ir
 
+namespace b200ir {
+bool circconv_dft32_launch(const void* a, int64_t a_bs, const void* b, int64_t b_bs, void* y, int64_t y_bs, int B, int C, int H,
+                           int W, int mode, cudaStream_t st, int* rc);   // circconv_dft.cu
+}
 using namespace b200ir;
 
 extern "C" int b200ir_circconv_patch(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, void* y,
@@ -207,6 +211,10 @@ extern "C" int b200ir_circconv_patch(const void* a, int64_t a_bstride, const voi
   B200IR_UNSUPPORTED(patch >= 2 && patch <= 32 && (patch & (patch - 1)) == 0, "circconv_patch: patch %d unsupported (2..32, power of 2)", patch);
   B200IR_UNSUPPORTED(B <= 65535 && C <= 65535, "circconv_patch: B, C <= 65535");
   const int npx = (W + patch - 1) / patch, npy = (H + patch - 1) / patch;
+  if (patch == 32 && dtype == B200IR_BF16) {   // tensor-core DFT (circconv_dft.cu); falls through for unaligned planes
+    int rc = 0;
+    if (circconv_dft32_launch(a, a_bstride, b, b_bstride, y, y_bstride, B, C, H, W, mode, (cudaStream_t)stream, &rc)) return rc;
+  }
   if (patch >= 16) {
     const int64_t total = (int64_t)B * C * npx * npy;
     B200IR_UNSUPPORTED((total + 3) / 4 < (1ll << 31), "circconv_patch: too many patches");
