@@ -57,6 +57,41 @@ circconv_patch_kernel(const T* __restrict__ a, int64_t a_bs, const T* __restrict
   }
 }
 
+// Small patches (p = 4 / 8: the two cheapest experts, 6-24 channels at full resolution): the kernel above launches one
+// 16- / 64-thread CTA per patch (165 us for 12 MB at cfg3).  Here a 256-thread CTA takes 256 / p^2 patches that are neighbours in
+// x (one p-row band, 64 B - 128 B contiguous per row), a thread owns one output pixel.
+template <int P, typename T>
+__global__ void __launch_bounds__(256)
+circconv_small_kernel(const T* __restrict__ a, int64_t a_bs, const T* __restrict__ b, int64_t b_bs, T* __restrict__ y,
+                      int64_t y_bs, int C, int H, int W, int ngx, int mode) {
+  constexpr int NP = 256 / (P * P), TW = NP * P, M = P - 1;
+  __shared__ float sa[P][TW + 1], sb[P][TW + 1];
+  const int grp = blockIdx.x % ngx, py = blockIdx.x / ngx, c = blockIdx.y, n = blockIdx.z;
+  const int y0 = py * P, x0 = grp * TW;
+  const int64_t plane = (int64_t)c * H * W;
+  {
+    const int r = threadIdx.x / TW, q = threadIdx.x % TW;   // 256 = P * TW
+    const bool in = (y0 + r) < H && (x0 + q) < W;
+    const int64_t off = plane + (int64_t)(y0 + r) * W + (x0 + q);
+    sa[r][q] = in ? to_f<T>(a[(int64_t)n * a_bs + off]) : 0.f;
+    sb[r][q] = in ? to_f<T>(b[(int64_t)n * b_bs + off]) : 0.f;
+  }
+  __syncthreads();
+  const int oi = threadIdx.x / TW, col = threadIdx.x % TW, pb = (col / P) * P, oj = col % P;
+  if (y0 + oi >= H || x0 + col >= W) return;
+  float acc = 0.f;
+#pragma unroll
+  for (int r = 0; r < P; ++r) {
+    const int br = mode == 0 ? ((oi - r) & M) : ((r - oi) & M);
+#pragma unroll
+    for (int q = 0; q < P; ++q) {
+      const int bq = mode == 0 ? ((oj - q) & M) : ((q - oj) & M);
+      acc = fmaf(sa[r][pb + q], sb[br][pb + bq], acc);
+    }
+  }
+  y[(int64_t)n * y_bs + plane + (int64_t)(y0 + oi) * W + (x0 + col)] = from_f<T>(acc);
+}
+
 // Register-tiled form for p = 16 / 32 (the two large experts; measured on B200 the shared-memory-bound kernel above ran
 // the p = 32 expert of cfg3 at 3.7 TMAC/s = 10 % of the FP32 peak and was half of the whole MoCE-IR forward): one WARP per
 // (patch, channel), a thread owns one output row (p = 32) or half of one (p = 16) in registers.  Per row a of the first
@@ -198,8 +233,8 @@ spatial_mean_cta_kernel(const T* __restrict__ x, int64_t x_bs, float* __restrict
 }  // namespace b200ir
 
 namespace b200ir {
-bool circconv_dft32_launch(const void* a, int64_t a_bs, const void* b, int64_t b_bs, void* y, int64_t y_bs, int B, int C, int H,
-                           int W, int mode, cudaStream_t st, int* rc);   // circconv_dft.cu
+bool circconv_dft_launch(const void* a, int64_t a_bs, const void* b, int64_t b_bs, void* y, int64_t y_bs, int B, int C, int H,
+                         int W, int patch, int mode, cudaStream_t st, int* rc);   // circconv_dft.cu
 }
 using namespace b200ir;
 
@@ -211,9 +246,10 @@ extern "C" int b200ir_circconv_patch(const void* a, int64_t a_bstride, const voi
   B200IR_UNSUPPORTED(patch >= 2 && patch <= 32 && (patch & (patch - 1)) == 0, "circconv_patch: patch %d unsupported (2..32, power of 2)", patch);
   B200IR_UNSUPPORTED(B <= 65535 && C <= 65535, "circconv_patch: B, C <= 65535");
   const int npx = (W + patch - 1) / patch, npy = (H + patch - 1) / patch;
-  if (patch == 32 && dtype == B200IR_BF16) {   // tensor-core DFT (circconv_dft.cu); falls through for unaligned planes
+  if (patch >= 16 && dtype == B200IR_BF16) {   // tensor-core DFT (circconv_dft.cu); falls through for unaligned planes
     int rc = 0;
-    if (circconv_dft32_launch(a, a_bstride, b, b_bstride, y, y_bstride, B, C, H, W, mode, (cudaStream_t)stream, &rc)) return rc;
+    if (circconv_dft_launch(a, a_bstride, b, b_bstride, y, y_bstride, B, C, H, W, patch, mode, (cudaStream_t)stream, &rc))
+      return rc;
   }
   if (patch >= 16) {
     const int64_t total = (int64_t)B * C * npx * npy;
@@ -237,6 +273,20 @@ extern "C" int b200ir_circconv_patch(const void* a, int64_t a_bstride, const voi
     }
 #undef B200IR_CC
     return check_launch("circconv_patch_warp");
+  }
+  if (patch == 4 || patch == 8) {
+    const int tw = 256 / patch, ngx = (W + tw - 1) / tw;
+    const dim3 g2((unsigned)(ngx * npy), (unsigned)C, (unsigned)B);
+#define B200IR_CS(P_, T_)                                                                                              \
+  circconv_small_kernel<P_, T_><<<g2, 256, 0, (cudaStream_t)stream>>>((const T_*)a, a_bstride, (const T_*)b, b_bstride, \
+                                                                      (T_*)y, y_bstride, C, H, W, ngx, mode)
+    if (patch == 4) {
+      if (dtype == B200IR_BF16) B200IR_CS(4, bf16); else B200IR_CS(4, float);
+    } else {
+      if (dtype == B200IR_BF16) B200IR_CS(8, bf16); else B200IR_CS(8, float);
+    }
+#undef B200IR_CS
+    return check_launch("circconv_small");
   }
   const dim3 grid((unsigned)(npx * npy), (unsigned)C, (unsigned)B);
   const size_t smem = (size_t)2 * patch * patch * sizeof(float);
