@@ -500,6 +500,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
         // activation tile): four 128-column accumulators rotate over (pixel tile, channel tile) items.
         const int mtiles = (P.Nslice + 127) >> 7;
         const uint32_t idesc = make_idesc_bf16(128, 128, 0, 1);
+        // same issue-loop form as below: weight descriptor low words tabulated once per CTA ((mt, kc, ks) -> s_bdesc), the
+        // activation descriptor of a stage advances by a constant per K step, stage / phase are counters
+        const int nent = mtiles * P.kchunks * 4;     // <= 256 (launcher)
+        for (int e = lane; e < nent; e += 32) {
+          const int ks = e & 3, kc = (e >> 2) % P.kchunks, mt = (e >> 2) / P.kchunks;
+          const int kglob = kc * P.BK + ks * 16;
+          s_bdesc[e] = (uint32_t)make_smem_desc_sw128(
+              w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)mt * 16384u + (kglob & 63) * 2u, 16u, 1024u);
+        }
+        __syncwarp();
+        const uint32_t desc_hi = (uint32_t)(make_smem_desc_sw128(0u, 16u, 1024u) >> 32);
+        const uint32_t x_lbo = (((uint32_t)P.BK * 128u) >> 4) << 16;
+        uint32_t st0 = 0, ph0 = 0;
         for (int tile = t_begin; tile < t_end; ++tile) {
           const int b = tile / P.tiles_per_sample;
           if (cur < 0 || (P.per_sample_w && b != cur)) {
@@ -507,32 +520,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmX, const __grid_constant__ 
             ++wload;
             cur = b;
           }
+          uint32_t stage = st0, ph = ph0;
           for (int mt = 0; mt < mtiles; ++mt, ++acc_it) {
             const uint32_t as = acc_it & 3, aph = (acc_it >> 2) & 1;
             mbar_wait(&bar_accempty[as], aph ^ 1);
             tc_fence_after();
             const uint32_t d_tmem = tmem_base + as * 128;
+            const uint32_t* wtab = s_bdesc + mt * P.kchunks * 4;
+            stage = st0; ph = ph0;
             for (int kc = 0; kc < P.kchunks; ++kc) {
-              const uint32_t cit = it + kc, stage = cit % P.S, ph = (cit / P.S) & 1;
               if (mt == 0) {
                 mbar_wait(&bar_full[stage], ph);
                 tc_fence_after();
               }
               const int rows = min(P.BK, P.Cin - kc * P.BK);
               const int ksteps = (rows + 15) >> 4;
-              for (int ks = 0; ks < ksteps; ++ks) {
-                const int kglob = kc * P.BK + ks * 16;
-                const uint64_t adesc = make_smem_desc_sw128(
-                    w_addr + (uint32_t)(kglob >> 6) * P.Nslice * 128u + (uint32_t)mt * 16384u + (kglob & 63) * 2u, 16u, 1024u);
-                const uint64_t bdesc = make_smem_desc_sw128(ring_addr + stage * kStageBytes + ks * 2048,
-                                                            (uint32_t)P.BK * 128u, 1024u);
-                umma_bf16_elect(d_tmem, adesc, bdesc, idesc, (kc | ks) != 0 ? 1u : 0u);
+              const uint4 wl = *reinterpret_cast<const uint4*>(wtab + kc * 4);
+              const uint32_t wlo[4] = {wl.x, wl.y, wl.z, wl.w};
+              uint32_t xlo = (((ring_addr + stage * kStageBytes) >> 4) & 0x3fffu) | x_lbo;
+#pragma unroll
+              for (int ks = 0; ks < 4; ++ks) {
+                if (ks < ksteps)
+                  umma_bf16_elect(d_tmem, ((uint64_t)desc_hi << 32) | wlo[ks], ((uint64_t)desc_hi << 32) | xlo, idesc,
+                                  (kc | ks) != 0 ? 1u : 0u);
+                xlo += 2048u >> 4;
               }
               if (mt == mtiles - 1) umma_commit_elect(&bar_empty[stage]);
+              if (++stage == (uint32_t)P.S) { stage = 0; ph ^= 1u; }
             }
             umma_commit_elect(&bar_accfull[as]);
           }
-          it += P.kchunks;
+          st0 = stage; ph0 = ph;
           if (P.per_sample_w && tile + 1 < t_end && (tile + 1) / P.tiles_per_sample != b) umma_commit_elect(bar_wempty);
         }
       } else
@@ -1153,6 +1171,7 @@ extern "C" int b200ir_gemm_tc_fwd_ex(const void* x, int64_t x_bstride, const voi
   P.per_sample_w = (Bw > 1) ? 1 : 0;
   P.inv_cin = 1.0f / (float)Cin;
   B200IR_UNSUPPORTED(mode4 || g.nchunks * g.kchunks * 4 <= 256, "gemm_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
+  B200IR_UNSUPPORTED(!mode4 || ((g.Nslice + 127) / 128) * g.kchunks * 4 <= 256, "gemm_tc: descriptor table too small (Cin=%d Cout=%d)", Cin, Cout);
   P.kpt = g.kchunks; P.H = P.W = P.TW = P.TWs = P.TH = P.tiles_x = P.tiles_y = 0;
   P.dbg = 0;
 #ifdef B200IR_AB
