@@ -74,6 +74,8 @@ def packed_weights(cache, key, w, bias, ln_type, ln_w, ln_b):
         ent = (sig, ops.pack_conv1x1(_p(w).reshape(cout, cin), _p(bias), ln_type, _p(ln_w), _p(ln_b)))
         if cache is not None:
             cache[key] = ent
+            if _REC is not None and key is not None and w.is_leaf:
+                _REC.append((cache, key, w, bias, ln_type, ln_w, ln_b, False))
     return ent[1]
 
 
@@ -84,7 +86,14 @@ def packed_weights_t(cache, key, w):
         ent = cache.get(("T", key))
         if ent is not None and ent[0] == _sig(w):
             return ent[1]
+    if _REC is not None and cache is not None and key is not None and w.is_leaf:
+        _REC.append((cache, key, w, None, L.LN_NONE, None, None, True))
     return ops.pack_conv1x1_t(_p(w).reshape(cout, cin))
+
+
+# train_step records here every pack that missed its cache during a step ((cache, key, w, bias, ln_type, ln_w, ln_b,
+# transposed)); the next steps do all of them in one launch (Prepacker(records=...)), whatever the model is made of
+_REC = None
 
 
 class Prepacker:
@@ -94,19 +103,24 @@ class Prepacker:
     ~260 launches of 3-5 us.  ``run()`` refreshes the (persistent) packed buffers and stamps the per-module caches with
     the current parameter signature, so that the forward / backward code paths find them instead of packing."""
 
-    def __init__(self, model):
-        import ctypes
-        import numpy as np
+    def __init__(self, model=None, records=None):
         from . import modules as M
         self.entries = []          # (cache dict, key, (w, bias, ln_w, ln_b), ln_type, packed tuple, transposed)
+        self.records = list(records or [])
         descs, blocks = [], 0
-        keep = []
+        seen = set()
 
         def add(cache, key, conv, norm, transposed):
-            nonlocal blocks
-            w, bias = conv.weight, (None if transposed else conv.bias)
-            cout, cin = w.shape[0], w.shape[1]
             ln_type, lw, lb = (M._ln_args(norm) if (norm is not None and not transposed) else (L.LN_NONE, None, None))
+            add_raw(cache, key, conv.weight, None if transposed else conv.bias, ln_type, lw, lb, transposed)
+
+        def add_raw(cache, key, w, bias, ln_type, lw, lb, transposed):
+            nonlocal blocks
+            tag = (id(cache), key, bool(transposed))
+            if tag in seen:
+                return
+            seen.add(tag)
+            cout, cin = w.shape[0], w.shape[1]
             geo = ops.gemm_tc_geometry(cout, cin) if transposed else ops.gemm_tc_geometry(cin, cout)
             if geo is None or w.dtype != torch.float32 or not w.is_cuda:
                 return
@@ -125,7 +139,9 @@ class Prepacker:
             descs.append(d)
             self.entries.append((cache, key, (w, bias, lw, lb), ln_type, (wp, st), transposed))
 
-        for m in model.modules():
+        for rec in self.records:
+            add_raw(*rec)
+        for m in (model.modules() if model is not None else ()):
             if isinstance(m, (M.TransformerBlock, M.EncoderBlock)):
                 if isinstance(m, M.TransformerBlock):
                     n1, attn, n2, ffn = m.norm1, m.attn, m.norm2, m.ffn

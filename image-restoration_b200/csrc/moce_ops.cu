@@ -10,6 +10,7 @@
 // library, no complex arithmetic, exact zero padding of ragged planes like F.pad at :391).  The two gradients are
 // circular cross-correlations and run on the same kernel (mode 1): dq = corr(dout, k), dk = corr(dout, q).
 #include "common.cuh"
+#include <cooperative_groups.h>
 
 namespace b200ir {
 
@@ -379,26 +380,59 @@ __global__ void rows_copy_kernel(const T* __restrict__ x, int64_t x_rs, T* __res
   }
 }
 
-// out[j] = sum_i a[ia(j), i] * b[ib(j), i]  (fp32, one CTA per row, fixed order): the gate gradient of the weighted combine
-template <typename T>
-__global__ void __launch_bounds__(256)
+// out[j] = sum_i a[ia(j), i] * b[ib(j), i]  (fp32): the gate gradient of the weighted combine.  A row is one sample of
+// an NCHW tensor (MBs) and a call has 1-3 rows, so one row is spread over a cluster of ROWDOT_CL CTAs; the CTA partials
+// are folded by rank 0 over distributed shared memory in rank order (fixed order, no workspace, no atomics).
+constexpr int ROWDOT_CL = 8, ROWDOT_T = 512;
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(ROWDOT_T)
 rowdot_kernel(const T* __restrict__ a, int64_t a_rs, const int* __restrict__ ia, const T* __restrict__ b, int64_t b_rs,
               const int* __restrict__ ib, float* __restrict__ out, int64_t per) {
-  __shared__ float red[8];
-  const int j = blockIdx.x;
+  namespace cg = cooperative_groups;
+  cg::cluster_group cl = cg::this_cluster();
+  __shared__ float red[ROWDOT_T / 32];
+  __shared__ float part;
+  const int j = blockIdx.y, r = (int)cl.block_rank();
   const T* pa = a + (int64_t)(ia ? ia[j] : j) * a_rs;
   const T* pb = b + (int64_t)(ib ? ib[j] : j) * b_rs;
   float s = 0.f;
-  for (int64_t i = threadIdx.x; i < per; i += 256) s = fmaf(to_f<T>(pa[i]), to_f<T>(pb[i]), s);
+  if constexpr (VEC) {
+    constexpr int V = 16 / (int)sizeof(T);
+    const int64_t nv = per / V;
+    const uint4* va = reinterpret_cast<const uint4*>(pa);
+    const uint4* vb = reinterpret_cast<const uint4*>(pb);
+    float s1 = 0.f;
+    for (int64_t i = (int64_t)r * ROWDOT_T + threadIdx.x; i < nv; i += (int64_t)ROWDOT_CL * ROWDOT_T) {
+      const uint4 qa = __ldg(va + i), qb = __ldg(vb + i);
+      const T* ea = reinterpret_cast<const T*>(&qa);
+      const T* eb = reinterpret_cast<const T*>(&qb);
+#pragma unroll
+      for (int e = 0; e < V; e += 2) {
+        s = fmaf(to_f<T>(ea[e]), to_f<T>(eb[e]), s);
+        s1 = fmaf(to_f<T>(ea[e + 1]), to_f<T>(eb[e + 1]), s1);
+      }
+    }
+    s += s1;
+  } else {
+    for (int64_t i = (int64_t)r * ROWDOT_T + threadIdx.x; i < per; i += (int64_t)ROWDOT_CL * ROWDOT_T)
+      s = fmaf(to_f<T>(pa[i]), to_f<T>(pb[i]), s);
+  }
   s = warp_sum(s);
   if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
   __syncthreads();
   if (threadIdx.x == 0) {
     float t = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += red[w];
+    for (int w = 0; w < ROWDOT_T / 32; ++w) t += red[w];
+    part = t;
+  }
+  cl.sync();
+  if (r == 0 && threadIdx.x == 0) {
+    float t = 0.f;
+    for (int q = 0; q < ROWDOT_CL; ++q) t += *cl.map_shared_rank(&part, q);
     out[j] = t;
   }
+  cl.sync();   // a CTA's shared memory must outlive rank 0's reads
 }
 
 // backward of spatial_mean: dx[b, c, i] = g[b, c] / HW * (gelu ? gelu'(x[b, c, i]) : 1)
@@ -447,12 +481,35 @@ extern "C" int b200ir_rowdot(const void* a, int64_t a_rowstride, const int* a_id
                              const int* b_idx, float* out, int n, int64_t per, int dtype, b200ir_stream_t stream) {
   B200IR_CHECK_ARG(a && b && out && n > 0 && per > 0, "rowdot: bad args");
   B200IR_CHECK_ARG(dtype_ok(dtype), "rowdot: bad dtype");
-  if (dtype == B200IR_BF16)
-    rowdot_kernel<bf16><<<n, 256, 0, (cudaStream_t)stream>>>((const bf16*)a, a_rowstride, a_idx, (const bf16*)b, b_rowstride,
-                                                             b_idx, out, per);
-  else
-    rowdot_kernel<float><<<n, 256, 0, (cudaStream_t)stream>>>((const float*)a, a_rowstride, a_idx, (const float*)b,
-                                                              b_rowstride, b_idx, out, per);
+  B200IR_CHECK_ARG(n <= 65535, "rowdot: more than 65535 rows");
+  const int esz = dtype == B200IR_BF16 ? 2 : 4, V = 16 / esz;
+  const bool vec = per % V == 0 && (a_rowstride * esz) % 16 == 0 && (b_rowstride * esz) % 16 == 0 &&
+                   ((uintptr_t)a & 15) == 0 && ((uintptr_t)b & 15) == 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(ROWDOT_CL, (unsigned)n);
+  cfg.blockDim = dim3(ROWDOT_T);
+  cfg.stream = (cudaStream_t)stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = ROWDOT_CL;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  cudaError_t e;
+  if (dtype == B200IR_BF16) {
+    const bf16 *pa = (const bf16*)a, *pb = (const bf16*)b;
+    e = vec ? cudaLaunchKernelEx(&cfg, rowdot_kernel<bf16, true>, pa, a_rowstride, a_idx, pb, b_rowstride, b_idx, out, per)
+            : cudaLaunchKernelEx(&cfg, rowdot_kernel<bf16, false>, pa, a_rowstride, a_idx, pb, b_rowstride, b_idx, out, per);
+  } else {
+    const float *pa = (const float*)a, *pb = (const float*)b;
+    e = vec ? cudaLaunchKernelEx(&cfg, rowdot_kernel<float, true>, pa, a_rowstride, a_idx, pb, b_rowstride, b_idx, out, per)
+            : cudaLaunchKernelEx(&cfg, rowdot_kernel<float, false>, pa, a_rowstride, a_idx, pb, b_rowstride, b_idx, out, per);
+  }
+  if (e != cudaSuccess) {
+    set_error("rowdot: %s", cudaGetErrorString(e));
+    return (int)e;
+  }
   return check_launch("rowdot");
 }
 

@@ -77,10 +77,14 @@ def _act(t: torch.Tensor, name: str):
         # of another GPU would be dereferenced on the wrong device
         raise ValueError(f"{name}: tensor lives on cuda:{t.device.index} but the current device is "
                          f"cuda:{torch.cuda.current_device()} (use torch.cuda.set_device / torch.cuda.device_of(x))")
-    if t.dtype not in _DT:
+    dt = _DT.get(t.dtype)
+    if dt is None:
         raise ValueError(f"{name}: dtype {t.dtype} unsupported (float32 / bfloat16)")
     if t.dim() != 4:
         raise ValueError(f"{name}: expected NCHW, got shape {tuple(t.shape)}")
+    if t.is_contiguous():      # the common case, one C call instead of the stride arithmetic below
+        sh = t.shape
+        return t.data_ptr(), sh[1] * sh[2] * sh[3], dt
     b, c, h, w = t.shape
     s = t.stride()
     ok = (s[3] == 1 or w == 1) and (s[2] == w or h == 1) and (s[1] == h * w or c == 1)

@@ -190,16 +190,30 @@ def train_step(net: nn.Module, opt: AdamW, degraded: torch.Tensor, clean: torch.
     restored = net(degrad); loss = L1(restored, clean); backward; (all-reduce); AdamW.  Returns the loss (device scalar)."""
     loss_fn = loss_fn or L1Loss()
     opt.zero_grad()
-    if degraded.is_cuda and getattr(net, "compute_dtype", None) == torch.bfloat16:
+    packing = degraded.is_cuda and getattr(net, "compute_dtype", None) == torch.bfloat16
+    if packing:
+        # every 1x1 weight pack of the step in ONE launch (the forward / backward find them cached).  The table is learnt:
+        # packs that still miss their cache during a step (first step, a newly routed MoCE-IR expert) are recorded and join
+        # the table for the following steps, whatever modules the model is made of.
         pre = net.__dict__.get("_b200ir_prepacker")
-        if pre is None or not pre.valid():
-            pre = net.__dict__["_b200ir_prepacker"] = A.Prepacker(net)
-        pre.run()     # every 1x1 weight pack of the step in one launch (the forward / backward find them cached)
-    restored = net(degraded)
-    loss = loss_fn(restored, clean)
-    if balance_loss_weight:     # MoCE-IR: loss += balance_loss_weight * net.total_loss (MoCE-IR-main/src/train.py:62,71)
-        loss = loss + balance_loss_weight * net.total_loss
-    _backward_side(loss)
+        if pre is not None and not pre.valid():
+            pre = net.__dict__["_b200ir_prepacker"] = None
+        if pre is not None:
+            pre.run()
+        elif not torch.cuda.is_current_stream_capturing():
+            A.bump_param_epoch()      # first step: every pack misses its cache and is recorded
+        A._REC = [] if not torch.cuda.is_current_stream_capturing() else None
+    try:
+        restored = net(degraded)
+        loss = loss_fn(restored, clean)
+        if balance_loss_weight:     # MoCE-IR: loss += balance_loss_weight * net.total_loss (MoCE-IR-main/src/train.py:62,71)
+            loss = loss + balance_loss_weight * net.total_loss
+        _backward_side(loss)
+    finally:
+        rec, A._REC = A._REC, None
+    if packing and rec:
+        old = pre.records if pre is not None else []
+        net.__dict__["_b200ir_prepacker"] = A.Prepacker(records=old + rec)
     flat_g = opt.gather_grads()
     scale = allreduce_flat_grads(flat_g, group)
     opt.step(grad_scale=scale, gathered=True)

@@ -233,6 +233,13 @@ def test_dispatch_combine_kernels(dtype):
     d = ops.rowdot(y, x, 3, b_idx=idx)
     rd = (y.float() * x[idx.long()].float()).flatten(1).sum(1)
     assert (d - rd).abs().max() <= 1e-3 * rd.abs().max()
+    for shp in ((4, 3, 7, 5), (2, 48, 64, 64)):      # unaligned rows (scalar loads) and rows spread over the whole cluster
+        u = torch.randn(*shp, generator=g).cuda().to(dtype)
+        v = torch.randn(*shp, generator=g).cuda().to(dtype)
+        d = ops.rowdot(u, v, shp[0])
+        rd = (u.double() * v.double()).flatten(1).sum(1)
+        assert (d.double() - rd).abs().max() <= 1e-4 * (u.double() * v.double()).abs().flatten(1).sum(1).max()
+        assert torch.equal(d, ops.rowdot(u, v, shp[0]))
     for gelu in (False, True):
         xs = x.float().clone().requires_grad_(True)
         m = (torch.nn.functional.gelu(xs) if gelu else xs).mean(dim=(-2, -1))
