@@ -84,6 +84,11 @@ SIGNATURES = {
     "b200ir_spatial_max": [_vp, _i64, _i, _vp, _i, _i, _i64, _vp],
     "b200ir_fre_combine": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
     "b200ir_affine2": [_vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_lowfreq_split_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_spatial_gate_bwd": [_vp, _i64, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i64, _vp, _i, _i, _i, _i, _i, _vp],
+    "b200ir_spatial_max_bwd": [_vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i64, _vp],
+    "b200ir_fre_combine_bwd": [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i, _i64, _vp],
+    "b200ir_affine2_bwd": [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _i, _i, _i, _i64, _vp],
     "b200ir_crop_augment_degrade": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
     "b200ir_psnr_ssim_nblocks": [_i, _i],
     "b200ir_psnr_ssim": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],

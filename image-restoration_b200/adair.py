@@ -1,7 +1,9 @@
 """AdaIR extras: mirrors of ``Chanel_Cross_Attention``, ``SpatialGate``, ``ChannelGate``, ``FreRefine`` and
 ``FreModule`` of ``/root/reference/AdaIR-main/net/model.py:177-372`` with the reference's parameter names, running on
 libb200ir kernels (``csrc/adair_ops.cu`` + the two-source MDTA).  Inference path (AdaIR's TransformerBlocks themselves are
-plain Restormer blocks and are taken by ``modules.TransformerBlock`` / ``dropin.accelerate``).
+plain Restormer blocks and are taken by ``modules.TransformerBlock`` / ``dropin.accelerate``).  Under autograd the same
+modules run through the Functions of ``autograd_ops`` (backward kernels: ``csrc/adair_bwd.cu``), as AdaIR-main/train.py
+needs; only the degraded image itself (``FreModule.forward``'s ``x``) cannot require a gradient.
 
 FreModule.fft keeps only the spectrum bins inside a centred rectangle of half-size (h_, w_) = int(H // 128 * t) as the
 "low" band; it is synthesised here from those few bins directly instead of fft2 -> mask -> ifft2 (see adair_ops.cu).
@@ -12,6 +14,7 @@ from __future__ import annotations
 
 import torch
 import torch.nn as nn
+import torch.nn.functional as F
 
 from . import _lib as L
 from . import autograd_ops as A
@@ -20,7 +23,11 @@ from .modules import CrossAttention
 
 
 def _mm(x2d, conv):
-    """[B, Cin] fp32 through a bias-free 1x1 nn.Conv2d's weight -> [B, Cout]."""
+    """[B, Cin] fp32 through a bias-free 1x1 nn.Conv2d's weight -> [B, Cout] (under autograd: F.linear on these few
+    numbers, so the MLP weights get their gradients from torch)."""
+    if A._needs_grad(x2d, conv.weight, conv.bias):
+        return F.linear(x2d.float(), conv.weight.view(conv.out_channels, conv.in_channels).float(),
+                        None if conv.bias is None else conv.bias.float())
     w = A._p(conv.weight).reshape(conv.out_channels, conv.in_channels)
     y = ops.ln_conv1x1(x2d.float().contiguous().view(x2d.shape[0], x2d.shape[1], 1, 1), w, A._p(conv.bias))
     return y.view(x2d.shape[0], -1)
@@ -59,7 +66,7 @@ class ChannelGate(nn.Module):
         return _mm(torch.relu(_mm(v, self.mlp[0])), self.mlp[2])
 
     def forward(self, x):
-        return torch.sigmoid(self._mlp(ops.spatial_mean(x)) + self._mlp(ops.spatial_max(x))).contiguous()   # fp32 [B, C]
+        return torch.sigmoid(self._mlp(A.spatial_mean(x)) + self._mlp(A.spatial_max(x))).contiguous()       # fp32 [B, C]
 
 
 class FreRefine(nn.Module):
@@ -70,7 +77,7 @@ class FreRefine(nn.Module):
         self.proj = nn.Conv2d(dim, dim, kernel_size=1)
 
     def forward(self, low, high):
-        out = ops.fre_combine(low, high, self.SpatialGate(high), self.ChannelGate(low))
+        out = A.fre_refine_gate(low, high, self.SpatialGate.spatial.weight, self.ChannelGate(low))
         return A.ln_conv1x1(out, self.proj.weight, self.proj.bias, L.LN_NONE, None, None, None,
                             cache=self.__dict__.setdefault("_b200ir_cache", {}), key="proj")
 
@@ -94,14 +101,15 @@ class FreModule(nn.Module):
     def fft(self, x, n=128, out_dtype=None):
         x = A.conv3x3(x, self.conv1.weight, None, None, L.SHUFFLE_NONE, out_dtype=out_dtype)
         B, C, h, w = x.shape
-        t = _mm(ops.ew(_mm(ops.spatial_mean(x), self.rate_conv[0]).contiguous(), None, ops.EW_GELU), self.rate_conv[2])
-        thr = torch.sigmoid(t)                                                                   # [B, 2]
-        counts = torch.stack([(h // n * thr[:, 0]).int(), (w // n * thr[:, 1]).int()], 1).contiguous()
-        return ops.lowfreq_split(x, counts, 4 * (h // n) * (w // n))
+        with torch.no_grad():      # the thresholds pass through .int() (model.py:345-346): no gradient reaches rate_conv
+            t = _mm(ops.ew(_mm(ops.spatial_mean(x), self.rate_conv[0]).contiguous(), None, ops.EW_GELU), self.rate_conv[2])
+            thr = torch.sigmoid(t)                                                               # [B, 2]
+            counts = torch.stack([(h // n * thr[:, 0]).int(), (w // n * thr[:, 1]).int()], 1).contiguous()
+        return A.lowfreq_split(x, counts, 4 * (h // n) * (w // n))
 
     def forward(self, x, y):
-        if torch.is_grad_enabled() and (y.requires_grad or x.requires_grad):
-            raise RuntimeError("b200ir.FreModule is an inference path")
+        if torch.is_grad_enabled() and x.requires_grad:
+            raise RuntimeError("b200ir.FreModule: no gradient with respect to the degraded image (bilinear-resize adjoint not built)")
         _, _, H, W = y.size()
         x = ops.bilinear_resize(x.contiguous(), H, W)
         high_feature, low_feature = self.fft(x, out_dtype=y.dtype)
@@ -109,4 +117,4 @@ class FreModule(nn.Module):
         low_feature = self.channel_cross_h(low_feature, y)
         agg = self.frequency_refine(low_feature, high_feature)
         out = self.channel_cross_agg(y, agg)
-        return ops.affine2(out, y, A._p(self.para1).reshape(-1), A._p(self.para2).reshape(-1))
+        return A.affine2(out, y, self.para1, self.para2)

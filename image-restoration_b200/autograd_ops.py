@@ -750,6 +750,101 @@ def spatial_mean(x, gelu=False):
     return _SpatialMean.apply(x, gelu) if _needs_grad(x) else ops.spatial_mean(x, gelu=gelu)
 
 
+# ---------------------------------------------------------------------------------------------------------------------
+# AdaIR frequency mining / modulation under autograd (csrc/adair_bwd.cu; AdaIR-main/net/model.py:234-372)
+# ---------------------------------------------------------------------------------------------------------------------
+class _SpatialMax(torch.autograd.Function):
+    """AdaptiveMaxPool2d(1) of ChannelGate (model.py:253): the gradient goes to the first maximum of each plane."""
+
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return ops.spatial_max(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        return ops.spatial_max_bwd(x, g.float().contiguous())
+
+
+def spatial_max(x):
+    x = _cg(x)
+    return _SpatialMax.apply(x) if _needs_grad(x) else ops.spatial_max(x)
+
+
+class _LowfreqSplit(torch.autograd.Function):
+    """FreModule.fft's fft2 -> mask -> ifft2 -> abs (model.py:340-372): (high, low).  hw_counts carries no gradient (the
+    thresholds pass through .int() in the reference)."""
+
+    @staticmethod
+    def forward(ctx, x, hw_counts, max_modes):
+        high, low, coef = ops.lowfreq_split(x, hw_counts, max_modes, return_coef=True)
+        ctx.save_for_backward(x, hw_counts, coef)
+        ctx.max_modes = max_modes
+        return high, low
+
+    @staticmethod
+    def backward(ctx, g_high, g_low):
+        x, hw_counts, coef = ctx.saved_tensors
+        return ops.lowfreq_split_bwd(x, hw_counts, coef, _cg(g_high), _cg(g_low), ctx.max_modes), None, None
+
+
+def lowfreq_split(x, hw_counts, max_modes):
+    x = _cg(x)
+    return _LowfreqSplit.apply(x, hw_counts, max_modes) if _needs_grad(x) else ops.lowfreq_split(x, hw_counts, max_modes)
+
+
+class _FreRefineGate(torch.autograd.Function):
+    """FreRefine up to its projection (model.py:279-285): low * SpatialGate(high) + high * channel_weight, with the 7x7
+    SpatialGate convolution inside (weight w7); channel_weight cw fp32 [B, C] comes from ChannelGate's tiny MLP."""
+
+    @staticmethod
+    def forward(ctx, low, high, w7, cw):
+        w = _p(w7)
+        gate, mm = ops.spatial_gate(high, w, return_mm=True)
+        cwc = cw.detach().float().contiguous()
+        ctx.save_for_backward(low, high, w, gate, mm, cwc)
+        return ops.fre_combine(low, high, gate, cwc)
+
+    @staticmethod
+    def backward(ctx, g):
+        low, high, w, gate, mm, cw = ctx.saved_tensors
+        dlow, dhigh, dsw, dcw = ops.fre_combine_bwd(_cg(g), low, high, gate, cw)
+        dhigh, dw7 = ops.spatial_gate_bwd(high, w, mm, gate, dsw, dx=dhigh)
+        return dlow, dhigh, dw7, dcw
+
+
+def fre_refine_gate(low, high, w7, cw):
+    low, high = _cg(low), _cg(high)
+    if _needs_grad(low, high, w7, cw):
+        return _FreRefineGate.apply(low, high, w7, cw)
+    return ops.fre_combine(low, high, ops.spatial_gate(high, _p(w7)), cw.float().contiguous())
+
+
+class _Affine2(torch.autograd.Function):
+    """out * para1 + y * para2 (model.py:324), para [C, 1, 1]."""
+
+    @staticmethod
+    def forward(ctx, a, b, p1, p2):
+        q1, q2 = _p(p1).reshape(-1), _p(p2).reshape(-1)
+        ctx.save_for_backward(a, b, q1, q2)
+        ctx.pshape = p1.shape
+        return ops.affine2(a, b, q1, q2)
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, q1, q2 = ctx.saved_tensors
+        da, db, d1, d2 = ops.affine2_bwd(_cg(g), a, b, q1, q2)
+        return da, db, d1.view(ctx.pshape), d2.view(ctx.pshape)
+
+
+def affine2(a, b, p1, p2):
+    a, b = _cg(a), _cg(b)
+    if _needs_grad(a, b, p1, p2):
+        return _Affine2.apply(a, b, p1, p2)
+    return ops.affine2(a, b, _p(p1).reshape(-1), _p(p2).reshape(-1))
+
+
 class _GatherRows(torch.autograd.Function):
     """y[j] = x[idx[j]]: SparseDispatcher.dispatch, ``inp[self._batch_index]`` for one expert (moce_ir.py:94-104)."""
 

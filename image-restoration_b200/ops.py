@@ -932,8 +932,9 @@ def rowdot(a, b, n, a_idx=None, b_idx=None):
 # ---------------------------------------------------------------------------------------------------
 # AdaIR frequency mining / modulation pieces (csrc/adair_ops.cu)
 # ---------------------------------------------------------------------------------------------------
-def lowfreq_split(x, hw_counts, max_modes):
-    """FreModule.fft's mask -> ifft2 -> abs (AdaIR-main/net/model.py:335-365): (high, low).  hw_counts int32 [B, 2]."""
+def lowfreq_split(x, hw_counts, max_modes, return_coef=False):
+    """FreModule.fft's mask -> ifft2 -> abs (AdaIR-main/net/model.py:335-365): (high, low).  hw_counts int32 [B, 2].
+    return_coef: also return the kept spectrum bins (fp32 [B, C, 64, 2]) for `lowfreq_split_bwd`."""
     B, C, H, W_ = x.shape
     xp, xbs, xdt = _act(x, "x")
     if hw_counts.dtype != torch.int32 or not hw_counts.is_cuda or tuple(hw_counts.shape) != (B, 2):
@@ -949,7 +950,27 @@ def lowfreq_split(x, hw_counts, max_modes):
         rc = lib.b200ir_lowfreq_split(xp, xbs, hw_counts.data_ptr(), ws.data_ptr(), hp, hbs, lp, lbs, xdt, B, C, H, W_,
                                       max_modes, _stream())
     L.check(rc, "b200ir_lowfreq_split")
-    return high, low
+    return (high, low, ws) if return_coef else (high, low)
+
+
+def lowfreq_split_bwd(x, hw_counts, coef, g_high, g_low, max_modes):
+    """dx of `lowfreq_split` (csrc/adair_bwd.cu)."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    ghp, ghbs, ghdt = _act(g_high, "g_high")
+    glp, glbs, gldt = _act(g_low, "g_low")
+    if ghdt != xdt or gldt != xdt or tuple(g_high.shape) != tuple(x.shape) or tuple(g_low.shape) != tuple(x.shape):
+        raise ValueError("lowfreq_split_bwd: gradient / input mismatch")
+    dx = torch.empty_like(x, memory_format=torch.contiguous_format)
+    dp, dbs, _ = _act(dx, "dx")
+    ws = torch.empty((B, C, 64, 2), device=x.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("lowfreq_split_bwd", B, C, H, W_, xdt):
+        rc = lib.b200ir_lowfreq_split_bwd(xp, xbs, hw_counts.data_ptr(), _par(coef, "coef", B * C * 128), ghp, ghbs, glp, glbs,
+                                          ws.data_ptr(), dp, dbs, xdt, B, C, H, W_, max_modes, _stream())
+    L.check(rc, "b200ir_lowfreq_split_bwd")
+    return dx
 
 
 def bilinear_resize(x, H, W_):
@@ -963,8 +984,9 @@ def bilinear_resize(x, H, W_):
     return y
 
 
-def spatial_gate(x, w7):
-    """fp32 [B, H*W] = sigmoid(conv7x7([max_c x, mean_c x])) (SpatialGate); w7 fp32 [1, 2, 7, 7]."""
+def spatial_gate(x, w7, return_mm=False):
+    """fp32 [B, H*W] = sigmoid(conv7x7([max_c x, mean_c x])) (SpatialGate); w7 fp32 [1, 2, 7, 7].
+    return_mm: also return the [B, 2, H*W] channel max / mean planes for `spatial_gate_bwd`."""
     B, C, H, W_ = x.shape
     xp, xbs, xdt = _act(x, "x")
     ws = torch.empty((B, 2, H * W_), device=x.device, dtype=torch.float32)
@@ -974,7 +996,29 @@ def spatial_gate(x, w7):
     with _timed("spatial_gate", B, C, H, W_, xdt):
         rc = lib.b200ir_spatial_gate(xp, xbs, xdt, _par(w7, "w7", 98), ws.data_ptr(), gate.data_ptr(), B, C, H, W_, _stream())
     L.check(rc, "b200ir_spatial_gate")
-    return gate
+    return (gate, ws) if return_mm else gate
+
+
+def spatial_gate_bwd(x, w7, mm, gate, dgate, dx=None):
+    """(dx, dw7 [1, 2, 7, 7]) of `spatial_gate`; a given `dx` is accumulated into."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    acc = dx is not None
+    if dx is None:
+        dx = torch.empty_like(x, memory_format=torch.contiguous_format)
+    dp, dbs, ddt = _act(dx, "dx")
+    if ddt != xdt or tuple(dx.shape) != tuple(x.shape):
+        raise ValueError("spatial_gate_bwd: dx / x mismatch")
+    ds = torch.empty((B, H * W_), device=x.device, dtype=torch.float32)
+    dw = torch.empty((1, 2, 7, 7), device=x.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 2
+    with _timed("spatial_gate_bwd", B, C, H, W_, xdt):
+        rc = lib.b200ir_spatial_gate_bwd(xp, xbs, xdt, _par(w7, "w7", 98), _par(mm, "mm", B * 2 * H * W_),
+                                         _par(gate, "gate", B * H * W_), _par(dgate, "dgate", B * H * W_), ds.data_ptr(), dp, dbs,
+                                         dw.data_ptr(), B, C, H, W_, int(acc), _stream())
+    L.check(rc, "b200ir_spatial_gate_bwd")
+    return dx, dw
 
 
 def spatial_max(x):
@@ -985,6 +1029,18 @@ def spatial_max(x):
         rc = lib.b200ir_spatial_max(xp, xbs, xdt, out.data_ptr(), B, C, H * W_, _stream())
     L.check(rc, "b200ir_spatial_max")
     return out
+
+
+def spatial_max_bwd(x, g):
+    """dx of `spatial_max`: g [B, C] fp32 at the first maximum of each plane, 0 elsewhere."""
+    B, C, H, W_ = x.shape
+    xp, xbs, xdt = _act(x, "x")
+    dx = torch.empty_like(x, memory_format=torch.contiguous_format)
+    dp, dbs, _ = _act(dx, "dx")
+    with _timed("spatial_max_bwd", B, C, H * W_, xdt):
+        rc = lib.b200ir_spatial_max_bwd(xp, xbs, _par(g, "g", B * C), dp, dbs, xdt, B, C, H * W_, _stream())
+    L.check(rc, "b200ir_spatial_max_bwd")
+    return dx
 
 
 def fre_combine(low, high, sw, cw):
@@ -1003,6 +1059,29 @@ def fre_combine(low, high, sw, cw):
     return y
 
 
+def fre_combine_bwd(g, low, high, sw, cw):
+    """(dlow, dhigh, dsw fp32 [B, H*W], dcw fp32 [B, C]) of `fre_combine`."""
+    B, C, H, W_ = low.shape
+    gp, gbs, gdt = _act(g, "g")
+    lp, lbs, ldt = _act(low, "low")
+    hp, hbs, hdt = _act(high, "high")
+    if not (gdt == ldt == hdt) or tuple(g.shape) != tuple(low.shape) or tuple(high.shape) != tuple(low.shape):
+        raise ValueError("fre_combine_bwd: operand mismatch")
+    dlow = torch.empty((B, C, H, W_), device=low.device, dtype=low.dtype)
+    dhigh = torch.empty((B, C, H, W_), device=low.device, dtype=low.dtype)
+    dlp, dlbs, _ = _act(dlow, "dlow")
+    dhp, dhbs, _ = _act(dhigh, "dhigh")
+    dsw = torch.empty((B, H * W_), device=low.device, dtype=torch.float32)
+    dcw = torch.empty((B, C), device=low.device, dtype=torch.float32)
+    global LAUNCHES
+    LAUNCHES += 1
+    with _timed("fre_combine_bwd", B, C, H * W_, ldt):
+        rc = lib.b200ir_fre_combine_bwd(gp, gbs, lp, lbs, hp, hbs, _par(sw, "sw", B * H * W_), _par(cw, "cw", B * C), dlp, dlbs,
+                                        dhp, dhbs, dsw.data_ptr(), dcw.data_ptr(), ldt, B, C, H * W_, _stream())
+    L.check(rc, "b200ir_fre_combine_bwd")
+    return dlow, dhigh, dsw, dcw
+
+
 def affine2(a, b, p1, p2):
     """a * p1[c] + b * p2[c]."""
     B, C, H, W_ = a.shape
@@ -1016,3 +1095,24 @@ def affine2(a, b, p1, p2):
         rc = lib.b200ir_affine2(ap, abs_, bp, bbs, _par(p1, "p1", C), _par(p2, "p2", C), yp, ybs, adt, B, C, H * W_, _stream())
     L.check(rc, "b200ir_affine2")
     return y
+
+
+def affine2_bwd(g, a, b, p1, p2):
+    """(da, db, dp1 [C], dp2 [C]) of `affine2`; the per-sample partial sums are folded over B in a fixed order."""
+    B, C, H, W_ = a.shape
+    gp, gbs, gdt = _act(g, "g")
+    ap, abs_, adt = _act(a, "a")
+    bp, bbs, bdt = _act(b, "b")
+    if not (gdt == adt == bdt) or tuple(g.shape) != tuple(a.shape) or tuple(b.shape) != tuple(a.shape):
+        raise ValueError("affine2_bwd: operand mismatch")
+    da = torch.empty((B, C, H, W_), device=a.device, dtype=a.dtype)
+    db = torch.empty((B, C, H, W_), device=a.device, dtype=a.dtype)
+    dap, dabs, _ = _act(da, "da")
+    dbp, dbbs, _ = _act(db, "db")
+    parts = torch.empty((B, C, 2), device=a.device, dtype=torch.float32)
+    with _timed("affine2_bwd", B, C, H * W_, adt):
+        rc = lib.b200ir_affine2_bwd(gp, gbs, ap, abs_, bp, bbs, _par(p1, "p1", C), _par(p2, "p2", C), dap, dabs, dbp, dbbs,
+                                    parts.data_ptr(), adt, B, C, H * W_, _stream())
+    L.check(rc, "b200ir_affine2_bwd")
+    dp = reduce_partials(parts.view(B, 2 * C), B, 2 * C).view(C, 2) if B > 1 else parts[0]
+    return da, db, dp[:, 0].contiguous(), dp[:, 1].contiguous()

@@ -356,6 +356,34 @@ int b200ir_fre_combine(const void* low, int64_t l_bstride, const void* high, int
 int b200ir_affine2(const void* a, int64_t a_bstride, const void* b, int64_t b_bstride, const float* p1, const float* p2,
                    void* y, int64_t y_bstride, int dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
 
+/* ---- backward of the AdaIR pieces (adair_bwd.cu): what torch autograd does on AdaIR-main/net/model.py:234-372 in
+ * AdaIR-main/train.py.  Every reduction is in a fixed order (bitwise deterministic). ----
+ * lowfreq_split_bwd: low = |P x|, high = |x - P x| (P = ifft2 . mask . fft2, Hermitian), so
+ * dx = Re(u_h) + Re(P (u_l - u_h)), u = g * z / |z| (0 where |z| = 0, torch's sgn).  coef = the forward's coef_ws;
+ * coefw_ws fp32 scratch [B][C][64][2].  Nothing flows to the thresholds (they pass through .int(), model.py:345-346). */
+int b200ir_lowfreq_split_bwd(const void* x, int64_t x_bstride, const int* hw_counts, const float* coef, const void* g_high,
+                             int64_t gh_bstride, const void* g_low, int64_t gl_bstride, float* coefw_ws, void* dx,
+                             int64_t dx_bstride, int dtype, int B, int C, int H, int W, int max_modes,
+                             b200ir_stream_t stream);
+/* SpatialGate backward: mm / gate as written by b200ir_spatial_gate, dgate fp32 [B][H*W], ds_ws fp32 scratch [B][H*W];
+ * dw7 fp32 [2][7][7]; dx (+)= dmean / C + [c == first argmax_c x] * dmax (accumulate != 0 adds to dx). */
+int b200ir_spatial_gate_bwd(const void* x, int64_t x_bstride, int dtype, const float* w7, const float* mm,
+                            const float* gate, const float* dgate, float* ds_ws, void* dx, int64_t dx_bstride, float* dw7,
+                            int B, int C, int H, int W, int accumulate, b200ir_stream_t stream);
+/* AdaptiveMaxPool2d(1) backward: dx[b][c][:] = 0 except g[b][c] at the first maximum of the plane. */
+int b200ir_spatial_max_bwd(const void* x, int64_t x_bstride, const float* g, void* dx, int64_t dx_bstride, int dtype, int B,
+                           int C, int64_t HW, b200ir_stream_t stream);
+/* fre_combine backward: dlow = g sw, dhigh = g cw, dsw[b][p] = sum_c g low, dcw[b][c] = sum_p g high (fp32). */
+int b200ir_fre_combine_bwd(const void* g, int64_t g_bstride, const void* low, int64_t l_bstride, const void* high,
+                           int64_t h_bstride, const float* sw, const float* cw, void* dlow, int64_t dl_bstride, void* dhigh,
+                           int64_t dh_bstride, float* dsw, float* dcw, int dtype, int B, int C, int64_t HW,
+                           b200ir_stream_t stream);
+/* affine2 backward: da = g p1[c], db = g p2[c], parts fp32 [B][C][2] = per-sample (sum_p g a, sum_p g b): the caller
+ * sums them over B for dp1 / dp2. */
+int b200ir_affine2_bwd(const void* g, int64_t g_bstride, const void* a, int64_t a_bstride, const void* b, int64_t b_bstride,
+                       const float* p1, const float* p2, void* da, int64_t da_bstride, void* db, int64_t db_bstride,
+                       float* parts, int dtype, int B, int C, int64_t HW, b200ir_stream_t stream);
+
 /* ---- input pipeline and evaluation metrics on the device (pipeline_ops.cu) ----
  * Random-crop + flip/rot90 augmentation (mode 0..7 of MoCE-IR-main/src/utils/image_utils.py:136-166) + Gaussian-noise
  * synthesis clip(clean + noise*sigma, 0, 255).astype(uint8) (degradation_utils.py:21-24) + ToTensor.  src uint8

@@ -136,6 +136,16 @@ FREMODULE_CASES = [
     ("adair_fre_c32_h2_small", 32, 2, False, 1, (64, 64), (64, 64), 99),     # h // 128 == 0: low = 0, high = |x|
 ]
 
+# FreModule under autograd (AdaIR-main/train.py): name, dim, heads, bias, B, image (Hi, Wi), feature (H, W), seed,
+# rate_scale (multiplies the synthetic rate_conv.2.weight so that the thresholds sit well away from the .int() steps).
+# loss = mean(out * r) with a seeded random r; stored: loss, the mask half-sizes, d loss / d feature (strided sample +
+# checksums) and every parameter gradient.
+FREMODULE_TRAIN_CASES = [
+    ("adair_fre_train_c16_256", 16, 1, True, 2, (128, 128), (256, 256), 197, -200.0),   # h // 128 = 2: 2x2 kept bins
+    ("adair_fre_train_c16_384", 16, 1, False, 1, (96, 96), (384, 256), 199, -400.0),    # 3 x 2 steps: a larger, uneven mask
+    ("adair_fre_train_c32_h2_64", 32, 2, False, 2, (64, 64), (64, 64), 198, 1.0),       # empty mask: low = 0, high = |x|
+]
+
 
 def fre_sample(t):
     """What the FreModule goldens keep of a [B, C, H, W] tensor (the full 512x512 tensors would be 16 MB): a strided

@@ -171,3 +171,108 @@ def test_adair_fremodule_vs_reference_golden():
             assert np.allclose(c, gold[key + "_sum"], rtol=1e-3, atol=1e-5), (name, key, c, gold[key + "_sum"])
         s16, _ = fre_sample(y16)
         assert np.linalg.norm(s16 - gold["y"]) <= 3e-2 * np.linalg.norm(gold["y"]), name
+
+
+def test_adair_backward_kernels_vs_torch():
+    """csrc/adair_bwd.cu piece by piece against torch autograd of the same formulas (fp32, and bf16 loosely)."""
+    import torch.nn.functional as F
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(11)
+    B, C, H, W = 2, 6, 20, 12
+    for dtype, tol in ((torch.float32, 2e-5), (torch.bfloat16, 3e-2)):
+        # --- low-pass split: fft2 -> mask -> ifft2 -> abs
+        x = torch.randn(B, C, H, W, generator=g).cuda()
+        counts = torch.tensor([[2, 1], [0, 3]], dtype=torch.int32).cuda()
+        xr = x.to(dtype).double().requires_grad_(True)
+        mask = torch.zeros(B, 1, H, W, dtype=torch.float64, device="cuda")
+        for i, (h_, w_) in enumerate(counts.tolist()):
+            mask[i, :, H // 2 - h_:H // 2 + h_, W // 2 - w_:W // 2 + w_] = 1
+        f = torch.roll(torch.fft.fft2(xr, norm="forward"), (H // 2, W // 2), (2, 3))
+        hi = torch.fft.ifft2(torch.roll(f * (1 - mask), (-(H // 2), -(W // 2)), (2, 3)), norm="forward").abs()
+        lo = torch.fft.ifft2(torch.roll(f * mask, (-(H // 2), -(W // 2)), (2, 3)), norm="forward").abs()
+        gh, gl = torch.randn(B, C, H, W, generator=g).cuda().to(dtype), torch.randn(B, C, H, W, generator=g).cuda().to(dtype)
+        (hi * gh.double() + lo * gl.double()).sum().backward()
+        xm = x.to(dtype).requires_grad_(True)
+        mh, ml = A.lowfreq_split(xm, counts, 64)
+        assert (mh.double() - hi).abs().max() <= tol * 10 and (ml.double() - lo).abs().max() <= tol * 10
+        (mh.float() * gh.float() + ml.float() * gl.float()).sum().backward()
+        assert (xm.grad.double() - xr.grad).abs().max() <= tol * 10 * max(1.0, float(xr.grad.abs().max())), dtype
+
+        # --- FreRefine gate: low * sigmoid(conv7x7([max_c high, mean_c high])) + high * cw
+        low = torch.randn(B, C, H, W, generator=g).cuda().to(dtype)
+        # distinct values along the channels of a pixel (a tie would make the arg-max, hence the gradient, ambiguous)
+        order = torch.rand(B, C, H, W, generator=g).argsort(dim=1).float()
+        high = ((order - C / 2) * 0.5 + 0.125 * torch.rand(B, C, H, W, generator=g)).cuda().to(dtype)
+        w7 = (torch.randn(1, 2, 7, 7, generator=g) * 0.2).cuda()
+        cw = torch.rand(B, C, generator=g).cuda()
+        gy = torch.randn(B, C, H, W, generator=g).cuda().to(dtype)
+        lr, hr, wr, cr = (t.double().requires_grad_(True) for t in (low, high, w7, cw))
+        sg = torch.sigmoid(F.conv2d(torch.cat([hr.max(1, keepdim=True)[0], hr.mean(1, keepdim=True)], 1), wr, padding=3))
+        yr = lr * sg + hr * cr.view(B, C, 1, 1)
+        (yr * gy.double()).sum().backward()
+        lm, hm, wm, cm = low.clone().requires_grad_(True), high.clone().requires_grad_(True), w7.clone().requires_grad_(True), \
+            cw.clone().requires_grad_(True)
+        ym = A.fre_refine_gate(lm, hm, wm, cm)
+        assert (ym.double() - yr).abs().max() <= tol * 10
+        (ym.float() * gy.float()).sum().backward()
+        for got, ref, nm in ((lm.grad, lr.grad, "dlow"), (hm.grad, hr.grad, "dhigh"), (wm.grad, wr.grad, "dw7"), (cm.grad, cr.grad, "dcw")):
+            assert (got.double() - ref).abs().max() <= tol * 10 * max(1.0, float(ref.abs().max())), (dtype, nm)
+
+        # --- AdaptiveMaxPool2d(1) and the final affine
+        planes = (torch.rand(B, C, H * W, generator=g).argsort(dim=2).float() / 64 - 1).view(B, C, H, W).cuda().to(dtype)
+        xr = planes.double().requires_grad_(True)
+        gm = torch.randn(B, C, generator=g).cuda()
+        (xr.amax(dim=(2, 3)) * gm.double()).sum().backward()
+        xm = planes.clone().requires_grad_(True)
+        (A.spatial_max(xm) * gm).sum().backward()
+        assert torch.equal(xm.grad.double(), xr.grad.to(dtype).double())
+        p1, p2 = torch.randn(C, 1, 1, generator=g).cuda(), torch.randn(C, 1, 1, generator=g).cuda()
+        ar, br, q1, q2 = (t.double().requires_grad_(True) for t in (low, high, p1, p2))
+        ((ar * q1 + br * q2) * gy.double()).sum().backward()
+        am, bm, m1, m2 = low.clone().requires_grad_(True), high.clone().requires_grad_(True), p1.clone().requires_grad_(True), \
+            p2.clone().requires_grad_(True)
+        (A.affine2(am, bm, m1, m2).float() * gy.float()).sum().backward()
+        for got, ref, nm in ((am.grad, ar.grad, "da"), (bm.grad, br.grad, "db"), (m1.grad, q1.grad, "dp1"), (m2.grad, q2.grad, "dp2")):
+            assert (got.double() - ref).abs().max() <= tol * 10 * max(1.0, float(ref.abs().max())), (dtype, nm)
+
+
+def test_adair_fremodule_training_vs_reference_golden():
+    """b200ir.FreModule under autograd against the reference FreModule's loss, d loss / d feature and parameter gradients
+    (oracle/gen_golden_adair_train.py; AdaIR-main/net/model.py:295-372 as AdaIR-main/train.py differentiates it)."""
+    import b200ir
+    from oracle.gen_golden_adair_train import fre_train_inputs, fre_train_state
+    from oracle.gen_golden_cases import FREMODULE_TRAIN_CASES, fre_sample
+    for name, dim, heads, bias, b, (hi, wi), (h, w), seed, rs in FREMODULE_TRAIN_CASES:
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+        for dtype in (torch.float32, torch.bfloat16):
+            mod = b200ir.FreModule(dim, heads, bias)
+            mod.load_state_dict(fre_train_state(mod, dim, seed, rs), strict=True)
+            mod = mod.cuda().train()
+            img, y2, r = fre_train_inputs(dim, b, hi, wi, h, w, seed)
+            y2 = y2.cuda().to(dtype).requires_grad_(True)
+            out = mod(img.cuda(), y2)
+            assert out.dtype == dtype
+            loss = (out.float() * r.cuda()).mean()
+            loss.backward()
+            f32 = dtype == torch.float32
+            s, c = fre_sample(out)
+            assert np.abs(s - gold["y"]).max() <= (5e-4 if f32 else 6e-2) * max(1.0, float(np.abs(gold["y"]).max())), (name, dtype)
+            assert abs(float(loss.detach()) - float(gold["loss"])) <= (2e-6 if f32 else 2e-4), (name, dtype, float(loss), float(gold["loss"]))
+            gs, gc = fre_sample(y2.grad)
+            ref = gold["dy"]
+            assert np.linalg.norm(gs - ref) <= (2e-3 if f32 else 4e-2) * np.linalg.norm(ref), (name, dtype, "dy")
+            if f32:
+                assert np.allclose(gc, gold["dy_sum"], rtol=2e-3, atol=1e-9), (name, gc, gold["dy_sum"])
+            bad = []
+            gmax = max(float(np.linalg.norm(gold[k])) for k in gold.files if k.startswith("g."))
+            for k, p in mod.named_parameters():
+                if "g." + k in gold.files:
+                    ref = torch.from_numpy(gold["g." + k])
+                    assert p.grad is not None, (name, k)
+                    got = p.grad.detach().float().cpu().view(ref.shape)
+                    # (some gradients are zero up to rounding in the reference, norm ~1e-9: hence the absolute term)
+                    if float((got - ref).norm()) > (3e-3 if f32 else 6e-2) * float(ref.norm()) + 1e-6 * gmax:
+                        bad.append((k, float((got - ref).norm()), float(ref.norm())))
+                else:
+                    assert p.grad is None, (name, k)      # conv, score_gen, rate_conv: untouched by the reference's backward too
+            assert not bad, (name, dtype, bad)
