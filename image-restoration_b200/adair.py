@@ -19,7 +19,7 @@ import torch.nn.functional as F
 from . import _lib as L
 from . import autograd_ops as A
 from . import ops
-from .modules import CrossAttention
+from .modules import CrossAttention, Restormer
 
 
 def _mm(x2d, conv):
@@ -118,3 +118,26 @@ class FreModule(nn.Module):
         agg = self.frequency_refine(low_feature, high_feature)
         out = self.channel_cross_agg(y, agg)
         return A.affine2(out, y, self.para1, self.para2)
+
+
+class AdaIR(Restormer):
+    """AdaIR-main/net/model.py:375-497: the Restormer U-Net with a FreModule after the latent, decoder_level3 and
+    decoder_level2 stacks (all three built with heads[2], as in the reference), same parameter names."""
+
+    def __init__(self, inp_channels=3, out_channels=3, dim=48, num_blocks=[4, 6, 6, 8], num_refinement_blocks=4,
+                 heads=[1, 2, 4, 8], ffn_expansion_factor=2.66, bias=False, LayerNorm_type='WithBias', decoder=True):
+        super().__init__(inp_channels, out_channels, dim, num_blocks, num_refinement_blocks, heads, ffn_expansion_factor,
+                         bias, LayerNorm_type, dual_pixel_task=False)
+        self.decoder = decoder
+        if self.decoder:
+            self.fre1 = FreModule(dim * 2 ** 3, num_heads=heads[2], bias=bias)
+            self.fre2 = FreModule(dim * 2 ** 2, num_heads=heads[2], bias=bias)
+            self.fre3 = FreModule(dim * 2 ** 1, num_heads=heads[2], bias=bias)
+
+    def _mix(self, stage, inp_img, feat):
+        if not self.decoder:
+            return feat
+        return (self.fre1, self.fre2, self.fre3)[stage - 1](inp_img, feat)
+
+    def forward(self, inp_img, noise_emb=None):
+        return super().forward(inp_img)

@@ -13,6 +13,8 @@ identity, so nothing of the reference is imported here):
   * cross-MDTA ``temperature, q, q_dwconv, kv, kv_dwconv, project_out``   (moce_ir.CrossAttention, moce_ir.py:325-368)
   * LayerNorm wrappers with a ``body`` holding ``weight`` (and ``bias``)   (Restormer.py:60-70)
   * ``Downsample`` / ``Upsample`` = Sequential(conv3x3 no-bias, PixelUnshuffle/PixelShuffle(2))  (Restormer.py:171-189)
+  * AdaIR's frequency module ``conv1, rate_conv, channel_cross_{l,h,agg}, frequency_refine, para1, para2``
+    (FreModule, AdaIR-main/net/model.py:295-372)
 
 The replacement adopts the reference's own ``nn.Conv2d`` / LayerNorm-body sub-modules, so ``state_dict()`` keys, the
 optimizer's parameter objects and checkpoints are unchanged.  Variants that carry the same attribute names but a
@@ -26,6 +28,7 @@ from typing import Dict, List, Tuple
 import torch
 import torch.nn as nn
 
+from . import adair as AD
 from . import modules as M
 
 
@@ -148,6 +151,35 @@ def _is_elementwise_gated(m) -> bool:
             and tuple(m.temperature.shape) == (m.num_heads, 1, 1) and c % m.num_heads == 0)
 
 
+def _is_fremodule(m) -> bool:
+    """AdaIR FreModule (AdaIR-main/net/model.py:295-372) with its FreRefine / SpatialGate / ChannelGate children."""
+    kids = set(dict(m.named_children()))
+    if kids != {"conv", "conv1", "score_gen", "channel_cross_l", "channel_cross_h", "channel_cross_agg", "frequency_refine",
+                "rate_conv"}:
+        return False
+    if {n for n, _ in m.named_parameters(recurse=False)} != {"para1", "para2"}:
+        return False
+    if not all(_is_cross(getattr(m, a)) for a in ("channel_cross_l", "channel_cross_h", "channel_cross_agg")):
+        return False
+    dim = m.channel_cross_l.q.in_channels
+    fr = m.frequency_refine
+    sg, cg = getattr(fr, "SpatialGate", None), getattr(fr, "ChannelGate", None)
+    if sg is None or cg is None or not hasattr(fr, "proj") or not hasattr(sg, "spatial") or not hasattr(cg, "mlp"):
+        return False
+    rc, mlp = m.rate_conv, cg.mlp
+    return (_conv_ok(m.conv1, 3, 1) and m.conv1.out_channels == dim and m.conv1.bias is None
+            and tuple(m.para1.shape) == (dim, 1, 1) == tuple(m.para2.shape)
+            and _conv_ok(sg.spatial, 7, 1) and sg.spatial.in_channels == 2 and sg.spatial.out_channels == 1
+            and sg.spatial.bias is None
+            and isinstance(mlp, nn.Sequential) and len(mlp) == 3 and _conv_ok(mlp[0], 1, 1) and isinstance(mlp[1], nn.ReLU)
+            and _conv_ok(mlp[2], 1, 1) and mlp[0].bias is None and mlp[2].bias is None
+            and mlp[0].in_channels == dim == mlp[2].out_channels
+            and _conv_ok(fr.proj, 1, 1) and fr.proj.in_channels == dim == fr.proj.out_channels
+            and isinstance(rc, nn.Sequential) and len(rc) == 3 and _conv_ok(rc[0], 1, 1) and isinstance(rc[1], nn.GELU)
+            and _conv_ok(rc[2], 1, 1) and rc[0].bias is None and rc[2].bias is None and rc[0].in_channels == dim
+            and rc[2].out_channels == 2)
+
+
 def _is_resize(m):
     """Sequential(conv3x3 (no bias), PixelUnshuffle(2) | PixelShuffle(2)) wrapped as `.body` -> 'down' | 'up' | None."""
     body = getattr(m, "body", None)
@@ -199,6 +231,26 @@ def _adopt_cross(m):
     return a
 
 
+def _adopt_fremodule(m):
+    f = _bare(AD.FreModule)
+    f.conv, f.conv1, f.score_gen = m.conv, m.conv1, m.score_gen      # (registration order = the reference's state_dict order)
+    f.para1, f.para2 = m.para1, m.para2
+    for a in ("channel_cross_l", "channel_cross_h", "channel_cross_agg"):
+        setattr(f, a, _adopt_cross(getattr(m, a)))
+    r = _bare(AD.FreRefine)
+    r.SpatialGate = _bare(AD.SpatialGate)
+    r.SpatialGate.spatial = m.frequency_refine.SpatialGate.spatial
+    r.ChannelGate = _bare(AD.ChannelGate)
+    for a in ("avg", "max"):
+        if hasattr(m.frequency_refine.ChannelGate, a):
+            setattr(r.ChannelGate, a, getattr(m.frequency_refine.ChannelGate, a))
+    r.ChannelGate.mlp = m.frequency_refine.ChannelGate.mlp
+    r.proj = m.frequency_refine.proj
+    f.frequency_refine = r
+    f.rate_conv = m.rate_conv
+    return f
+
+
 def _adopt_split_gate_ffn(m):
     f = _bare(M.GatedSpatialFFN)
     f.project_in, f.dwconv_gate, f.dwconv_content, f.project_out = m.project_in, m.dwconv_gate, m.dwconv_content, m.project_out
@@ -223,9 +275,11 @@ def _adopt(m):
     """-> (replacement, kind) or (None, None)."""
     if isinstance(m, (M.TransformerBlock, M.EncoderBlock, M.Attention, M.CrossAttention, M.GatedMDTA,
                       M.GatedTransformerBlock, M.FeedForward, M.LayerNorm, M.Downsample, M.Upsample,
-                      M.GatedSpatialFFN, M.ElementwiseGatedAttention)):
+                      M.GatedSpatialFFN, M.ElementwiseGatedAttention, AD.FreModule)):
         return None, None
     kids = dict(m.named_children())
+    if _is_fremodule(m):
+        return _adopt_fremodule(m), "frequency_module"
     if set(kids) == {"norm1", "attn", "norm2", "ffn"} and _is_ln(m.norm1) and _is_ln(m.norm2) and _is_mdta(m.attn) \
             and _is_gdfn(m.ffn) and not list(m.named_parameters(recurse=False)):
         b = _bare(M.TransformerBlock)
@@ -271,6 +325,8 @@ def _in_channels(new, kind):
         return new.project_in.in_channels
     if kind == "cross_attention":
         return new.q.in_channels
+    if kind == "frequency_module":
+        return new.conv1.in_channels
     if kind == "feedforward":
         return new.project_in.in_channels
     if kind == "layernorm":
@@ -292,6 +348,9 @@ def _agrees(old, new, kind, tol):
     try:
         if kind == "cross_attention":
             y = (torch.rand(x.shape, generator=g) * 2 - 1).to(p.device)
+            ref, got = old(x, y), new(x, y)
+        elif kind == "frequency_module":      # (image, feature); the image is resized to the feature's size inside
+            y = (torch.rand(2, new.conv1.out_channels, 8, 12, generator=g) * 2 - 1).to(p.device)
             ref, got = old(x, y), new(x, y)
         else:
             ref = old(x)

@@ -512,18 +512,18 @@ class Restormer(nn.Module):
         out_enc_level3 = self._run_stack(self.encoder_level3, inp_enc_level3,
                                          None if grad or len(self.encoder_level3) == 0 else cat3[:, dim * 4:])
         inp_enc_level4 = self.down3_4(out_enc_level3)
-        latent = self._run_stack(self.latent, inp_enc_level4)
+        latent = self._mix(1, inp_img, self._run_stack(self.latent, inp_enc_level4))
 
         inp_dec_level3 = self._cat(self.up4_3, latent, out_enc_level3, cat3, dim * 4)
         cache = self.__dict__.setdefault("_b200ir_cache", {})
         inp_dec_level3 = A.ln_conv1x1(inp_dec_level3, self.reduce_chan_level3.weight, self.reduce_chan_level3.bias,
                                       L.LN_NONE, None, None, None, cache=cache, key="rc3")
-        out_dec_level3 = self._run_stack(self.decoder_level3, inp_dec_level3)
+        out_dec_level3 = self._mix(2, inp_img, self._run_stack(self.decoder_level3, inp_dec_level3))
 
         inp_dec_level2 = self._cat(self.up3_2, out_dec_level3, out_enc_level2, cat2, dim * 2)
         inp_dec_level2 = A.ln_conv1x1(inp_dec_level2, self.reduce_chan_level2.weight, self.reduce_chan_level2.bias,
                                       L.LN_NONE, None, None, None, cache=cache, key="rc2")
-        out_dec_level2 = self._run_stack(self.decoder_level2, inp_dec_level2)
+        out_dec_level2 = self._mix(3, inp_img, self._run_stack(self.decoder_level2, inp_dec_level2))
 
         inp_dec_level1 = self._cat(self.up2_1, out_dec_level2, out_enc_level1, cat1, dim)
         out_dec_level1 = self._run_stack(self.decoder_level1, inp_dec_level1)
@@ -536,6 +536,11 @@ class Restormer(nn.Module):
                              out_dtype=inp_img.dtype)
         return A.conv3x3(out_dec_level1, self.output.weight, self.output.bias, inp_img, L.SHUFFLE_NONE,
                          out_dtype=inp_img.dtype)
+
+    def _mix(self, stage, inp_img, feat):
+        """Hook after the latent (1), decoder_level3 (2) and decoder_level2 (3) stacks: identity in Restormer; AdaIR's
+        frequency modules sit here (AdaIR-main/net/model.py:463-485)."""
+        return feat
 
     @staticmethod
     def _cat(up, x, skip, buf, c_up):

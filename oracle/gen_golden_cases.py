@@ -146,6 +146,22 @@ FREMODULE_TRAIN_CASES = [
     ("adair_fre_train_c32_h2_64", 32, 2, False, 2, (64, 64), (64, 64), 198, 1.0),       # empty mask: low = 0, high = |x|
 ]
 
+# The whole AdaIR network (AdaIR-main/net/model.py:375-497): name, constructor kwargs, B, H, W, seed, training golden?,
+# rate_scale (as above, applied to fre3.rate_conv.2.weight).  Training: loss = L1(restored, clean) as in
+# AdaIR-main/train.py:38-46; every parameter gradient stored (scaled fp16; tensors above 4096 elements as the strided
+# sample `grad_sample` takes).
+ADAIR_NET_CFG = dict(dim=16, num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, heads=[1, 2, 2, 4])
+ADAIR_NET_CASES = [
+    ("adair_net_d16_b2_64", ADAIR_NET_CFG, 2, 64, 64, 211, True, 1.0),
+    ("adair_net_d16_b1_512", ADAIR_NET_CFG, 1, 512, 512, 212, False, (30.0, -400.0)),   # fre3 at 256x256: a 2x2-bin mask
+]
+
+
+def grad_sample(g):
+    """flattened gradient, every ceil(numel / 4096)-th element."""
+    f = g.reshape(-1)
+    return f[::max(1, -(-f.shape[0] // 4096))]
+
 
 def fre_sample(t):
     """What the FreModule goldens keep of a [B, C, H, W] tensor (the full 512x512 tensors would be 16 MB): a strided

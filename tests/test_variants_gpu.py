@@ -276,3 +276,81 @@ def test_adair_fremodule_training_vs_reference_golden():
                 else:
                     assert p.grad is None, (name, k)      # conv, score_gen, rate_conv: untouched by the reference's backward too
             assert not bad, (name, dtype, bad)
+
+
+def test_adair_network_vs_reference_golden():
+    """b200ir.AdaIR (Restormer U-Net + three FreModules, AdaIR-main/net/model.py:375-497): restored image at 64x64 and at
+    512x512 (non-empty spectrum mask in fre3), and the L1 training step's loss and parameter gradients."""
+    import b200ir
+    from oracle.gen_golden_adair_train import adair_net_inputs, adair_net_state
+    from oracle.gen_golden_cases import ADAIR_NET_CASES, fre_sample, grad_sample
+    for name, cfg, b, h, w, seed, train, rs in ADAIR_NET_CASES:
+        gold = np.load(os.path.join(GOLDEN, name + ".npz"))
+        net = b200ir.AdaIR(**cfg)
+        assert sorted(net.state_dict()) == sorted(str(k) for k in gold["keys"])
+        net.load_state_dict(adair_net_state(net, seed, rs), strict=True)
+        net = net.cuda()
+        x, clean = adair_net_inputs(b, h, w, seed)
+        if not train:
+            net.eval()
+            with torch.no_grad():
+                y32 = net.set_compute_dtype(torch.float32)(x.cuda())
+                y16 = net.set_compute_dtype(torch.bfloat16)(x.cuda()).float()
+            s, c = fre_sample(y32)
+            assert np.abs(s - gold["y"]).max() <= 3e-4, (name, float(np.abs(s - gold["y"]).max()))
+            assert np.allclose(c, gold["y_sum"], rtol=1e-4), (name, c, gold["y_sum"])
+            s16, _ = fre_sample(y16)
+            mse = float(((s16 - gold["y"]) ** 2).mean())
+            assert 10 * np.log10(1.0 / mse) >= 40.0, (name, 10 * np.log10(1.0 / mse))
+            continue
+        for dtype in (torch.float32, torch.bfloat16):
+            f32 = dtype == torch.float32
+            net.set_compute_dtype(dtype).train()
+            net.zero_grad(set_to_none=True)
+            y = net(x.cuda())
+            loss = b200ir.L1Loss()(y, clean.cuda())
+            loss.backward()
+            ref = torch.from_numpy(gold["y"])
+            assert (y.detach().float().cpu() - ref).abs().max() <= (3e-4 if f32 else 8e-2), (name, dtype)
+            assert abs(float(loss.detach()) - float(gold["loss"])) <= (1e-5 if f32 else 3e-3), (name, dtype, float(loss.detach()))
+            bad, gmax = [], max(float(gold[k]) for k in gold.files if k.startswith("s."))
+            for k, p in net.named_parameters():
+                if "g." + k not in gold.files:
+                    assert p.grad is None, (name, k)
+                    continue
+                assert p.grad is not None, (name, k)
+                r = gold["g." + k].astype(np.float64) * float(gold["s." + k])
+                g = grad_sample(p.grad.detach().float().cpu().numpy()).astype(np.float64)
+                err = np.abs(g - r).max()
+                if err > (2e-3 if f32 else 0.25) * np.abs(r).max() + 1e-5 * gmax:
+                    bad.append((k, float(err), float(np.abs(r).max())))
+            assert not bad, (name, dtype, bad[:8], len(bad))
+
+
+def test_accelerate_adopts_adair_frequency_module():
+    """dropin.accelerate() takes a module with FreModule's structure (tests/torch_models.py RefFreModule is bit-identical
+    to AdaIR-main/net/model.py:295-372, checked in the build container); the adopted module keeps the state_dict and trains."""
+    import b200ir
+    from torch_models import RefAdaIRTail
+    torch.manual_seed(6)
+    net = RefAdaIRTail(32, 2)
+    with torch.no_grad():
+        net.fre.para1.add_(0.5 + torch.rand(32, 1, 1))
+    keys = list(net.state_dict())
+    img = O.synth_image(2, 24, 40, seed=9)
+    ref = net(img)
+    ref.square().mean().backward()
+    gref = {k: q.grad.clone() for k, q in net.named_parameters() if q.grad is not None}
+    net.zero_grad(set_to_none=True)
+    net = net.cuda()
+    net, stats = b200ir.accelerate(net, verify=True)
+    assert stats == {"frequency_module": 1}, stats
+    assert isinstance(net.fre, b200ir.FreModule) and list(net.state_dict()) == keys
+    got = net(img.cuda())
+    assert (got.detach().cpu() - ref.detach()).abs().max() <= 2e-4 * max(1.0, ref.abs().max().item())
+    got.square().mean().backward()
+    for k, q in net.named_parameters():
+        if k in gref:
+            assert q.grad is not None and _rel(q.grad.cpu(), gref[k]) <= 3e-3, (k, _rel(q.grad.cpu(), gref[k]))
+        else:
+            assert q.grad is None, k

@@ -258,3 +258,84 @@ class RefRectiBlock(nn.Module):
     def forward(self, x, dynamic_temp=None):
         x = x + self.attn(self.norm1(x), dynamic_temp)
         return x + self.ffn(self.norm2(x))
+
+
+class _RefSpatialGate(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.spatial = nn.Conv2d(2, 1, 7, padding=3, bias=False)
+
+    def forward(self, x):
+        pooled = torch.cat([x.amax(dim=1, keepdim=True), x.mean(dim=1, keepdim=True)], 1)
+        return torch.sigmoid(self.spatial(pooled))
+
+
+class _RefChannelGate(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.mlp = nn.Sequential(nn.Conv2d(dim, dim // 16, 1, bias=False), nn.ReLU(), nn.Conv2d(dim // 16, dim, 1, bias=False))
+
+    def forward(self, x):
+        return torch.sigmoid(self.mlp(x.mean(dim=(2, 3), keepdim=True)) + self.mlp(x.amax(dim=(2, 3), keepdim=True)))
+
+
+class _RefFreRefine(nn.Module):
+    def __init__(self, dim):
+        super().__init__()
+        self.SpatialGate = _RefSpatialGate()
+        self.ChannelGate = _RefChannelGate(dim)
+        self.proj = nn.Conv2d(dim, dim, 1)
+
+    def forward(self, low, high):
+        return self.proj(low * self.SpatialGate(high) + high * self.ChannelGate(low))
+
+
+class RefFreModule(nn.Module):
+    """Stand-in with the structure and arithmetic of AdaIR's FreModule (AdaIR-main/net/model.py:295-372): bilinear resize
+    of the image, conv3x3, a centred spectrum rectangle of half size int(H // 128 * t) split off with fft2 / ifft2, three
+    channel cross attentions, FreRefine, per-channel affine.  Checked against the reference in the build container
+    (outputs and gradients equal to rounding)."""
+
+    def __init__(self, dim, num_heads, bias, in_dim=3):
+        super().__init__()
+        self.conv = nn.Conv2d(in_dim, dim, 3, 1, 1, bias=False)
+        self.conv1 = nn.Conv2d(in_dim, dim, 3, 1, 1, bias=False)
+        self.score_gen = nn.Conv2d(2, 2, 7, padding=3)
+        self.para1 = nn.Parameter(torch.zeros(dim, 1, 1))
+        self.para2 = nn.Parameter(torch.ones(dim, 1, 1))
+        self.channel_cross_l = RefChanelCrossAttention(dim, num_heads, bias)
+        self.channel_cross_h = RefChanelCrossAttention(dim, num_heads, bias)
+        self.channel_cross_agg = RefChanelCrossAttention(dim, num_heads, bias)
+        self.frequency_refine = _RefFreRefine(dim)
+        self.rate_conv = nn.Sequential(nn.Conv2d(dim, dim // 8, 1, bias=False), nn.GELU(), nn.Conv2d(dim // 8, 2, 1, bias=False))
+
+    def bands(self, x, n=128):
+        x = self.conv1(x)
+        B, C, H, W = x.shape
+        t = torch.sigmoid(self.rate_conv(x.mean(dim=(2, 3), keepdim=True)))
+        keep = torch.zeros_like(x)
+        for i in range(B):
+            hh, ww = int(H // n * t[i, 0, 0, 0]), int(W // n * t[i, 1, 0, 0])
+            keep[i, :, H // 2 - hh:H // 2 + hh, W // 2 - ww:W // 2 + ww] = 1
+        spec = torch.roll(torch.fft.fft2(x, norm="forward"), (H // 2, W // 2), (2, 3))
+        back = lambda s: torch.fft.ifft2(torch.roll(s, (-(H // 2), -(W // 2)), (2, 3)), norm="forward").abs()   # noqa: E731
+        return back(spec * (1 - keep)), back(spec * keep)
+
+    def forward(self, x, y):
+        x = torch.nn.functional.interpolate(x, y.shape[-2:], mode="bilinear")
+        high, low = self.bands(x)
+        high, low = self.channel_cross_l(high, y), self.channel_cross_h(low, y)
+        out = self.channel_cross_agg(y, self.frequency_refine(low, high))
+        return out * self.para1 + y * self.para2
+
+
+class RefAdaIRTail(nn.Module):
+    """A feature extractor followed by a frequency module, the way AdaIR calls it (model.py:463-465)."""
+
+    def __init__(self, dim=32, heads=2):
+        super().__init__()
+        self.embed = nn.Conv2d(3, dim, 3, 1, 1)
+        self.fre = RefFreModule(dim, heads, True)
+
+    def forward(self, img):
+        return self.fre(img, self.embed(img))
