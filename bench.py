@@ -180,6 +180,7 @@ def main():
     ap.add_argument("--no-train", action="store_true", help="skip the cfg4 training-step leg")
     ap.add_argument("--no-hires", action="store_true", help="skip the cfg5 1024x1024 leg")
     ap.add_argument("--no-moce", action="store_true", help="skip the cfg3 MoCE-IR leg")
+    ap.add_argument("--no-adair", action="store_true", help="skip the AdaIR leg")
     ap.add_argument("--kernel-table", default=None, help="write a per-kernel CUDA-event timing table (JSON) here")
     ap.add_argument("--no-incumbent", action="store_true", help="skip the eager-PyTorch-on-GPU informational leg")
     args = ap.parse_args()
@@ -372,6 +373,56 @@ def main():
         del mnet, min_
         torch.cuda.empty_cache()
 
+    # ---- AdaIR leg (no BASELINE config): the Restormer U-Net + three FreModules, forward and training step ----
+    adair = None
+    if not args.no_adair and world == 1:
+        from oracle.gen_golden_cases import synth_like
+        AB = 8
+        anet = b200ir.AdaIR()
+        asd = synth_like(anet.state_dict(), 83)
+        for k in asd:
+            if k.endswith("para1"):                       # (init is zeros: the frequency branch would be multiplied away)
+                asd[k] = torch.full_like(asd[k], 0.5)
+        anet.load_state_dict(asd, strict=True)
+        anet = anet.to(dev).eval().set_compute_dtype(cd)
+        ain = [O.synth_image(AB, H, W, seed=655 + i).to(dev) for i in range(2)]
+        afwd = b200ir.GraphedForward(anet, ain[0])
+        for i in range(args.warmup):
+            afwd(ain[i % 2])
+        torch.cuda.synchronize()
+        e0.record()
+        for i in range(args.steps):
+            afwd(ain[i % 2])
+        e1.record()
+        torch.cuda.synchronize()
+        ms_ad = e0.elapsed_time(e1) / args.steps
+        adair = {"workload": f"AdaIR(dim=48,[4,6,6,8]) forward, {H}x{W}, batch {AB}, {args.dtype}, b200ir.GraphedForward, single GPU",
+                 "value": AB * H * W / 1e6 / (ms_ad * 1e-3), "unit": "MP/s", "ms_per_step": ms_ad,
+                 "gpu_launches_per_step": afwd.launches_per_call}
+        del afwd, ain
+        if not args.no_train:
+            anet.train()
+            aopt = b200ir.AdamW(anet.parameters(), lr=2e-4)
+            ac = [torch.rand(AB, 3, 128, 128, generator=torch.Generator().manual_seed(950 + i)).to(dev) for i in range(2)]
+            adg = [(c + 25.0 / 255.0 * torch.randn_like(c)).clamp(0, 1) for c in ac]
+            astep = b200ir.GraphedTrainStep(anet, aopt, adg[0], ac[0])
+            for i in range(args.warmup):
+                astep(adg[i % 2], ac[i % 2])
+            torch.cuda.synchronize()
+            e0.record()
+            for i in range(args.steps):
+                aloss = astep(adg[i % 2], ac[i % 2])
+            e1.record()
+            torch.cuda.synchronize()
+            ms_at = e0.elapsed_time(e1) / args.steps
+            adair["train_step"] = {"workload": f"AdaIR training step (L1, AdamW; AdaIR-main/train.py:38-46), 128x128, batch {AB}, "
+                                               f"{args.dtype}, b200ir.GraphedTrainStep, single GPU",
+                                   "value": AB * 128 * 128 / 1e6 / (ms_at * 1e-3), "unit": "MP/s", "ms_per_step": ms_at,
+                                   "loss": float(aloss)}
+            del astep, aopt, ac, adg
+        del anet
+        torch.cuda.empty_cache()
+
     # ---- training-step leg (BASELINE configs[3]): L1 + AdamW, 128x128 patches, batch 8 per GPU, DDP all-reduce --------
     train = None
     if not args.no_train:
@@ -459,6 +510,8 @@ def main():
         out["hires"] = hires
     if moce is not None:
         out["moce_ir"] = moce
+    if adair is not None:
+        out["adair"] = adair
     if incumbent is not None:
         out["incumbent_gpu"] = incumbent
     if not args.no_cpu_baseline:

@@ -540,7 +540,7 @@ __global__ void __launch_bounds__(MB_THREADS)
 mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
                       const float* __restrict__ temperature, const float* __restrict__ w_out,
                       const float* __restrict__ dM, float* __restrict__ mqk, float* __restrict__ dtemp_part, int C,
-                      int d, int temp_per_sample) {
+                      int d, int temp_per_sample, int CO) {
   extern __shared__ float sm[];
   const int D1 = d + 1;
   float* at = sm;                        // attn  [d][d+1]
@@ -566,26 +566,36 @@ mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float
     na[j] = fmaxf(sqrtf(s), 1e-12f);  // na[d..2d) aliases nb
   }
   __syncthreads();
-  // stage this head's column blocks W_out[:, hd:hd+d] and dM_b[:, hd:hd+d] (C x d each) in shared memory
-  float* wsm = cs + d;                   // [C][d]
-  float* dsm = wsm + (size_t)C * d;      // [C][d]
-  for (int e = tid; e < C * d; e += MB_THREADS) {
-    const int o = e / d, i = e - o * d;
-    wsm[e] = w_out[(size_t)o * C + h * d + i];
-    dsm[e] = dMb[(size_t)o * C + h * d + i];
-  }
-  __syncthreads();
   for (int e = tid; e < d * d; e += MB_THREADS) {
     const int i = e / d, j = e % d;
     float s = 0.f;
     for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];
     gh[i * D1 + j] = s / (na[i] * nb[j]);
     at[i * D1 + j] = a_g[e];
-    // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
-    float acc = 0.f;
+    da[i * D1 + j] = 0.f;
+  }
+  // stage this head's column blocks W_out[:, hd:hd+d] and dM_b[:, hd:hd+d] in shared memory, CO rows at a time (CO = C
+  // unless C x d x 2 floats do not fit: AdaIR's FreModule runs C = 384 with 4 heads); the element's fma chain over o runs
+  // in the same order whatever CO is, through da[] between chunks, so the result does not depend on CO
+  float* wsm = cs + d;                   // [CO][d]
+  float* dsm = wsm + (size_t)CO * d;     // [CO][d]
+  for (int o0 = 0; o0 < C; o0 += CO) {
+    const int co = min(CO, C - o0);
+    __syncthreads();
+    for (int e = tid; e < co * d; e += MB_THREADS) {
+      const int o = e / d, i = e - o * d;
+      wsm[e] = w_out[(size_t)(o0 + o) * C + h * d + i];
+      dsm[e] = dMb[(size_t)(o0 + o) * C + h * d + i];
+    }
+    __syncthreads();
+    for (int e = tid; e < d * d; e += MB_THREADS) {
+      const int i = e / d, j = e % d;
+      // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
+      float acc = da[i * D1 + j];
 #pragma unroll 8
-    for (int o = 0; o < C; ++o) acc = fmaf(wsm[o * d + i], dsm[o * d + j], acc);
-    da[i * D1 + j] = acc;
+      for (int o = 0; o < co; ++o) acc = fmaf(wsm[o * d + i], dsm[o * d + j], acc);
+      da[i * D1 + j] = acc;
+    }
   }
   __syncthreads();
   for (int i = warp; i < d; i += NW) {  // row sums of dattn o attn
@@ -964,8 +974,13 @@ extern "C" int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float*
   B200IR_CHECK_ARG(nslab > 0 && B > 0 && C > 0 && heads > 0 && C % heads == 0 && B <= 65535, "mdta_bwd: bad shape");
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
-  const size_t smem = (3 * (size_t)d * (d + 1) + 4 * (size_t)d + 2 * (size_t)C * d) * sizeof(float);
-  B200IR_UNSUPPORTED(smem <= 220 * 1024, "mdta_bwd: C=%d head dim %d needs %zu B of shared memory", C, d, smem);
+  // fixed part (three d x (d+1) matrices + four vectors) + the staged W_out / dM rows, CO of C at a time
+  const size_t fixed = (3 * (size_t)d * (d + 1) + 4 * (size_t)d) * sizeof(float), limit = 220 * 1024;
+  B200IR_UNSUPPORTED(fixed + 2 * 8 * (size_t)d * sizeof(float) <= limit, "mdta_bwd: head dim %d needs %zu B of shared memory",
+                     d, fixed);
+  int CO = (int)((limit - fixed) / (2 * (size_t)d * sizeof(float)));
+  if (CO > C) CO = C;
+  const size_t smem = fixed + 2 * (size_t)CO * d * sizeof(float);
   const size_t smem2 = ((size_t)d * (d + 1) + 64 * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
@@ -974,7 +989,7 @@ extern "C" int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float*
     attr_set = true;
   }
   mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
-      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0);
+      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0, CO);
   int rc = check_launch("mdta_bwd_chain");
   if (rc) return rc;
   mdta_bwd_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem2,

@@ -121,7 +121,8 @@ def test_gelu_gate_backward(b200ir, Hd, H, W, bias):
 
 
 @pytest.mark.parametrize("C,heads,H,W,bias", [(48, 1, 16, 16, False), (64, 2, 8, 24, True), (96, 2, 16, 8, True),
-                                              (96, 1, 16, 16, False)])
+                                              (96, 1, 16, 16, False),
+                                              (384, 4, 8, 8, True)])     # AdaIR fre1: head dim 96 at C = 384 (chunked staging)
 def test_mdta_core_backward(b200ir, C, heads, H, W, bias):
     from b200ir import autograd_ops as A
     g = torch.Generator().manual_seed(6)
