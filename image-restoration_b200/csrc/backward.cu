@@ -412,24 +412,26 @@ ln_bwd_bf16_reg_kernel(const bf16* __restrict__ x, int64_t x_bs, const bf16* __r
   }
 }
 
-// out[k] = sum_{i<n} in[i*stride + k].  CTA = 32 outputs x 8 slices of the partial index; each slice is summed
-// sequentially, the 8 slice sums are combined in fixed order (deterministic).
-__global__ void __launch_bounds__(256)
+// out[k] = sum_{i<n} in[i*stride + k].  CTA = 32 outputs x SL slices of the partial index; each slice is summed
+// sequentially, the SL slice sums are combined in fixed order (deterministic).  SL = 8, or 32 when there are few outputs
+// and many partials (the dgamma / dbeta folds: 3-12 CTAs each walking hundreds of partials were latency-bound at 11 us).
+template <int SL>
+__global__ void __launch_bounds__(32 * SL)
 reduce_partials_kernel(const float* __restrict__ in, float* __restrict__ out, int n, int64_t K, int64_t stride) {
-  __shared__ float red[8][32];
+  __shared__ float red[SL][32];
   const int lane = threadIdx.x & 31, sl = threadIdx.x >> 5;
   for (int64_t k0 = (int64_t)blockIdx.x * 32; k0 < K; k0 += (int64_t)gridDim.x * 32) {
     const int64_t k = k0 + lane;
     float s = 0.f;
     if (k < K)
-      for (int i = sl; i < n; i += 8) s += in[(size_t)i * stride + k];
+      for (int i = sl; i < n; i += SL) s += in[(size_t)i * stride + k];
     __syncthreads();
     red[sl][lane] = s;
     __syncthreads();
     if (sl == 0 && k < K) {
       float t = 0.f;
 #pragma unroll
-      for (int w = 0; w < 8; ++w) t += red[w][lane];
+      for (int w = 0; w < SL; ++w) t += red[w][lane];
       out[k] = t;
     }
   }
@@ -895,7 +897,10 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
 extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride,
                                       b200ir_stream_t stream) {
   B200IR_CHECK_ARG(in && out && n > 0 && K > 0 && stride >= K, "reduce_partials: bad args");
-  reduce_partials_kernel<<<grid_1d(K, 32, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
+  if (K <= 32 * (int64_t)num_sms() && n >= 64)
+    reduce_partials_kernel<32><<<grid_1d(K, 32, num_sms() * 16), 1024, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
+  else
+    reduce_partials_kernel<8><<<grid_1d(K, 32, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
   return check_launch("reduce_partials");
 }
 

@@ -5,6 +5,7 @@ TAG=${1:-rX}
 O=gpurun_out
 mkdir -p $O
 python -m pytest tests -m gpu -q 2>&1 | tail -4 > $O/${TAG}_pytest.log
+python -c "import __graft_entry__ as g; g.smoke()" > $O/${TAG}_smoke.log 2>&1; echo "smoke rc=$?" >> $O/${TAG}_smoke.log
 python bench.py --kernel-table $O/${TAG}_kernel_table.json > $O/${TAG}_bench.json 2> $O/${TAG}_bench.err || exit 1
 python bench.py --steps 1 --no-train --no-cpu-baseline > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 2500 --csv --log-file $O/${TAG}_launches_ncu.csv \
