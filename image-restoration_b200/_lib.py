@@ -90,6 +90,8 @@ SIGNATURES = {
     "b200ir_fre_combine_bwd": [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _vp, _i, _i, _i, _i64, _vp],
     "b200ir_affine2_bwd": [_vp, _i64, _vp, _i64, _vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _vp, _i, _i, _i, _i64, _vp],
     "b200ir_crop_augment_degrade": [_vp, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
+    "b200ir_tile_gather": [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
+    "b200ir_tile_blend": [_vp, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_psnr_ssim_nblocks": [_i, _i],
     "b200ir_psnr_ssim": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "b200ir_adamw_step": [_vp, _vp, _vp, _vp, _i64, _f, _f, _f, _f, _f, _i, _vp, _f, _vp],

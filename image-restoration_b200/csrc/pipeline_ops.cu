@@ -138,6 +138,71 @@ __global__ void metrics_finish_kernel(const float* __restrict__ se, const float*
 
 using namespace b200ir;
 
+// ---- full-frame inference in tiles (the E / W recipe of the reference's tile helper, e.g.
+// 20260104_CG_IR/src/data/dataset_utils.py:513-534: E[.., h:h+t, w:w+t] += out_patch, W += 1, restored = E / W) ----
+namespace b200ir {
+// patches[(ti * B + b)][c][y][x] = src[b][c][h0(ti) + y][w0(ti) + x]
+__global__ void tile_gather_kernel(const float* __restrict__ src, const int* __restrict__ origins, float* __restrict__ dst,
+                                   int B, int C, int H, int W, int t) {
+  const int ti = blockIdx.z, b = blockIdx.y;
+  const int h0 = origins[2 * ti], w0 = origins[2 * ti + 1];
+  const int64_t per = (int64_t)C * t * t;
+  float* d = dst + ((int64_t)ti * B + b) * per;
+  const float* s = src + (int64_t)b * C * H * W;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (int64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % t), y = (int)((i / t) % t), c = (int)(i / ((int64_t)t * t));
+    d[i] = s[((int64_t)c * H + h0 + y) * W + w0 + x];
+  }
+}
+// out[b][c][y][x] = clamp01( (sum over the tiles covering (y, x), in tile order, of their pixel) / (number of such tiles) ):
+// pull form of the accumulate -- no atomics, and the same order of additions as the reference's loop over h_idx, w_idx
+__global__ void tile_blend_kernel(const float* __restrict__ patches, const int* __restrict__ hs, int nh,
+                                  const int* __restrict__ ws, int nw, float* __restrict__ out, int B, int C, int H, int W, int t,
+                                  int clamp01) {
+  const int b = blockIdx.y;
+  const int64_t per = (int64_t)C * H * W, pp = (int64_t)C * t * t;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < per; i += (int64_t)gridDim.x * blockDim.x) {
+    const int x = (int)(i % W), y = (int)((i / W) % H), c = (int)(i / ((int64_t)W * H));
+    float e = 0.f, wsum = 0.f;
+    for (int a = 0; a < nh; ++a) {
+      const int dy = y - hs[a];
+      if (dy < 0 || dy >= t) continue;
+      for (int q = 0; q < nw; ++q) {
+        const int dx = x - ws[q];
+        if (dx < 0 || dx >= t) continue;
+        e += patches[((int64_t)(a * nw + q) * B + b) * pp + ((int64_t)c * t + dy) * t + dx];
+        wsum += 1.f;
+      }
+    }
+    float v = e / wsum;
+    if (clamp01) v = fminf(fmaxf(v, 0.f), 1.f);
+    out[(int64_t)b * per + i] = v;
+  }
+}
+}  // namespace b200ir
+
+extern "C" int b200ir_tile_gather(const float* src, const int* origins, float* patches, int ntiles, int B, int C, int H, int W,
+                                  int tile, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(src && origins && patches && ntiles > 0 && ntiles <= 65535 && B > 0 && B <= 65535 && C > 0 && tile > 0 &&
+                   tile <= H && tile <= W, "tile_gather: bad args");
+  int gx = (int)(((int64_t)C * tile * tile + 255) / 256);
+  if (gx > 64) gx = 64;
+  b200ir::tile_gather_kernel<<<dim3((unsigned)gx, (unsigned)B, (unsigned)ntiles), 256, 0, (cudaStream_t)stream>>>(
+      src, origins, patches, B, C, H, W, tile);
+  return b200ir::check_launch("tile_gather");
+}
+
+extern "C" int b200ir_tile_blend(const float* patches, const int* h_idx, int nh, const int* w_idx, int nw, float* out, int B,
+                                 int C, int H, int W, int tile, int clamp01, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(patches && h_idx && w_idx && out && nh > 0 && nw > 0 && B > 0 && B <= 65535 && C > 0 && tile > 0 &&
+                   tile <= H && tile <= W, "tile_blend: bad args");
+  int64_t gx = ((int64_t)C * H * W + 255) / 256;
+  if (gx > (int64_t)b200ir::num_sms() * 8) gx = (int64_t)b200ir::num_sms() * 8;
+  b200ir::tile_blend_kernel<<<dim3((unsigned)gx, (unsigned)B), 256, 0, (cudaStream_t)stream>>>(patches, h_idx, nh, w_idx, nw, out,
+                                                                                              B, C, H, W, tile, clamp01);
+  return b200ir::check_launch("tile_blend");
+}
+
 extern "C" int b200ir_crop_augment_degrade(const uint8_t* src, int Hs, int Ws, const int* offsets, const int* modes,
                                            const float* sigma, const float* noise, float* clean, float* degraded, int B,
                                            int P, b200ir_stream_t stream) {

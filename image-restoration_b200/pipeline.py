@@ -57,3 +57,51 @@ def psnr_ssim(restored: torch.Tensor, clean: torch.Tensor) -> torch.Tensor:
     L.check(lib.b200ir_psnr_ssim(r.data_ptr(), c.data_ptr(), ws.data_ptr(), out.data_ptr(), B, C, H, W, ops._stream()),
             "b200ir_psnr_ssim")
     return out
+
+
+def tile_index_lists(h: int, w: int, tile: int, tile_overlap: int):
+    """(tile, h_idx_list, w_idx_list) exactly as the reference's tile helper builds them
+    (20260104_CG_IR/src/data/dataset_utils.py:515-521): tile = min(tile, h, w), stride = tile - overlap, start offsets
+    range(0, h - tile, stride) plus the last one that ends at the border."""
+    tile = min(tile, h, w)
+    if tile % 8:
+        raise ValueError("tile size should be multiple of 8")
+    stride = tile - tile_overlap
+    if stride <= 0:
+        raise ValueError("tile_overlap must be smaller than the tile")
+    return tile, list(range(0, h - tile, stride)) + [h - tile], list(range(0, w - tile, stride)) + [w - tile]
+
+
+@torch.no_grad()
+def tiled_restore(net, x: torch.Tensor, tile: int = 128, tile_overlap: int = 0, tile_batch: int = 16,
+                  clamp: bool = True) -> torch.Tensor:
+    """Full-frame inference for frames too large for one pass: the frame is cut into overlapping ``tile`` x ``tile``
+    patches, ``net`` restores them ``tile_batch`` at a time, and the patches are averaged where they overlap
+    (``E[.., h:h+t, w:w+t] += patch; W += 1; restored = clamp(E / W, 0, 1)``: the reference's tile helper,
+    20260104_CG_IR/src/data/dataset_utils.py:513-534, MEASNet-main/MEASNet/utils/dataset_utils.py:226-247).
+    x fp32 CUDA [B, C, H, W]; -> fp32 [B, C_out, H, W].  Gather and blend are libb200ir kernels (csrc/pipeline_ops.cu)."""
+    if x.dim() != 4 or not x.is_cuda or x.dtype != torch.float32:
+        raise ValueError("tiled_restore: fp32 CUDA NCHW input expected (no CPU fallback)")
+    x = x.contiguous()
+    B, C, H, W = x.shape
+    t, hs, ws = tile_index_lists(H, W, tile, tile_overlap)
+    nh, nw = len(hs), len(ws)
+    T = nh * nw
+    origins = torch.tensor([(a, b) for a in hs for b in ws], dtype=torch.int32).to(x.device)
+    hs_d, ws_d = torch.tensor(hs, dtype=torch.int32).to(x.device), torch.tensor(ws, dtype=torch.int32).to(x.device)
+    pin = torch.empty((T * B, C, t, t), device=x.device, dtype=torch.float32)
+    ops.LAUNCHES += 1
+    L.check(lib.b200ir_tile_gather(x.data_ptr(), origins.data_ptr(), pin.data_ptr(), T, B, C, H, W, t, ops._stream()),
+            "b200ir_tile_gather")
+    pout = None
+    for i in range(0, T * B, tile_batch):
+        y = net(pin[i:i + tile_batch])
+        if pout is None:
+            pout = torch.empty((T * B,) + tuple(y.shape[1:]), device=x.device, dtype=torch.float32)
+        ops.copy_cast(y, pout[i:i + tile_batch])
+    Co = pout.shape[1]
+    out = torch.empty((B, Co, H, W), device=x.device, dtype=torch.float32)
+    ops.LAUNCHES += 1
+    L.check(lib.b200ir_tile_blend(pout.data_ptr(), hs_d.data_ptr(), nh, ws_d.data_ptr(), nw, out.data_ptr(), B, Co, H, W, t,
+                                  int(clamp), ops._stream()), "b200ir_tile_blend")
+    return out

@@ -393,6 +393,15 @@ int b200ir_affine2_bwd(const void* g, int64_t g_bstride, const void* a, int64_t 
 int b200ir_crop_augment_degrade(const uint8_t* src, int Hs, int Ws, const int* offsets, const int* modes,
                                 const float* sigma, const float* noise, float* clean, float* degraded, int B, int P,
                                 b200ir_stream_t stream);
+/* Full-frame inference in tiles (the E / W accumulate of the reference's tile helper, 20260104_CG_IR/src/data/
+ * dataset_utils.py:513-534, MEASNet-main/MEASNet/utils/dataset_utils.py:226-247).  tile_gather: patches fp32
+ * [ntiles][B][C][tile][tile] cut from src fp32 [B][C][H][W] at origins int32 [ntiles][2] (row, column).  tile_blend: out =
+ * (sum of the tiles covering a pixel, in (h_idx, w_idx) order) / (their number), optionally clamped to [0, 1]; patches are
+ * ordered h_idx-major ([nh * nw][B][C][tile][tile]).  No atomics: bitwise the reference's accumulate order. */
+int b200ir_tile_gather(const float* src, const int* origins, float* patches, int ntiles, int B, int C, int H, int W, int tile,
+                       b200ir_stream_t stream);
+int b200ir_tile_blend(const float* patches, const int* h_idx, int nh, const int* w_idx, int nw, float* out, int B, int C,
+                      int H, int W, int tile, int clamp01, b200ir_stream_t stream);
 /* out fp32 [B][2] = (PSNR, SSIM) of clamp(restored,0,1) vs clean, fp32 NCHW, skimage semantics (test.py:46-52):
  * data_range 1, SSIM with an 11x11 Gaussian window (sigma 1.5), sample covariance, mean without a 5-pixel border, then
  * over channels.  ws: fp32 scratch [B * (1 + C) * b200ir_psnr_ssim_nblocks(H, W)]. */

@@ -71,3 +71,29 @@ def ssim(clean: np.ndarray, restored: np.ndarray) -> float:
         pad = (win - 1) // 2
         vals.append(S[pad:-pad, pad:-pad].mean())
     return float(np.mean(vals))
+
+
+def tile_restore_reference(fn, x, tile=128, tile_overlap=0):
+    """Tile helper of the reference (20260104_CG_IR/src/data/dataset_utils.py:513-534; same code in
+    MEASNet-main/MEASNet/utils/dataset_utils.py:226-247 and AdaptIR-main/utils/dataset_utils.py:346-367), with the network
+    call the reference's copies leave out (``out_patch = in_patch``) supplied as ``fn`` and its last two lines completed the
+    way the recipe ends everywhere it is used (``restored = E.div_(W)``, then the reference's own ``torch.clamp(restored, 0,
+    1)``).  x: torch fp32 [B, C, H, W] on the CPU; fn: patch -> restored patch.  Parity note: the reference's helper is dead
+    code (``restored`` is never assigned), so this pins the index lists and the accumulate order, not an output."""
+    import torch
+    b, c, h, w = x.shape
+    tile = min(tile, h, w)
+    assert tile % 8 == 0, "tile size should be multiple of 8"
+    stride = tile - tile_overlap
+    h_idx_list = list(range(0, h - tile, stride)) + [h - tile]
+    w_idx_list = list(range(0, w - tile, stride)) + [w - tile]
+    E = W = None
+    for h_idx in h_idx_list:
+        for w_idx in w_idx_list:
+            out_patch = fn(x[..., h_idx:h_idx + tile, w_idx:w_idx + tile])
+            if E is None:
+                E = torch.zeros(b, out_patch.shape[1], h, w, dtype=x.dtype)
+                W = torch.zeros_like(E)
+            E[..., h_idx:h_idx + tile, w_idx:w_idx + tile].add_(out_patch)
+            W[..., h_idx:h_idx + tile, w_idx:w_idx + tile].add_(torch.ones_like(out_patch))
+    return torch.clamp(E.div_(W), 0, 1)

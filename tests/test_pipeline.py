@@ -84,3 +84,43 @@ def test_psnr_ssim_kernel_vs_oracle(B, H, W):
         c, r = clean[i].transpose(1, 2, 0), np.clip(rest[i], 0, 1).transpose(1, 2, 0)
         assert abs(out[i, 0] - PO.psnr(c, r)) < 1e-3
         assert abs(out[i, 1] - PO.ssim(c, r)) < 2e-5
+
+
+def test_tile_oracle_identity_and_index_lists():
+    """oracle.tile_restore_reference with fn = identity gives the clamped frame back (every pixel is covered, overlapping
+    copies average to themselves), and the index lists are the reference's: range(0, h - tile, stride) + [h - tile]."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("b200ir_pipeline_src", os.path.join(os.path.dirname(os.path.dirname(
+        os.path.abspath(__file__))), "image-restoration_b200", "pipeline.py"))
+    src = open(spec.origin).read()
+    ns = {}
+    exec(src[src.index("def tile_index_lists"):src.index("@torch.no_grad()")], ns)     # the pure-Python helper only
+    assert ns["tile_index_lists"](200, 264, 64, 16) == (64, [0, 48, 96, 136], [0, 48, 96, 144, 192, 200])
+    assert ns["tile_index_lists"](96, 40, 128, 0) == (40, [0, 40, 56], [0])
+    with pytest.raises(ValueError):
+        ns["tile_index_lists"](100, 100, 100, 0)
+    g = torch.Generator().manual_seed(3)
+    x = torch.rand(2, 3, 72, 104, generator=g) * 1.2 - 0.1
+    y = PO.tile_restore_reference(lambda p: p, x, tile=32, tile_overlap=8)
+    assert (y - x.clamp(0, 1)).abs().max() <= 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W,tile,overlap", [(200, 264, 64, 16), (96, 40, 128, 0), (128, 128, 64, 0)])
+def test_tiled_restore_vs_oracle(H, W, tile, overlap):
+    """b200ir.tiled_restore (gather kernel, batched tiles through the network, pull-form blend kernel) against the
+    reference's tile recipe run tile by tile (oracle/pipeline_oracle.py tile_restore_reference) with the same network."""
+    import b200ir
+    from oracle import restormer_oracle as O
+    net = b200ir.Restormer(dim=16, num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, heads=[1, 2, 2, 4])
+    net.load_state_dict(O.synth_state_dict(dict(dim=16, num_blocks=[1, 1, 1, 1], num_refinement_blocks=1, heads=[1, 2, 2, 4]),
+                                           seed=4), strict=True)
+    net = net.cuda().eval()
+    x = O.synth_image(2, H, W, seed=12)
+    with torch.no_grad():
+        ref = PO.tile_restore_reference(lambda p: net(p.contiguous().cuda()).cpu(), x, tile=tile, tile_overlap=overlap)
+        got = b200ir.tiled_restore(net, x.cuda(), tile=tile, tile_overlap=overlap, tile_batch=5).cpu()
+        ident = b200ir.tiled_restore(lambda p: p, x.cuda() * 1.2 - 0.1, tile=tile, tile_overlap=overlap).cpu()
+    assert got.shape == ref.shape == x.shape
+    assert (got - ref).abs().max() <= 2e-5, float((got - ref).abs().max())
+    assert (ident - (x * 1.2 - 0.1).clamp(0, 1)).abs().max() <= 1e-6
