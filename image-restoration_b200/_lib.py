@@ -13,6 +13,7 @@ F32, BF16 = 0, 1
 LN_NONE, LN_WITHBIAS, LN_BIASFREE = 0, 1, 2
 SHUFFLE_NONE, UNSHUFFLE2, SHUFFLE2 = 0, 1, 2
 IMPL_AUTO, IMPL_SIMT, IMPL_TC = 0, 1, 2
+MDTA_BWD_CHAIN, MDTA_BWD_FOLD = 1, 2
 GEMM_AUTO, GEMM_RESIDENT, GEMM_STREAM, GEMM_RESIDENT_CH = 0, 1, 2, 3
 
 _vp, _i64, _i, _sz, _f = C.c_void_p, C.c_int64, C.c_int, C.c_size_t, C.c_float
@@ -67,6 +68,7 @@ SIGNATURES = {
     "b200ir_dwconv3x3_gelu_sigmoid_gate_bwd": [_vp, _i64, _vp, _vp, _vp, _i64, _vp, _i64, _i, _vp, _i, _i, _i, _i, _i, _vp],
     "b200ir_mdta_bwd": [_vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
     "b200ir_mdta_bwd_ex": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+    "b200ir_mdta_bwd_parts": [_vp, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
     "b200ir_pixel_shuffle": [_vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_l1_loss_fwd": [_vp, _i, _vp, _i, _i64, _vp, _i, _vp, _vp],
     "b200ir_l1_loss_fwd_noalloc": [_vp, _i, _vp, _i, _i64, _vp, _vp],

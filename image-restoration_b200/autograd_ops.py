@@ -340,6 +340,15 @@ _SIDE_USED = False
 _SIDE_KEEP = []
 _SIDE_GRADS = []   # (parameter, gradient computed on the side stream), assigned at join_side()
 SIDE_SITES = {"conv1x1", "dw3x3", "conv3x3", "lnfold", "gatefold"}   # which weight gradients fork (A/B, debugging)
+FORK_ATTN_BWD = True   # the two independent halves of the attention backward on two streams (inside train_step only)
+_AUX_STREAMS = {}
+
+
+def _aux_stream(dev):
+    s = _AUX_STREAMS.get(dev)
+    if s is None:
+        s = _AUX_STREAMS[dev] = torch.cuda.Stream(device=dev)
+    return s
 
 
 class _side:
@@ -596,10 +605,26 @@ class _MdtaCore(torch.autograd.Function):
         C = C3 // 3
         v = qkv[:, 2 * C:]
         dM, db = ops.conv_wgrad(dout, v, 1, per_sample=True, want_bias=ctx.has_bias)
-        mt, mqk, dw, dtemp = ops.mdta_bwd(partials, attn, _temp(temperature), _p(w_out).reshape(C, C), dM.contiguous())
+        dM = dM.contiguous()
         dqkv = torch.empty_like(qkv)
-        _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
-        _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])
+        if SIDE_WGRAD and FORK_ATTN_BWD:
+            # inside b200ir.train_step: the two halves only share inputs -- {M_b^T, dW_out, dv = M_b^T . dout} on a second
+            # stream, {softmax / temperature / normalize chain, d[q;k] = mqk_b . [q;k]} on this one; joined before returning
+            main = torch.cuda.current_stream()
+            aux = _aux_stream(main.device.index)
+            aux.wait_stream(main)
+            with torch.cuda.stream(aux):
+                mt, dw = ops.mdta_bwd_fold(attn, _p(w_out).reshape(C, C), dM, ctx.heads)
+                _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
+                dw.record_stream(main)
+                del mt
+            mqk, dtemp = ops.mdta_bwd_chain(partials, attn, _temp(temperature), _p(w_out).reshape(C, C), dM)
+            _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])
+            main.wait_stream(aux)
+        else:
+            mt, mqk, dw, dtemp = ops.mdta_bwd(partials, attn, _temp(temperature), _p(w_out).reshape(C, C), dM)
+            _per_sample_gemm(dout, mt, None, None, out=dqkv[:, 2 * C:])
+            _per_sample_gemm(qkv[:, :2 * C], mqk, None, None, out=dqkv[:, :2 * C])
         return (dqkv, dtemp.view(temperature.shape).to(temperature.dtype), dw.view(w_out.shape).to(w_out.dtype), db,
                 dout if ctx.has_res else None, None, None)
 

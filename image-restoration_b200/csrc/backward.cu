@@ -972,8 +972,18 @@ extern "C" int b200ir_mdta_bwd(const float* partials, int nslab, const float* at
 extern "C" int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float* attn, const float* temperature,
                                   int temp_per_sample, const float* w_out, const float* dM, float* mt, float* mqk,
                                   float* dw_out_part, float* dtemp_part, int B, int C, int heads, b200ir_stream_t stream) {
-  B200IR_CHECK_ARG(partials && attn && temperature && w_out && dM && mt && mqk && dw_out_part && dtemp_part,
-                   "mdta_bwd: null pointer");
+  return b200ir_mdta_bwd_parts(partials, nslab, attn, temperature, temp_per_sample, w_out, dM, mt, mqk, dw_out_part,
+                               dtemp_part, B, C, heads, B200IR_MDTA_BWD_CHAIN | B200IR_MDTA_BWD_FOLD, stream);
+}
+
+extern "C" int b200ir_mdta_bwd_parts(const float* partials, int nslab, const float* attn, const float* temperature,
+                                     int temp_per_sample, const float* w_out, const float* dM, float* mt, float* mqk,
+                                     float* dw_out_part, float* dtemp_part, int B, int C, int heads, int parts,
+                                     b200ir_stream_t stream) {
+  const bool chain = parts & B200IR_MDTA_BWD_CHAIN, fold = parts & B200IR_MDTA_BWD_FOLD;
+  B200IR_CHECK_ARG(chain || fold, "mdta_bwd: no part selected");
+  B200IR_CHECK_ARG(attn && w_out && dM && (!chain || (partials && temperature && mqk && dtemp_part)) &&
+                   (!fold || (mt && dw_out_part)), "mdta_bwd: null pointer");
   B200IR_CHECK_ARG(nslab > 0 && B > 0 && C > 0 && heads > 0 && C % heads == 0 && B <= 65535, "mdta_bwd: bad shape");
   const int d = C / heads;
   B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
@@ -991,12 +1001,15 @@ extern "C" int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float*
     cudaFuncSetAttribute(mdta_bwd_fold_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
     attr_set = true;
   }
-  mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
-      partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0, CO);
-  int rc = check_launch("mdta_bwd_chain");
-  if (rc) return rc;
-  mdta_bwd_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem2,
-                         (cudaStream_t)stream>>>(attn, w_out, dM, mt, dw_out_part, C, d);
+  if (chain) {
+    mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
+        partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0, CO);
+    const int rc = check_launch("mdta_bwd_chain");
+    if (rc) return rc;
+  }
+  if (fold)
+    mdta_bwd_fold_kernel<<<dim3((unsigned)((C + 31) / 32), (unsigned)heads, (unsigned)B), 256, smem2,
+                           (cudaStream_t)stream>>>(attn, w_out, dM, mt, dw_out_part, C, d);
   return check_launch("mdta_bwd");
 }
 

@@ -729,6 +729,38 @@ def mdta_bwd(partials, attn, temperature, w_out, dM):
     return mt, mqk, dw, dt
 
 
+def mdta_bwd_chain(partials, attn, temperature, w_out, dM):
+    """The softmax / temperature / normalize half of `mdta_bwd` alone: -> (mqk [B,2C,2C], dtemperature)."""
+    B, heads, nslab, per = partials.shape
+    C = w_out.shape[0]
+    mqk = torch.empty((B, 2 * C, 2 * C), device=partials.device, dtype=torch.float32)
+    dtp = torch.empty((B, heads), device=partials.device, dtype=torch.float32)
+    per_sample = temperature.dim() == 2
+    with _timed("mdta_bwd_chain", B, C, heads):
+        rc = lib.b200ir_mdta_bwd_parts(partials.data_ptr(), nslab, attn.data_ptr(),
+                                       _par(temperature, "temperature", B * heads if per_sample else heads), int(per_sample),
+                                       _par(w_out, "w_out", C * C), _par(dM, "dM", B * C * C), None, mqk.data_ptr(), None,
+                                       dtp.data_ptr(), B, C, heads, L.MDTA_BWD_CHAIN, _stream())
+    L.check(rc, "b200ir_mdta_bwd_parts")
+    dt = dtp if per_sample else (dtp.view(heads) if B == 1 else reduce_partials(dtp, B, heads))
+    return mqk, dt
+
+
+def mdta_bwd_fold(attn, w_out, dM, heads):
+    """The other half: -> (mt [B,C,C] = the dv operand M_b^T, dW_out [C,C])."""
+    C = w_out.shape[0]
+    B = dM.shape[0]
+    mt = torch.empty((B, C, C), device=dM.device, dtype=torch.float32)
+    dwp = torch.empty((B, C, C), device=dM.device, dtype=torch.float32)
+    with _timed("mdta_bwd_fold", B, C, heads):
+        rc = lib.b200ir_mdta_bwd_parts(None, 1, attn.data_ptr(), None, 0, _par(w_out, "w_out", C * C),
+                                       _par(dM, "dM", B * C * C), mt.data_ptr(), None, dwp.data_ptr(), None, B, C, heads,
+                                       L.MDTA_BWD_FOLD, _stream())
+    L.check(rc, "b200ir_mdta_bwd_parts")
+    dw = dwp.view(C, C) if B == 1 else reduce_partials(dwp, B, C * C).view(C, C)
+    return mt, dw
+
+
 def pixel_shuffle(x, mode):
     B, C, H, W_ = x.shape
     xp, xbs, xdt = _act(x, "x")

@@ -262,6 +262,14 @@ int b200ir_mdta_bwd(const float* partials, int nslab, const float* attn, const f
 int b200ir_mdta_bwd_ex(const float* partials, int nslab, const float* attn, const float* temperature, int temp_per_sample,
                        const float* w_out, const float* dM, float* mt, float* mqk, float* dw_out_part, float* dtemp_part,
                        int B, int C, int heads, b200ir_stream_t stream);
+/* The two halves of b200ir_mdta_bwd_ex separately (they only share inputs, so a training step runs them on two streams):
+ * CHAIN = softmax / temperature / normalize backward -> mqk, dtemp_part; FOLD = mt (the dv operand) and dw_out_part.
+ * Outputs of a half that is not selected may be NULL. */
+enum { B200IR_MDTA_BWD_CHAIN = 1, B200IR_MDTA_BWD_FOLD = 2 };
+int b200ir_mdta_bwd_parts(const float* partials, int nslab, const float* attn, const float* temperature,
+                          int temp_per_sample, const float* w_out, const float* dM, float* mt, float* mqk,
+                          float* dw_out_part, float* dtemp_part, int B, int C, int heads, int parts,
+                          b200ir_stream_t stream);
 /* nn.PixelShuffle(2) / nn.PixelUnshuffle(2) as a copy (x [B,C,H,W]; gradients of Upsample / Downsample). */
 int b200ir_pixel_shuffle(const void* x, int64_t x_bstride, void* y, int64_t y_bstride, int dtype, int B, int C, int H,
                          int W, int mode, b200ir_stream_t stream);
