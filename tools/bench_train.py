@@ -20,9 +20,12 @@ def main():
     ap.add_argument("--breakdown", action="store_true")
     ap.add_argument("--graph", action="store_true")
     ap.add_argument("--no-side", action="store_true", help="single-stream backward (A/B of the side-stream weight gradients)")
+    ap.add_argument("--no-fork", action="store_true", help="attention backward on one stream (A/B)")
     a = ap.parse_args()
     if a.no_side:
         b200ir.training.SIDE_WGRAD = False
+    if a.no_fork:
+        b200ir.autograd_ops.FORK_ATTN_BWD = False
     torch.manual_seed(0)
     net = b200ir.Restormer().cuda()
     net.set_compute_dtype(torch.bfloat16 if a.dtype == "bf16" else torch.float32)
