@@ -87,16 +87,16 @@ ln_fwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, int ln_type, c
 // dx (+)= res (gradient arriving through the residual path of TransformerBlock, Restormer.py:147-148).
 // parts: fp32 [gridDim.x][2][C] partial dgamma / dbeta; a channel is only ever touched by one warp of the CTA, which
 // accumulates it tile after tile in shared memory: fixed order, deterministic.
-template <int DT>
-__global__ void __launch_bounds__(256)
+template <int DT, int NW>
+__global__ void __launch_bounds__(32 * NW)
 ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __restrict__ g, int64_t g_bs, int g_dt,
               int ln_type, const float* __restrict__ lw, const float* __restrict__ lb, const void* __restrict__ res,
               int64_t res_bs, int res_dt, void* __restrict__ dx, int64_t dx_bs, int dx_dt, void* __restrict__ xn,
               int64_t xn_bs, float* __restrict__ parts, int C, int64_t HW, int tps, int64_t ntiles) {
   extern __shared__ float acc[];  // [2][C]
-  __shared__ float red4[8][4][LN_PX];
+  __shared__ float red4[NW][4][LN_PX];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int i = threadIdx.x; i < 2 * C; i += 256) acc[i] = 0.f;
+  for (int i = threadIdx.x; i < 2 * C; i += 32 * NW) acc[i] = 0.f;
   __syncthreads();
   const float invC = 1.0f / (float)C;
   for (int64_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
@@ -109,7 +109,7 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
     float S1 = 0.f, S2 = 0.f, H1 = 0.f, H2 = 0.f;
     if (valid) {
 #pragma unroll 4
-      for (int c = warp; c < C; c += 8) {
+      for (int c = warp; c < C; c += NW) {
         const float d = ldt<DT>(x, x_dt, xo + (int64_t)c * HW) - x0;
         const float h = ldt<DT>(g, g_dt, go + (int64_t)c * HW) * __ldg(lw + c);
         S1 += d;
@@ -126,7 +126,7 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
     __syncthreads();
     S1 = S2 = H1 = H2 = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) {
+    for (int w = 0; w < NW; ++w) {
       S1 += red4[w][0][lane];
       S2 += red4[w][1][lane];
       H1 += red4[w][2][lane];
@@ -141,7 +141,7 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
     // pass B: dx, and this tile's contribution to dgamma / dbeta
     const int64_t dxo = (int64_t)b * dx_bs + p, ro = (int64_t)b * res_bs + p, no = (int64_t)b * xn_bs + p;
 #pragma unroll 2
-    for (int c = warp; c < C; c += 8) {
+    for (int c = warp; c < C; c += NW) {
       float xv = 0.f, gv = 0.f, rv = 0.f;
       if (valid) {
         xv = ldt<DT>(x, x_dt, xo + (int64_t)c * HW);
@@ -173,7 +173,7 @@ ln_bwd_kernel(const void* __restrict__ x, int64_t x_bs, int x_dt, const void* __
   }
   __syncthreads();
   float* out = parts + (size_t)blockIdx.x * 2 * C;
-  for (int i = threadIdx.x; i < 2 * C; i += 256) out[i] = acc[i];
+  for (int i = threadIdx.x; i < 2 * C; i += 32 * NW) out[i] = acc[i];
 }
 
 // bf16 fast path of ln_bwd_kernel: a lane owns TWO adjacent pixels (bf16x2 accesses: 128 B per warp instruction, half the
@@ -861,10 +861,20 @@ extern "C" int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, cons
   B200IR_UNSUPPORTED(C <= 4096, "ln_bwd: C=%d > 4096 unsupported", C);
   const int tps = (int)((HW + LN_PX - 1) / LN_PX);
   const int64_t ntiles = (int64_t)B * tps;
+  // few tiles (the deep U-Net levels: 64 / 256 CTAs with one 32-pixel tile each): 32 warps per CTA, so that a warp walks
+  // C / 32 channels instead of C / 8 -- these launches are latency chains (C = 384 at 16 x 16 x 8: 47 -> see DESIGN 4b)
+  const bool wide = ntiles <= 2 * (int64_t)num_sms() && C >= 128;
 #define B200IR_LN_BWD(DT)                                                                                   \
-  ln_bwd_kernel<DT><<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(                          \
-      x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, ln_b, res, res_bstride, res_dtype, dx,           \
-      dx_bstride, dx_dtype, xn, xn_bstride, parts, C, HW, tps, ntiles)
+  do {                                                                                                      \
+    if (wide)                                                                                               \
+      ln_bwd_kernel<DT, 32><<<nparts, 1024, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(                 \
+          x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, ln_b, res, res_bstride, res_dtype, dx,       \
+          dx_bstride, dx_dtype, xn, xn_bstride, parts, C, HW, tps, ntiles);                                         \
+    else                                                                                                    \
+      ln_bwd_kernel<DT, 8><<<nparts, 256, (size_t)2 * C * sizeof(float), (cudaStream_t)stream>>>(                   \
+          x, x_bstride, x_dtype, g, g_bstride, g_dtype, ln_type, ln_w, ln_b, res, res_bstride, res_dtype, dx,       \
+          dx_bstride, dx_dtype, xn, xn_bstride, parts, C, HW, tps, ntiles);                                         \
+  } while (0)
   const bool same = x_dtype == g_dtype && x_dtype == dx_dtype && (!res || res_dtype == x_dtype);
   auto even = [](const void* q, int64_t bs) { return !q || (((uintptr_t)q & 3) == 0 && (bs & 1) == 0); };
   // (tiny planes keep the 32-pixel tiles: twice as many CTAs to spread the channel loop over)
