@@ -541,7 +541,7 @@ __global__ void __launch_bounds__(MB_THREADS)
 mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float* __restrict__ attn,
                       const float* __restrict__ temperature, const float* __restrict__ w_out,
                       const float* __restrict__ dM, float* __restrict__ mqk, float* __restrict__ dtemp_part, int C,
-                      int d, int temp_per_sample, int CO) {
+                      int d, int temp_per_sample, int CO, int S) {
   extern __shared__ float sm[];
   const int D1 = d + 1;
   float* at = sm;                        // attn  [d][d+1]
@@ -561,40 +561,61 @@ mdta_bwd_chain_kernel(const float* __restrict__ partials, int nslab, const float
   const float* dMb = dM + (size_t)b * C * C;
   const float temp = temperature[temp_per_sample ? (size_t)b * heads + h : h];   // [B][heads]: dynamic temperature
 
-  for (int j = tid; j < 2 * d; j += MB_THREADS) {
+  // sum over the Gram slabs: eight loads in flight, added in slab order (the order of the plain loop)
+  auto slab_sum = [&](size_t off) {
     float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + (size_t)d * d + j];
-    na[j] = fmaxf(sqrtf(s), 1e-12f);  // na[d..2d) aliases nb
-  }
+    int sl = 0;
+    for (; sl + 8 <= nslab; sl += 8) {
+      float v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) v[q] = base[(size_t)(sl + q) * per + off];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) s += v[q];
+    }
+    for (; sl < nslab; ++sl) s += base[(size_t)sl * per + off];
+    return s;
+  };
+  for (int j = tid; j < 2 * d; j += MB_THREADS)
+    na[j] = fmaxf(sqrtf(slab_sum((size_t)d * d + j)), 1e-12f);  // na[d..2d) aliases nb
   __syncthreads();
   for (int e = tid; e < d * d; e += MB_THREADS) {
     const int i = e / d, j = e % d;
-    float s = 0.f;
-    for (int sl = 0; sl < nslab; ++sl) s += base[(size_t)sl * per + e];
+    const float s = slab_sum((size_t)e);
     gh[i * D1 + j] = s / (na[i] * nb[j]);
     at[i * D1 + j] = a_g[e];
     da[i * D1 + j] = 0.f;
   }
-  // stage this head's column blocks W_out[:, hd:hd+d] and dM_b[:, hd:hd+d] in shared memory, CO rows at a time (CO = C
-  // unless C x d x 2 floats do not fit: AdaIR's FreModule runs C = 384 with 4 heads); the element's fma chain over o runs
-  // in the same order whatever CO is, through da[] between chunks, so the result does not depend on CO
-  float* wsm = cs + d;                   // [CO][d]
-  float* dsm = wsm + (size_t)CO * d;     // [CO][d]
+  // stage this head's column blocks W_out[:, hd:hd+d] and dM_b[:, hd:hd+d] in shared memory TRANSPOSED ([i][o], row stride S
+  // with S % 32 == 4: a lane's float4 along o is conflict-free across the j of a warp), CO rows of o at a time (CO = C
+  // unless the two blocks do not fit: AdaIR's FreModule runs C = 384 with 4 heads).  An element's fma chain over o runs in
+  // the same order whatever CO is, through da[] between chunks, so the result does not depend on CO; the zero padding of
+  // o up to a multiple of 4 adds fma(0, 0, acc) = acc.
+  float* wsm = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(cs + d) + 15) & ~(uintptr_t)15);   // [d][S], 16-B aligned
+  float* dsm = wsm + (size_t)d * S;      // [d][S]
   for (int o0 = 0; o0 < C; o0 += CO) {
-    const int co = min(CO, C - o0);
+    const int co = min(CO, C - o0), co4 = (co + 3) & ~3;
     __syncthreads();
-    for (int e = tid; e < co * d; e += MB_THREADS) {
+    for (int e = tid; e < co4 * d; e += MB_THREADS) {
       const int o = e / d, i = e - o * d;
-      wsm[e] = w_out[(size_t)(o0 + o) * C + h * d + i];
-      dsm[e] = dMb[(size_t)(o0 + o) * C + h * d + i];
+      const bool in = o < co;
+      wsm[i * S + o] = in ? w_out[(size_t)(o0 + o) * C + h * d + i] : 0.f;
+      dsm[i * S + o] = in ? dMb[(size_t)(o0 + o) * C + h * d + i] : 0.f;
     }
     __syncthreads();
     for (int e = tid; e < d * d; e += MB_THREADS) {
       const int i = e / d, j = e % d;
       // dattn[i][j] = sum_o W[o][hd+i] * dM[o][hd+j]
       float acc = da[i * D1 + j];
-#pragma unroll 8
-      for (int o = 0; o < co; ++o) acc = fmaf(wsm[o * d + i], dsm[o * d + j], acc);
+      const float4* wp = reinterpret_cast<const float4*>(wsm + i * S);
+      const float4* dp = reinterpret_cast<const float4*>(dsm + j * S);
+#pragma unroll 4
+      for (int o = 0; o < co4 / 4; ++o) {
+        const float4 a = wp[o], b = dp[o];
+        acc = fmaf(a.x, b.x, acc);
+        acc = fmaf(a.y, b.y, acc);
+        acc = fmaf(a.z, b.z, acc);
+        acc = fmaf(a.w, b.w, acc);
+      }
       da[i * D1 + j] = acc;
     }
   }
@@ -999,11 +1020,14 @@ extern "C" int b200ir_mdta_bwd_parts(const float* partials, int nslab, const flo
   B200IR_UNSUPPORTED(d <= 128, "mdta_bwd: head dim %d > 128 unsupported", d);
   // fixed part (three d x (d+1) matrices + four vectors) + the staged W_out / dM rows, CO of C at a time
   const size_t fixed = (3 * (size_t)d * (d + 1) + 4 * (size_t)d) * sizeof(float), limit = 220 * 1024;
-  B200IR_UNSUPPORTED(fixed + 2 * 8 * (size_t)d * sizeof(float) <= limit, "mdta_bwd: head dim %d needs %zu B of shared memory",
+  B200IR_UNSUPPORTED(fixed + 2 * 72 * (size_t)d * sizeof(float) <= limit, "mdta_bwd: head dim %d needs %zu B of shared memory",
                      d, fixed);
-  int CO = (int)((limit - fixed) / (2 * (size_t)d * sizeof(float)));
-  if (CO > C) CO = C;
-  const size_t smem = fixed + 2 * (size_t)CO * d * sizeof(float);
+  // rows of o staged at a time (multiple of 4) and the padded row stride S of the transposed blocks (S % 32 == 4)
+  int CO = (int)((limit - fixed - 16) / (2 * (size_t)d * sizeof(float))) - 32;
+  if (CO > C) CO = (C + 3) & ~3;
+  CO &= ~3;
+  const int S = CO + ((36 - CO % 32) % 32);
+  const size_t smem = fixed + 16 + 2 * (size_t)d * S * sizeof(float);
   const size_t smem2 = ((size_t)d * (d + 1) + 64 * (size_t)(d + 1)) * sizeof(float);
   static bool attr_set = false;
   if (!attr_set) {
@@ -1013,7 +1037,7 @@ extern "C" int b200ir_mdta_bwd_parts(const float* partials, int nslab, const flo
   }
   if (chain) {
     mdta_bwd_chain_kernel<<<dim3((unsigned)heads, (unsigned)B), MB_THREADS, smem, (cudaStream_t)stream>>>(
-        partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0, CO);
+        partials, nslab, attn, temperature, w_out, dM, mqk, dtemp_part, C, d, temp_per_sample ? 1 : 0, CO, S);
     const int rc = check_launch("mdta_bwd_chain");
     if (rc) return rc;
   }

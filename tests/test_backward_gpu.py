@@ -482,3 +482,19 @@ def test_ln_bwd_with_normalised_byproduct(b200ir, dtype, ln, B, C, H, W):
     assert rel(dlw, lwr.grad) < (1e-5 if dtype == torch.float32 else 2e-3)
     if ln == "WithBias":
         assert rel(dlb, lbr.grad) < (1e-5 if dtype == torch.float32 else 2e-3)
+
+
+def test_backward_rooted_at_a_tma_kernel(b200ir):
+    """`y.backward(dy)` with one of the library's Functions as the ROOT of the graph: its backward runs in an autograd
+    worker thread whose first CUDA call is then a driver-API tensor-map encode (no runtime call has bound the context to
+    that thread yet) -- the encode helper binds it and retries (csrc/gemm_tc.cu make_tmap_bf16_sw)."""
+    from b200ir import autograd_ops as A
+    g = torch.Generator().manual_seed(31)
+    B, C, H = 8, 96, 128
+    qkv = (torch.randn(B, 3 * C, H, H, generator=g) * 0.5).cuda().bfloat16().requires_grad_(True)
+    temp = torch.ones(1, 1, 1, device="cuda", requires_grad=True)
+    w = (torch.randn(C, C, 1, 1, generator=g) / C ** 0.5).cuda().requires_grad_(True)
+    dy = torch.randn(B, C, H, H, generator=g).cuda().bfloat16()
+    A.mdta_core(qkv, temp, w, None, 1, None).backward(dy)
+    torch.cuda.synchronize()
+    assert qkv.grad is not None and torch.isfinite(qkv.grad.float()).all() and w.grad is not None
