@@ -106,13 +106,23 @@ class AdamW(torch.optim.Optimizer):
         """Collect ``p.grad`` into the flat gradient buffer (no-op for gradients that already live there) and note which
         parameters have one: the update runs over the contiguous runs of those."""
         src, dst, present = [], [], []
+        odd = []
         for p, gv in zip(self.params, self.grad_views):
-            present.append(p.grad is not None)
-            if p.grad is not None and p.grad.data_ptr() != gv.data_ptr():
-                src.append(p.grad)
-                dst.append(gv)
+            g = p.grad
+            present.append(g is not None)
+            if g is not None and g.data_ptr() != gv.data_ptr():
+                # torch._foreach_copy_ takes its multi-tensor route only if EVERY pair matches in strides and dtype; one
+                # strided gradient (the depthwise taps are views into a [C, 10] fold) sends all ~500 tensors down the
+                # per-tensor route: one memcpy / copy kernel each.  So the odd ones are copied on their own.
+                if g.is_contiguous() and g.dtype == gv.dtype and g.shape == gv.shape:
+                    src.append(g)
+                    dst.append(gv)
+                else:
+                    odd.append((gv, g))
         if src:
             torch._foreach_copy_(dst, src)
+        for gv, g in odd:
+            gv.copy_(g.view(gv.shape) if g.shape != gv.shape and g.is_contiguous() else g)
         if present != self._present:
             self._present, self._runs, start = present, [], None
             for i, ok in enumerate(present):
