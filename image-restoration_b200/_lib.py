@@ -59,6 +59,7 @@ SIGNATURES = {
     "b200ir_ln_bwd": [_vp, _i64, _i, _vp, _i64, _i, _i, _vp, _vp, _vp, _i64, _i, _vp, _i64, _i, _vp, _i64, _vp, _i, _i, _i,
                       _i64, _vp],
     "b200ir_reduce_partials": [_vp, _vp, _i, _i64, _i64, _vp],
+    "b200ir_reduce_partials_taps": [_vp, _vp, _vp, _i, _i, _i, _vp],
     "b200ir_conv_wgrad_nsplit": [_i, _i, _i, _i, _i64, _i],
     "b200ir_conv_wgrad": [_vp, _i64, _i, _vp, _i64, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _i, _vp],
     "b200ir_im2col3x3": [_vp, _i64, _i, _vp, _i, _i, _i, _i, _vp],

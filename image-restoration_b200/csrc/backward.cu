@@ -436,6 +436,32 @@ reduce_partials_kernel(const float* __restrict__ in, float* __restrict__ out, in
   }
 }
 
+// The same fold for the depthwise-conv partial sums parts[i][c][nv] (nv - 1 taps + the bias sum per channel), written as two
+// dense tensors: dw[c][nv - 1] and db[c] -- the parameter gradients themselves, not strided views into a [C][nv] buffer.
+__global__ void __launch_bounds__(256)
+reduce_partials_taps_kernel(const float* __restrict__ in, float* __restrict__ dw, float* __restrict__ db, int n, int C, int nv) {
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, sl = threadIdx.x >> 5;
+  const int64_t K = (int64_t)C * nv;
+  for (int64_t k0 = (int64_t)blockIdx.x * 32; k0 < K; k0 += (int64_t)gridDim.x * 32) {
+    const int64_t k = k0 + lane;
+    float s = 0.f;
+    if (k < K)
+      for (int i = sl; i < n; i += 8) s += in[(size_t)i * K + k];
+    __syncthreads();
+    red[sl][lane] = s;
+    __syncthreads();
+    if (sl == 0 && k < K) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][lane];
+      const int c = (int)(k / nv), q = (int)(k - (int64_t)c * nv);
+      if (q < nv - 1) dw[(size_t)c * (nv - 1) + q] = t;
+      else if (db) db[c] = t;
+    }
+  }
+}
+
 // =====================================================================================================
 // Weight gradient of a 1x1 conv (taps=1) or a dense 3x3 conv (taps=9): reduction over pixels
 //   dW[g][o][c*taps+t] = sum_{b in g} sum_p dy[b,o,p] * x[b,c,p+shift(t)],   db[g][o] = sum dy[b,o,p]
@@ -932,6 +958,13 @@ extern "C" int b200ir_reduce_partials(const float* in, float* out, int n, int64_
   reduce_partials_kernel<8><<<grid_1d(K, 32, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(in, out, n, K, stride);
   return check_launch("reduce_partials");
 }
+
+extern "C" int b200ir_reduce_partials_taps(const float* in, float* dw, float* db, int n, int C, int nv, b200ir_stream_t stream) {
+  B200IR_CHECK_ARG(in && dw && n > 0 && C > 0 && nv > 1, "reduce_partials_taps: bad args");
+  reduce_partials_taps_kernel<<<grid_1d((int64_t)C * nv, 32, num_sms() * 16), 256, 0, (cudaStream_t)stream>>>(in, dw, db, n, C, nv);
+  return check_launch("reduce_partials_taps");
+}
+
 
 namespace b200ir {
 bool wgrad_tc_supported(const void* dy, int64_t dy_bs, int dy_dt, const void* x, int64_t x_bs, int x_dt, int taps,

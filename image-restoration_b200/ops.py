@@ -182,9 +182,8 @@ def dwconv_kxk_bwd(dy, x, w, want_bias=False, want_input=True):
     with _timed("dwconv_kxk_wgrad", B, C, H, W_, K, gdt):
         rc = lib.b200ir_dwconv_kxk_wgrad(gp, gbs, xp, xbs, gdt, parts.data_ptr(), nparts, B, C, H, W_, K, _stream())
     L.check(rc, "b200ir_dwconv_kxk_wgrad")
-    d = reduce_partials(parts, nparts, C * nv).view(C, nv)
-    dw = d[:, :K * K].reshape(C, 1, K, K)
-    return dx, dw, (d[:, K * K].contiguous() if want_bias else None)
+    dw, db = reduce_partials_taps(parts, nparts, C, nv, want_bias)
+    return dx, dw.view(C, 1, K, K), db
 
 
 def sigmoid_gate(u, g, out=None):
@@ -586,6 +585,17 @@ def reduce_partials(parts, n, K, stride=None, out=None):
     return out
 
 
+def reduce_partials_taps(parts, nparts, C, nv, want_bias):
+    """(dw [C, nv-1], db [C] or None) = fold of the depthwise partial sums parts [nparts, C, nv]: dense tensors (a strided
+    view as a parameter gradient would push the optimizer's gradient gather off torch's multi-tensor route)."""
+    dw = torch.empty((C, nv - 1), device=parts.device, dtype=torch.float32)
+    db = torch.empty((C,), device=parts.device, dtype=torch.float32) if want_bias else None
+    with _timed("reduce_partials", nparts, C * nv):
+        L.check(lib.b200ir_reduce_partials_taps(parts.data_ptr(), dw.data_ptr(), db.data_ptr() if want_bias else None, nparts, C,
+                                                nv, _stream()), "b200ir_reduce_partials_taps")
+    return dw, db
+
+
 def ln_fwd(x, ln_type, ln_w, ln_b, out_dtype=None):
     """LN(x) materialised (only the backward needs it as a tensor)."""
     B, C, H, W_ = x.shape
@@ -678,8 +688,8 @@ def dwconv3x3_wgrad(dy, x, want_bias=False):
     with _timed("dwconv3x3_wgrad", B, C, H, W_, xdt):
         L.check(lib.b200ir_dwconv3x3_wgrad(dp, dbs, xp, xbs, xdt, parts.data_ptr(), nparts, B, C, H, W_, _stream()),
                 "b200ir_dwconv3x3_wgrad")
-    d = parts.view(C, 10) if nparts == 1 else reduce_partials(parts, nparts, C * 10).view(C, 10)
-    return d[:, :9].reshape(C, 1, 3, 3), (d[:, 9] if want_bias else None)
+    dw, db = reduce_partials_taps(parts, nparts, C, 10, want_bias)
+    return dw.view(C, 1, 3, 3), db
 
 
 def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None, sigmoid_gate=False):
@@ -701,8 +711,8 @@ def dwconv3x3_gelu_gate_bwd(t, w, bias, dg, want_bias=False, fold=None, sigmoid_
                 Hd, H, W_, _stream())
     L.check(rc, "b200ir_dwconv3x3_gelu_gate_bwd")
     def finish():
-        d = parts.view(C2, 10) if nparts == 1 else reduce_partials(parts, nparts, C2 * 10).view(C2, 10)
-        return d[:, :9].reshape(C2, 1, 3, 3), (d[:, 9] if want_bias else None)
+        dw, db = reduce_partials_taps(parts, nparts, C2, 10, want_bias)
+        return dw.view(C2, 1, 3, 3), db
     dw, db = fold(finish, parts) if fold is not None else finish()   # see ln_bwd
     return da, dw, db
 

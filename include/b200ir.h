@@ -222,6 +222,9 @@ int b200ir_ln_bwd(const void* x, int64_t x_bstride, int x_dtype, const void* g, 
                   float* parts, int nparts, int B, int C, int64_t HW, b200ir_stream_t stream);
 /* out[k] = sum_{i<n} in[i*stride+k], fixed order. */
 int b200ir_reduce_partials(const float* in, float* out, int n, int64_t K, int64_t stride, b200ir_stream_t stream);
+/* The fold of depthwise-conv partial sums in[n][C][nv] (nv - 1 taps and the bias sum per channel) into the two parameter
+ * gradients as dense tensors: dw fp32 [C][nv - 1], db fp32 [C] (NULL: no bias).  Same order of additions. */
+int b200ir_reduce_partials_taps(const float* in, float* dw, float* db, int n, int C, int nv, b200ir_stream_t stream);
 /* Weight (+bias) gradient of a 1x1 (taps=1) or dense 3x3 pad-1 (taps=9) conv = reduction over pixels:
  *   parts_w[split][g][o][c*taps+t] = partial sum_p dy[b,o,p]*x[b,c,p+shift(t)],  parts_b[split][g][o] = partial sum_p dy
  * g = sample if per_sample (MDTA: dM_b = dout_b.v_b^T, gradient of the folded per-sample weight) else the whole batch
