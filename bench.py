@@ -354,11 +354,11 @@ def main():
             mopt = b200ir.AdamW(mnet.parameters(), lr=2e-4)
             mc = [torch.rand(MB, 3, 128, 128, generator=torch.Generator().manual_seed(900 + i)).to(dev) for i in range(2)]
             md = [(c + 25.0 / 255.0 * torch.randn_like(c)).clamp(0, 1) for c in mc]
-            for i in range(max(args.warmup, 2)):
+            for i in range(max(args.warmup, 4)):     # (the first steps also learn the weight-pack table of the routed experts)
                 b200ir.train_step(mnet, mopt, md[i % 2], mc[i % 2], balance_loss_weight=0.01)
             torch.cuda.synchronize()
             ml0 = ops.LAUNCHES
-            nst = max(args.steps // 2, 2)
+            nst = max(args.steps // 2, 4)
             e0.record()
             for i in range(nst):
                 mloss = b200ir.train_step(mnet, mopt, md[i % 2], mc[i % 2], balance_loss_weight=0.01)
