@@ -282,7 +282,9 @@ def _temp(temperature):
 def _bias_st(bias, C, nrows, device, cache=None):
     """(s, t) epilogue vectors of the per-sample GEMM: s unused (no LayerNorm), t = project_out bias.  Cached only in
     the owning module's cache (a tensor's address alone does not identify it once it has been freed)."""
-    sig = _sig(bias) + (C, nrows)
+    # (without a bias the vectors are zeros whatever the parameters are: no parameter epoch in the key, or every optimizer
+    # step would refill them -- 44 fill launches per training step)
+    sig = (_sig(bias) if bias is not None else ("nobias",)) + (C, nrows)
     ent = cache.get("bias_st") if cache is not None else None
     if ent is None or ent[0] != sig:
         st = torch.zeros((2, nrows), device=device, dtype=torch.float32)
